@@ -1,0 +1,46 @@
+# Builds libpint_cuda.so (the product) for sm_100a, in-tree.
+#   make            -> pint_b200/lib/libpint_cuda.so
+#   make oracle     -> the checker (oracle/liboracle.so, oracle/_ref where /root/reference exists)
+#   make tools      -> build/tune (kernel variant sweep), build/cpp_api_test
+NVCC ?= nvcc
+ARCH := -gencode arch=compute_100a,code=sm_100a
+NVFLAGS := -std=c++17 -O3 $(ARCH) -lineinfo -Xcompiler -fPIC -Iinclude -Ipint_b200/csrc
+SRC := pint_b200/csrc
+OBJ := build/obj
+LIB := pint_b200/lib/libpint_cuda.so
+HDRS := $(wildcard include/pint/*.hpp include/pint/*.cuh include/*.h $(SRC)/*.hpp $(SRC)/*.def)
+PARTS := 0 1 2 3
+OBJS := $(OBJ)/api.o $(OBJ)/api_aux.o $(OBJ)/generic.o $(foreach p,$(PARTS),$(OBJ)/registry_part$(p).o)
+
+all: $(LIB)
+
+$(OBJ)/%.o: $(SRC)/%.cu $(HDRS)
+	@mkdir -p $(OBJ)
+	$(NVCC) $(NVFLAGS) -c $< -o $@
+
+$(OBJ)/registry_part%.o: $(SRC)/registry_part.cu $(HDRS)
+	@mkdir -p $(OBJ)
+	$(NVCC) $(NVFLAGS) -DPINT_REG_PART=$* -c $< -o $@
+
+$(LIB): $(OBJS)
+	@mkdir -p pint_b200/lib
+	$(NVCC) $(ARCH) -shared -cudart static -o $@ $(OBJS)
+
+oracle:
+	$(MAKE) -C oracle liboracle.so
+	@if [ -f /root/reference/include/pint/pint.hpp ]; then $(MAKE) -C oracle ref; fi
+
+tools: build/tune build/cpp_api_test
+
+build/tune: tools/tune.cu $(HDRS)
+	@mkdir -p build
+	$(NVCC) $(NVFLAGS) -o $@ tools/tune.cu
+
+build/cpp_api_test: tests/cpp/cpp_api_test.cpp include/pint/cuda.hpp $(LIB)
+	@mkdir -p build
+	g++ -std=c++11 -O2 -Iinclude -I/usr/local/cuda/include -o $@ tests/cpp/cpp_api_test.cpp -Lpint_b200/lib -lpint_cuda -Wl,-rpath,'$$ORIGIN/../pint_b200/lib'
+
+clean:
+	rm -rf build pint_b200/lib
+
+.PHONY: all oracle tools clean

@@ -1,0 +1,246 @@
+// pint/cuda_kernels_planes.cuh -- per-field kernels: unpack (get / get_signed),
+// repack (field constructor / make_truncate) and the fused
+// unpack -> arithmetic -> repack pipeline.  Included by cuda_kernels.cuh.
+//
+// Bytes per element (W = sizeof(Integer), F planes of P bytes):
+//   unpack  W + P*F      repack  P*F + W      fused  3W (planes stay in registers)
+#pragma once
+
+namespace pint {
+namespace cuda {
+namespace kernels {
+
+// ---------------------------------------------------------------------------
+// Field iteration policies: compile-time (offsets and widths are immediates,
+// the loop is fully unrolled) and run-time (table in the constant bank).
+
+template <class SL>
+struct static_fields {
+    using word = typename SL::word;
+    template <class F, std::size_t... Is>
+    __device__ __forceinline__ static void each_impl(F&& f, std::index_sequence<Is...>)
+    {
+        (f(uint32_t(Is), uint32_t(SL::fields.off[Is]), uint32_t(SL::fields.bits[Is])), ...);
+    }
+    // fields of one element: f(index, offset, width)
+    template <class F>
+    __device__ __forceinline__ static void each_elem_field(F&& f)
+    {
+        each_impl(static_cast<F&&>(f), std::make_index_sequence<SL::fields.nfields>());
+    }
+    // fields of one Word (element fields replicated)
+    template <class F>
+    __device__ __forceinline__ static void each_word_field(F&& f)
+    {
+        each_impl(static_cast<F&&>(f), std::make_index_sequence<SL::fields.nword_fields>());
+    }
+    __device__ __forceinline__ static constexpr word A() { return SL::masks.A; }
+};
+
+template <class Word>
+struct runtime_fields {
+    using word = Word;
+    field_table t;
+    Word a_mask;
+    template <class F>
+    __device__ __forceinline__ void each_elem_field(F&& f) const
+    {
+        for (uint32_t i = 0; i < t.nfields; ++i) f(i, uint32_t(t.off[i]), uint32_t(t.bits[i]));
+    }
+    template <class F>
+    __device__ __forceinline__ void each_word_field(F&& f) const
+    {
+        for (uint32_t i = 0; i < t.nword_fields; ++i) f(i, uint32_t(t.off[i]), uint32_t(t.bits[i]));
+    }
+    __device__ __forceinline__ Word A() const { return a_mask; }
+};
+
+struct plane_ptrs {
+    void* p[kMaxFields];  // device pointers, one per field; null = field not wanted (unpack only)
+};
+
+// ---------------------------------------------------------------------------
+// Field extraction on a register holding one element zero-extended to a Word.
+
+// get<I>, pint.hpp:799-807
+template <class Word>
+__device__ __forceinline__ Word field_get(Word e, uint32_t off, uint32_t w)
+{
+    constexpr uint32_t WB = 8 * sizeof(Word);
+    return (e << (WB - off - w)) >> (WB - w);
+}
+
+// get_signed<I>, pint.hpp:809-822: field MSB to the register MSB, arithmetic
+// shift back.  On a 32-bit register holding a narrower Integer this yields the
+// reference's make_signed<Integer> value sign-extended to 32 bits.
+template <class Word>
+__device__ __forceinline__ typename std::make_signed<Word>::type field_get_signed(Word e, uint32_t off, uint32_t w)
+{
+    using S = typename std::make_signed<Word>::type;
+    constexpr uint32_t WB = 8 * sizeof(Word);
+    return S(e << (WB - off - w)) >> (WB - w);
+}
+
+// ---------------------------------------------------------------------------
+// Four consecutive elements per thread ("quad"): plane accesses are 16-byte
+// vectors (int32 planes) or 2 x 16 bytes (int64 planes); a warp covers 512
+// contiguous bytes of every plane.
+
+template <class Elem, class Word>
+__device__ __forceinline__ void load_quad(const Elem* p, Word (&e)[4])
+{
+    if constexpr (sizeof(Elem) == 8) {
+        const uint4 v0 = ld16<CACHE_STREAMING>(reinterpret_cast<const uint4*>(p));
+        const uint4 v1 = ld16<CACHE_STREAMING>(reinterpret_cast<const uint4*>(p) + 1);
+        e[0] = (uint64_t(v0.y) << 32) | v0.x; e[1] = (uint64_t(v0.w) << 32) | v0.z;
+        e[2] = (uint64_t(v1.y) << 32) | v1.x; e[3] = (uint64_t(v1.w) << 32) | v1.z;
+    } else if constexpr (sizeof(Elem) == 4) {
+        const uint4 v = ld16<CACHE_STREAMING>(reinterpret_cast<const uint4*>(p));
+        e[0] = v.x; e[1] = v.y; e[2] = v.z; e[3] = v.w;
+    } else if constexpr (sizeof(Elem) == 2) {
+        const uint2 v = __ldcs(reinterpret_cast<const uint2*>(p));
+        e[0] = v.x & 0xFFFFu; e[1] = v.x >> 16; e[2] = v.y & 0xFFFFu; e[3] = v.y >> 16;
+    } else {
+        const uint32_t v = __ldcs(reinterpret_cast<const uint32_t*>(p));
+        e[0] = v & 0xFFu; e[1] = (v >> 8) & 0xFFu; e[2] = (v >> 16) & 0xFFu; e[3] = v >> 24;
+    }
+}
+
+template <class Elem, class Word>
+__device__ __forceinline__ void store_quad(Elem* p, const Word (&e)[4])
+{
+    if constexpr (sizeof(Elem) == 8) {
+        st16<CACHE_STREAMING>(reinterpret_cast<uint4*>(p),
+                              make_uint4(uint32_t(e[0]), uint32_t(e[0] >> 32), uint32_t(e[1]), uint32_t(e[1] >> 32)));
+        st16<CACHE_STREAMING>(reinterpret_cast<uint4*>(p) + 1,
+                              make_uint4(uint32_t(e[2]), uint32_t(e[2] >> 32), uint32_t(e[3]), uint32_t(e[3] >> 32)));
+    } else if constexpr (sizeof(Elem) == 4) {
+        st16<CACHE_STREAMING>(reinterpret_cast<uint4*>(p), make_uint4(e[0], e[1], e[2], e[3]));
+    } else if constexpr (sizeof(Elem) == 2) {
+        __stcs(reinterpret_cast<uint2*>(p),
+               make_uint2((e[0] & 0xFFFFu) | (e[1] << 16), (e[2] & 0xFFFFu) | (e[3] << 16)));
+    } else {
+        __stcs(reinterpret_cast<uint32_t*>(p),
+               (e[0] & 0xFFu) | ((e[1] & 0xFFu) << 8) | ((e[2] & 0xFFu) << 16) | (e[3] << 24));
+    }
+}
+
+// Plane element type: int32_t/uint32_t/int64_t/uint64_t handled as 4- or 8-byte words.
+template <int PlaneBytes>
+__device__ __forceinline__ void store_plane_quad(void* plane, size_t q, const uint64_t (&v)[4])
+{
+    if constexpr (PlaneBytes == 4) {
+        st16<CACHE_STREAMING>(reinterpret_cast<uint4*>(plane) + q,
+                              make_uint4(uint32_t(v[0]), uint32_t(v[1]), uint32_t(v[2]), uint32_t(v[3])));
+    } else {
+        uint4* d = reinterpret_cast<uint4*>(plane) + 2 * q;
+        st16<CACHE_STREAMING>(d, make_uint4(uint32_t(v[0]), uint32_t(v[0] >> 32), uint32_t(v[1]), uint32_t(v[1] >> 32)));
+        st16<CACHE_STREAMING>(d + 1, make_uint4(uint32_t(v[2]), uint32_t(v[2] >> 32), uint32_t(v[3]), uint32_t(v[3] >> 32)));
+    }
+}
+
+template <int PlaneBytes>
+__device__ __forceinline__ void load_plane_quad(const void* plane, size_t q, uint64_t (&v)[4])
+{
+    if constexpr (PlaneBytes == 4) {
+        const uint4 x = ld16<CACHE_STREAMING>(reinterpret_cast<const uint4*>(plane) + q);
+        // int32 plane values are converted to the Integer as the field
+        // constructor's value_type parameters are (pint.hpp:771-772): sign-extend
+        v[0] = uint64_t(int64_t(int32_t(x.x))); v[1] = uint64_t(int64_t(int32_t(x.y)));
+        v[2] = uint64_t(int64_t(int32_t(x.z))); v[3] = uint64_t(int64_t(int32_t(x.w)));
+    } else {
+        const uint4* s = reinterpret_cast<const uint4*>(plane) + 2 * q;
+        const uint4 x = ld16<CACHE_STREAMING>(s), y = ld16<CACHE_STREAMING>(s + 1);
+        v[0] = (uint64_t(x.y) << 32) | x.x; v[1] = (uint64_t(x.w) << 32) | x.z;
+        v[2] = (uint64_t(y.y) << 32) | y.x; v[3] = (uint64_t(y.w) << 32) | y.z;
+    }
+}
+
+// packed -> planes.  get<I> (pint.hpp:799-807) or get_signed<I> (:809-822) for
+// every wanted field of 4 consecutive elements per thread.
+template <class Elem, int PlaneBytes, bool Signed, class FP>
+__global__ void __launch_bounds__(256)
+unpack_quad_kernel(const Elem* packed, const __grid_constant__ plane_ptrs planes, size_t nquads,
+                   const __grid_constant__ FP fp)
+{
+    using W = typename FP::word;
+    for (size_t q = size_t(blockIdx.x) * blockDim.x + threadIdx.x; q < nquads; q += size_t(gridDim.x) * blockDim.x) {
+        W e[4];
+        load_quad<Elem, W>(packed + 4 * q, e);
+        fp.each_elem_field([&](uint32_t i, uint32_t off, uint32_t w) {
+            void* dst = planes.p[i];
+            if (!dst) return;
+            uint64_t v[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                v[j] = Signed ? uint64_t(int64_t(field_get_signed<W>(e[j], off, w))) : uint64_t(field_get<W>(e[j], off, w));
+            store_plane_quad<PlaneBytes>(dst, q, v);
+        });
+    }
+}
+
+template <class Elem, int PlaneBytes, bool Signed, class FP>
+__global__ void __launch_bounds__(256)
+unpack_elem_kernel(const Elem* packed, const __grid_constant__ plane_ptrs planes, size_t first, size_t n,
+                   const __grid_constant__ FP fp)
+{
+    using W = typename FP::word;
+    for (size_t i = first + size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < first + n;
+         i += size_t(gridDim.x) * blockDim.x) {
+        const W e = W(packed[i]);
+        fp.each_elem_field([&](uint32_t f, uint32_t off, uint32_t w) {
+            void* dst = planes.p[f];
+            if (!dst) return;
+            const uint64_t v = Signed ? uint64_t(int64_t(field_get_signed<W>(e, off, w))) : uint64_t(field_get<W>(e, off, w));
+            if constexpr (PlaneBytes == 4) static_cast<uint32_t*>(dst)[i] = uint32_t(v);
+            else static_cast<uint64_t*>(dst)[i] = v;
+        });
+    }
+}
+
+// planes -> packed.  The field constructor (pint.hpp:770-774) = make_truncate
+// (:592-601) = OR_i ((v_i & ones(w_i)) << off_i) (:390-407).
+template <class Elem, int PlaneBytes, class FP>
+__global__ void __launch_bounds__(256)
+repack_quad_kernel(const __grid_constant__ plane_ptrs planes, Elem* packed, size_t nquads,
+                   const __grid_constant__ FP fp)
+{
+    using W = typename FP::word;
+    constexpr uint32_t WB = 8 * sizeof(W);
+    for (size_t q = size_t(blockIdx.x) * blockDim.x + threadIdx.x; q < nquads; q += size_t(gridDim.x) * blockDim.x) {
+        W e[4] = {0, 0, 0, 0};
+        fp.each_elem_field([&](uint32_t i, uint32_t off, uint32_t w) {
+            uint64_t v[4];
+            load_plane_quad<PlaneBytes>(planes.p[i], q, v);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) e[j] |= (W(v[j]) << (WB - w)) >> (WB - w - off);
+        });
+        store_quad<Elem, W>(packed + 4 * q, e);
+    }
+}
+
+template <class Elem, int PlaneBytes, class FP>
+__global__ void __launch_bounds__(256)
+repack_elem_kernel(const __grid_constant__ plane_ptrs planes, Elem* packed, size_t first, size_t n,
+                   const __grid_constant__ FP fp)
+{
+    using W = typename FP::word;
+    constexpr uint32_t WB = 8 * sizeof(W);
+    for (size_t i = first + size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < first + n;
+         i += size_t(gridDim.x) * blockDim.x) {
+        W e = 0;
+        fp.each_elem_field([&](uint32_t f, uint32_t off, uint32_t w) {
+            uint64_t v;
+            if constexpr (PlaneBytes == 4) v = uint64_t(int64_t(static_cast<const int32_t*>(planes.p[f])[i]));
+            else v = static_cast<const uint64_t*>(planes.p[f])[i];
+            e |= (W(v) << (WB - w)) >> (WB - w - off);
+        });
+        packed[i] = Elem(e);
+    }
+}
+
+}  // namespace kernels
+}  // namespace cuda
+}  // namespace pint
+
+#include "cuda_kernels_fused.cuh"

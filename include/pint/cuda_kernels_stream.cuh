@@ -1,0 +1,282 @@
+// pint/cuda_kernels_stream.cuh -- packed -> packed streaming kernels
+// (binary ops: 2 reads + 1 write = 3W bytes/element; unary ops: 2W).
+// Included by cuda_kernels.cuh.
+#pragma once
+
+namespace pint {
+namespace cuda {
+namespace kernels {
+
+// ---------------------------------------------------------------------------
+// 128-bit global accesses with an explicit cache policy.  Nothing in these
+// kernels is read twice, so the default is "streaming" (evict-first) in both
+// directions; the variants exist so the choice is a measured one (tools/tune.cu).
+enum : int { CACHE_DEFAULT = 0, CACHE_NO_ALLOCATE = 1, CACHE_STREAMING = 2 };
+
+template <int Policy>
+__device__ __forceinline__ uint4 ld16(const uint4* p)
+{
+    uint4 r;
+    if constexpr (Policy == CACHE_NO_ALLOCATE) {
+        asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    } else if constexpr (Policy == CACHE_STREAMING) {
+        asm volatile("ld.global.cs.v4.u32 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    } else {
+        asm volatile("ld.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    }
+    return r;
+}
+
+template <int Policy>
+__device__ __forceinline__ void st16(uint4* p, const uint4& v)
+{
+    if constexpr (Policy == CACHE_NO_ALLOCATE) {
+        asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};"
+                     :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+    } else if constexpr (Policy == CACHE_STREAMING) {
+        asm volatile("st.global.cs.v4.u32 [%0], {%1,%2,%3,%4};"
+                     :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+    } else {
+        asm volatile("st.global.v4.u32 [%0], {%1,%2,%3,%4};"
+                     :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+    }
+}
+
+template <int Unroll, int Block, int Ld = CACHE_STREAMING, int St = CACHE_STREAMING>
+struct stream_cfg {
+    static constexpr int UNROLL = Unroll;  // independent 16-byte loads in flight per operand per thread
+    static constexpr int BLOCK = Block;    // threads per CTA
+    static constexpr int LD = Ld;
+    static constexpr int ST = St;
+};
+using default_stream_cfg = stream_cfg<4, 256>;
+
+// apply a Word function to the 16 bytes of a vector
+template <class Word, class F>
+__device__ __forceinline__ uint4 map_words2(const uint4& a, const uint4& b, F f)
+{
+    uint4 r;
+    if constexpr (sizeof(Word) == 4) {
+        r.x = f(a.x, b.x); r.y = f(a.y, b.y); r.z = f(a.z, b.z); r.w = f(a.w, b.w);
+    } else {
+        const uint64_t a0 = (uint64_t(a.y) << 32) | a.x, a1 = (uint64_t(a.w) << 32) | a.z;
+        const uint64_t b0 = (uint64_t(b.y) << 32) | b.x, b1 = (uint64_t(b.w) << 32) | b.z;
+        const uint64_t r0 = f(a0, b0), r1 = f(a1, b1);
+        r.x = uint32_t(r0); r.y = uint32_t(r0 >> 32); r.z = uint32_t(r1); r.w = uint32_t(r1 >> 32);
+    }
+    return r;
+}
+
+template <class Word, class F>
+__device__ __forceinline__ uint4 map_words1(const uint4& a, F f)
+{
+    uint4 r;
+    if constexpr (sizeof(Word) == 4) {
+        r.x = f(a.x); r.y = f(a.y); r.z = f(a.z); r.w = f(a.w);
+    } else {
+        const uint64_t a0 = (uint64_t(a.y) << 32) | a.x, a1 = (uint64_t(a.w) << 32) | a.z;
+        const uint64_t r0 = f(a0), r1 = f(a1);
+        r.x = uint32_t(r0); r.y = uint32_t(r0 >> 32); r.z = uint32_t(r1); r.w = uint32_t(r1 >> 32);
+    }
+    return r;
+}
+
+// The SWAR op as a function object over one Word.
+template <int Op, class P>
+struct swar_fn {
+    using word = typename P::word;
+    P p;
+    __device__ __forceinline__ word operator()(word a, word b) const { return apply_op<Op>(a, b, p); }
+};
+
+// ---------------------------------------------------------------------------
+// out[i] = op(a[i], b[i]) over 16-byte vectors.  A CTA walks tiles of
+// BLOCK * UNROLL vectors with a grid stride; within a tile consecutive threads
+// touch consecutive vectors (every warp access is 512 contiguous bytes) and
+// all 2 * UNROLL loads are issued before the first use.  `out` may alias a or b:
+// each vector is read and written by the same thread, read first.
+//
+// Fn is the per-Word function object (swar_fn below, or fused_fn in
+// cuda_kernels_planes.cuh); it travels as a __grid_constant__ parameter, so a
+// static-mask Fn is empty and a runtime-mask Fn lives in the constant bank.
+template <class Fn, class Cfg>
+__global__ void __launch_bounds__(Cfg::BLOCK)
+binary_stream_kernel(const uint4* a, const uint4* b, uint4* out, size_t nvec, const __grid_constant__ Fn fn)
+{
+    using W = typename Fn::word;
+    constexpr int U = Cfg::UNROLL, B = Cfg::BLOCK;
+    constexpr size_t tile = size_t(U) * B;
+    const size_t nfull = nvec / tile;
+    auto f = [&](W x, W y) { return fn(x, y); };
+
+    for (size_t t = blockIdx.x; t < nfull; t += gridDim.x) {
+        const size_t base = t * tile + threadIdx.x;
+        uint4 va[U], vb[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) va[u] = ld16<Cfg::LD>(a + base + size_t(u) * B);
+#pragma unroll
+        for (int u = 0; u < U; ++u) vb[u] = ld16<Cfg::LD>(b + base + size_t(u) * B);
+#pragma unroll
+        for (int u = 0; u < U; ++u) st16<Cfg::ST>(out + base + size_t(u) * B, map_words2<W>(va[u], vb[u], f));
+    }
+    // the partial last tile goes to the CTA whose turn it would be
+    if (blockIdx.x == nfull % gridDim.x) {
+        for (size_t i = nfull * tile + threadIdx.x; i < nvec; i += B)
+            st16<Cfg::ST>(out + i, map_words2<W>(ld16<Cfg::LD>(a + i), ld16<Cfg::LD>(b + i), f));
+    }
+}
+
+// Element-granular variant: array heads/tails shorter than a vector and
+// operands whose addresses are not congruent modulo 16.  One element is
+// zero-extended into a Word; the replicated masks act on zeros above it.
+template <class Elem, class Fn>
+__global__ void __launch_bounds__(256)
+binary_elem_kernel(const Elem* a, const Elem* b, Elem* out, size_t n, const __grid_constant__ Fn fn)
+{
+    using W = typename Fn::word;
+    for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x)
+        out[i] = Elem(fn(W(a[i]), W(b[i])));
+}
+
+template <class Word, class Cfg>
+__global__ void __launch_bounds__(Cfg::BLOCK)
+unary_stream_kernel(const uint4* in, uint4* out, size_t nvec, const __grid_constant__ unary_params<Word> u)
+{
+    constexpr int U = Cfg::UNROLL, B = Cfg::BLOCK;
+    constexpr size_t tile = size_t(U) * B;
+    const size_t nfull = nvec / tile;
+    auto f = [&](Word x) { return apply_unary(x, u); };
+    for (size_t t = blockIdx.x; t < nfull; t += gridDim.x) {
+        const size_t base = t * tile + threadIdx.x;
+        uint4 v[U];
+#pragma unroll
+        for (int k = 0; k < U; ++k) v[k] = ld16<Cfg::LD>(in + base + size_t(k) * B);
+#pragma unroll
+        for (int k = 0; k < U; ++k) st16<Cfg::ST>(out + base + size_t(k) * B, map_words1<Word>(v[k], f));
+    }
+    if (blockIdx.x == nfull % gridDim.x) {
+        for (size_t i = nfull * tile + threadIdx.x; i < nvec; i += B)
+            st16<Cfg::ST>(out + i, map_words1<Word>(ld16<Cfg::LD>(in + i), f));
+    }
+}
+
+template <class Elem, class Word>
+__global__ void __launch_bounds__(256)
+unary_elem_kernel(const Elem* in, Elem* out, size_t n, const __grid_constant__ unary_params<Word> u)
+{
+    for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x)
+        out[i] = Elem(apply_unary(Word(in[i]), u));
+}
+
+// ---------------------------------------------------------------------------
+// Launch geometry: persistent grid of num_sms * ctas_per_sm CTAs (a multiple of
+// the 148 SMs of a B200), or one CTA per tile when there are fewer tiles.
+struct launch_geom {
+    int num_sms = 148;
+    int ctas_per_sm = 8;
+    unsigned long long* launch_counter = nullptr;  // bumped once per kernel launch
+};
+
+inline unsigned grid_for(size_t ntiles, const launch_geom& g)
+{
+    const size_t cap = size_t(g.num_sms) * size_t(g.ctas_per_sm > 0 ? g.ctas_per_sm : 1);
+    size_t n = ntiles < cap ? ntiles : cap;
+    return unsigned(n ? n : 1);
+}
+
+inline void count_launch(const launch_geom& g)
+{
+    if (g.launch_counter) __atomic_fetch_add(g.launch_counter, 1ULL, __ATOMIC_RELAXED);
+}
+
+// Split [0, n) elements into head (element kernel), body (vector kernel) and
+// tail (element kernel) given the operand addresses.  Returns false when the
+// addresses are not congruent modulo 16 (everything goes element-wise).
+inline bool split_aligned(size_t elem_bytes, size_t n, const void* const* ptrs, int nptrs,
+                          size_t* head, size_t* nvec, size_t* tail)
+{
+    const uintptr_t off = reinterpret_cast<uintptr_t>(ptrs[0]) & 15u;
+    for (int i = 1; i < nptrs; ++i)
+        if ((reinterpret_cast<uintptr_t>(ptrs[i]) & 15u) != off) return false;
+    if (off % elem_bytes) return false;
+    size_t h = off ? (16 - off) / elem_bytes : 0;
+    if (h > n) h = n;
+    const size_t per_vec = 16 / elem_bytes;
+    *head = h;
+    *nvec = (n - h) / per_vec;
+    *tail = (n - h) - *nvec * per_vec;
+    return true;
+}
+
+template <class Elem, class Fn, class Cfg = default_stream_cfg>
+cudaError_t launch_binary(const void* a, const void* b, void* out, size_t n, const Fn& fn,
+                          cudaStream_t stream, const launch_geom& g)
+{
+    if (n == 0) return cudaSuccess;
+    const Elem* ea = static_cast<const Elem*>(a);
+    const Elem* eb = static_cast<const Elem*>(b);
+    Elem* eo = static_cast<Elem*>(out);
+    const void* ptrs[3] = {a, b, out};
+    size_t head = 0, nvec = 0, tail = 0;
+    const bool vec_ok = split_aligned(sizeof(Elem), n, ptrs, 3, &head, &nvec, &tail);
+    auto elems = [&](size_t first, size_t count) {
+        if (!count) return;
+        const unsigned grid = grid_for((count + 255) / 256, g);
+        binary_elem_kernel<Elem, Fn><<<grid, 256, 0, stream>>>(ea + first, eb + first, eo + first, count, fn);
+        count_launch(g);
+    };
+    if (!vec_ok) {
+        elems(0, n);
+        return cudaGetLastError();
+    }
+    elems(0, head);
+    if (nvec) {
+        constexpr size_t tile = size_t(Cfg::UNROLL) * Cfg::BLOCK;
+        const unsigned grid = grid_for((nvec + tile - 1) / tile, g);
+        binary_stream_kernel<Fn, Cfg><<<grid, Cfg::BLOCK, 0, stream>>>(
+            reinterpret_cast<const uint4*>(ea + head), reinterpret_cast<const uint4*>(eb + head),
+            reinterpret_cast<uint4*>(eo + head), nvec, fn);
+        count_launch(g);
+    }
+    elems(n - tail, tail);
+    return cudaGetLastError();
+}
+
+template <class Elem, class Word, class Cfg = default_stream_cfg>
+cudaError_t launch_unary(const void* in, void* out, size_t n, const unary_params<Word>& u,
+                         cudaStream_t stream, const launch_geom& g)
+{
+    if (n == 0) return cudaSuccess;
+    const Elem* ei = static_cast<const Elem*>(in);
+    Elem* eo = static_cast<Elem*>(out);
+    const void* ptrs[2] = {in, out};
+    size_t head = 0, nvec = 0, tail = 0;
+    const bool vec_ok = split_aligned(sizeof(Elem), n, ptrs, 2, &head, &nvec, &tail);
+    auto elems = [&](size_t first, size_t count) {
+        if (!count) return;
+        const unsigned grid = grid_for((count + 255) / 256, g);
+        unary_elem_kernel<Elem, Word><<<grid, 256, 0, stream>>>(ei + first, eo + first, count, u);
+        count_launch(g);
+    };
+    if (!vec_ok) {
+        elems(0, n);
+        return cudaGetLastError();
+    }
+    elems(0, head);
+    if (nvec) {
+        constexpr size_t tile = size_t(Cfg::UNROLL) * Cfg::BLOCK;
+        const unsigned grid = grid_for((nvec + tile - 1) / tile, g);
+        unary_stream_kernel<Word, Cfg><<<grid, Cfg::BLOCK, 0, stream>>>(
+            reinterpret_cast<const uint4*>(ei + head), reinterpret_cast<uint4*>(eo + head), nvec, u);
+        count_launch(g);
+    }
+    elems(n - tail, tail);
+    return cudaGetLastError();
+}
+
+}  // namespace kernels
+}  // namespace cuda
+}  // namespace pint

@@ -1,0 +1,177 @@
+/*
+ * pint_cuda.h -- C ABI of libpint_cuda.so: the batched (array) form of pint's
+ * per-element operations, executed by hand-written sm_100a CUDA kernels.
+ *
+ * The reference (bad-ed/pint) is a header-only C++ template library with no
+ * FFI boundary of its own: its whole interface is the free-function templates
+ * of include/pint/pint.hpp ("pint.hpp:N" below), each one value in / one value
+ * out, and its only array workload is the element loop of
+ * tests/pint_bench.cpp:90-94.  Each entry point below is the array form of one
+ * of those templates and says which; include/pint/cuda.hpp is the C++ template
+ * layer (same names as the scalar API) that a pint user calls and that binds
+ * to these symbols.  INTEGRATION.md shows the binding.
+ *
+ * Conventions
+ *   - A layout (a C++ type in the reference) crosses the ABI as a descriptor.
+ *   - All array pointers are DEVICE pointers owned by the caller; element type
+ *     is the layout's Integer (uint8/16/32/64_t); packed_int<Integer,...> is
+ *     trivially copyable and the same size as Integer (pint.hpp:758-787), so
+ *     arrays of either are interchangeable.  16-byte alignment is the fast
+ *     path; any Integer-aligned pointer is accepted.
+ *   - `out` may alias an input exactly (same address), not partially.
+ *   - Calls are asynchronous on `stream` (a cudaStream_t; NULL = default
+ *     stream) of the CURRENT device, never allocate, never synchronise, and
+ *     are thread-safe for distinct streams.
+ *   - Return value: 0 success; < 0 argument/layout error (PINT_E_*), the
+ *     conditions the reference rejects at compile time; > 0 a cudaError_t.
+ *   - There is no CPU fallback: without a CUDA device every compute entry
+ *     point returns the CUDA error.
+ */
+#ifndef PINT_CUDA_H
+#define PINT_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PINT_CUDA_ABI_VERSION 1
+#define PINT_MAX_FIELDS 64
+
+/* packed_int<Integer, Bits0, Bits...> (pint.hpp:758-787) as data. */
+typedef struct pint_layout {
+    uint32_t elem_bytes;            /* sizeof(Integer): 1, 2, 4 or 8 (pint.hpp:731-734) */
+    uint32_t nfields;               /* sizeof...(Bits) + 1, 1..64 */
+    uint8_t  bits[PINT_MAX_FIELDS]; /* Bits0, Bits...; field 0 is least significant */
+} pint_layout;
+
+typedef void* pint_stream_t; /* cudaStream_t */
+
+enum pint_op {
+    PINT_ADD_WRAP = 0,               /* pint::add_wrap               pint.hpp:826-838  */
+    PINT_ADD_UNSIGNED_SATURATE = 1,  /* pint::add_unsigned_saturate  pint.hpp:840-855  */
+    PINT_ADD_SIGNED_SATURATE = 2,    /* pint::add_signed_saturate    pint.hpp:857-866  */
+    PINT_SUB_WRAP = 3,               /* pint::sub_wrap               pint.hpp:870-884  */
+    PINT_SUB_UNSIGNED_SATURATE = 4,  /* pint::sub_unsigned_saturate  pint.hpp:886-908  */
+    PINT_SUB_SIGNED_SATURATE = 5,    /* pint::sub_signed_saturate    pint.hpp:910-919  */
+    PINT_OR = 6,                     /* packed_int::operator|        pint.hpp:781      */
+    PINT_AND = 7,                    /* packed_int::operator&        pint.hpp:782      */
+    PINT_XOR = 8,                    /* packed_int::operator^        pint.hpp:783      */
+    PINT_MIN_UNSIGNED = 9,           /* pint::min_unsigned           pint.hpp:936-950  */
+    PINT_MAX_UNSIGNED = 10,          /* pint::max_unsigned           pint.hpp:952-966  */
+    PINT_MIN_SIGNED = 11,            /* pint::min_signed             pint.hpp:968-985  */
+    PINT_MAX_SIGNED = 12,            /* pint::max_signed             pint.hpp:987-1004 */
+    PINT_NUM_BINARY_OPS = 13
+};
+
+enum pint_error {
+    PINT_OK = 0,
+    PINT_E_NULL = -1,          /* null layout or null array with n > 0 */
+    PINT_E_ELEM_BYTES = -2,    /* Integer is not uint8/16/32/64_t (pint.hpp:727-734, 761-762) */
+    PINT_E_NFIELDS = -3,       /* 0 or more than 64 fields */
+    PINT_E_ZERO_WIDTH = -4,    /* a field of 0 bits */
+    PINT_E_TOO_WIDE = -5,      /* sum(Bits) > 8 * sizeof(Integer) (pint.hpp:763-764) */
+    PINT_E_OP = -10,           /* unknown operation code */
+    PINT_E_INDEX = -12,        /* field index / slice bounds (pint.hpp:748, 802, 813) */
+    PINT_E_PLANE_BYTES = -13,  /* plane element size is not 4 or 8 */
+    PINT_E_ALIAS = -14,        /* partially overlapping in/out */
+    PINT_E_ARG = -15           /* other invalid argument */
+};
+
+/* ---- library ---- */
+int pint_cuda_abi_version(void);
+const char* pint_cuda_error_string(int rc);
+/* kernels launched by this library since it was loaded (all threads) */
+unsigned long long pint_cuda_launch_count(void);
+/* Tuning/testing knobs: "force_generic" (1 = always use the runtime-mask
+ * kernels even for layouts that have compiled-in constants),
+ * "ctas_per_sm" (persistent grid size = SMs * this).  Returns 0 or PINT_E_ARG. */
+int pint_cuda_set_option(const char* key, long value);
+long pint_cuda_get_option(const char* key);
+
+/* ---- layouts (compile-time machinery of pint.hpp:27-373, 707-754 as functions) ---- */
+int pint_cuda_layout_validate(const pint_layout* layout);
+/* make_packed_int's storage choice (pint.hpp:789-795); 0 if unsupported */
+uint32_t pint_cuda_storage_bytes(uint32_t total_bits);
+/* mask_hiorder / mask_loorder / all_ones<sum> / detect_saturation_mask_type
+ * (pint.hpp:324-348, 443-456) of one element, as the mask generator computes them */
+int pint_cuda_layout_masks(const pint_layout* layout, uint64_t* H, uint64_t* L, uint64_t* A, uint32_t* sat_type);
+/* 1 if kernels with compiled-in mask constants exist for this layout, else 0 */
+int pint_cuda_layout_is_specialized(const pint_layout* layout);
+/* result layout of slice<start, end> (sliced_int, pint.hpp:746-754) */
+int pint_cuda_slice_layout(const pint_layout* layout, uint32_t start, uint32_t end, pint_layout* result);
+
+/* ---- packed -> packed (3 * sizeof(Integer) bytes per element) ---- */
+/* out[i] = OP(a[i], b[i]); array form of the pint_op templates above. */
+int pint_cuda_binary(int op, const pint_layout* layout, const void* a, const void* b, void* out,
+                     size_t n, pint_stream_t stream);
+/* Same function computed as unpack -> per-field arithmetic -> repack inside one
+ * kernel (planes in registers); bit-identical to pint_cuda_binary. */
+int pint_cuda_fused_unpack_arith_repack(int op, const pint_layout* layout, const void* a, const void* b,
+                                        void* out, size_t n, pint_stream_t stream);
+/* out[i] = shift_left(in[i], amount) (pint.hpp:1006-1017) or
+ * shift_right_unsigned (pint.hpp:1019-1029) when left == 0; uniform amount. */
+int pint_cuda_shift(int left, const pint_layout* layout, uint64_t amount, const void* in, void* out,
+                    size_t n, pint_stream_t stream);
+/* out[i] = slice<start, end>(in[i]).value() (pint.hpp:923-932); same Integer. */
+int pint_cuda_slice(const pint_layout* layout, uint32_t start, uint32_t end, const void* in, void* out,
+                    size_t n, pint_stream_t stream);
+
+/* ---- packed <-> planes ---- */
+/* planes[f][i] = get<f>(packed[i]) (pint.hpp:799-807) or get_signed<f>
+ * (pint.hpp:809-822) when is_signed.  `planes` is a HOST array of nfields
+ * DEVICE pointers; a null entry skips that field.  plane_bytes is 4
+ * (int32_t/uint32_t planes) or 8; the value is narrowed or widened to the
+ * plane type as a C cast would. */
+int pint_cuda_unpack(const pint_layout* layout, int is_signed, const void* packed, void* const* planes,
+                     int plane_bytes, size_t n, pint_stream_t stream);
+/* packed[i] = packed_int(planes[0][i], planes[1][i], ...) -- the truncating
+ * field constructor = make_truncate (pint.hpp:770-774, 592-601, 390-407). */
+int pint_cuda_repack(const pint_layout* layout, const void* const* planes, int plane_bytes, void* packed,
+                     size_t n, pint_stream_t stream);
+
+/* ---- the benchmark's exact loop shape (tests/pint_bench.cpp:90-94) ---- */
+/* *sum_dev (device uint64_t) = sum_i OP(pairs[2i], pairs[2i+1]) mod 2^64 over an
+ * AoS array of (first, second) Integer pairs; the benchmark's uint32_t `sum`
+ * is the low 32 bits. */
+int pint_cuda_pairs_reduce(int op, const pint_layout* layout, const void* pairs, size_t n,
+                           uint64_t* sum_dev, pint_stream_t stream);
+
+/* ---- synthetic inputs and checksums ---- */
+/* out[i] = (Integer) splitmix64(seed + start + i) */
+int pint_cuda_fill_splitmix(void* out, uint32_t elem_bytes, size_t n, uint64_t seed, uint64_t start,
+                            pint_stream_t stream);
+/* result_dev[0] = sum, result_dev[1] = xor of the elements zero-extended to 64 bit */
+int pint_cuda_checksum(const void* x, uint32_t elem_bytes, size_t n, uint64_t* result_dev,
+                       pint_stream_t stream);
+
+/* ---- multi-GPU partitioner: independent contiguous shards, no collective ---- */
+/* Splits n elements into nshards contiguous ranges whose starts are multiples
+ * of 128 bytes; the remainder goes to the last shard. */
+int pint_cuda_plan_shards(size_t n, uint32_t elem_bytes, int nshards, size_t* begin, size_t* count);
+/* Launches pint_cuda_binary on every device's shard (a[k], b[k], out[k] are
+ * device pointers on devices[k], counts[k] elements) on streams[k] (may be
+ * NULL = per-device default streams); returns after all launches, does not
+ * synchronise.  Restores the caller's current device. */
+int pint_cuda_sharded_binary(int op, const pint_layout* layout, int ngpu, const int* devices,
+                             const void* const* a, const void* const* b, void* const* out,
+                             const size_t* counts, const pint_stream_t* streams);
+
+/* ---- host-buffer entry points (the end-to-end path) ---- */
+/* Pinned host memory for the calls below (cudaHostAlloc / cudaFreeHost). */
+int pint_cuda_host_alloc(void** ptr, size_t bytes);
+int pint_cuda_host_free(void* ptr);
+/* out_host[i] = OP(a_host[i], b_host[i]) with HOST arrays: chunks are copied to
+ * the current device, processed and copied back on a ring of streams so that
+ * H2D, kernel and D2H overlap.  Synchronous: results are in out_host on
+ * return.  Fast when the buffers are pinned (pint_cuda_host_alloc or
+ * cudaHostRegister); pageable memory works at pageable-copy speed. */
+int pint_cuda_binary_host(int op, const pint_layout* layout, const void* a_host, const void* b_host,
+                          void* out_host, size_t n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PINT_CUDA_H */

@@ -1,0 +1,321 @@
+// api_aux.cu -- synthetic inputs, checksums, the benchmark-shaped pair
+// reduction, the multi-GPU partitioner and the host-buffer (end-to-end) path.
+#include <mutex>
+
+#include "api_common.hpp"
+
+namespace pint_cuda_impl {
+namespace {
+
+using namespace pint::cuda;
+using namespace pint::cuda::kernels;
+
+__device__ __forceinline__ uint64_t splitmix64(uint64_t x)
+{
+    x += 0x9E3779B97F4A7C15ULL;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBULL;
+    return x ^ (x >> 31);
+}
+
+// out[i] = (Elem) splitmix64(seed + start + i)
+template <class Elem>
+__global__ void __launch_bounds__(256) fill_kernel(Elem* out, size_t n, uint64_t base)
+{
+    constexpr int PER = 16 / sizeof(Elem);
+    const size_t nvec = (reinterpret_cast<uintptr_t>(out) & 15u) ? 0 : n / PER;
+    for (size_t v = size_t(blockIdx.x) * blockDim.x + threadIdx.x; v < nvec; v += size_t(gridDim.x) * blockDim.x) {
+        union { uint4 q; Elem e[PER]; } u;
+#pragma unroll
+        for (int j = 0; j < PER; ++j) u.e[j] = Elem(splitmix64(base + v * PER + j));
+        st16<CACHE_STREAMING>(reinterpret_cast<uint4*>(out) + v, u.q);
+    }
+    for (size_t i = nvec * PER + size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x)
+        out[i] = Elem(splitmix64(base + i));
+}
+
+__device__ __forceinline__ void block_reduce_sum_xor(uint64_t s, uint64_t x, uint64_t* result)
+{
+    __shared__ uint64_t ss[8], sx[8];
+    for (int o = 16; o; o >>= 1) {
+        s += __shfl_down_sync(0xffffffffu, s, o);
+        x ^= __shfl_down_sync(0xffffffffu, x, o);
+    }
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) { ss[warp] = s; sx[warp] = x; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < (int)(blockDim.x >> 5); ++w) { s += ss[w]; x ^= sx[w]; }
+        atomicAdd(reinterpret_cast<unsigned long long*>(result), (unsigned long long)s);
+        if (result + 1) atomicXor(reinterpret_cast<unsigned long long*>(result + 1), (unsigned long long)x);
+    }
+}
+
+// result[0] += sum of elements, result[1] ^= xor of elements (integer, so the
+// order of the atomics does not matter: bit-exact and deterministic)
+template <class Elem>
+__global__ void __launch_bounds__(256) checksum_kernel(const Elem* x, size_t n, uint64_t* result)
+{
+    uint64_t s = 0, r = 0;
+    for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) {
+        const uint64_t v = x[i];
+        s += v;
+        r ^= v;
+    }
+    block_reduce_sum_xor(s, r, result);
+}
+
+template <class Elem>
+__global__ void __launch_bounds__(256) checksum_vec_kernel(const uint4* x, size_t nvec, uint64_t* result)
+{
+    constexpr int PER = 16 / sizeof(Elem);
+    uint64_t s = 0, r = 0;
+    for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += size_t(gridDim.x) * blockDim.x) {
+        union { uint4 q; Elem e[PER]; } u;
+        u.q = ld16<CACHE_STREAMING>(x + i);
+#pragma unroll
+        for (int j = 0; j < PER; ++j) { s += u.e[j]; r ^= u.e[j]; }
+    }
+    block_reduce_sum_xor(s, r, result);
+}
+
+// tests/pint_bench.cpp:90-94: sum += op(P(pair.first), P(pair.second)).value()
+template <class Elem, int Op>
+__global__ void __launch_bounds__(256)
+pairs_reduce_kernel(const Elem* pairs, size_t n, uint64_t* sum, const __grid_constant__ runtime_masks<word_of<Elem>> p)
+{
+    using W = word_of<Elem>;
+    constexpr int PER = 8 / sizeof(Elem);  // pairs per 16-byte vector
+    uint64_t s = 0;
+    const bool vec_ok = (reinterpret_cast<uintptr_t>(pairs) & 15u) == 0;
+    const size_t nvec = vec_ok ? n / PER : 0;
+    for (size_t v = size_t(blockIdx.x) * blockDim.x + threadIdx.x; v < nvec; v += size_t(gridDim.x) * blockDim.x) {
+        union { uint4 q; Elem e[2 * PER]; } u;
+        u.q = ld16<CACHE_STREAMING>(reinterpret_cast<const uint4*>(pairs) + v);
+#pragma unroll
+        for (int j = 0; j < PER; ++j) s += Elem(apply_op<Op>(W(u.e[2 * j]), W(u.e[2 * j + 1]), p));
+    }
+    for (size_t i = nvec * PER + size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x)
+        s += Elem(apply_op<Op>(W(pairs[2 * i]), W(pairs[2 * i + 1]), p));
+    block_reduce_sum_xor(s, 0, sum);
+}
+
+template <class Elem, int... Ops>
+cudaError_t pairs_ops(int op, const layout_desc& d, const void* pairs, size_t n, uint64_t* sum, cudaStream_t s,
+                      const launch_geom& g, std::integer_sequence<int, Ops...>)
+{
+    using W = word_of<Elem>;
+    runtime_masks<W> p{make_word_masks<W>(d)};
+    const unsigned grid = grid_for((n + 1023) / 1024, g);
+    ((op == Ops ? (pairs_reduce_kernel<Elem, Ops><<<grid, 256, 0, s>>>((const Elem*)pairs, n, sum, p), 0) : 0), ...);
+    count_launch(g);
+    return cudaGetLastError();
+}
+
+}  // namespace
+}  // namespace pint_cuda_impl
+
+using namespace pint_cuda_impl;
+
+extern "C" {
+
+int pint_cuda_fill_splitmix(void* out, uint32_t elem_bytes, size_t n, uint64_t seed, uint64_t start, pint_stream_t stream)
+{
+    if (elem_bytes != 1 && elem_bytes != 2 && elem_bytes != 4 && elem_bytes != 8) return PINT_E_ELEM_BYTES;
+    if (n == 0) return PINT_OK;
+    if (!out) return PINT_E_NULL;
+    if ((uintptr_t)out % elem_bytes) return PINT_E_ARG;
+    const launch_geom g = geom();
+    const unsigned grid = grid_for((n * elem_bytes / 16 + 255) / 256, g);
+    cudaStream_t s = (cudaStream_t)stream;
+    const uint64_t base = seed + start;
+    switch (elem_bytes) {
+    case 1: fill_kernel<uint8_t><<<grid, 256, 0, s>>>((uint8_t*)out, n, base); break;
+    case 2: fill_kernel<uint16_t><<<grid, 256, 0, s>>>((uint16_t*)out, n, base); break;
+    case 4: fill_kernel<uint32_t><<<grid, 256, 0, s>>>((uint32_t*)out, n, base); break;
+    default: fill_kernel<uint64_t><<<grid, 256, 0, s>>>((uint64_t*)out, n, base); break;
+    }
+    count_launch(g);
+    return (int)cudaGetLastError();
+}
+
+int pint_cuda_checksum(const void* x, uint32_t elem_bytes, size_t n, uint64_t* result_dev, pint_stream_t stream)
+{
+    if (elem_bytes != 1 && elem_bytes != 2 && elem_bytes != 4 && elem_bytes != 8) return PINT_E_ELEM_BYTES;
+    if (!result_dev) return PINT_E_NULL;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (cudaError_t e = cudaMemsetAsync(result_dev, 0, 2 * sizeof(uint64_t), s)) return (int)e;
+    if (n == 0) return PINT_OK;
+    if (!x) return PINT_E_NULL;
+    if ((uintptr_t)x % elem_bytes) return PINT_E_ARG;
+    const launch_geom g = geom();
+    const bool vec_ok = ((uintptr_t)x & 15u) == 0;
+    const size_t per = 16 / elem_bytes;
+    const size_t nvec = vec_ok ? n / per : 0, rest = n - nvec * per;
+    const char* tail = (const char*)x + nvec * 16;
+#define PINT_CK(T)                                                                                            \
+    do {                                                                                                      \
+        if (nvec) { checksum_vec_kernel<T><<<grid_for((nvec + 1023) / 1024, g), 256, 0, s>>>((const uint4*)x, nvec, result_dev); count_launch(g); } \
+        if (rest) { checksum_kernel<T><<<grid_for((rest + 255) / 256, g), 256, 0, s>>>((const T*)tail, rest, result_dev); count_launch(g); }        \
+    } while (0)
+    switch (elem_bytes) {
+    case 1: PINT_CK(uint8_t); break;
+    case 2: PINT_CK(uint16_t); break;
+    case 4: PINT_CK(uint32_t); break;
+    default: PINT_CK(uint64_t); break;
+    }
+#undef PINT_CK
+    return (int)cudaGetLastError();
+}
+
+int pint_cuda_pairs_reduce(int op, const pint_layout* layout, const void* pairs, size_t n, uint64_t* sum_dev,
+                           pint_stream_t stream)
+{
+    layout_desc d;
+    if (int rc = check_layout(layout, &d)) return rc;
+    if (op < 0 || op >= PINT_NUM_BINARY_OPS) return PINT_E_OP;
+    if (!sum_dev) return PINT_E_NULL;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (cudaError_t e = cudaMemsetAsync(sum_dev, 0, sizeof(uint64_t), s)) return (int)e;
+    if (n == 0) return PINT_OK;
+    if (!pairs) return PINT_E_NULL;
+    if ((uintptr_t)pairs % d.elem_bytes) return PINT_E_ARG;
+    const launch_geom g = geom();
+    auto ops = std::make_integer_sequence<int, pint::cuda::OP_NUM_BINARY>();
+    switch (d.elem_bytes) {
+    case 1: return (int)pairs_ops<uint8_t>(op, d, pairs, n, sum_dev, s, g, ops);
+    case 2: return (int)pairs_ops<uint16_t>(op, d, pairs, n, sum_dev, s, g, ops);
+    case 4: return (int)pairs_ops<uint32_t>(op, d, pairs, n, sum_dev, s, g, ops);
+    default: return (int)pairs_ops<uint64_t>(op, d, pairs, n, sum_dev, s, g, ops);
+    }
+}
+
+int pint_cuda_plan_shards(size_t n, uint32_t elem_bytes, int nshards, size_t* begin, size_t* count)
+{
+    if (elem_bytes != 1 && elem_bytes != 2 && elem_bytes != 4 && elem_bytes != 8) return PINT_E_ELEM_BYTES;
+    if (nshards < 1 || !begin || !count) return PINT_E_ARG;
+    const size_t per128 = 128 / elem_bytes;           // elements per 128 bytes
+    size_t base = (n / (size_t)nshards) / per128 * per128;  // shard length rounded down to 128 B
+    size_t pos = 0;
+    for (int k = 0; k < nshards; ++k) {
+        begin[k] = pos;
+        count[k] = (k == nshards - 1) ? n - pos : base;
+        pos += count[k];
+    }
+    return PINT_OK;
+}
+
+int pint_cuda_sharded_binary(int op, const pint_layout* layout, int ngpu, const int* devices, const void* const* a,
+                             const void* const* b, void* const* out, const size_t* counts, const pint_stream_t* streams)
+{
+    if (ngpu < 1 || !devices || !a || !b || !out || !counts) return PINT_E_ARG;
+    int prev = 0;
+    if (cudaError_t e = cudaGetDevice(&prev)) return (int)e;
+    int rc = PINT_OK;
+    for (int k = 0; k < ngpu && rc == PINT_OK; ++k) {
+        if (cudaError_t e = cudaSetDevice(devices[k])) { rc = (int)e; break; }
+        rc = binary_impl(op, false, layout, a[k], b[k], out[k], counts[k], streams ? (cudaStream_t)streams[k] : nullptr);
+    }
+    cudaSetDevice(prev);
+    return rc;
+}
+
+int pint_cuda_host_alloc(void** ptr, size_t bytes)
+{
+    if (!ptr) return PINT_E_NULL;
+    return (int)cudaHostAlloc(ptr, bytes ? bytes : 1, cudaHostAllocDefault);
+}
+
+int pint_cuda_host_free(void* ptr) { return ptr ? (int)cudaFreeHost(ptr) : PINT_OK; }
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------
+// Host-buffer path: a ring of `host_slots` slots, each with its own stream and
+// device staging for one chunk of a, b and out.  On a slot's stream the order is
+// H2D(a), H2D(b), kernel, D2H(out); different slots overlap, so both copy
+// engines and the SMs are busy at once.  Staging is allocated on first use per
+// device and kept (the device entry points above never allocate).
+namespace pint_cuda_impl {
+namespace {
+
+struct host_ring {
+    int device = -1;
+    size_t chunk_bytes = 0;
+    int slots = 0;
+    cudaStream_t stream[8] = {};
+    void* buf[8][3] = {};
+};
+
+std::mutex g_ring_mutex;
+host_ring g_rings[64];
+
+void ring_release(host_ring& r)
+{
+    for (int i = 0; i < r.slots; ++i) {
+        for (int j = 0; j < 3; ++j) if (r.buf[i][j]) cudaFree(r.buf[i][j]);
+        if (r.stream[i]) cudaStreamDestroy(r.stream[i]);
+    }
+    r = host_ring{};
+}
+
+cudaError_t ring_get(host_ring** out)
+{
+    int dev = 0;
+    if (cudaError_t e = cudaGetDevice(&dev)) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    host_ring& r = g_rings[dev];
+    const size_t want = (size_t)opts().host_chunk_bytes / 16 * 16;
+    const int slots = (int)opts().host_slots;
+    if (r.device != dev || r.chunk_bytes != want || r.slots != slots) {
+        ring_release(r);
+        r.device = dev; r.chunk_bytes = want; r.slots = slots;
+        for (int i = 0; i < slots; ++i) {
+            if (cudaError_t e = cudaStreamCreateWithFlags(&r.stream[i], cudaStreamNonBlocking)) return e;
+            for (int j = 0; j < 3; ++j)
+                if (cudaError_t e = cudaMalloc(&r.buf[i][j], want)) return e;
+        }
+    }
+    *out = &r;
+    return cudaSuccess;
+}
+
+}  // namespace
+}  // namespace pint_cuda_impl
+
+extern "C" int pint_cuda_binary_host(int op, const pint_layout* layout, const void* a_host, const void* b_host,
+                                     void* out_host, size_t n)
+{
+    layout_desc d;
+    if (int rc = check_layout(layout, &d)) return rc;
+    if (op < 0 || op >= PINT_NUM_BINARY_OPS) return PINT_E_OP;
+    if (n == 0) return PINT_OK;
+    if (!a_host || !b_host || !out_host) return PINT_E_NULL;
+    std::lock_guard<std::mutex> lock(g_ring_mutex);
+    host_ring* r = nullptr;
+    if (cudaError_t e = ring_get(&r)) return (int)e;
+    const size_t chunk_elems = r->chunk_bytes / d.elem_bytes;
+    const char* pa = (const char*)a_host;
+    const char* pb = (const char*)b_host;
+    char* po = (char*)out_host;
+    int rc = PINT_OK;
+    size_t done = 0;
+    for (int it = 0; done < n && rc == PINT_OK; ++it) {
+        const int slot = it % r->slots;
+        cudaStream_t s = r->stream[slot];
+        const size_t cnt = n - done < chunk_elems ? n - done : chunk_elems;
+        const size_t bytes = cnt * d.elem_bytes, off = done * d.elem_bytes;
+        // stream order makes the slot's previous D2H finish before its buffers are overwritten
+        if (cudaError_t e = cudaMemcpyAsync(r->buf[slot][0], pa + off, bytes, cudaMemcpyHostToDevice, s)) { rc = (int)e; break; }
+        if (cudaError_t e = cudaMemcpyAsync(r->buf[slot][1], pb + off, bytes, cudaMemcpyHostToDevice, s)) { rc = (int)e; break; }
+        rc = binary_impl(op, false, layout, r->buf[slot][0], r->buf[slot][1], r->buf[slot][2], cnt, s);
+        if (rc != PINT_OK) break;
+        if (cudaError_t e = cudaMemcpyAsync(po + off, r->buf[slot][2], bytes, cudaMemcpyDeviceToHost, s)) { rc = (int)e; break; }
+        done += cnt;
+    }
+    for (int i = 0; i < r->slots; ++i) {
+        const cudaError_t e = cudaStreamSynchronize(r->stream[i]);
+        if (e != cudaSuccess && rc == PINT_OK) rc = (int)e;
+    }
+    return rc;
+}

@@ -1,0 +1,29 @@
+// api_common.hpp -- shared by api.cu and api_aux.cu.
+#pragma once
+
+#include <cstdint>
+#include <cstring>
+
+#include "pint_cuda.h"
+#include "registry.hpp"
+
+namespace pint_cuda_impl {
+
+struct options {
+    long force_generic = 0;
+    long ctas_per_sm = 8;
+    long host_chunk_bytes = 32L << 20;  // per operand per pipeline slot
+    long host_slots = 3;
+};
+options& opts();
+
+extern unsigned long long g_launches;
+
+int check_layout(const pint_layout* l, layout_desc* d);
+int current_sms();
+launch_geom geom();
+const layout_kernels* find_static(const layout_desc& d);
+int binary_impl(int op, bool fused, const pint_layout* layout, const void* a, const void* b, void* out, size_t n,
+                cudaStream_t s);
+
+}  // namespace pint_cuda_impl

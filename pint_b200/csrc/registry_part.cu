@@ -1,0 +1,83 @@
+// registry_part.cu -- instantiates the static-mask kernels for the layouts of
+// one part of registry_layouts.def.  Compile with -DPINT_REG_PART=<0..3>.
+#include "registry.hpp"
+
+#ifndef PINT_REG_PART
+#error "compile with -DPINT_REG_PART=n"
+#endif
+
+namespace pint_cuda_impl {
+namespace {
+
+using namespace pint::cuda;
+using namespace pint::cuda::kernels;
+
+template <class SL, int Op>
+cudaError_t binary_entry(const void* a, const void* b, void* out, size_t n, cudaStream_t s, const launch_geom& g)
+{
+    using Fn = swar_fn<Op, static_masks<SL>>;
+    return launch_binary<typename SL::integer, Fn>(a, b, out, n, Fn{}, s, g);
+}
+
+template <class SL, int Op>
+cudaError_t fused_entry(const void* a, const void* b, void* out, size_t n, cudaStream_t s, const launch_geom& g)
+{
+    using Fn = fused_fn<Op, static_fields<SL>>;
+    return launch_binary<typename SL::integer, Fn>(a, b, out, n, Fn{}, s, g);
+}
+
+template <class SL, bool Signed, int PB>
+cudaError_t unpack_entry(const void* packed, const plane_ptrs& planes, size_t n, cudaStream_t s, const launch_geom& g)
+{
+    return launch_unpack<typename SL::integer, PB, Signed>(packed, planes, SL::desc.nfields, n, static_fields<SL>{}, s, g);
+}
+
+template <class SL, int PB>
+cudaError_t repack_entry(const plane_ptrs& planes, void* packed, size_t n, cudaStream_t s, const launch_geom& g)
+{
+    return launch_repack<typename SL::integer, PB>(planes, SL::desc.nfields, packed, n, static_fields<SL>{}, s, g);
+}
+
+template <class SL, int... Ops>
+layout_kernels make_kernels(std::integer_sequence<int, Ops...>)
+{
+    layout_kernels k{};
+    k.desc = SL::desc;
+    ((k.binary[Ops] = &binary_entry<SL, Ops>), ...);
+    ((k.fused[Ops] = &fused_entry<SL, Ops>), ...);
+    k.unpack[0][0] = &unpack_entry<SL, false, 4>;
+    k.unpack[0][1] = &unpack_entry<SL, false, 8>;
+    k.unpack[1][0] = &unpack_entry<SL, true, 4>;
+    k.unpack[1][1] = &unpack_entry<SL, true, 8>;
+    k.repack[0] = &repack_entry<SL, 4>;
+    k.repack[1] = &repack_entry<SL, 8>;
+    return k;
+}
+
+template <int Part, int P, class I, std::size_t... B>
+void add(layout_kernels* tab, int& n)
+{
+    if constexpr (Part == P)
+        tab[n++] = make_kernels<static_layout<I, B...>>(std::make_integer_sequence<int, OP_NUM_BINARY>());
+}
+
+}  // namespace
+
+#define PINT_CAT2(a, b) a##b
+#define PINT_CAT(a, b) PINT_CAT2(a, b)
+
+const layout_kernels* PINT_CAT(registry_part, PINT_REG_PART)(int* count)
+{
+    static layout_kernels tab[16];
+    static int n = [] {
+        int k = 0;
+#define X(part, I, ...) add<PINT_REG_PART, part, I, __VA_ARGS__>(tab, k);
+#include "registry_layouts.def"
+#undef X
+        return k;
+    }();
+    *count = n;
+    return tab;
+}
+
+}  // namespace pint_cuda_impl

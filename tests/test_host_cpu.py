@@ -1,0 +1,135 @@
+"""CPU-side checks: the C-ABI library loads without a GPU and exports every
+symbol include/pint_cuda.h declares; layout validation, the mask generator and
+the shard planner (host logic) agree with the oracle.  No kernel is launched."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import pint_b200
+from pint_b200 import _lib, sharded
+
+
+def declared_symbols():
+    src = open(_lib.HEADER_PATH).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(pint_cuda_\w+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = _lib.lib()
+    names = declared_symbols()
+    assert len(names) >= 24
+    for name in names:
+        assert hasattr(lib, name), f"{name} declared in include/pint_cuda.h but not exported"
+    assert sorted(lib._pint_symbols) == names, "pint_b200/_lib.py binds exactly the declared ABI"
+    assert lib.pint_cuda_abi_version() == 1
+
+
+def test_no_cpu_fallback():
+    """Without a device a compute call returns a CUDA error; it never computes on the host."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("has a GPU")
+    L = pint_b200.Layout.make(5, 6, 5)
+    a = np.arange(64, dtype=np.uint16)
+    out = np.zeros_like(a)
+    rc = _lib.lib().pint_cuda_binary(0, L.ref, a.ctypes.data, a.ctypes.data, out.ctypes.data, a.size, None)
+    assert rc > 0, "expected a cudaError_t"
+    assert not out.any()
+    from pint_b200 import ops
+    with pytest.raises(TypeError):
+        ops.add_wrap(L, torch.zeros(4, dtype=torch.int16), torch.zeros(4, dtype=torch.int16))
+
+
+def test_layout_validation_matches_oracle(oracle):
+    rng = np.random.default_rng(7)
+    lib = _lib.lib()
+    for _ in range(2000):
+        eb = int(rng.choice([1, 2, 3, 4, 8, 16]))
+        nf = int(rng.integers(0, 12))
+        bits = [int(x) for x in rng.integers(0, 20, nf)]
+        l = _lib.PintLayout()
+        l.elem_bytes, l.nfields = eb, nf
+        for i, b in enumerate(bits):
+            l.bits[i] = b
+        assert lib.pint_cuda_layout_validate(C.byref(l)) == oracle.validate(eb, bits), (eb, bits)
+
+
+def test_mask_generator_matches_oracle(oracle, refvec):
+    for _, eb, bits in refvec.layouts():
+        got = pint_b200.Layout(eb, *bits).masks()
+        _, m = oracle.masks(eb, bits)
+        assert got == {"H": m.H, "L": m.L, "A": m.A, "sat_type": m.sat_type}, (eb, bits)
+    rng = np.random.default_rng(11)
+    seen = set()
+    for _ in range(500):
+        eb = int(rng.choice([1, 2, 4, 8]))
+        bits, room = [], 8 * eb
+        while room > 0 and len(bits) < 64 and rng.random() < 0.85:
+            w = int(rng.integers(1, min(room, 20) + 1))
+            bits.append(w)
+            room -= w
+        if not bits:
+            continue
+        got = pint_b200.Layout(eb, *bits).masks()
+        _, m = oracle.masks(eb, bits)
+        assert got == {"H": m.H, "L": m.L, "A": m.A, "sat_type": m.sat_type}, (eb, bits)
+        seen.add(m.sat_type)
+    assert seen == {0, 1, 2}
+
+
+def test_storage_bytes_matches_reference_static_asserts(kats):
+    for k in kats:
+        if k["kind"] == "storage":
+            assert pint_b200.storage_bytes(k["total_bits"]) == k["elem_bytes"]
+    assert pint_b200.storage_bytes(0) == 0 and pint_b200.storage_bytes(65) == 0
+    assert pint_b200.Layout.make(5, 6, 5).elem_bytes == 2
+    assert pint_b200.Layout.make(3, 7, 11, 13, 17, 13).elem_bytes == 8
+
+
+def test_registry_has_baseline_layouts():
+    for eb, bits in [(2, (5, 6, 5)), (4, (8, 8, 8, 8)), (8, (16, 16, 16, 16)), (8, (3, 7, 11, 13, 17, 13))]:
+        assert pint_b200.Layout(eb, *bits).is_specialized()
+    assert not pint_b200.Layout(4, 7, 9, 3).is_specialized()
+
+
+def test_slice_layout():
+    L = pint_b200.Layout(2, 1, 2, 3, 4, 5)
+    assert L.sliced(2, 4) == pint_b200.Layout(2, 3, 4)   # tests/pint_test.cpp:135-146
+    with pytest.raises(ValueError):
+        L.sliced(3, 3)
+    res = _lib.PintLayout()
+    assert _lib.lib().pint_cuda_slice_layout(L.ref, 2, 4, C.byref(res)) == 0
+    assert (res.elem_bytes, res.nfields, res.bits[0], res.bits[1]) == (2, 2, 3, 4)
+    assert _lib.lib().pint_cuda_slice_layout(L.ref, 4, 6, C.byref(res)) == -12
+
+
+@pytest.mark.parametrize("n", [0, 1, 127, 128, 1000003, 2 ** 31, 2 ** 33 + 5])
+@pytest.mark.parametrize("eb", [1, 2, 4, 8])
+@pytest.mark.parametrize("k", [1, 2, 3, 4, 8])
+def test_plan_shards(n, eb, k):
+    plan = sharded.plan_shards(n, eb, k)
+    assert len(plan) == k
+    pos = 0
+    for i, (b, c) in enumerate(plan):
+        assert b == pos
+        assert (b * eb) % 128 == 0, "shard starts on a 128-byte boundary"
+        pos += c
+    assert pos == n
+    if n >= k * 128:
+        counts = [c for _, c in plan]
+        assert max(counts) - min(counts) < k * (128 // eb) + 128 // eb
+
+
+def test_options_roundtrip():
+    from pint_b200 import ops
+    ops.set_option("force_generic", 1)
+    assert ops.get_option("force_generic") == 1
+    assert not pint_b200.Layout(4, 8, 8, 8, 8).is_specialized()
+    ops.set_option("force_generic", 0)
+    assert pint_b200.Layout(4, 8, 8, 8, 8).is_specialized()
+    with pytest.raises(_lib.PintCudaError):
+        ops.set_option("no_such_option", 1)

@@ -1,0 +1,162 @@
+// tools/tune.cu -- kernel-variant sweep for the streaming kernels (run on a B200
+// through gpurun; results are copied to profiles/).  Not part of the library.
+//   build/tune [log2_elems=30] [reps=10]
+// Prints one line per variant: achieved algorithmic GB/s (12 B/elem for the
+// binary op on uint32 RGBA8, 24 B/elem for uint64) measured with CUDA events,
+// best and median over reps, buffers >> L2.
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+
+#include "pint/cuda_kernels.cuh"
+#include "pint/cuda_kernels_bulk.cuh"
+
+using namespace pint::cuda;
+using namespace pint::cuda::kernels;
+
+#define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { std::printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e_), __FILE__, __LINE__); std::exit(1); } } while (0)
+
+static int g_reps = 10;
+static int g_sms = 148;
+
+template <class F>
+static void time_it(const char* name, double bytes, F launch)
+{
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    for (int i = 0; i < 3; ++i) launch();
+    CK(cudaDeviceSynchronize());
+    std::vector<float> ms(g_reps);
+    for (int i = 0; i < g_reps; ++i) {
+        CK(cudaEventRecord(e0));
+        launch();
+        CK(cudaEventRecord(e1));
+        CK(cudaEventSynchronize(e1));
+        CK(cudaEventElapsedTime(&ms[i], e0, e1));
+    }
+    CK(cudaGetLastError());
+    std::sort(ms.begin(), ms.end());
+    std::printf("%-64s best %8.1f GB/s  median %8.1f GB/s  (%.3f ms)\n", name, bytes / ms[0] / 1e6, bytes / ms[g_reps / 2] / 1e6, ms[g_reps / 2]);
+    std::fflush(stdout);
+}
+
+template <class Fn, int U, int B, int LD, int ST>
+static void run_stream(const char* tag, const void* a, const void* b, void* out, size_t nvec, int ctas_per_sm)
+{
+    using Cfg = stream_cfg<U, B, LD, ST>;
+    constexpr size_t tile = size_t(U) * B;
+    const size_t ntiles = (nvec + tile - 1) / tile;
+    const size_t grid = ctas_per_sm > 0 ? std::min(ntiles, size_t(g_sms) * ctas_per_sm) : ntiles;
+    char name[128];
+    std::snprintf(name, sizeof name, "%s stream U%d B%d ld%d st%d ctas/sm %d", tag, U, B, LD, ST, ctas_per_sm);
+    time_it(name, double(nvec) * 48, [&] {
+        binary_stream_kernel<Fn, Cfg><<<unsigned(grid), B>>>((const uint4*)a, (const uint4*)b, (uint4*)out, nvec, Fn{});
+    });
+}
+
+template <class Fn, int S, int TB, int B>
+static void run_bulk(const char* tag, const void* a, const void* b, void* out, size_t nvec, int ctas_per_sm)
+{
+    using Cfg = bulk::bulk_cfg<S, TB, B>;
+    const size_t ntiles = nvec / (TB / 16);
+    CK(cudaFuncSetAttribute(bulk::binary_bulk_kernel<Fn, Cfg>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    const size_t grid = std::min(ntiles, size_t(g_sms) * ctas_per_sm);
+    char name[128];
+    std::snprintf(name, sizeof name, "%s bulk  S%d tile%dK B%d ctas/sm %d (smem %d KB)", tag, S, TB / 1024, B, ctas_per_sm, Cfg::SMEM_BYTES / 1024);
+    time_it(name, double(ntiles) * TB * 3, [&] {
+        bulk::binary_bulk_kernel<Fn, Cfg><<<unsigned(grid), B, Cfg::SMEM_BYTES>>>((const uint4*)a, (const uint4*)b, (uint4*)out, ntiles, Fn{});
+    });
+}
+
+__global__ void fill(uint4* p, size_t nvec, uint32_t seed)
+{
+    for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += size_t(gridDim.x) * blockDim.x) {
+        uint32_t x = uint32_t(i) * 2654435761u ^ seed;
+        p[i] = make_uint4(x, x * 3 + 1, x ^ 0x9E3779B9u, x * 7 + 5);
+    }
+}
+
+__global__ void compare(const uint4* x, const uint4* y, size_t nvec, unsigned long long* bad)
+{
+    for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += size_t(gridDim.x) * blockDim.x) {
+        uint4 p = x[i], q = y[i];
+        if (p.x != q.x || p.y != q.y || p.z != q.z || p.w != q.w) atomicAdd(bad, 1ULL);
+    }
+}
+
+int main(int argc, char** argv)
+{
+    const int log2n = argc > 1 ? std::atoi(argv[1]) : 30;
+    g_reps = argc > 2 ? std::atoi(argv[2]) : 10;
+    const size_t bytes = (size_t(1) << log2n) * 4;  // per array
+    const size_t nvec = bytes / 16;
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, 0));
+    g_sms = prop.multiProcessorCount;
+    std::printf("device %s, %d SMs, array %.2f GiB x3\n", prop.name, g_sms, bytes / 1073741824.0);
+    void *a, *b, *out, *out2;
+    CK(cudaMalloc(&a, bytes)); CK(cudaMalloc(&b, bytes)); CK(cudaMalloc(&out, bytes)); CK(cudaMalloc(&out2, bytes));
+    fill<<<g_sms * 8, 256>>>((uint4*)a, nvec, 1u);
+    fill<<<g_sms * 8, 256>>>((uint4*)b, nvec, 2u);
+    CK(cudaDeviceSynchronize());
+
+    time_it("cudaMemcpyAsync D2D (1R+1W; bytes = 2 x array)", double(bytes) * 2, [&] { CK(cudaMemcpyAsync(out, a, bytes, cudaMemcpyDeviceToDevice)); });
+
+    using RGBA = static_layout<uint32_t, 8, 8, 8, 8>;
+    using FnU = swar_fn<OP_ADD_UNSIGNED_SATURATE, static_masks<RGBA>>;
+    using FnS = swar_fn<OP_ADD_SIGNED_SATURATE, static_masks<RGBA>>;
+    using IRR = static_layout<uint64_t, 3, 7, 11, 13, 17, 13>;
+    using FnI = swar_fn<OP_ADD_SIGNED_SATURATE, static_masks<IRR>>;
+    using FnIF = fused_fn<OP_ADD_SIGNED_SATURATE, static_fields<IRR>>;
+    using FnX = swar_fn<OP_XOR, static_masks<RGBA>>;
+
+    // --- grid / unroll / block sweep with the streaming policy ---
+    for (int cps : {0, 2, 4, 8, 16, 32}) run_stream<FnU, 4, 256, 2, 2>("usat rgba8", a, b, out, nvec, cps);
+    for (int cps : {0, 4, 8, 16}) run_stream<FnU, 1, 256, 2, 2>("usat rgba8", a, b, out, nvec, cps);
+    for (int cps : {0, 4, 8, 16}) run_stream<FnU, 2, 256, 2, 2>("usat rgba8", a, b, out, nvec, cps);
+    for (int cps : {0, 2, 4, 8}) run_stream<FnU, 8, 256, 2, 2>("usat rgba8", a, b, out, nvec, cps);
+    for (int cps : {0, 2, 4, 8}) run_stream<FnU, 4, 512, 2, 2>("usat rgba8", a, b, out, nvec, cps);
+    for (int cps : {0, 8, 16, 32}) run_stream<FnU, 4, 128, 2, 2>("usat rgba8", a, b, out, nvec, cps);
+    for (int cps : {0, 2, 4}) run_stream<FnU, 2, 1024, 2, 2>("usat rgba8", a, b, out, nvec, cps);
+    // --- cache policy sweep ---
+    run_stream<FnU, 4, 256, 0, 0>("usat rgba8", a, b, out, nvec, 8);
+    run_stream<FnU, 4, 256, 1, 1>("usat rgba8", a, b, out, nvec, 8);
+    run_stream<FnU, 4, 256, 2, 0>("usat rgba8", a, b, out, nvec, 8);
+    run_stream<FnU, 4, 256, 0, 2>("usat rgba8", a, b, out, nvec, 8);
+    run_stream<FnU, 4, 256, 1, 2>("usat rgba8", a, b, out, nvec, 8);
+    run_stream<FnU, 4, 256, 1, 0>("usat rgba8", a, b, out, nvec, 0);
+    run_stream<FnU, 4, 256, 0, 0>("usat rgba8", a, b, out, nvec, 0);
+    // --- other ops: is anything ALU-bound? ---
+    run_stream<FnX, 4, 256, 2, 2>("xor  rgba8", a, b, out, nvec, 8);
+    run_stream<FnS, 4, 256, 2, 2>("ssat rgba8", a, b, out, nvec, 8);
+    run_stream<FnI, 4, 256, 2, 2>("ssat irregular u64 swar ", a, b, out, nvec, 8);
+    run_stream<FnIF, 4, 256, 2, 2>("ssat irregular u64 fused", a, b, out, nvec, 8);
+    run_stream<FnI, 2, 256, 2, 2>("ssat irregular u64 swar ", a, b, out, nvec, 8);
+    run_stream<FnIF, 2, 256, 2, 2>("ssat irregular u64 fused", a, b, out, nvec, 8);
+
+    // --- TMA bulk variants ---
+    run_bulk<FnU, 4, 8192, 256>("usat rgba8", a, b, out2, nvec, 3);
+    // correctness of the bulk path against the stream path
+    {
+        run_stream<FnU, 4, 256, 2, 2>("usat rgba8 (reference for compare)", a, b, out, nvec, 8);
+        unsigned long long* bad;
+        CK(cudaMallocManaged(&bad, 8));
+        *bad = 0;
+        const size_t covered = nvec / 512 * 512;
+        compare<<<g_sms * 8, 256>>>((const uint4*)out, (const uint4*)out2, covered, bad);
+        CK(cudaDeviceSynchronize());
+        std::printf("bulk vs stream mismatching vectors: %llu of %zu\n", *bad, covered);
+    }
+    run_bulk<FnU, 3, 8192, 256>("usat rgba8", a, b, out2, nvec, 4);
+    run_bulk<FnU, 6, 4096, 256>("usat rgba8", a, b, out2, nvec, 4);
+    run_bulk<FnU, 4, 16384, 256>("usat rgba8", a, b, out2, nvec, 1);
+    run_bulk<FnU, 3, 16384, 512>("usat rgba8", a, b, out2, nvec, 2);
+    run_bulk<FnU, 6, 16384, 512>("usat rgba8", a, b, out2, nvec, 1);
+    run_bulk<FnU, 8, 4096, 128>("usat rgba8", a, b, out2, nvec, 3);
+    run_bulk<FnU, 4, 4096, 128>("usat rgba8", a, b, out2, nvec, 6);
+    run_bulk<FnU, 2, 32768, 512>("usat rgba8", a, b, out2, nvec, 1);
+    run_bulk<FnI, 4, 8192, 256>("ssat irregular u64 swar ", a, b, out2, nvec, 3);
+    std::printf("done\n");
+    return 0;
+}
