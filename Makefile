@@ -38,7 +38,7 @@ build/tune: tools/tune.cu $(HDRS)
 
 build/cpp_api_test: tests/cpp/cpp_api_test.cpp include/pint/cuda.hpp $(LIB)
 	@mkdir -p build
-	g++ -std=c++11 -O2 -Iinclude -I/usr/local/cuda/include -o $@ tests/cpp/cpp_api_test.cpp -Lpint_b200/lib -lpint_cuda -Wl,-rpath,'$$ORIGIN/../pint_b200/lib'
+	g++ -std=c++11 -O2 -Iinclude -I/usr/local/cuda/include -o $@ tests/cpp/cpp_api_test.cpp -Lpint_b200/lib -lpint_cuda -L/usr/local/cuda/lib64 -lcudart -Wl,-rpath,'$$ORIGIN/../pint_b200/lib'
 
 clean:
 	rm -rf build pint_b200/lib

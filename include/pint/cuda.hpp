@@ -1,0 +1,241 @@
+// pint/cuda.hpp -- the pint::cuda batch layer: host C++ templates over device arrays.
+//
+// The scalar API of pint (/root/reference/include/pint/pint.hpp, "pint.hpp:N"
+// below) is unchanged; this header adds, beside it, the same operations applied
+// elementwise to arrays of packed_int<Integer, Bits...> in GPU memory:
+//
+//     using rgba = pint::packed_int<uint32_t, 8, 8, 8, 8>;
+//     rgba *a, *b, *out;                       // device pointers, n elements
+//     pint::cuda::add_signed_saturate(a, b, out, n, stream);
+//     // out[i] == pint::add_signed_saturate(a[i], b[i])      (pint.hpp:857-866)
+//
+// Names, argument order and per-element meaning are the scalar API's.  Each
+// template turns the Bits... pack into a pint_layout descriptor at compile time
+// and calls the C ABI of libpint_cuda.so (include/pint_cuda.h), where
+// hand-written sm_100a kernels do the work; layouts listed in the library's
+// registry run kernels with the field masks compiled in, all others run the
+// same kernels with the masks as kernel parameters.  No CPU fallback.
+//
+// C++11, header-only, needs neither nvcc nor pint.hpp: packed_int is only
+// forward-declared (exactly as pint.hpp:25 declares it), pointers to it are
+// passed through untouched.  Include pint.hpp as well to use the scalar API.
+//
+// Errors: the conditions pint rejects at compile time are rejected here at
+// compile time too (static_asserts below mirror pint.hpp:761-764, 748, 802,
+// 813); runtime failures (CUDA errors, null or overlapping arrays) throw
+// pint::cuda::error carrying the ABI's return code.  Every call is asynchronous
+// on `stream`.
+#pragma once
+
+#include <cstddef>
+#include <cstdint>
+#include <stdexcept>
+#include <string>
+#include <type_traits>
+
+#include "../pint_cuda.h"
+
+namespace pint {
+
+using std::size_t;
+template <class Integer, size_t Bits0, size_t... Bits> class packed_int;  // pint.hpp:25
+
+namespace cuda {
+
+typedef pint_stream_t stream_t;  // a cudaStream_t
+
+class error : public std::runtime_error {
+public:
+    error(int rc, const char* what_call)
+        : std::runtime_error(std::string(what_call) + ": " + pint_cuda_error_string(rc)), code(rc) {}
+    int code;
+};
+
+inline void check(int rc, const char* what_call)
+{
+    if (rc != PINT_OK) throw error(rc, what_call);
+}
+
+namespace detail {
+
+template <size_t... Bits> struct sum_bits;
+template <> struct sum_bits<> { static const size_t value = 0; };
+template <size_t B0, size_t... Bits> struct sum_bits<B0, Bits...> { static const size_t value = B0 + sum_bits<Bits...>::value; };
+
+template <size_t... Bits> struct all_positive;
+template <> struct all_positive<> { static const bool value = true; };
+template <size_t B0, size_t... Bits> struct all_positive<B0, Bits...> { static const bool value = (B0 > 0) && all_positive<Bits...>::value; };
+
+// sum of the first N values of the pack (slice offsets, pint.hpp:927-928)
+template <size_t N, size_t... Bits> struct sum_front;
+template <size_t... Bits> struct sum_front<0, Bits...> { static const size_t value = 0; };
+template <size_t N, size_t B0, size_t... Bits> struct sum_front<N, B0, Bits...> { static const size_t value = B0 + sum_front<N - 1, Bits...>::value; };
+
+// compile-time checks of packed_int (pint.hpp:761-764) + descriptor
+template <class Integer, size_t... Bits>
+struct layout_of {
+    static_assert(std::is_integral<Integer>::value && std::is_unsigned<Integer>::value,
+                  "Integer must be unsigned integer");
+    static_assert(sizeof(Integer) == 1 || sizeof(Integer) == 2 || sizeof(Integer) == 4 || sizeof(Integer) == 8,
+                  "Integer must be uint8_t, uint16_t, uint32_t or uint64_t");
+    static_assert(sizeof(Integer) * 8 >= sum_bits<Bits...>::value, "Integer won't fit given number of bits");
+    static_assert(all_positive<Bits...>::value, "fields must have at least 1 bit");
+    static_assert(sizeof...(Bits) >= 1 && sizeof...(Bits) <= PINT_MAX_FIELDS, "1..64 fields");
+
+    static pint_layout get()
+    {
+        pint_layout l = {(uint32_t)sizeof(Integer), (uint32_t)sizeof...(Bits), {(uint8_t)Bits...}};
+        return l;
+    }
+};
+
+// slice<Start, End> result type (sliced_int, pint.hpp:746-754), without pint.hpp's type lists:
+// skip `Skip` widths, take `Take` widths, wrap them in packed_int.
+template <size_t... Bits> struct bits_pack {};
+template <int State, size_t Skip, size_t Take, class Integer, class Taken, size_t... Rest> struct slice_step;
+template <size_t Skip, size_t Take, class Integer, class Taken, size_t... Rest>
+struct slice_next {
+    typedef typename slice_step<(Skip > 0 ? 0 : (Take > 0 ? 1 : 2)), Skip, Take, Integer, Taken, Rest...>::type type;
+};
+template <size_t Skip, size_t Take, class Integer, size_t B0, size_t... Rest>
+struct slice_step<0, Skip, Take, Integer, bits_pack<>, B0, Rest...> {
+    typedef typename slice_next<Skip - 1, Take, Integer, bits_pack<>, Rest...>::type type;
+};
+template <size_t Take, class Integer, size_t... Taken, size_t B0, size_t... Rest>
+struct slice_step<1, 0, Take, Integer, bits_pack<Taken...>, B0, Rest...> {
+    typedef typename slice_next<0, Take - 1, Integer, bits_pack<Taken..., B0>, Rest...>::type type;
+};
+template <class Integer, size_t T0, size_t... Taken, size_t... Rest>
+struct slice_step<2, 0, 0, Integer, bits_pack<T0, Taken...>, Rest...> {
+    typedef packed_int<Integer, T0, Taken...> type;
+};
+
+}  // namespace detail
+
+// packed_int<Integer, Bits...> as the ABI's descriptor
+template <class Integer, size_t Bits0, size_t... Bits>
+inline pint_layout layout(const packed_int<Integer, Bits0, Bits...>* = nullptr)
+{
+    return detail::layout_of<Integer, Bits0, Bits...>::get();
+}
+
+template <size_t Start, size_t End, class Integer, size_t Bits0, size_t... Bits>
+struct sliced_int {
+    static_assert(Start < End && End <= sizeof...(Bits) + 1, "Incorrect slice bounds");  // pint.hpp:748
+    typedef typename detail::slice_next<Start, End - Start, Integer, detail::bits_pack<>, Bits0, Bits...>::type type;
+};
+
+// ---- the 13 binary operations: out[i] = OP(a[i], b[i]); out may be a or b ----
+#define PINT_CUDA_BINARY(NAME, CODE)                                                                    \
+    template <class Integer, size_t Bits0, size_t... Bits>                                              \
+    inline void NAME(const packed_int<Integer, Bits0, Bits...>* a, const packed_int<Integer, Bits0, Bits...>* b, \
+                     packed_int<Integer, Bits0, Bits...>* out, size_t n, stream_t stream = nullptr)     \
+    {                                                                                                   \
+        const pint_layout l = detail::layout_of<Integer, Bits0, Bits...>::get();                        \
+        check(pint_cuda_binary(CODE, &l, a, b, out, n, stream), "pint::cuda::" #NAME);                  \
+    }
+
+PINT_CUDA_BINARY(add_wrap, PINT_ADD_WRAP)                            // pint.hpp:826-838
+PINT_CUDA_BINARY(add_unsigned_saturate, PINT_ADD_UNSIGNED_SATURATE)  // pint.hpp:840-855
+PINT_CUDA_BINARY(add_signed_saturate, PINT_ADD_SIGNED_SATURATE)      // pint.hpp:857-866
+PINT_CUDA_BINARY(sub_wrap, PINT_SUB_WRAP)                            // pint.hpp:870-884
+PINT_CUDA_BINARY(sub_unsigned_saturate, PINT_SUB_UNSIGNED_SATURATE)  // pint.hpp:886-908
+PINT_CUDA_BINARY(sub_signed_saturate, PINT_SUB_SIGNED_SATURATE)      // pint.hpp:910-919
+PINT_CUDA_BINARY(bit_or, PINT_OR)                                    // pint.hpp:781
+PINT_CUDA_BINARY(bit_and, PINT_AND)                                  // pint.hpp:782
+PINT_CUDA_BINARY(bit_xor, PINT_XOR)                                  // pint.hpp:783
+PINT_CUDA_BINARY(min_unsigned, PINT_MIN_UNSIGNED)                    // pint.hpp:936-950
+PINT_CUDA_BINARY(max_unsigned, PINT_MAX_UNSIGNED)                    // pint.hpp:952-966
+PINT_CUDA_BINARY(min_signed, PINT_MIN_SIGNED)                        // pint.hpp:968-985
+PINT_CUDA_BINARY(max_signed, PINT_MAX_SIGNED)                        // pint.hpp:987-1004
+#undef PINT_CUDA_BINARY
+
+// Any of the above, computed as unpack -> per-field arithmetic -> repack in one kernel.
+template <class Integer, size_t Bits0, size_t... Bits>
+inline void fused_unpack_arith_repack(pint_op op, const packed_int<Integer, Bits0, Bits...>* a,
+                                      const packed_int<Integer, Bits0, Bits...>* b,
+                                      packed_int<Integer, Bits0, Bits...>* out, size_t n, stream_t stream = nullptr)
+{
+    const pint_layout l = detail::layout_of<Integer, Bits0, Bits...>::get();
+    check(pint_cuda_fused_unpack_arith_repack(op, &l, a, b, out, n, stream), "pint::cuda::fused_unpack_arith_repack");
+}
+
+// shift_left / shift_right_unsigned with a uniform amount (pint.hpp:1006-1029)
+template <class Integer, size_t Bits0, size_t... Bits>
+inline void shift_left(const packed_int<Integer, Bits0, Bits...>* in, size_t shift_amount,
+                       packed_int<Integer, Bits0, Bits...>* out, size_t n, stream_t stream = nullptr)
+{
+    const pint_layout l = detail::layout_of<Integer, Bits0, Bits...>::get();
+    check(pint_cuda_shift(1, &l, shift_amount, in, out, n, stream), "pint::cuda::shift_left");
+}
+
+template <class Integer, size_t Bits0, size_t... Bits>
+inline void shift_right_unsigned(const packed_int<Integer, Bits0, Bits...>* in, size_t shift_amount,
+                                 packed_int<Integer, Bits0, Bits...>* out, size_t n, stream_t stream = nullptr)
+{
+    const pint_layout l = detail::layout_of<Integer, Bits0, Bits...>::get();
+    check(pint_cuda_shift(0, &l, shift_amount, in, out, n, stream), "pint::cuda::shift_right_unsigned");
+}
+
+// slice<Start, End> (pint.hpp:923-932): out is an array of the narrower layout, same Integer
+template <size_t Start, size_t End, class Integer, size_t Bits0, size_t... Bits>
+inline void slice(const packed_int<Integer, Bits0, Bits...>* in,
+                  typename sliced_int<Start, End, Integer, Bits0, Bits...>::type* out, size_t n,
+                  stream_t stream = nullptr)
+{
+    const pint_layout l = detail::layout_of<Integer, Bits0, Bits...>::get();
+    check(pint_cuda_slice(&l, (uint32_t)Start, (uint32_t)End, in, out, n, stream), "pint::cuda::slice");
+}
+
+// get<I> / get_signed<I> over the whole array (pint.hpp:799-822): planes[f][i] = field f of
+// packed[i].  Plane is int32_t/uint32_t or int64_t/uint64_t; a null plane skips the field.
+template <class Plane, class Integer, size_t Bits0, size_t... Bits>
+inline void unpack(const packed_int<Integer, Bits0, Bits...>* packed, Plane* const (&planes)[sizeof...(Bits) + 1],
+                   size_t n, stream_t stream = nullptr)
+{
+    static_assert(std::is_integral<Plane>::value && (sizeof(Plane) == 4 || sizeof(Plane) == 8),
+                  "planes are 32- or 64-bit integers");
+    const pint_layout l = detail::layout_of<Integer, Bits0, Bits...>::get();
+    void* p[sizeof...(Bits) + 1];
+    for (size_t i = 0; i < sizeof...(Bits) + 1; ++i) p[i] = planes[i];
+    check(pint_cuda_unpack(&l, std::is_signed<Plane>::value ? 1 : 0, packed, p, (int)sizeof(Plane), n, stream),
+          "pint::cuda::unpack");
+}
+
+// the truncating field constructor over arrays (pint.hpp:770-774)
+template <class Plane, class Integer, size_t Bits0, size_t... Bits>
+inline void repack(const Plane* const (&planes)[sizeof...(Bits) + 1], packed_int<Integer, Bits0, Bits...>* packed,
+                   size_t n, stream_t stream = nullptr)
+{
+    static_assert(std::is_integral<Plane>::value && (sizeof(Plane) == 4 || sizeof(Plane) == 8),
+                  "planes are 32- or 64-bit integers");
+    const pint_layout l = detail::layout_of<Integer, Bits0, Bits...>::get();
+    const void* p[sizeof...(Bits) + 1];
+    for (size_t i = 0; i < sizeof...(Bits) + 1; ++i) p[i] = planes[i];
+    check(pint_cuda_repack(&l, p, (int)sizeof(Plane), packed, n, stream), "pint::cuda::repack");
+}
+
+// multi-GPU: independent contiguous shards, one per device, no collective
+namespace sharded {
+
+inline void plan(size_t n, size_t elem_bytes, int nshards, size_t* begin, size_t* count)
+{
+    check(pint_cuda_plan_shards(n, (uint32_t)elem_bytes, nshards, begin, count), "pint::cuda::sharded::plan");
+}
+
+template <class Integer, size_t Bits0, size_t... Bits>
+inline void binary(pint_op op, int ngpu, const int* devices, const packed_int<Integer, Bits0, Bits...>* const* a,
+                   const packed_int<Integer, Bits0, Bits...>* const* b, packed_int<Integer, Bits0, Bits...>* const* out,
+                   const size_t* counts, const stream_t* streams = nullptr)
+{
+    const pint_layout l = detail::layout_of<Integer, Bits0, Bits...>::get();
+    check(pint_cuda_sharded_binary(op, &l, ngpu, devices, reinterpret_cast<const void* const*>(a),
+                                   reinterpret_cast<const void* const*>(b), reinterpret_cast<void* const*>(out), counts,
+                                   streams),
+          "pint::cuda::sharded::binary");
+}
+
+}  // namespace sharded
+
+}  // namespace cuda
+}  // namespace pint

@@ -52,7 +52,7 @@ struct stream_cfg {
     static constexpr int LD = Ld;
     static constexpr int ST = St;
 };
-using default_stream_cfg = stream_cfg<4, 256>;
+using default_stream_cfg = stream_cfg<2, 256>;
 
 // apply a Word function to the 16 bytes of a vector
 template <class Word, class F>
@@ -172,18 +172,26 @@ unary_elem_kernel(const Elem* in, Elem* out, size_t n, const __grid_constant__ u
 }
 
 // ---------------------------------------------------------------------------
-// Launch geometry: persistent grid of num_sms * ctas_per_sm CTAs (a multiple of
-// the 148 SMs of a B200), or one CTA per tile when there are fewer tiles.
+// Launch geometry.  ctas_per_sm == 0 (default): one CTA per tile, handed out in
+// address order by the hardware block scheduler -- measured 10-15 % faster on
+// B200 than any persistent grid-stride grid (profiles/r01_tune_sweep1.log: 7.0-7.1
+// vs 6.0-6.5 TB/s), because the SMs' working window over the arrays stays
+// compact.  ctas_per_sm > 0: persistent grid of num_sms * ctas_per_sm CTAs
+// walking the tiles with a grid stride (kept for comparison and for tuning).
 struct launch_geom {
     int num_sms = 148;
-    int ctas_per_sm = 8;
+    int ctas_per_sm = 0;
     unsigned long long* launch_counter = nullptr;  // bumped once per kernel launch
 };
 
 inline unsigned grid_for(size_t ntiles, const launch_geom& g)
 {
-    const size_t cap = size_t(g.num_sms) * size_t(g.ctas_per_sm > 0 ? g.ctas_per_sm : 1);
-    size_t n = ntiles < cap ? ntiles : cap;
+    size_t n = ntiles;
+    if (g.ctas_per_sm > 0) {
+        const size_t cap = size_t(g.num_sms) * size_t(g.ctas_per_sm);
+        if (n > cap) n = cap;
+    }
+    if (n > 0x7FFFFFFFull) n = 0x7FFFFFFFull;  // gridDim.x limit; the kernels grid-stride beyond it
     return unsigned(n ? n : 1);
 }
 

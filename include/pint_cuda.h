@@ -87,7 +87,8 @@ const char* pint_cuda_error_string(int rc);
 unsigned long long pint_cuda_launch_count(void);
 /* Tuning/testing knobs: "force_generic" (1 = always use the runtime-mask
  * kernels even for layouts that have compiled-in constants),
- * "ctas_per_sm" (persistent grid size = SMs * this).  Returns 0 or PINT_E_ARG. */
+ * "ctas_per_sm" (0 = one CTA per tile, the default; k > 0 = persistent grid of SMs * k CTAs),
+ * "host_chunk_bytes" / "host_slots" (staging ring of the host-buffer path).  Returns 0 or PINT_E_ARG. */
 int pint_cuda_set_option(const char* key, long value);
 long pint_cuda_get_option(const char* key);
 
@@ -170,6 +171,13 @@ int pint_cuda_host_free(void* ptr);
  * cudaHostRegister); pageable memory works at pageable-copy speed. */
 int pint_cuda_binary_host(int op, const pint_layout* layout, const void* a_host, const void* b_host,
                           void* out_host, size_t n);
+/* outs_host[j][i] = ops[j](a_host[i], b_host[i]) for nops (1..PINT_MAX_HOST_OPS)
+ * operations on the SAME inputs: each chunk of a and b is uploaded once and every
+ * op's result is downloaded, which halves the PCIe traffic per result of a
+ * two-op pass such as add_unsigned_saturate + add_signed_saturate. */
+#define PINT_MAX_HOST_OPS 4
+int pint_cuda_binary_multi_host(int nops, const int* ops, const pint_layout* layout, const void* a_host,
+                                const void* b_host, void* const* outs_host, size_t n);
 
 #ifdef __cplusplus
 }

@@ -63,6 +63,7 @@ def lib():
             "pint_cuda_host_alloc": (i, [C.POINTER(vp), sz]),
             "pint_cuda_host_free": (i, [vp]),
             "pint_cuda_binary_host": (i, [i, LP, vp, vp, vp, sz]),
+            "pint_cuda_binary_multi_host": (i, [i, C.POINTER(i), LP, vp, vp, C.POINTER(vp), sz]),
         }
         for name, (res, args) in sigs.items():
             f = getattr(L, name)

@@ -235,7 +235,8 @@ int pint_cuda_host_free(void* ptr) { return ptr ? (int)cudaFreeHost(ptr) : PINT_
 // device staging for one chunk of a, b and out.  On a slot's stream the order is
 // H2D(a), H2D(b), kernel, D2H(out); different slots overlap, so both copy
 // engines and the SMs are busy at once.  Staging is allocated on first use per
-// device and kept (the device entry points above never allocate).
+// device and kept (the device entry points above never allocate).  Several ops on
+// the same inputs share one upload (pint_cuda_binary_multi_host).
 namespace pint_cuda_impl {
 namespace {
 
@@ -244,7 +245,7 @@ struct host_ring {
     size_t chunk_bytes = 0;
     int slots = 0;
     cudaStream_t stream[8] = {};
-    void* buf[8][3] = {};
+    void* buf[8][2 + PINT_MAX_HOST_OPS] = {};  // a, b, one output per op
 };
 
 std::mutex g_ring_mutex;
@@ -253,13 +254,13 @@ host_ring g_rings[64];
 void ring_release(host_ring& r)
 {
     for (int i = 0; i < r.slots; ++i) {
-        for (int j = 0; j < 3; ++j) if (r.buf[i][j]) cudaFree(r.buf[i][j]);
+        for (int j = 0; j < 2 + PINT_MAX_HOST_OPS; ++j) if (r.buf[i][j]) cudaFree(r.buf[i][j]);
         if (r.stream[i]) cudaStreamDestroy(r.stream[i]);
     }
     r = host_ring{};
 }
 
-cudaError_t ring_get(host_ring** out)
+cudaError_t ring_get(host_ring** out, int nops)
 {
     int dev = 0;
     if (cudaError_t e = cudaGetDevice(&dev)) return e;
@@ -270,12 +271,13 @@ cudaError_t ring_get(host_ring** out)
     if (r.device != dev || r.chunk_bytes != want || r.slots != slots) {
         ring_release(r);
         r.device = dev; r.chunk_bytes = want; r.slots = slots;
-        for (int i = 0; i < slots; ++i) {
+        for (int i = 0; i < slots; ++i)
             if (cudaError_t e = cudaStreamCreateWithFlags(&r.stream[i], cudaStreamNonBlocking)) return e;
-            for (int j = 0; j < 3; ++j)
-                if (cudaError_t e = cudaMalloc(&r.buf[i][j], want)) return e;
-        }
     }
+    for (int i = 0; i < slots; ++i)
+        for (int j = 0; j < 2 + nops; ++j)
+            if (!r.buf[i][j])
+                if (cudaError_t e = cudaMalloc(&r.buf[i][j], want)) return e;
     *out = &r;
     return cudaSuccess;
 }
@@ -283,21 +285,24 @@ cudaError_t ring_get(host_ring** out)
 }  // namespace
 }  // namespace pint_cuda_impl
 
-extern "C" int pint_cuda_binary_host(int op, const pint_layout* layout, const void* a_host, const void* b_host,
-                                     void* out_host, size_t n)
+extern "C" int pint_cuda_binary_multi_host(int nops, const int* ops, const pint_layout* layout, const void* a_host,
+                                           const void* b_host, void* const* outs_host, size_t n)
 {
     layout_desc d;
     if (int rc = check_layout(layout, &d)) return rc;
-    if (op < 0 || op >= PINT_NUM_BINARY_OPS) return PINT_E_OP;
+    if (nops < 1 || nops > PINT_MAX_HOST_OPS || !ops || !outs_host) return PINT_E_ARG;
+    for (int j = 0; j < nops; ++j)
+        if (ops[j] < 0 || ops[j] >= PINT_NUM_BINARY_OPS) return PINT_E_OP;
     if (n == 0) return PINT_OK;
-    if (!a_host || !b_host || !out_host) return PINT_E_NULL;
+    if (!a_host || !b_host) return PINT_E_NULL;
+    for (int j = 0; j < nops; ++j)
+        if (!outs_host[j]) return PINT_E_NULL;
     std::lock_guard<std::mutex> lock(g_ring_mutex);
     host_ring* r = nullptr;
-    if (cudaError_t e = ring_get(&r)) return (int)e;
+    if (cudaError_t e = ring_get(&r, nops)) return (int)e;
     const size_t chunk_elems = r->chunk_bytes / d.elem_bytes;
     const char* pa = (const char*)a_host;
     const char* pb = (const char*)b_host;
-    char* po = (char*)out_host;
     int rc = PINT_OK;
     size_t done = 0;
     for (int it = 0; done < n && rc == PINT_OK; ++it) {
@@ -305,12 +310,14 @@ extern "C" int pint_cuda_binary_host(int op, const pint_layout* layout, const vo
         cudaStream_t s = r->stream[slot];
         const size_t cnt = n - done < chunk_elems ? n - done : chunk_elems;
         const size_t bytes = cnt * d.elem_bytes, off = done * d.elem_bytes;
-        // stream order makes the slot's previous D2H finish before its buffers are overwritten
+        // stream order makes the slot's previous D2H copies finish before its buffers are overwritten
         if (cudaError_t e = cudaMemcpyAsync(r->buf[slot][0], pa + off, bytes, cudaMemcpyHostToDevice, s)) { rc = (int)e; break; }
         if (cudaError_t e = cudaMemcpyAsync(r->buf[slot][1], pb + off, bytes, cudaMemcpyHostToDevice, s)) { rc = (int)e; break; }
-        rc = binary_impl(op, false, layout, r->buf[slot][0], r->buf[slot][1], r->buf[slot][2], cnt, s);
-        if (rc != PINT_OK) break;
-        if (cudaError_t e = cudaMemcpyAsync(po + off, r->buf[slot][2], bytes, cudaMemcpyDeviceToHost, s)) { rc = (int)e; break; }
+        for (int j = 0; j < nops && rc == PINT_OK; ++j) {
+            rc = binary_impl(ops[j], false, layout, r->buf[slot][0], r->buf[slot][1], r->buf[slot][2 + j], cnt, s);
+            if (rc != PINT_OK) break;
+            if (cudaError_t e = cudaMemcpyAsync((char*)outs_host[j] + off, r->buf[slot][2 + j], bytes, cudaMemcpyDeviceToHost, s)) rc = (int)e;
+        }
         done += cnt;
     }
     for (int i = 0; i < r->slots; ++i) {
@@ -318,4 +325,11 @@ extern "C" int pint_cuda_binary_host(int op, const pint_layout* layout, const vo
         if (e != cudaSuccess && rc == PINT_OK) rc = (int)e;
     }
     return rc;
+}
+
+extern "C" int pint_cuda_binary_host(int op, const pint_layout* layout, const void* a_host, const void* b_host,
+                                     void* out_host, size_t n)
+{
+    void* outs[1] = {out_host};
+    return pint_cuda_binary_multi_host(1, &op, layout, a_host, b_host, outs, n);
 }

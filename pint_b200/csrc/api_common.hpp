@@ -11,7 +11,7 @@ namespace pint_cuda_impl {
 
 struct options {
     long force_generic = 0;
-    long ctas_per_sm = 8;
+    long ctas_per_sm = 0;  // 0 = one CTA per tile (fastest, see launch_geom)
     long host_chunk_bytes = 32L << 20;  // per operand per pipeline slot
     long host_slots = 3;
 };

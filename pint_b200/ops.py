@@ -223,6 +223,27 @@ def binary_host(op, layout, a, b, out):
     return out
 
 
+def binary_multi_host(op_list, layout, a, b, outs):
+    """Several ops on the same HOST inputs with one upload (pint_cuda_binary_multi_host)."""
+    def ptr_n(x):
+        if isinstance(x, torch.Tensor):
+            return x.data_ptr(), x.numel(), x.element_size()
+        return x.ctypes.data, x.size, x.itemsize
+    (pa, n, es), (pb, nb, _) = ptr_n(a), ptr_n(b)
+    if n != nb or es != layout.elem_bytes or len(outs) != len(op_list):
+        raise ValueError("host arrays must match the layout and each other")
+    codes = (C.c_int * len(op_list))(*[OP_CODE[o] if isinstance(o, str) else int(o) for o in op_list])
+    po = (C.c_void_p * len(outs))()
+    for j, o in enumerate(outs):
+        pj, nj, _ = ptr_n(o)
+        if nj != n:
+            raise ValueError("output size mismatch")
+        po[j] = pj
+    _lib.check(_lib.lib().pint_cuda_binary_multi_host(len(op_list), codes, layout.ref, pa, pb, po, n),
+               "pint_cuda_binary_multi_host")
+    return outs
+
+
 def launch_count():
     return _lib.lib().pint_cuda_launch_count()
 

@@ -1,0 +1,133 @@
+// cpp_api_test.cpp -- exercises include/pint/cuda.hpp (the pint::cuda template
+// layer) the way a pint user would: device arrays of packed_int<...>, same
+// function names as the scalar API.  C++11, no nvcc, no pint.hpp needed: the
+// expected values come from a naive per-field model written here.
+// Built by `make tools` into build/cpp_api_test; run on a GPU by tests/test_gpu_cpp_api.py.
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "pint/cuda.hpp"
+
+#define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { std::printf("CUDA error %s at line %d\n", cudaGetErrorString(e_), __LINE__); return 2; } } while (0)
+
+typedef pint::packed_int<uint32_t, 8, 8, 8, 8> rgba;
+typedef pint::packed_int<uint64_t, 3, 7, 11, 13, 17, 13> irregular;
+typedef pint::packed_int<uint16_t, 1, 2, 3, 4, 5> p5;
+
+static uint64_t splitmix64(uint64_t x)
+{
+    x += 0x9E3779B97F4A7C15ULL;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBULL;
+    return x ^ (x >> 31);
+}
+
+static uint32_t rgba_add_ssat(uint32_t a, uint32_t b)
+{
+    uint32_t r = 0;
+    for (int f = 0; f < 4; ++f) {
+        int x = (int8_t)(a >> (8 * f)), y = (int8_t)(b >> (8 * f)), s = x + y;
+        s = s > 127 ? 127 : (s < -128 ? -128 : s);
+        r |= (uint32_t)(uint8_t)s << (8 * f);
+    }
+    return r;
+}
+
+static uint32_t rgba_add_usat(uint32_t a, uint32_t b)
+{
+    uint32_t r = 0;
+    for (int f = 0; f < 4; ++f) {
+        unsigned s = ((a >> (8 * f)) & 255u) + ((b >> (8 * f)) & 255u);
+        r |= (s > 255u ? 255u : s) << (8 * f);
+    }
+    return r;
+}
+
+int main()
+{
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { std::printf("no CUDA device\n"); return 3; }
+    const size_t n = (1u << 20) + 13;
+    int fails = 0;
+
+    // ---- binary ops on RGBA8 ----
+    std::vector<uint32_t> ha(n), hb(n), ho(n);
+    for (size_t i = 0; i < n; ++i) { ha[i] = (uint32_t)splitmix64(1 + i); hb[i] = (uint32_t)splitmix64(0x1000000 + i); }
+    rgba *a, *b, *out;
+    CK(cudaMalloc((void**)&a, n * 4)); CK(cudaMalloc((void**)&b, n * 4)); CK(cudaMalloc((void**)&out, n * 4));
+    CK(cudaMemcpy(a, ha.data(), n * 4, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(b, hb.data(), n * 4, cudaMemcpyHostToDevice));
+    cudaStream_t s;
+    CK(cudaStreamCreate(&s));
+    try {
+        pint::cuda::add_signed_saturate(a, b, out, n, s);
+        CK(cudaStreamSynchronize(s));
+        CK(cudaMemcpy(ho.data(), out, n * 4, cudaMemcpyDeviceToHost));
+        for (size_t i = 0; i < n; ++i) if (ho[i] != rgba_add_ssat(ha[i], hb[i])) { ++fails; if (fails < 5) std::printf("ssat mismatch at %zu\n", i); }
+        pint::cuda::add_unsigned_saturate(a, b, out, n, s);
+        CK(cudaStreamSynchronize(s));
+        CK(cudaMemcpy(ho.data(), out, n * 4, cudaMemcpyDeviceToHost));
+        for (size_t i = 0; i < n; ++i) if (ho[i] != rgba_add_usat(ha[i], hb[i])) { ++fails; if (fails < 5) std::printf("usat mismatch at %zu\n", i); }
+        pint::cuda::fused_unpack_arith_repack(PINT_ADD_SIGNED_SATURATE, a, b, out, n, s);
+        CK(cudaStreamSynchronize(s));
+        CK(cudaMemcpy(ho.data(), out, n * 4, cudaMemcpyDeviceToHost));
+        for (size_t i = 0; i < n; ++i) if (ho[i] != rgba_add_ssat(ha[i], hb[i])) { ++fails; if (fails < 5) std::printf("fused mismatch at %zu\n", i); }
+        pint::cuda::bit_xor(a, b, out, n, s);
+        CK(cudaStreamSynchronize(s));
+        CK(cudaMemcpy(ho.data(), out, n * 4, cudaMemcpyDeviceToHost));
+        for (size_t i = 0; i < n; ++i) if (ho[i] != (ha[i] ^ hb[i])) ++fails;
+
+        // ---- unpack (get_signed) to int32 planes and repack on the irregular u64 layout ----
+        const int widths[6] = {3, 7, 11, 13, 17, 13};
+        std::vector<uint64_t> hx(n), hy(n);
+        for (size_t i = 0; i < n; ++i) hx[i] = splitmix64(77 + i);
+        irregular *x, *y;
+        CK(cudaMalloc((void**)&x, n * 8)); CK(cudaMalloc((void**)&y, n * 8));
+        CK(cudaMemcpy(x, hx.data(), n * 8, cudaMemcpyHostToDevice));
+        int32_t* planes[6];
+        for (int f = 0; f < 6; ++f) CK(cudaMalloc((void**)&planes[f], n * 4));
+        pint::cuda::unpack(x, planes, n, s);
+        const int32_t* cplanes[6];
+        for (int f = 0; f < 6; ++f) cplanes[f] = planes[f];
+        pint::cuda::repack(cplanes, y, n, s);
+        CK(cudaStreamSynchronize(s));
+        CK(cudaMemcpy(hy.data(), y, n * 8, cudaMemcpyDeviceToHost));
+        for (size_t i = 0; i < n; ++i) if (hy[i] != hx[i]) { ++fails; if (fails < 5) std::printf("repack(unpack) mismatch at %zu\n", i); }
+        std::vector<int32_t> hp(n);
+        int off = 0;
+        for (int f = 0; f < 6; ++f) {
+            CK(cudaMemcpy(hp.data(), planes[f], n * 4, cudaMemcpyDeviceToHost));
+            for (size_t i = 0; i < n; i += 97) {
+                int64_t v = (int64_t)(hx[i] << (64 - off - widths[f])) >> (64 - widths[f]);
+                if (hp[i] != (int32_t)v) { ++fails; if (fails < 5) std::printf("get_signed<%d> mismatch at %zu\n", f, i); }
+            }
+            off += widths[f];
+        }
+
+        // ---- slice<2,4> on <uint16_t,1,2,3,4,5> (tests/pint_test.cpp:135-146 shape) ----
+        std::vector<uint16_t> hs(n), hr(n);
+        for (size_t i = 0; i < n; ++i) hs[i] = (uint16_t)splitmix64(5 + i);
+        p5* sv;
+        pint::cuda::sliced_int<2, 4, uint16_t, 1, 2, 3, 4, 5>::type* sr;  // packed_int<uint16_t, 3, 4>
+        CK(cudaMalloc((void**)&sv, n * 2)); CK(cudaMalloc((void**)&sr, n * 2));
+        CK(cudaMemcpy(sv, hs.data(), n * 2, cudaMemcpyHostToDevice));
+        pint::cuda::slice<2, 4>(sv, sr, n, s);
+        pint::cuda::shift_left(sv, 2, sv, n, s);
+        CK(cudaStreamSynchronize(s));
+        CK(cudaMemcpy(hr.data(), sr, n * 2, cudaMemcpyDeviceToHost));
+        for (size_t i = 0; i < n; ++i) if (hr[i] != ((hs[i] >> 3) & 0x7F)) { ++fails; if (fails < 5) std::printf("slice mismatch at %zu\n", i); }
+
+        // ---- runtime errors throw ----
+        bool threw = false;
+        try { pint::cuda::add_wrap(a, b, (rgba*)((char*)a + 4), n - 1, s); } catch (const pint::cuda::error& e) { threw = e.code == PINT_E_ALIAS; }
+        if (!threw) { ++fails; std::printf("partial overlap did not throw PINT_E_ALIAS\n"); }
+    } catch (const pint::cuda::error& e) {
+        std::printf("pint::cuda::error: %s\n", e.what());
+        return 1;
+    }
+    std::printf("cpp_api_test: %d failures, %llu kernel launches\n", fails, pint_cuda_launch_count());
+    return fails ? 1 : 0;
+}

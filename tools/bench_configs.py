@@ -1,0 +1,121 @@
+#!/usr/bin/env python
+"""tools/bench_configs.py -- every BASELINE.json config (C0..C4) on one B200,
+through the C ABI, as achieved algorithmic GB/s (SURVEY.md 8(d) bytes/element)
+and elements/s.  CUDA events, 3 warm-ups, `reps` timed launches, best and
+median; buffers far larger than L2 (C0 rotates over 8 buffer sets).
+Writes one JSON line per measurement; used to fill profiles/ and DESIGN.md."""
+import json
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import pint_b200  # noqa: E402
+from pint_b200 import ops  # noqa: E402
+
+PEAK = 6553.0
+try:
+    PEAK = json.load(open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json")))["hbm_gbs"]
+except Exception:
+    pass
+UDT = {1: torch.uint8, 2: torch.uint16, 4: torch.uint32, 8: torch.uint64}
+
+
+def timed(fn, reps=10, warm=3):
+    for _ in range(warm):
+        fn(0)
+    torch.cuda.synchronize()
+    ms = []
+    for i in range(reps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn(i)
+        e1.record()
+        e1.synchronize()
+        ms.append(e0.elapsed_time(e1))
+    ms.sort()
+    return ms[0], ms[len(ms) // 2]
+
+
+def report(name, n, bytes_per_elem, best, med, **extra):
+    gbs_b, gbs_m = n * bytes_per_elem / best / 1e6, n * bytes_per_elem / med / 1e6
+    line = dict(config=name, elements=n, bytes_per_element=bytes_per_elem, ms_best=round(best, 4), ms_median=round(med, 4),
+                gbs_best=round(gbs_b, 1), gbs_median=round(gbs_m, 1), gelem_s_median=round(n / med / 1e6, 2),
+                frac_measured_peak=round(gbs_m / PEAK, 3), frac_spec_8000=round(gbs_m / 8000, 3), **extra)
+    print(json.dumps(line), flush=True)
+
+
+def alloc(layout, n, seed):
+    t = torch.empty(n, dtype=UDT[layout.elem_bytes], device="cuda")
+    ops.fill_splitmix(t, seed)
+    return t
+
+
+def binary_case(name, layout, n, op_list, sets=1, fused=False, generic=False):
+    bufs = [(alloc(layout, n, 11 + 3 * k), alloc(layout, n, 12 + 3 * k), torch.empty(n, dtype=UDT[layout.elem_bytes], device="cuda"))
+            for k in range(sets)]
+    ops.set_option("force_generic", int(generic))
+    for op in op_list:
+        def run(i):
+            a, b, o = bufs[i % sets]
+            ops.binary(op, layout, a, b, out=o, fused=fused)
+        best, med = timed(run)
+        report(name, n, 3 * layout.elem_bytes, best, med, op=op, layout=repr(layout),
+               kernel=("fused" if fused else "swar") + ("/runtime-masks" if generic else "/static-masks" if layout.is_specialized() else "/runtime-masks"))
+    ops.set_option("force_generic", 0)
+    del bufs
+    torch.cuda.empty_cache()
+
+
+def main():
+    which = sys.argv[1:] or ["C0", "C1", "C2", "C3", "C4", "extra"]
+    torch.cuda.set_device(0)
+    if "C0" in which:
+        binary_case("C0", pint_b200.Layout.make(5, 6, 5), 1 << 26, ["add_wrap", "add_unsigned_saturate", "add_signed_saturate"], sets=8)
+    if "C1" in which:
+        L = pint_b200.Layout(4, 8, 8, 8, 8)
+        binary_case("C1", L, 1 << 30, ["add_unsigned_saturate", "add_signed_saturate"])
+        binary_case("C1-runtime-masks", L, 1 << 30, ["add_unsigned_saturate", "add_signed_saturate"], generic=True)
+    if "C2" in which:
+        binary_case("C2", pint_b200.Layout(8, 16, 16, 16, 16), 1 << 31, ["sub_signed_saturate", "add_signed_saturate"])
+    if "C3" in which:
+        L = pint_b200.Layout(8, 3, 7, 11, 13, 17, 13)
+        n = 1 << 28
+        x = alloc(L, n, 5)
+        planes = [torch.empty(n, dtype=torch.int32, device="cuda") for _ in L.bits]
+        best, med = timed(lambda i: ops.unpack(L, x, signed=True, out=planes))
+        report("C3", n, 8 + 4 * 6, best, med, op="unpack get_signed -> 6 int32 planes", layout=repr(L))
+        out = torch.empty_like(x)
+        best, med = timed(lambda i: ops.repack(L, planes, out=out))
+        report("C3", n, 8 + 4 * 6, best, med, op="repack 6 int32 planes -> packed", layout=repr(L))
+        assert torch.equal(out.view(torch.int64), x.view(torch.int64)), "repack(unpack(x)) != x"
+        best, med = timed(lambda i: ops.slice(L, 1, 4, x, out=out))
+        report("C3", n, 16, best, med, op="slice<1,4>", layout=repr(L))
+        ops.set_option("force_generic", 1)
+        best, med = timed(lambda i: ops.unpack(L, x, signed=True, out=planes))
+        report("C3-runtime-masks", n, 8 + 4 * 6, best, med, op="unpack get_signed -> 6 int32 planes", layout=repr(L))
+        ops.set_option("force_generic", 0)
+        del x, planes, out
+        torch.cuda.empty_cache()
+    if "C4" in which:
+        L = pint_b200.Layout(8, 3, 7, 11, 13, 17, 13)
+        binary_case("C4 (per-GPU share: 8 GiB/array)", L, 1 << 30, ["add_signed_saturate", "add_unsigned_saturate"], fused=True)
+        binary_case("C4-swar (same op, SWAR kernel)", L, 1 << 30, ["add_signed_saturate", "add_unsigned_saturate"])
+    if "extra" in which:
+        binary_case("bench-layout type2", pint_b200.Layout(4, 1, 2, 3, 4, 5, 6, 11), 1 << 30, ["add_wrap", "add_unsigned_saturate", "add_signed_saturate"])
+        binary_case("u8 <1,1,1>", pint_b200.Layout(1, 1, 1, 1), 1 << 30, ["add_signed_saturate", "sub_wrap"])
+        binary_case("unregistered u32 <7,9,3> (runtime masks)", pint_b200.Layout(4, 7, 9, 3), 1 << 30, ["add_signed_saturate", "min_signed"])
+        L = pint_b200.Layout(4, 8, 8, 8, 8)
+        n = 1 << 30
+        x = alloc(L, n, 9)
+        out = torch.empty_like(x)
+        best, med = timed(lambda i: ops.shift_left(L, x, 3, out=out))
+        report("shift", n, 8, best, med, op="shift_left 3", layout=repr(L))
+        pairs = alloc(L, n, 21)
+        best, med = timed(lambda i: ops.pairs_reduce("add_signed_saturate", L, pairs))
+        report("pairs_reduce (tests/pint_bench.cpp:90-94 shape)", n // 2, 8, best, med, op="add_signed_saturate", layout=repr(L))
+
+
+if __name__ == "__main__":
+    main()

@@ -69,6 +69,49 @@ static void run_bulk(const char* tag, const void* a, const void* b, void* out, s
     });
 }
 
+// persistent CTAs that take tiles in address order from a global counter (instead of a grid stride)
+template <class Fn, class Cfg>
+__global__ void __launch_bounds__(Cfg::BLOCK)
+binary_stream_dyn_kernel(const uint4* a, const uint4* b, uint4* out, size_t nvec, unsigned long long* counter, const __grid_constant__ Fn fn)
+{
+    using W = typename Fn::word;
+    constexpr int U = Cfg::UNROLL, B = Cfg::BLOCK;
+    constexpr size_t tile = size_t(U) * B;
+    const size_t nfull = nvec / tile;
+    auto f = [&](W x, W y) { return fn(x, y); };
+    __shared__ unsigned long long next;
+    for (;;) {
+        if (threadIdx.x == 0) next = atomicAdd(counter, 1ULL);
+        __syncthreads();
+        const size_t t = next;
+        __syncthreads();
+        if (t >= nfull) break;
+        const size_t base = t * tile + threadIdx.x;
+        uint4 va[U], vb[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) va[u] = ld16<Cfg::LD>(a + base + size_t(u) * B);
+#pragma unroll
+        for (int u = 0; u < U; ++u) vb[u] = ld16<Cfg::LD>(b + base + size_t(u) * B);
+#pragma unroll
+        for (int u = 0; u < U; ++u) st16<Cfg::ST>(out + base + size_t(u) * B, map_words2<W>(va[u], vb[u], f));
+    }
+}
+
+static unsigned long long* g_counter = nullptr;
+
+template <class Fn, int U, int B>
+static void run_dyn(const char* tag, const void* a, const void* b, void* out, size_t nvec, int ctas_per_sm)
+{
+    using Cfg = stream_cfg<U, B, 2, 2>;
+    if (!g_counter) CK(cudaMalloc(&g_counter, 8));
+    char name[128];
+    std::snprintf(name, sizeof name, "%s dyn    U%d B%d ctas/sm %d (atomic tile counter)", tag, U, B, ctas_per_sm);
+    time_it(name, double(nvec) * 48, [&] {
+        CK(cudaMemsetAsync(g_counter, 0, 8));
+        binary_stream_dyn_kernel<Fn, Cfg><<<unsigned(g_sms * ctas_per_sm), B>>>((const uint4*)a, (const uint4*)b, (uint4*)out, nvec, g_counter, Fn{});
+    });
+}
+
 __global__ void fill(uint4* p, size_t nvec, uint32_t seed)
 {
     for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += size_t(gridDim.x) * blockDim.x) {
@@ -111,6 +154,40 @@ int main(int argc, char** argv)
     using FnIF = fused_fn<OP_ADD_SIGNED_SATURATE, static_fields<IRR>>;
     using FnX = swar_fn<OP_XOR, static_masks<RGBA>>;
 
+    if (argc > 3 && std::atoi(argv[3]) == 2) {
+        // second sweep: one CTA per tile for every representative op, and dynamic persistent grids
+        using C16 = static_layout<uint64_t, 16, 16, 16, 16>;
+        using FnC2a = swar_fn<OP_ADD_SIGNED_SATURATE, static_masks<C16>>;
+        using FnC2s = swar_fn<OP_SUB_SIGNED_SATURATE, static_masks<C16>>;
+        using C565 = static_layout<uint16_t, 5, 6, 5>;
+        using FnC0 = swar_fn<OP_ADD_WRAP, static_masks<C565>>;
+        using FnC0s = swar_fn<OP_ADD_SIGNED_SATURATE, static_masks<C565>>;
+        using T2 = static_layout<uint32_t, 1, 2, 3, 4, 5, 6, 11>;
+        using FnT2 = swar_fn<OP_ADD_SIGNED_SATURATE, static_masks<T2>>;
+        using FnRT = swar_fn<OP_ADD_SIGNED_SATURATE, runtime_masks<uint64_t>>;
+#define SWEEP(FN, TAG)                                                   \
+        run_stream<FN, 1, 256, 2, 2>(TAG, a, b, out, nvec, 0);           \
+        run_stream<FN, 2, 256, 2, 2>(TAG, a, b, out, nvec, 0);           \
+        run_stream<FN, 4, 256, 2, 2>(TAG, a, b, out, nvec, 0);           \
+        run_stream<FN, 2, 512, 2, 2>(TAG, a, b, out, nvec, 0);           \
+        run_stream<FN, 1, 1024, 2, 2>(TAG, a, b, out, nvec, 0);          \
+        run_stream<FN, 2, 1024, 2, 2>(TAG, a, b, out, nvec, 0);
+        SWEEP(FnU, "usat rgba8")
+        SWEEP(FnS, "ssat rgba8")
+        SWEEP(FnC2a, "add_ssat u64 16x4")
+        SWEEP(FnC2s, "sub_ssat u64 16x4")
+        SWEEP(FnI, "add_ssat irregular u64 swar")
+        SWEEP(FnIF, "add_ssat irregular u64 fused")
+        SWEEP(FnC0, "add_wrap u16 565")
+        SWEEP(FnC0s, "add_ssat u16 565")
+        SWEEP(FnT2, "add_ssat u32 type2")
+        for (int cps : {2, 4, 8}) run_dyn<FnU, 2, 256>("usat rgba8", a, b, out, nvec, cps);
+        for (int cps : {1, 2}) run_dyn<FnU, 2, 1024>("usat rgba8", a, b, out, nvec, cps);
+        for (int cps : {2, 4}) run_dyn<FnU, 4, 512>("usat rgba8", a, b, out, nvec, cps);
+        for (int cps : {2, 4, 8}) run_dyn<FnI, 2, 256>("add_ssat irregular u64 swar", a, b, out, nvec, cps);
+        std::printf("done\n");
+        return 0;
+    }
     // --- grid / unroll / block sweep with the streaming policy ---
     for (int cps : {0, 2, 4, 8, 16, 32}) run_stream<FnU, 4, 256, 2, 2>("usat rgba8", a, b, out, nvec, cps);
     for (int cps : {0, 4, 8, 16}) run_stream<FnU, 1, 256, 2, 2>("usat rgba8", a, b, out, nvec, cps);
