@@ -84,28 +84,69 @@ struct static_masks {
     {
         return lsb_impl(c, std::make_index_sequence<SL::masks.nsh>());
     }
+    template <std::size_t... Ks>
+    __device__ __forceinline__ static constexpr word smear_impl(word x, std::index_sequence<Ks...>)
+    {
+        ((x |= word((x >> (1u << Ks)) & SL::masks.keep[Ks])), ...);
+        return x;
+    }
+    // all bits of every field whose MSB flag is set in c (c subset of H): the
+    // value of make_unsigned_saturation_mask, pint.hpp:544-551 ((c << 1) - lsb(c)
+    // there; both are the union of the flagged fields' bit ranges)
+    __device__ __forceinline__ static constexpr word fill(word c)
+    {
+        if constexpr (SL::masks.use_smear != 0) return smear_impl(c, std::make_index_sequence<SL::masks.nsmear>());
+        else return c | (c - lsb(c));
+    }
+    // the bits under the MSB of every flagged field: make_signed_saturation_mask, pint.hpp:563-567
+    __device__ __forceinline__ static constexpr word below(word c)
+    {
+        if constexpr (SL::masks.use_smear != 0) return fill(c) ^ c;
+        else return c - lsb(c);
+    }
 };
 
+// Runtime masks: a fixed-structure copy of the plan so that every constant sits
+// at a fixed offset of the kernel parameter (constant bank operands cost
+// nothing; a loop over a table with a dynamic index does -- measured 2x slower).
+// Single-width layouts move the flag with one shift; all others smear.
 template <class Word>
 struct runtime_masks {
     using word = Word;
-    word_masks<Word> m;
-    __device__ __forceinline__ word H() const { return m.H; }
-    __device__ __forceinline__ word L() const { return m.L; }
-    __device__ __forceinline__ word A() const { return m.A; }
-    __device__ __forceinline__ word M1() const { return m.M1; }
-    __device__ __forceinline__ word HL() const { return m.HL; }
-    __device__ __forceinline__ word LM1() const { return m.LM1; }
-    __device__ __forceinline__ word lsb(word c) const
+    Word mH, mL, mA, mM1, mHL, mLM1;
+    Word keep[6];
+    uint32_t shift0;   // w - 1 when all fields have the same width
+    uint32_t nsmear;   // 0: single-width layout (shift plan), else number of smear steps
+
+    runtime_masks() = default;
+    explicit runtime_masks(const word_masks<Word>& m)
+        : mH(m.H), mL(m.L), mA(m.A), mM1(m.M1), mHL(m.HL), mLM1(m.LM1), keep{m.keep[0], m.keep[1], m.keep[2], m.keep[3], m.keep[4], m.keep[5]},
+          shift0(m.sh[0]), nsmear(m.nsh == 1 ? 0 : m.nsmear) {}
+
+    __device__ __forceinline__ word H() const { return mH; }
+    __device__ __forceinline__ word L() const { return mL; }
+    __device__ __forceinline__ word A() const { return mA; }
+    __device__ __forceinline__ word M1() const { return mM1; }
+    __device__ __forceinline__ word HL() const { return mHL; }
+    __device__ __forceinline__ word LM1() const { return mLM1; }
+    __device__ __forceinline__ word fill(word c) const
     {
-        word r = 0;
-        if (m.per_shift_mask) {
-            for (uint32_t k = 0; k < m.nsh; ++k) r |= (c >> m.sh[k]) & m.mk[k];
-        } else {
-            for (uint32_t k = 0; k < m.nsh; ++k) r |= c >> m.sh[k];
-            r &= m.L;
+        if (nsmear == 0) return c | (c - (c >> shift0));
+        word x = c;
+        x |= (x >> 1) & keep[0];
+        if (nsmear > 1) x |= (x >> 2) & keep[1];
+        if (nsmear > 2) x |= (x >> 4) & keep[2];
+        if (nsmear > 3) x |= (x >> 8) & keep[3];
+        if (nsmear > 4) x |= (x >> 16) & keep[4];
+        if constexpr (sizeof(Word) == 8) {
+            if (nsmear > 5) x |= (x >> 32) & keep[5];
         }
-        return r;
+        return x;
+    }
+    __device__ __forceinline__ word below(word c) const
+    {
+        if (nsmear == 0) return c - (c >> shift0);
+        return fill(c) ^ c;
     }
 };
 
@@ -115,13 +156,10 @@ struct runtime_masks {
 // exclude them, pint.hpp:832-833, 877-878), passed through by | & ^
 // (pint.hpp:781-783), taken from b by min/max (pint.hpp:603-606).
 
-// all bits of every field whose MSB flag is set in c (c subset of H).
-// Same value as make_unsigned_saturation_mask's (c << 1) - lsb(c)
-// (pint.hpp:544-551): both are the union of the flagged fields' bit ranges.
 template <class P>
 __device__ __forceinline__ typename P::word field_fill(typename P::word c, const P& p)
 {
-    return c | (c - p.lsb(c));
+    return p.fill(c);
 }
 
 // add_wrap, pint.hpp:826-838
@@ -143,9 +181,9 @@ template <class P>
 __device__ __forceinline__ typename P::word signed_clamp(typename P::word r, typename P::word ov, const P& p)
 {
     using W = typename P::word;
-    const W below = ov - p.lsb(ov);          // bits under the MSB of overflowed fields
+    const W below = p.below(ov);             // bits under the MSB of overflowed fields
     const W neg = ov & ~r;                   // overflowed towards -inf (wrapped result looks positive)
-    const W below_neg = neg - p.lsb(neg);
+    const W below_neg = p.below(neg);
     return ((r ^ ov) | below) ^ below_neg;   // 0111..1 for +overflow, 1000..0 for -overflow
 }
 

@@ -11,13 +11,92 @@ namespace kernels {
 // planes of the unfused pipeline (unpack kernel, arithmetic kernel per plane,
 // repack kernel: 168 bytes/element for the 6-field u64 layout) never exist in
 // memory, so the traffic is the 3W bytes/element of a plain binary op.
-//
-// Fields are unpacked LEFT-ALIGNED (the first half of get_signed,
-// pint.hpp:820: value << (W - hi_order_bit_no)): the field's MSB sits on the
-// register's MSB, so the register's own carry flag / sign bit are the field's,
-// for every width from 1 to the full Word, and wrap-around needs no masking.
 // The result must equal the SWAR op of swar_fn bit for bit; tests check both
 // against the oracle and against each other.
+//
+// Two unpacked forms, chosen per field (at compile time for static layouts, by a
+// warp-uniform branch for runtime ones):
+//  * fields of up to 31 bits are unpacked RIGHT-ALIGNED into a 32-bit register
+//    exactly as get (pint.hpp:805-806) / get_signed (pint.hpp:819-821) do, the
+//    arithmetic is plain int32/uint32 with min/max for the saturation (the
+//    sum of two w-bit values fits when w <= 31), and the result is truncated and
+//    shifted back (make_truncated_int, pint.hpp:394).  A field of a 64-bit
+//    element that lies in one 32-bit half is handled in that half; one that
+//    straddles the halves is fetched with a funnel shift.
+//  * wider fields (32..64 bits) are unpacked LEFT-ALIGNED (the first half of
+//    get_signed, value << (W - hi_order_bit_no)): the register's own carry and
+//    sign bits are then the field's, for every width up to the full Word.
+
+// right-aligned 32-bit field arithmetic: xa/xb hold the field at bit offset o
+// (o + w <= 32, 1 <= w <= 31, bits above the field may be anything); returns the
+// result in the low w bits, higher bits unspecified (the caller masks on insert)
+template <int Op>
+__device__ __forceinline__ uint32_t field_op32(uint32_t xa, uint32_t xb, uint32_t o, uint32_t w)
+{
+    constexpr bool is_signed = (Op == OP_ADD_SIGNED_SATURATE || Op == OP_SUB_SIGNED_SATURATE ||
+                                Op == OP_MIN_SIGNED || Op == OP_MAX_SIGNED);
+    const uint32_t fm = 0xFFFFFFFFu >> (32 - w);
+    if constexpr (is_signed) {
+        const int sa = int(xa << (32 - o - w)) >> (32 - w);  // get_signed, pint.hpp:819-821
+        const int sb = int(xb << (32 - o - w)) >> (32 - w);
+        const int smax = int(fm >> 1), smin = ~smax;
+        int t;
+        if constexpr (Op == OP_ADD_SIGNED_SATURATE) t = max(min(sa + sb, smax), smin);
+        else if constexpr (Op == OP_SUB_SIGNED_SATURATE) t = max(min(sa - sb, smax), smin);
+        else if constexpr (Op == OP_MIN_SIGNED) t = min(sa, sb);
+        else t = max(sa, sb);
+        return uint32_t(t);
+    } else {
+        const uint32_t ua = (xa >> o) & fm, ub = (xb >> o) & fm;  // get, pint.hpp:805-806
+        if constexpr (Op == OP_ADD_WRAP) return ua + ub;
+        else if constexpr (Op == OP_ADD_UNSIGNED_SATURATE) return min(ua + ub, fm);
+        else if constexpr (Op == OP_SUB_WRAP) return ua - ub;
+        else if constexpr (Op == OP_SUB_UNSIGNED_SATURATE) return ua - min(ua, ub);
+        else if constexpr (Op == OP_MIN_UNSIGNED) return min(ua, ub);
+        else return max(ua, ub);
+    }
+}
+
+// left-aligned arithmetic on a full Word (fields of 32..64 bits, or the full 32-bit field)
+template <int Op, class W>
+__device__ __forceinline__ W field_op_wide(W a, W b, uint32_t off, uint32_t w)
+{
+    using S = typename std::make_signed<W>::type;
+    constexpr uint32_t WB = 8 * sizeof(W);
+    constexpr W SIGN = W(1) << (WB - 1);
+    const uint32_t sl = WB - off - w;
+    const W top = ~W(0) << (WB - w);  // the field's bits once left-aligned
+    const W xa = (a << sl) & top, xb = (b << sl) & top;
+    W t;
+    if constexpr (Op == OP_ADD_WRAP) {
+        t = xa + xb;
+    } else if constexpr (Op == OP_ADD_UNSIGNED_SATURATE) {
+        t = xa + xb;
+        t = t < xa ? top : t;
+    } else if constexpr (Op == OP_ADD_SIGNED_SATURATE) {
+        t = xa + xb;
+        const W sat = (xa & SIGN) ? SIGN : W(~SIGN & top);
+        t = ((xa ^ t) & (xb ^ t) & SIGN) ? sat : t;
+    } else if constexpr (Op == OP_SUB_WRAP) {
+        t = xa - xb;
+    } else if constexpr (Op == OP_SUB_UNSIGNED_SATURATE) {
+        t = xa < xb ? W(0) : W(xa - xb);
+    } else if constexpr (Op == OP_SUB_SIGNED_SATURATE) {
+        t = xa - xb;
+        const W sat = (xa & SIGN) ? SIGN : W(~SIGN & top);
+        t = ((xa ^ xb) & (xa ^ t) & SIGN) ? sat : t;
+    } else if constexpr (Op == OP_MIN_UNSIGNED) {
+        t = xa < xb ? xa : xb;
+    } else if constexpr (Op == OP_MAX_UNSIGNED) {
+        t = xa > xb ? xa : xb;
+    } else if constexpr (Op == OP_MIN_SIGNED) {
+        t = S(xa) < S(xb) ? xa : xb;
+    } else {
+        t = S(xa) > S(xb) ? xa : xb;
+    }
+    return (t >> (WB - w)) << off;  // repack, pint.hpp:394
+}
+
 template <int Op, class FP>
 struct fused_fn {
     using word = typename FP::word;
@@ -26,46 +105,42 @@ struct fused_fn {
     __device__ __forceinline__ word operator()(word a, word b) const
     {
         using W = word;
-        using S = typename std::make_signed<W>::type;
-        constexpr uint32_t WB = 8 * sizeof(W);
-        constexpr W SIGN = W(1) << (WB - 1);
         if constexpr (Op == OP_OR) return a | b;
         if constexpr (Op == OP_AND) return a & b;
         if constexpr (Op == OP_XOR) return a ^ b;
         W r = 0;
-        fp.each_word_field([&](uint32_t, uint32_t off, uint32_t w) {
-            const uint32_t sl = WB - off - w;
-            const W top = ~W(0) << (WB - w);  // the field's bits once left-aligned
-            const W xa = (a << sl) & top, xb = (b << sl) & top;
-            W t;
-            if constexpr (Op == OP_ADD_WRAP) {
-                t = xa + xb;
-            } else if constexpr (Op == OP_ADD_UNSIGNED_SATURATE) {
-                t = xa + xb;
-                t = t < xa ? top : t;
-            } else if constexpr (Op == OP_ADD_SIGNED_SATURATE) {
-                t = xa + xb;
-                const W sat = (xa & SIGN) ? SIGN : W(~SIGN & top);
-                t = ((xa ^ t) & (xb ^ t) & SIGN) ? sat : t;
-            } else if constexpr (Op == OP_SUB_WRAP) {
-                t = xa - xb;
-            } else if constexpr (Op == OP_SUB_UNSIGNED_SATURATE) {
-                t = xa < xb ? W(0) : W(xa - xb);
-            } else if constexpr (Op == OP_SUB_SIGNED_SATURATE) {
-                t = xa - xb;
-                const W sat = (xa & SIGN) ? SIGN : W(~SIGN & top);
-                t = ((xa ^ xb) & (xa ^ t) & SIGN) ? sat : t;
-            } else if constexpr (Op == OP_MIN_UNSIGNED) {
-                t = xa < xb ? xa : xb;
-            } else if constexpr (Op == OP_MAX_UNSIGNED) {
-                t = xa > xb ? xa : xb;
-            } else if constexpr (Op == OP_MIN_SIGNED) {
-                t = S(xa) < S(xb) ? xa : xb;
-            } else {
-                t = S(xa) > S(xb) ? xa : xb;
-            }
-            r |= (t >> (WB - w)) << off;  // repack, pint.hpp:394
-        });
+        if constexpr (sizeof(W) == 4) {
+            fp.each_word_field([&](uint32_t, uint32_t off, uint32_t w) {
+                if (w <= 31) {
+                    const uint32_t fm = 0xFFFFFFFFu >> (32 - w);
+                    r |= (field_op32<Op>(a, b, off, w) << off) & (fm << off);
+                } else {
+                    r |= field_op_wide<Op, W>(a, b, off, w);
+                }
+            });
+        } else {
+            const uint32_t alo = uint32_t(a), ahi = uint32_t(a >> 32), blo = uint32_t(b), bhi = uint32_t(b >> 32);
+            uint32_t rlo = 0, rhi = 0;
+            fp.each_word_field([&](uint32_t, uint32_t off, uint32_t w) {
+                if (w > 31) {
+                    r |= field_op_wide<Op, W>(a, b, off, w);
+                } else {
+                    const uint32_t fm = 0xFFFFFFFFu >> (32 - w);
+                    if (off + w <= 32) {          // in the low half
+                        rlo |= (field_op32<Op>(alo, blo, off, w) << off) & (fm << off);
+                    } else if (off >= 32) {       // in the high half
+                        const uint32_t o = off - 32;
+                        rhi |= (field_op32<Op>(ahi, bhi, o, w) << o) & (fm << o);
+                    } else {                      // straddles: funnel-shift it down to bit 0
+                        const uint32_t xa = __funnelshift_r(alo, ahi, off), xb = __funnelshift_r(blo, bhi, off);
+                        const uint32_t t = field_op32<Op>(xa, xb, 0, w) & fm;
+                        rlo |= t << off;
+                        rhi |= t >> (32 - off);
+                    }
+                }
+            });
+            r |= (uint64_t(rhi) << 32) | rlo;
+        }
         if constexpr (Op >= OP_MIN_UNSIGNED) r |= b & ~fp.A();  // min/max keep b's unused bits
         return r;
     }

@@ -90,6 +90,14 @@ struct word_masks {
     uint32_t per_shift_mask;
     uint32_t sh[kMaxUnique];
     Word mk[kMaxUnique];
+    // Alternative "smear" plan for layouts with many distinct widths: all bits of
+    // every flagged field directly, by log-step propagation of the MSB flag down
+    // the field:  x = c; for k < nsmear: x |= (x >> (1 << k)) & keep[k];
+    // keep[k] has bit i set iff bits i and i + 2^k belong to the same field.
+    // use_smear is the generator's choice (cheaper of the two plans).
+    uint32_t nsmear;
+    uint32_t use_smear;
+    Word keep[6];
     // Per unique width: the width and the LSBs of the fields of that width
     // (shift_left / shift_right_unsigned masks, pint.hpp:630-705).
     uint32_t nuniq;
@@ -205,6 +213,35 @@ constexpr word_masks<Word> make_word_masks(const layout_desc& d)
     } else {
         m.per_shift_mask = 1;
         for (uint32_t k = 0; k < nuniq && k < (uint32_t)kMaxUnique; ++k) m.mk[k] = Word(rlo[k]);
+    }
+    // Smear plan and the choice between the two (cost in 32-bit ALU ops per
+    // Word-half: a shift or a 3-input logic op each count 1).
+    {
+        uint32_t k = 0;
+        while ((uint32_t(1) << k) < maxb) ++k;   // 2^k - 1 >= maxb - 1
+        m.nsmear = k;
+        // field id of every bit of the replicated word (0 = not in a field)
+        uint32_t fid[64] = {};
+        uint32_t id = 0;
+        for (uint32_t r = 0; r < reps; ++r) {
+            uint32_t o = r * ebits;
+            for (uint32_t i = 0; i < d.nfields; ++i) {
+                ++id;
+                for (uint32_t b = 0; b < d.bits[i]; ++b) fid[o + b] = id;
+                o += d.bits[i];
+            }
+        }
+        for (uint32_t j = 0; j < k && j < 6; ++j) {
+            const uint32_t s = uint32_t(1) << j;
+            uint64_t keep = 0;
+            for (uint32_t i = 0; i + s < wbits; ++i)
+                if (fid[i] && fid[i] == fid[i + s]) keep |= uint64_t(1) << i;
+            m.keep[j] = Word(keep);
+        }
+        const uint32_t cost_shift = m.nsh * (1 + m.per_shift_mask) + (m.nsh - 1) / 2 + 2 +
+                                    ((m.nsh > 1 && !m.per_shift_mask) ? 1 : 0);
+        const uint32_t cost_smear = 2 * k;
+        m.use_smear = (m.nsh > 1 && cost_smear < cost_shift) ? 1 : 0;
     }
     return m;
 }

@@ -105,7 +105,7 @@ cudaError_t pairs_ops(int op, const layout_desc& d, const void* pairs, size_t n,
                       const launch_geom& g, std::integer_sequence<int, Ops...>)
 {
     using W = word_of<Elem>;
-    runtime_masks<W> p{make_word_masks<W>(d)};
+    runtime_masks<W> p(make_word_masks<W>(d));
     const unsigned grid = grid_for((n + 1023) / 1024, g);
     ((op == Ops ? (pairs_reduce_kernel<Elem, Ops><<<grid, 256, 0, s>>>((const Elem*)pairs, n, sum, p), 0) : 0), ...);
     count_launch(g);
@@ -148,7 +148,8 @@ int pint_cuda_checksum(const void* x, uint32_t elem_bytes, size_t n, uint64_t* r
     if (n == 0) return PINT_OK;
     if (!x) return PINT_E_NULL;
     if ((uintptr_t)x % elem_bytes) return PINT_E_ARG;
-    const launch_geom g = geom();
+    launch_geom g = geom();
+    g.ctas_per_sm = 8;  // reductions end in one atomic per CTA: keep the grid at 8 CTAs per SM
     const bool vec_ok = ((uintptr_t)x & 15u) == 0;
     const size_t per = 16 / elem_bytes;
     const size_t nvec = vec_ok ? n / per : 0, rest = n - nvec * per;
@@ -180,7 +181,8 @@ int pint_cuda_pairs_reduce(int op, const pint_layout* layout, const void* pairs,
     if (n == 0) return PINT_OK;
     if (!pairs) return PINT_E_NULL;
     if ((uintptr_t)pairs % d.elem_bytes) return PINT_E_ARG;
-    const launch_geom g = geom();
+    launch_geom g = geom();
+    g.ctas_per_sm = 8;  // one atomic per CTA at the end: persistent grid
     auto ops = std::make_integer_sequence<int, pint::cuda::OP_NUM_BINARY>();
     switch (d.elem_bytes) {
     case 1: return (int)pairs_ops<uint8_t>(op, d, pairs, n, sum_dev, s, g, ops);

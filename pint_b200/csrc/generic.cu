@@ -21,7 +21,7 @@ cudaError_t binary_one(bool fused, const layout_desc& d, const void* a, const vo
         return launch_binary<Elem, Fn>(a, b, out, n, fn, s, g);
     }
     using Fn = swar_fn<Op, runtime_masks<W>>;
-    Fn fn{{make_word_masks<W>(d)}};
+    Fn fn{runtime_masks<W>(make_word_masks<W>(d))};
     return launch_binary<Elem, Fn>(a, b, out, n, fn, s, g);
 }
 

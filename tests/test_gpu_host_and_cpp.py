@@ -1,0 +1,103 @@
+"""GPU: the host-buffer (end-to-end) entry points, the single-process multi-device
+partitioner, and the C++ template layer (include/pint/cuda.hpp) binary."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from gpu_util import to_dev, to_np  # noqa: E402
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_binary_host_matches_oracle(oracle):
+    import pint_b200
+    from pint_b200 import ops
+    ops.set_option("host_chunk_bytes", 1 << 20)   # force many chunks and slot reuse
+    try:
+        for eb, bits in [(4, (8, 8, 8, 8)), (8, (3, 7, 11, 13, 17, 13)), (2, (5, 6, 5)), (1, (2, 3, 3))]:
+            L = pint_b200.Layout(eb, *bits)
+            n = 3 * (1 << 20) // eb + 12345
+            a, b = oracle.fill(eb, n, 41), oracle.fill(eb, n, 42)
+            out = np.zeros_like(a)
+            ops.binary_host("sub_signed_saturate", L, a, b, out)          # pageable numpy memory
+            np.testing.assert_array_equal(out, oracle.binary("sub_signed_saturate", eb, bits, a, b))
+            outs = [np.zeros_like(a), np.zeros_like(a)]
+            ops.binary_multi_host(["add_unsigned_saturate", "add_signed_saturate"], L, a, b, outs)
+            np.testing.assert_array_equal(outs[0], oracle.binary("add_unsigned_saturate", eb, bits, a, b))
+            np.testing.assert_array_equal(outs[1], oracle.binary("add_signed_saturate", eb, bits, a, b))
+    finally:
+        ops.set_option("host_chunk_bytes", 32 << 20)
+
+
+def test_binary_host_pinned(oracle):
+    import pint_b200
+    from pint_b200 import _lib, ops
+    L = pint_b200.Layout(4, 8, 8, 8, 8)
+    n = (1 << 22) + 7
+    lib = _lib.lib()
+    ptrs = [C.c_void_p() for _ in range(3)]
+    for p in ptrs:
+        assert lib.pint_cuda_host_alloc(C.byref(p), 4 * n) == 0
+    a = np.ctypeslib.as_array((C.c_uint32 * n).from_address(ptrs[0].value))
+    b = np.ctypeslib.as_array((C.c_uint32 * n).from_address(ptrs[1].value))
+    out = np.ctypeslib.as_array((C.c_uint32 * n).from_address(ptrs[2].value))
+    a[:], b[:] = oracle.fill(4, n, 1), oracle.fill(4, n, 2)
+    ops.binary_host("add_signed_saturate", L, a, b, out)
+    np.testing.assert_array_equal(out, oracle.binary("add_signed_saturate", 4, (8, 8, 8, 8), a, b))
+    del a, b, out
+    for p in ptrs:
+        assert lib.pint_cuda_host_free(p) == 0
+
+
+def test_sharded_binary_single_process(oracle):
+    """pint_cuda_sharded_binary over the visible devices (1 device: both shards on it)."""
+    import pint_b200
+    from pint_b200 import sharded
+    L = pint_b200.Layout(8, 16, 16, 16, 16)
+    n = (1 << 20) + 99
+    ndev = torch.cuda.device_count()
+    k = max(2, ndev)
+    plan = sharded.plan_shards(n, 8, k)
+    a_h, b_h = oracle.fill(8, n, 5), oracle.fill(8, n, 6)
+    a_s, b_s, o_s = [], [], []
+    for i, (beg, cnt) in enumerate(plan):
+        with torch.cuda.device(i % ndev):
+            a_s.append(to_dev(a_h[beg:beg + cnt]).to(f"cuda:{i % ndev}"))
+            b_s.append(to_dev(b_h[beg:beg + cnt]).to(f"cuda:{i % ndev}"))
+            o_s.append(torch.empty_like(a_s[-1]))
+    sharded.sharded_binary("sub_signed_saturate", L, a_s, b_s, o_s)
+    for d in range(ndev):
+        torch.cuda.synchronize(d)
+    got = np.concatenate([to_np(o) for o in o_s])
+    np.testing.assert_array_equal(got, oracle.binary("sub_signed_saturate", 8, (16, 16, 16, 16), a_h, b_h))
+
+
+def test_persistent_grid_option_gives_same_results(oracle):
+    import pint_b200
+    from pint_b200 import ops
+    L = pint_b200.Layout(4, 1, 2, 3, 4, 5, 6, 11)
+    n = (1 << 21) + 3
+    a_h, b_h = oracle.fill(4, n, 8), oracle.fill(4, n, 9)
+    a, b = to_dev(a_h), to_dev(b_h)
+    want = oracle.binary("add_signed_saturate", 4, L.bits, a_h, b_h)
+    for cps in (1, 8, 0):
+        ops.set_option("ctas_per_sm", cps)
+        np.testing.assert_array_equal(to_np(ops.add_signed_saturate(L, a, b)), want)
+        planes = ops.unpack(L, a, signed=True)
+        np.testing.assert_array_equal(to_np(ops.repack(L, planes)), a_h)
+    ops.set_option("ctas_per_sm", 0)
+
+
+def test_cpp_template_layer():
+    exe = os.path.join(ROOT, "build", "cpp_api_test")
+    if not os.path.exists(exe):
+        pytest.skip("build/cpp_api_test not built (make tools)")
+    out = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert "0 failures" in out.stdout
