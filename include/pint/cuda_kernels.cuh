@@ -57,6 +57,8 @@ namespace kernels {
 template <class SL>
 struct static_masks {
     using word = typename SL::word;
+    // many distinct widths make the saturating ops ALU-heavy: their kernels run with a deeper unroll
+    static constexpr bool heavy_fill = SL::masks.nsh >= 3;
     __device__ __forceinline__ static constexpr word H() { return SL::masks.H; }
     __device__ __forceinline__ static constexpr word L() { return SL::masks.L; }
     __device__ __forceinline__ static constexpr word A() { return SL::masks.A; }
@@ -113,6 +115,7 @@ struct static_masks {
 template <class Word>
 struct runtime_masks {
     using word = Word;
+    static constexpr bool heavy_fill = true;
     Word mH, mL, mA, mM1, mHL, mLM1;
     Word keep[6];
     uint32_t shift0;   // w - 1 when all fields have the same width
@@ -132,15 +135,14 @@ struct runtime_masks {
     __device__ __forceinline__ word fill(word c) const
     {
         if (nsmear == 0) return c | (c - (c >> shift0));
+        // all steps, unconditionally: keep[k] is 0 for the steps a layout does not need
         word x = c;
         x |= (x >> 1) & keep[0];
-        if (nsmear > 1) x |= (x >> 2) & keep[1];
-        if (nsmear > 2) x |= (x >> 4) & keep[2];
-        if (nsmear > 3) x |= (x >> 8) & keep[3];
-        if (nsmear > 4) x |= (x >> 16) & keep[4];
-        if constexpr (sizeof(Word) == 8) {
-            if (nsmear > 5) x |= (x >> 32) & keep[5];
-        }
+        x |= (x >> 2) & keep[1];
+        x |= (x >> 4) & keep[2];
+        x |= (x >> 8) & keep[3];
+        x |= (x >> 16) & keep[4];
+        if constexpr (sizeof(Word) == 8) x |= (x >> 32) & keep[5];
         return x;
     }
     __device__ __forceinline__ word below(word c) const

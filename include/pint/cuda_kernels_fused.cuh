@@ -100,6 +100,7 @@ __device__ __forceinline__ W field_op_wide(W a, W b, uint32_t off, uint32_t w)
 template <int Op, class FP>
 struct fused_fn {
     using word = typename FP::word;
+    static constexpr bool heavy = !(Op == OP_OR || Op == OP_AND || Op == OP_XOR);
     FP fp;
 
     __device__ __forceinline__ word operator()(word a, word b) const

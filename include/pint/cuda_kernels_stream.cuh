@@ -52,7 +52,14 @@ struct stream_cfg {
     static constexpr int LD = Ld;
     static constexpr int ST = St;
 };
+// Measured on B200 (profiles/r01_tune_sweep2.log): bandwidth-bound ops are best
+// with 2 vectors per operand per thread (7.03-7.08 TB/s vs 6.93-6.95 with 4),
+// ALU-heavy ones (many distinct widths, fused per-field arithmetic) with 4
+// (irregular u64 add_signed_saturate 6.58 vs 5.80 TB/s).
 using default_stream_cfg = stream_cfg<2, 256>;
+using heavy_stream_cfg = stream_cfg<4, 256>;
+template <class Fn>
+using stream_cfg_for = typename std::conditional<Fn::heavy, heavy_stream_cfg, default_stream_cfg>::type;
 
 // apply a Word function to the 16 bytes of a vector
 template <class Word, class F>
@@ -88,6 +95,7 @@ __device__ __forceinline__ uint4 map_words1(const uint4& a, F f)
 template <int Op, class P>
 struct swar_fn {
     using word = typename P::word;
+    static constexpr bool heavy = P::heavy_fill && !(Op == OP_ADD_WRAP || Op == OP_SUB_WRAP || Op == OP_OR || Op == OP_AND || Op == OP_XOR);
     P p;
     __device__ __forceinline__ word operator()(word a, word b) const { return apply_op<Op>(a, b, p); }
 };
@@ -219,7 +227,7 @@ inline bool split_aligned(size_t elem_bytes, size_t n, const void* const* ptrs, 
     return true;
 }
 
-template <class Elem, class Fn, class Cfg = default_stream_cfg>
+template <class Elem, class Fn, class Cfg = stream_cfg_for<Fn>>
 cudaError_t launch_binary(const void* a, const void* b, void* out, size_t n, const Fn& fn,
                           cudaStream_t stream, const launch_geom& g)
 {
