@@ -327,7 +327,7 @@ def main():
                          "traffic": traffic, "kernel": "binary_stream_kernel<swar_fn<op, static RGBA8 masks>>",
                          "peak_source": peak_src, "frac_of_spec_8000": achieved / 8000.0,
                          "algorithmic_bytes_per_launch": BYTES_PER_ELEM * count},
-            "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+            "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches) * world, "clocks": clocks,
             "hbm_gbs_whole_job": achieved * world, "out_checksum": list(chk),
         }
         print(json.dumps(line), flush=True)
