@@ -154,6 +154,41 @@ int main(int argc, char** argv)
     using FnIF = fused_fn<OP_ADD_SIGNED_SATURATE, static_fields<IRR>>;
     using FnX = swar_fn<OP_XOR, static_masks<RGBA>>;
 
+    if (argc > 3 && std::atoi(argv[3]) == 3) {
+        // small arrays (C0: 2^26 uint16 = 128 MiB per array): rotate over 8 disjoint windows of the
+        // big buffers so that no launch finds its data in the 126 MB L2
+        using C565 = static_layout<uint16_t, 5, 6, 5>;
+        using FnC0 = swar_fn<OP_ADD_WRAP, static_masks<C565>>;
+        const size_t small = size_t(1) << 23;  // vectors = 128 MiB
+        int it = 0;
+        auto small_run = [&](auto cfg_tag, const char* label, int cps) {
+            using Cfg = decltype(cfg_tag);
+            constexpr size_t tile = size_t(Cfg::UNROLL) * Cfg::BLOCK;
+            const size_t ntiles = (small + tile - 1) / tile;
+            const size_t grid = cps > 0 ? std::min(ntiles, size_t(g_sms) * cps) : ntiles;
+            char name[128];
+            std::snprintf(name, sizeof name, "add_wrap u16 565, 128 MiB arrays: %s ctas/sm %d", label, cps);
+            time_it(name, double(small) * 48, [&] {
+                const size_t off = size_t(it++ % 8) * small;
+                binary_stream_kernel<FnC0, Cfg><<<unsigned(grid), Cfg::BLOCK>>>((const uint4*)a + off, (const uint4*)b + off, (uint4*)out + off, small, FnC0{});
+            });
+        };
+        g_reps = 40;
+        for (int cps : {0, 4, 8}) {
+            small_run(stream_cfg<1, 256, 2, 2>{}, "U1 B256", cps);
+            small_run(stream_cfg<2, 256, 2, 2>{}, "U2 B256", cps);
+            small_run(stream_cfg<4, 256, 2, 2>{}, "U4 B256", cps);
+            small_run(stream_cfg<2, 512, 2, 2>{}, "U2 B512", cps);
+            small_run(stream_cfg<2, 1024, 2, 2>{}, "U2 B1024", cps);
+            small_run(stream_cfg<8, 256, 2, 2>{}, "U8 B256", cps);
+        }
+        time_it("cudaMemcpyAsync D2D 128 MiB (bytes = 2 x array)", double(small) * 32, [&] {
+            const size_t off = size_t(it++ % 8) * small;
+            CK(cudaMemcpyAsync((uint4*)out + off, (const uint4*)a + off, small * 16, cudaMemcpyDeviceToDevice));
+        });
+        std::printf("done\n");
+        return 0;
+    }
     if (argc > 3 && std::atoi(argv[3]) == 2) {
         // second sweep: one CTA per tile for every representative op, and dynamic persistent grids
         using C16 = static_layout<uint64_t, 16, 16, 16, 16>;
