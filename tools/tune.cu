@@ -154,6 +154,33 @@ int main(int argc, char** argv)
     using FnIF = fused_fn<OP_ADD_SIGNED_SATURATE, static_fields<IRR>>;
     using FnX = swar_fn<OP_XOR, static_masks<RGBA>>;
 
+    if (argc > 3 && std::atoi(argv[3]) == 4) {
+        // one CTA per tile, residency capped by an unused dynamic shared-memory request
+        // (227 KB per SM / request = CTAs per SM): is full occupancy the best occupancy?
+        using C16 = static_layout<uint64_t, 16, 16, 16, 16>;
+        using FnC2 = swar_fn<OP_ADD_SIGNED_SATURATE, static_masks<C16>>;
+        auto occ_run = [&](auto fn_tag, auto cfg_tag, const char* label, int ctas) {
+            using Fn = decltype(fn_tag);
+            using Cfg = decltype(cfg_tag);
+            constexpr size_t tile = size_t(Cfg::UNROLL) * Cfg::BLOCK;
+            const size_t ntiles = (nvec + tile - 1) / tile;
+            const int smem = ctas > 0 ? (227 * 1024 / ctas - 1024) / 1024 * 1024 : 0;
+            CK(cudaFuncSetAttribute(binary_stream_kernel<Fn, Cfg>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            char name[160];
+            std::snprintf(name, sizeof name, "%s U%d B%d one CTA/tile, <= %d CTAs/SM (smem pad %d KB)", label, Cfg::UNROLL, Cfg::BLOCK, ctas, smem / 1024);
+            time_it(name, double(nvec) * 48, [&] {
+                binary_stream_kernel<Fn, Cfg><<<unsigned(ntiles), Cfg::BLOCK, smem>>>((const uint4*)a, (const uint4*)b, (uint4*)out, nvec, Fn{});
+            });
+        };
+        for (int ctas : {0, 7, 6, 5, 4, 3, 2}) occ_run(FnU{}, stream_cfg<2, 256, 2, 2>{}, "usat rgba8", ctas);
+        for (int ctas : {0, 3, 2, 1}) occ_run(FnU{}, stream_cfg<2, 512, 2, 2>{}, "usat rgba8", ctas);
+        for (int ctas : {0, 6, 4, 3, 2}) occ_run(FnU{}, stream_cfg<4, 256, 2, 2>{}, "usat rgba8", ctas);
+        for (int ctas : {0, 6, 5, 4, 3}) occ_run(FnC2{}, stream_cfg<2, 256, 2, 2>{}, "add_ssat u64 16x4", ctas);
+        for (int ctas : {0, 6, 4}) occ_run(FnI{}, stream_cfg<4, 256, 2, 2>{}, "add_ssat irregular u64 swar", ctas);
+        for (int ctas : {0, 6, 4}) occ_run(FnIF{}, stream_cfg<4, 256, 2, 2>{}, "add_ssat irregular u64 fused", ctas);
+        std::printf("done\n");
+        return 0;
+    }
     if (argc > 3 && std::atoi(argv[3]) == 3) {
         // small arrays (C0: 2^26 uint16 = 128 MiB per array): rotate over 8 disjoint windows of the
         // big buffers so that no launch finds its data in the 126 MB L2
