@@ -126,16 +126,17 @@ __device__ __forceinline__ void store_quad(Elem* p, const Word (&e)[4])
 }
 
 // Plane element type: int32_t/uint32_t/int64_t/uint64_t handled as 4- or 8-byte words.
-template <int PlaneBytes>
+template <int PlaneBytes, int St = CACHE_STREAMING>
 __device__ __forceinline__ void store_plane_quad(void* plane, size_t q, const uint64_t (&v)[4])
 {
+    constexpr int CACHE_ST = St;
     if constexpr (PlaneBytes == 4) {
-        st16<CACHE_STREAMING>(reinterpret_cast<uint4*>(plane) + q,
+        st16<CACHE_ST>(reinterpret_cast<uint4*>(plane) + q,
                               make_uint4(uint32_t(v[0]), uint32_t(v[1]), uint32_t(v[2]), uint32_t(v[3])));
     } else {
         uint4* d = reinterpret_cast<uint4*>(plane) + 2 * q;
-        st16<CACHE_STREAMING>(d, make_uint4(uint32_t(v[0]), uint32_t(v[0] >> 32), uint32_t(v[1]), uint32_t(v[1] >> 32)));
-        st16<CACHE_STREAMING>(d + 1, make_uint4(uint32_t(v[2]), uint32_t(v[2] >> 32), uint32_t(v[3]), uint32_t(v[3] >> 32)));
+        st16<CACHE_ST>(d, make_uint4(uint32_t(v[0]), uint32_t(v[0] >> 32), uint32_t(v[1]), uint32_t(v[1] >> 32)));
+        st16<CACHE_ST>(d + 1, make_uint4(uint32_t(v[2]), uint32_t(v[2] >> 32), uint32_t(v[3]), uint32_t(v[3] >> 32)));
     }
 }
 
@@ -157,24 +158,35 @@ __device__ __forceinline__ void load_plane_quad(const void* plane, size_t q, uin
 }
 
 // packed -> planes.  get<I> (pint.hpp:799-807) or get_signed<I> (:809-822) for
-// every wanted field of 4 consecutive elements per thread.
-template <class Elem, int PlaneBytes, bool Signed, class FP>
+// every wanted field of Q x 4 consecutive elements per thread (Q quads, strided by
+// the block so that every warp access stays contiguous).
+template <class Elem, int PlaneBytes, bool Signed, class FP, int Q = 1, int St = CACHE_STREAMING>
 __global__ void __launch_bounds__(256)
 unpack_quad_kernel(const Elem* packed, const __grid_constant__ plane_ptrs planes, size_t nquads,
                    const __grid_constant__ FP fp)
 {
     using W = typename FP::word;
-    for (size_t q = size_t(blockIdx.x) * blockDim.x + threadIdx.x; q < nquads; q += size_t(gridDim.x) * blockDim.x) {
-        W e[4];
-        load_quad<Elem, W>(packed + 4 * q, e);
+    const size_t tile = size_t(Q) * blockDim.x;
+    for (size_t t = blockIdx.x; t * tile < nquads; t += gridDim.x) {
+        W e[Q][4];
+        size_t q[Q];
+#pragma unroll
+        for (int k = 0; k < Q; ++k) {
+            q[k] = t * tile + size_t(k) * blockDim.x + threadIdx.x;
+            if (q[k] < nquads) load_quad<Elem, W>(packed + 4 * q[k], e[k]);
+        }
         fp.each_elem_field([&](uint32_t i, uint32_t off, uint32_t w) {
             void* dst = planes.p[i];
             if (!dst) return;
-            uint64_t v[4];
 #pragma unroll
-            for (int j = 0; j < 4; ++j)
-                v[j] = Signed ? uint64_t(int64_t(field_get_signed<W>(e[j], off, w))) : uint64_t(field_get<W>(e[j], off, w));
-            store_plane_quad<PlaneBytes>(dst, q, v);
+            for (int k = 0; k < Q; ++k) {
+                if (q[k] >= nquads) continue;
+                uint64_t v[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    v[j] = Signed ? uint64_t(int64_t(field_get_signed<W>(e[k][j], off, w))) : uint64_t(field_get<W>(e[k][j], off, w));
+                store_plane_quad<PlaneBytes, St>(dst, q[k], v);
+            }
         });
     }
 }

@@ -58,9 +58,12 @@ def binary_case(name, layout, n, op_list, sets=1, fused=False, generic=False):
     ops.set_option("force_generic", int(generic))
     for op in op_list:
         def run(i):
-            a, b, o = bufs[i % sets]
-            ops.binary(op, layout, a, b, out=o, fused=fused)
+            # one timed sample = one launch per buffer set, queued back to back, so that a short
+            # kernel's time is not dominated by the host's launch latency between two events
+            for a, b, o in bufs:
+                ops.binary(op, layout, a, b, out=o, fused=fused)
         best, med = timed(run)
+        best, med = best / sets, med / sets
         report(name, n, 3 * layout.elem_bytes, best, med, op=op, layout=repr(layout),
                kernel=("fused" if fused else "swar") + ("/runtime-masks" if generic else "/static-masks" if layout.is_specialized() else "/runtime-masks"))
     ops.set_option("force_generic", 0)

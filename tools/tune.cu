@@ -154,6 +154,29 @@ int main(int argc, char** argv)
     using FnIF = fused_fn<OP_ADD_SIGNED_SATURATE, static_fields<IRR>>;
     using FnX = swar_fn<OP_XOR, static_masks<RGBA>>;
 
+    if (argc > 3 && std::atoi(argv[3]) == 5) {
+        // unpack (C3): 2^28 irregular u64 elements -> 6 int32 planes; quads per thread, block, store policy
+        const size_t n = size_t(1) << 28;            // 2 GiB packed in `a`, planes in b/out (4 GiB each = 3+3 planes of 1 GiB)
+        plane_ptrs pp{};
+        for (int f = 0; f < 6; ++f) pp.p[f] = (char*)(f < 3 ? b : out) + size_t(f % 3) * (n * 4);
+        auto unpack_run = [&](auto q_tag, auto st_tag, int block) {
+            constexpr int Q = decltype(q_tag)::value, ST = decltype(st_tag)::value;
+            const size_t nquads = n / 4, tile = size_t(Q) * block;
+            char name[160];
+            std::snprintf(name, sizeof name, "unpack irregular u64 -> 6 x int32: Q%d B%d st%d", Q, block, ST);
+            time_it(name, double(n) * 32, [&] {
+                unpack_quad_kernel<uint64_t, 4, true, static_fields<IRR>, Q, ST><<<unsigned((nquads + tile - 1) / tile), block>>>((const uint64_t*)a, pp, nquads, static_fields<IRR>{});
+            });
+        };
+        using I1 = std::integral_constant<int, 1>; using I2 = std::integral_constant<int, 2>; using I4 = std::integral_constant<int, 4>; using I0 = std::integral_constant<int, 0>;
+        for (int block : {128, 256}) {
+            unpack_run(I1{}, I2{}, block); unpack_run(I2{}, I2{}, block); unpack_run(I4{}, I2{}, block);
+            unpack_run(I1{}, I0{}, block); unpack_run(I2{}, I0{}, block);
+            unpack_run(I1{}, I1{}, block);
+        }
+        std::printf("done\n");
+        return 0;
+    }
     if (argc > 3 && std::atoi(argv[3]) == 4) {
         // one CTA per tile, residency capped by an unused dynamic shared-memory request
         // (227 KB per SM / request = CTAs per SM): is full occupancy the best occupancy?
