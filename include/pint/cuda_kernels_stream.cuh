@@ -137,6 +137,92 @@ binary_stream_kernel(const uint4* a, const uint4* b, uint4* out, size_t nvec, co
     }
 }
 
+struct tile_counter {
+    unsigned long long next;  // next tile to hand out
+    unsigned long long done;  // CTAs that have finished; the last one re-arms both fields
+};
+constexpr unsigned kTileCounterSlots = 4096;
+
+// Ordered persistent variant for bandwidth-bound functors.  num_sms * k CTAs stay
+// resident and draw tiles in ADDRESS ORDER from a global counter, so the window of
+// the arrays that the whole chip is working on stays as compact as with one CTA
+// per tile, while the number of resident warps is chosen by the grid size rather
+// than by the register budget.  Measured on B200 (profiles/r01_tune_dyn_scheduler.log):
+// 4 CTAs of 256 threads per SM give 7.12-7.21 TB/s on the light ops against 7.02-7.05
+// for one CTA per tile (8 resident CTAs per SM) and 6.0-6.5 for a grid-stride grid.
+// The last CTA to finish re-arms the counter, so a launch needs no memset; launches
+// that may overlap use different slots of a counter ring.
+template <class Fn, class Cfg>
+__global__ void __launch_bounds__(Cfg::BLOCK)
+binary_stream_ordered_kernel(const uint4* a, const uint4* b, uint4* out, size_t nvec, tile_counter* tc,
+                             const __grid_constant__ Fn fn)
+{
+    using W = typename Fn::word;
+    constexpr int U = Cfg::UNROLL, B = Cfg::BLOCK;
+    constexpr size_t tile = size_t(U) * B;
+    const size_t nfull = nvec / tile;
+    auto f = [&](W x, W y) { return fn(x, y); };
+    __shared__ unsigned long long drawn;
+    for (;;) {
+        if (threadIdx.x == 0) drawn = atomicAdd(&tc->next, 1ULL);
+        __syncthreads();
+        const size_t t = drawn;
+        __syncthreads();
+        if (t > nfull) break;
+        if (t == nfull) {  // the partial last tile
+            for (size_t i = nfull * tile + threadIdx.x; i < nvec; i += B)
+                st16<Cfg::ST>(out + i, map_words2<W>(ld16<Cfg::LD>(a + i), ld16<Cfg::LD>(b + i), f));
+            continue;
+        }
+        const size_t base = t * tile + threadIdx.x;
+        uint4 va[U], vb[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) va[u] = ld16<Cfg::LD>(a + base + size_t(u) * B);
+#pragma unroll
+        for (int u = 0; u < U; ++u) vb[u] = ld16<Cfg::LD>(b + base + size_t(u) * B);
+#pragma unroll
+        for (int u = 0; u < U; ++u) st16<Cfg::ST>(out + base + size_t(u) * B, map_words2<W>(va[u], vb[u], f));
+    }
+    if (threadIdx.x == 0 && atomicAdd(&tc->done, 1ULL) == gridDim.x - 1) {
+        tc->next = 0;  // every CTA has made its last draw: re-arm for the next launch
+        tc->done = 0;
+    }
+}
+
+template <class Word, class Cfg>
+__global__ void __launch_bounds__(Cfg::BLOCK)
+unary_stream_ordered_kernel(const uint4* in, uint4* out, size_t nvec, tile_counter* tc,
+                            const __grid_constant__ unary_params<Word> u)
+{
+    constexpr int U = Cfg::UNROLL, B = Cfg::BLOCK;
+    constexpr size_t tile = size_t(U) * B;
+    const size_t nfull = nvec / tile;
+    auto f = [&](Word x) { return apply_unary(x, u); };
+    __shared__ unsigned long long drawn;
+    for (;;) {
+        if (threadIdx.x == 0) drawn = atomicAdd(&tc->next, 1ULL);
+        __syncthreads();
+        const size_t t = drawn;
+        __syncthreads();
+        if (t > nfull) break;
+        if (t == nfull) {
+            for (size_t i = nfull * tile + threadIdx.x; i < nvec; i += B)
+                st16<Cfg::ST>(out + i, map_words1<Word>(ld16<Cfg::LD>(in + i), f));
+            continue;
+        }
+        const size_t base = t * tile + threadIdx.x;
+        uint4 v[U];
+#pragma unroll
+        for (int k = 0; k < U; ++k) v[k] = ld16<Cfg::LD>(in + base + size_t(k) * B);
+#pragma unroll
+        for (int k = 0; k < U; ++k) st16<Cfg::ST>(out + base + size_t(k) * B, map_words1<Word>(v[k], f));
+    }
+    if (threadIdx.x == 0 && atomicAdd(&tc->done, 1ULL) == gridDim.x - 1) {
+        tc->next = 0;
+        tc->done = 0;
+    }
+}
+
 // Element-granular variant: array heads/tails shorter than a vector and
 // operands whose addresses are not congruent modulo 16.  One element is
 // zero-extended into a Word; the replicated masks act on zeros above it.
@@ -190,7 +276,18 @@ struct launch_geom {
     int num_sms = 148;
     int ctas_per_sm = 0;
     unsigned long long* launch_counter = nullptr;  // bumped once per kernel launch
+    // Ordered persistent mode for bandwidth-bound functors (see binary_stream_ordered_kernel):
+    // a ring of zeroed device counters, a host cursor into it, and the grid size per SM.
+    tile_counter* counters = nullptr;
+    unsigned* counter_cursor = nullptr;
+    int ordered_ctas_per_sm = 0;  // 0 = off
 };
+
+inline tile_counter* next_tile_counter(const launch_geom& g)
+{
+    const unsigned slot = __atomic_fetch_add(g.counter_cursor, 1u, __ATOMIC_RELAXED) % kTileCounterSlots;
+    return g.counters + slot;
+}
 
 inline unsigned grid_for(size_t ntiles, const launch_geom& g)
 {
@@ -251,10 +348,17 @@ cudaError_t launch_binary(const void* a, const void* b, void* out, size_t n, con
     elems(0, head);
     if (nvec) {
         constexpr size_t tile = size_t(Cfg::UNROLL) * Cfg::BLOCK;
-        const unsigned grid = grid_for((nvec + tile - 1) / tile, g);
-        binary_stream_kernel<Fn, Cfg><<<grid, Cfg::BLOCK, 0, stream>>>(
-            reinterpret_cast<const uint4*>(ea + head), reinterpret_cast<const uint4*>(eb + head),
-            reinterpret_cast<uint4*>(eo + head), nvec, fn);
+        const size_t ntiles = (nvec + tile - 1) / tile;
+        const size_t ordered_grid = size_t(g.num_sms) * size_t(g.ordered_ctas_per_sm > 0 ? g.ordered_ctas_per_sm : 0);
+        if (!Fn::heavy && g.counters && g.ctas_per_sm == 0 && ordered_grid && ntiles > 2 * ordered_grid) {
+            binary_stream_ordered_kernel<Fn, Cfg><<<unsigned(ordered_grid), Cfg::BLOCK, 0, stream>>>(
+                reinterpret_cast<const uint4*>(ea + head), reinterpret_cast<const uint4*>(eb + head),
+                reinterpret_cast<uint4*>(eo + head), nvec, next_tile_counter(g), fn);
+        } else {
+            binary_stream_kernel<Fn, Cfg><<<grid_for(ntiles, g), Cfg::BLOCK, 0, stream>>>(
+                reinterpret_cast<const uint4*>(ea + head), reinterpret_cast<const uint4*>(eb + head),
+                reinterpret_cast<uint4*>(eo + head), nvec, fn);
+        }
         count_launch(g);
     }
     elems(n - tail, tail);
@@ -284,9 +388,16 @@ cudaError_t launch_unary(const void* in, void* out, size_t n, const unary_params
     elems(0, head);
     if (nvec) {
         constexpr size_t tile = size_t(Cfg::UNROLL) * Cfg::BLOCK;
-        const unsigned grid = grid_for((nvec + tile - 1) / tile, g);
-        unary_stream_kernel<Word, Cfg><<<grid, Cfg::BLOCK, 0, stream>>>(
-            reinterpret_cast<const uint4*>(ei + head), reinterpret_cast<uint4*>(eo + head), nvec, u);
+        const size_t ntiles = (nvec + tile - 1) / tile;
+        const size_t ordered_grid = size_t(g.num_sms) * size_t(g.ordered_ctas_per_sm > 0 ? g.ordered_ctas_per_sm : 0);
+        if (g.counters && g.ctas_per_sm == 0 && ordered_grid && ntiles > 2 * ordered_grid) {
+            unary_stream_ordered_kernel<Word, Cfg><<<unsigned(ordered_grid), Cfg::BLOCK, 0, stream>>>(
+                reinterpret_cast<const uint4*>(ei + head), reinterpret_cast<uint4*>(eo + head), nvec,
+                next_tile_counter(g), u);
+        } else {
+            unary_stream_kernel<Word, Cfg><<<grid_for(ntiles, g), Cfg::BLOCK, 0, stream>>>(
+                reinterpret_cast<const uint4*>(ei + head), reinterpret_cast<uint4*>(eo + head), nvec, u);
+        }
         count_launch(g);
     }
     elems(n - tail, tail);

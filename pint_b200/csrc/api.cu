@@ -38,12 +38,37 @@ int current_sms()
     return v;
 }
 
+// Counter ring of the ordered persistent kernels: static device memory (zero at
+// module load, re-armed by the kernels themselves), so no call ever allocates.
+__device__ pint::cuda::kernels::tile_counter g_tile_counters[pint::cuda::kernels::kTileCounterSlots];
+unsigned g_counter_cursor = 0;
+
+pint::cuda::kernels::tile_counter* current_counters()
+{
+    static pint::cuda::kernels::tile_counter* addr[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    pint::cuda::kernels::tile_counter* p = __atomic_load_n(&addr[dev], __ATOMIC_ACQUIRE);
+    if (!p) {
+        void* sym = nullptr;
+        if (cudaGetSymbolAddress(&sym, g_tile_counters) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+        p = static_cast<pint::cuda::kernels::tile_counter*>(sym);
+        __atomic_store_n(&addr[dev], p, __ATOMIC_RELEASE);
+    }
+    return p;
+}
+
 launch_geom geom()
 {
     launch_geom g;
     g.num_sms = current_sms();
     g.ctas_per_sm = (int)opts().ctas_per_sm;
     g.launch_counter = &g_launches;
+    g.ordered_ctas_per_sm = (int)opts().ordered_ctas_per_sm;
+    if (g.ordered_ctas_per_sm > 0) {
+        g.counters = current_counters();
+        g.counter_cursor = &g_counter_cursor;
+    }
     return g;
 }
 
@@ -151,6 +176,7 @@ int pint_cuda_set_option(const char* key, long value)
     if (!key) return PINT_E_ARG;
     if (!std::strcmp(key, "force_generic")) { opts().force_generic = value != 0; return PINT_OK; }
     if (!std::strcmp(key, "ctas_per_sm")) { if (value < 0 || value > 64) return PINT_E_ARG; opts().ctas_per_sm = value; return PINT_OK; }
+    if (!std::strcmp(key, "ordered_ctas_per_sm")) { if (value < 0 || value > 32) return PINT_E_ARG; opts().ordered_ctas_per_sm = value; return PINT_OK; }
     if (!std::strcmp(key, "host_chunk_bytes")) { if (value < 4096) return PINT_E_ARG; opts().host_chunk_bytes = value; return PINT_OK; }
     if (!std::strcmp(key, "host_slots")) { if (value < 1 || value > 8) return PINT_E_ARG; opts().host_slots = value; return PINT_OK; }
     return PINT_E_ARG;
@@ -161,6 +187,7 @@ long pint_cuda_get_option(const char* key)
     if (!key) return -1;
     if (!std::strcmp(key, "force_generic")) return opts().force_generic;
     if (!std::strcmp(key, "ctas_per_sm")) return opts().ctas_per_sm;
+    if (!std::strcmp(key, "ordered_ctas_per_sm")) return opts().ordered_ctas_per_sm;
     if (!std::strcmp(key, "host_chunk_bytes")) return opts().host_chunk_bytes;
     if (!std::strcmp(key, "host_slots")) return opts().host_slots;
     return -1;

@@ -94,6 +94,36 @@ def test_persistent_grid_option_gives_same_results(oracle):
     ops.set_option("ctas_per_sm", 0)
 
 
+def test_ordered_persistent_mode_matches_one_cta_per_tile(oracle):
+    """Large light ops run the ordered persistent kernel (atomic tile counter); same bits either way,
+    also on repeated launches (the counter re-arms itself) and on concurrent streams (counter ring)."""
+    import pint_b200
+    from pint_b200 import ops
+    for eb, bits in [(4, (8, 8, 8, 8)), (2, (5, 6, 5)), (8, (16, 16, 16, 16))]:
+        L = pint_b200.Layout(eb, *bits)
+        n = (24 << 20) // eb + 1029     # > 2 * 148 * 4 tiles of 8 KiB, ragged tail
+        a_h, b_h = oracle.fill(eb, n, 31), oracle.fill(eb, n, 32)
+        a, b = to_dev(a_h), to_dev(b_h)
+        want = {op: oracle.binary(op, eb, bits, a_h, b_h) for op in ("add_unsigned_saturate", "sub_wrap", "bit_xor")}
+        want_shift = oracle.shift(0, eb, bits, 1, a_h)
+        for mode in (4, 0, 4):
+            ops.set_option("ordered_ctas_per_sm", mode)
+            for rep in range(3):
+                for op, w in want.items():
+                    np.testing.assert_array_equal(to_np(ops.binary(op, L, a, b)), w, err_msg=f"{L} {op} ordered={mode}")
+                np.testing.assert_array_equal(to_np(ops.shift_right_unsigned(L, a, 1)), want_shift)
+        ops.set_option("ordered_ctas_per_sm", 4)
+        streams = [torch.cuda.Stream() for _ in range(3)]
+        outs = [torch.empty_like(a) for _ in streams]
+        torch.cuda.synchronize()
+        for _ in range(4):
+            for s, o in zip(streams, outs):
+                ops.binary("add_unsigned_saturate", L, a, b, out=o, stream=s)
+        torch.cuda.synchronize()
+        for o in outs:
+            np.testing.assert_array_equal(to_np(o), want["add_unsigned_saturate"])
+
+
 def test_cpp_template_layer():
     exe = os.path.join(ROOT, "build", "cpp_api_test")
     if not os.path.exists(exe):

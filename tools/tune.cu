@@ -154,6 +154,33 @@ int main(int argc, char** argv)
     using FnIF = fused_fn<OP_ADD_SIGNED_SATURATE, static_fields<IRR>>;
     using FnX = swar_fn<OP_XOR, static_masks<RGBA>>;
 
+    if (argc > 3 && std::atoi(argv[3]) == 6) {
+        // persistent CTAs + atomic tile counter (tiles handed out in address order): how robust is the
+        // best CTAs/SM across ops, element types and array sizes?
+        using C16 = static_layout<uint64_t, 16, 16, 16, 16>;
+        using FnC2 = swar_fn<OP_SUB_SIGNED_SATURATE, static_masks<C16>>;
+        using C565 = static_layout<uint16_t, 5, 6, 5>;
+        using FnC0 = swar_fn<OP_ADD_WRAP, static_masks<C565>>;
+        using T2 = static_layout<uint32_t, 1, 2, 3, 4, 5, 6, 11>;
+        using FnT2 = swar_fn<OP_ADD_SIGNED_SATURATE, static_masks<T2>>;
+        for (size_t nv : {nvec, nvec / 8}) {
+            std::printf("--- %zu vectors per array (%.2f GiB)\n", nv, nv * 16 / 1073741824.0);
+            run_stream<FnU, 2, 256, 2, 2>("usat rgba8 (one CTA per tile)", a, b, out, nv, 0);
+            for (int cps : {3, 4, 5, 6}) run_dyn<FnU, 2, 256>("usat rgba8", a, b, out, nv, cps);
+            for (int cps : {3, 4, 5, 6}) run_dyn<FnS, 2, 256>("ssat rgba8", a, b, out, nv, cps);
+            for (int cps : {3, 4, 5, 6}) run_dyn<FnC2, 2, 256>("sub_ssat u64 16x4", a, b, out, nv, cps);
+            for (int cps : {3, 4, 5, 6}) run_dyn<FnC0, 2, 256>("add_wrap u16 565", a, b, out, nv, cps);
+            for (int cps : {4, 6, 8}) run_dyn<FnT2, 2, 256>("add_ssat u32 type2", a, b, out, nv, cps);
+            for (int cps : {4, 6, 8}) run_dyn<FnI, 2, 256>("add_ssat irregular u64 swar", a, b, out, nv, cps);
+            for (int cps : {4, 6, 8}) run_dyn<FnIF, 2, 256>("add_ssat irregular u64 fused", a, b, out, nv, cps);
+            for (int cps : {2, 3, 4}) run_dyn<FnI, 4, 256>("add_ssat irregular u64 swar", a, b, out, nv, cps);
+            for (int cps : {2, 3, 4}) run_dyn<FnIF, 4, 256>("add_ssat irregular u64 fused", a, b, out, nv, cps);
+            for (int cps : {2, 3}) run_dyn<FnU, 2, 512>("usat rgba8", a, b, out, nv, cps);
+            for (int cps : {1, 2}) run_dyn<FnU, 4, 512>("usat rgba8", a, b, out, nv, cps);
+        }
+        std::printf("done\n");
+        return 0;
+    }
     if (argc > 3 && std::atoi(argv[3]) == 5) {
         // unpack (C3): 2^28 irregular u64 elements -> 6 int32 planes; quads per thread, block, store policy
         const size_t n = size_t(1) << 28;            // 2 GiB packed in `a`, planes in b/out (4 GiB each = 3+3 planes of 1 GiB)
