@@ -143,13 +143,16 @@ struct tile_counter {
 };
 constexpr unsigned kTileCounterSlots = 4096;
 
-// Ordered persistent variant for bandwidth-bound functors.  num_sms * k CTAs stay
-// resident and draw tiles in ADDRESS ORDER from a global counter, so the window of
-// the arrays that the whole chip is working on stays as compact as with one CTA
-// per tile, while the number of resident warps is chosen by the grid size rather
-// than by the register budget.  Measured on B200 (profiles/r01_tune_dyn_scheduler.log):
-// 4 CTAs of 256 threads per SM give 7.12-7.21 TB/s on the light ops against 7.02-7.05
-// for one CTA per tile (8 resident CTAs per SM) and 6.0-6.5 for a grid-stride grid.
+// Ordered persistent variant for bandwidth-bound functors (OPTIONAL, off by default).
+// num_sms * k CTAs stay resident and draw tiles in ADDRESS ORDER from a global
+// counter, so the window of the arrays the chip is working on stays as compact as
+// with one CTA per tile while the number of resident warps is set by the grid size
+// rather than the register budget.  On B200 4 CTAs of 256 threads per SM reached
+// 7.13-7.22 TB/s on the light ops in some runs (profiles/r01_tune_dyn_scheduler.log)
+// against a rock-steady 7.02-7.05 for one CTA per tile, but the gain does not
+// reproduce run to run and neighbouring grid sizes fall off a cliff (5.3-6.6 TB/s;
+// profiles/r01_tune_ordered_vs_tile.log), so the library default stays one CTA per
+// tile; pint_cuda_set_option("ordered_ctas_per_sm", k) enables this path.
 // The last CTA to finish re-arms the counter, so a launch needs no memset; launches
 // that may overlap use different slots of a counter ring.
 template <class Fn, class Cfg>

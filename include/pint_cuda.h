@@ -88,8 +88,8 @@ unsigned long long pint_cuda_launch_count(void);
 /* Tuning/testing knobs: "force_generic" (1 = always use the runtime-mask
  * kernels even for layouts that have compiled-in constants),
  * "ctas_per_sm" (0 = one CTA per tile, the default; k > 0 = persistent grid of SMs * k CTAs),
- * "ordered_ctas_per_sm" (bandwidth-bound ops on large arrays run a persistent grid of SMs * this
- * CTAs that draw tiles in address order; default 4, 0 = always one CTA per tile),
+ * "ordered_ctas_per_sm" (k > 0: bandwidth-bound ops on large arrays run a persistent grid of
+ * SMs * k CTAs that draw tiles in address order; default 0 = always one CTA per tile),
  * "host_chunk_bytes" / "host_slots" (staging ring of the host-buffer path).  Returns 0 or PINT_E_ARG. */
 int pint_cuda_set_option(const char* key, long value);
 long pint_cuda_get_option(const char* key);

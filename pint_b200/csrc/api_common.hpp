@@ -14,7 +14,7 @@ struct options {
     long ctas_per_sm = 0;  // 0 = one CTA per tile (fastest, see launch_geom)
     long host_chunk_bytes = 32L << 20;  // per operand per pipeline slot
     long host_slots = 3;
-    long ordered_ctas_per_sm = 4;  // ordered persistent grid for bandwidth-bound functors; 0 = off
+    long ordered_ctas_per_sm = 0;  // ordered persistent grid for bandwidth-bound functors; 0 = off (default, see cuda_kernels_stream.cuh)
 };
 options& opts();
 

@@ -154,6 +154,42 @@ int main(int argc, char** argv)
     using FnIF = fused_fn<OP_ADD_SIGNED_SATURATE, static_fields<IRR>>;
     using FnX = swar_fn<OP_XOR, static_masks<RGBA>>;
 
+    if (argc > 3 && std::atoi(argv[3]) == 7) {
+        // library ordered kernel (self re-arming counter ring) vs the tune-local dyn kernel (memset per launch)
+        tile_counter* ring;
+        CK(cudaMalloc(&ring, sizeof(tile_counter) * kTileCounterSlots));
+        CK(cudaMemset(ring, 0, sizeof(tile_counter) * kTileCounterSlots));
+        unsigned cursor = 0;
+        auto lib_run = [&](auto fn_tag, const char* label, int cps, bool same_slot) {
+            using Fn = decltype(fn_tag);
+            using Cfg = stream_cfg<2, 256, 2, 2>;
+            char name[160];
+            std::snprintf(name, sizeof name, "%s library ordered kernel ctas/sm %d %s", label, cps, same_slot ? "(one slot)" : "(ring)");
+            time_it(name, double(nvec) * 48, [&] {
+                tile_counter* tc = ring + (same_slot ? 0 : (cursor++ % kTileCounterSlots));
+                binary_stream_ordered_kernel<Fn, Cfg><<<unsigned(g_sms * cps), 256>>>((const uint4*)a, (const uint4*)b, (uint4*)out, nvec, tc, Fn{});
+            });
+        };
+        for (int rep = 0; rep < 2; ++rep) {
+            run_stream<FnU, 2, 256, 2, 2>("usat rgba8 (one CTA per tile)", a, b, out, nvec, 0);
+            run_stream<FnS, 2, 256, 2, 2>("ssat rgba8 (one CTA per tile)", a, b, out, nvec, 0);
+            run_dyn<FnU, 2, 256>("usat rgba8", a, b, out, nvec, 4);
+            run_dyn<FnS, 2, 256>("ssat rgba8", a, b, out, nvec, 4);
+            lib_run(FnU{}, "usat rgba8", 4, false);
+            lib_run(FnS{}, "ssat rgba8", 4, false);
+            lib_run(FnU{}, "usat rgba8", 4, true);
+            lib_run(FnS{}, "ssat rgba8", 4, true);
+            lib_run(FnU{}, "usat rgba8", 5, false);
+            lib_run(FnS{}, "ssat rgba8", 5, false);
+        }
+        // different buffers: swap roles (out -> a) to change relative alignment of the three streams
+        run_dyn<FnS, 2, 256>("ssat rgba8 (a=out2,b=a,out=b)", out2, a, b, nvec, 4);
+        run_dyn<FnU, 2, 256>("usat rgba8 (a=out2,b=a,out=b)", out2, a, b, nvec, 4);
+        run_dyn<FnS, 2, 256>("ssat rgba8 (a=b,b=out,out=a)", b, out, a, nvec, 4);
+        run_stream<FnS, 2, 256, 2, 2>("ssat rgba8 one CTA per tile (a=out2,b=a,out=b)", out2, a, b, nvec, 0);
+        std::printf("done\n");
+        return 0;
+    }
     if (argc > 3 && std::atoi(argv[3]) == 6) {
         // persistent CTAs + atomic tile counter (tiles handed out in address order): how robust is the
         // best CTAs/SM across ops, element types and array sizes?
