@@ -162,6 +162,19 @@ int pint_cuda_sharded_binary(int op, const pint_layout* layout, int ngpu, const 
                              const void* const* a, const void* const* b, void* const* out,
                              const size_t* counts, const pint_stream_t* streams);
 
+/* Same for the fused unpack -> arithmetic -> repack kernel (config C4: one launch per device). */
+int pint_cuda_sharded_fused_unpack_arith_repack(int op, const pint_layout* layout, int ngpu, const int* devices,
+                                                const void* const* a, const void* const* b, void* const* out,
+                                                const size_t* counts, const pint_stream_t* streams);
+/* Sharded unpack / repack: packed[k] and planes[k * nfields + f] live on devices[k];
+ * plane arrays are sharded with the same element ranges as the packed array. */
+int pint_cuda_sharded_unpack(const pint_layout* layout, int is_signed, int ngpu, const int* devices,
+                             const void* const* packed, void* const* planes, int plane_bytes,
+                             const size_t* counts, const pint_stream_t* streams);
+int pint_cuda_sharded_repack(const pint_layout* layout, int ngpu, const int* devices,
+                             const void* const* planes, int plane_bytes, void* const* packed,
+                             const size_t* counts, const pint_stream_t* streams);
+
 /* ---- host-buffer entry points (the end-to-end path) ---- */
 /* Pinned host memory for the calls below (cudaHostAlloc / cudaFreeHost). */
 int pint_cuda_host_alloc(void** ptr, size_t bytes);

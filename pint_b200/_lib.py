@@ -60,6 +60,12 @@ def lib():
             "pint_cuda_plan_shards": (i, [sz, u32, i, C.POINTER(sz), C.POINTER(sz)]),
             "pint_cuda_sharded_binary": (i, [i, LP, i, C.POINTER(i), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp),
                                             C.POINTER(sz), C.POINTER(vp)]),
+            "pint_cuda_sharded_fused_unpack_arith_repack": (i, [i, LP, i, C.POINTER(i), C.POINTER(vp), C.POINTER(vp),
+                                                               C.POINTER(vp), C.POINTER(sz), C.POINTER(vp)]),
+            "pint_cuda_sharded_unpack": (i, [LP, i, i, C.POINTER(i), C.POINTER(vp), C.POINTER(vp), i, C.POINTER(sz),
+                                            C.POINTER(vp)]),
+            "pint_cuda_sharded_repack": (i, [LP, i, C.POINTER(i), C.POINTER(vp), i, C.POINTER(vp), C.POINTER(sz),
+                                            C.POINTER(vp)]),
             "pint_cuda_host_alloc": (i, [C.POINTER(vp), sz]),
             "pint_cuda_host_free": (i, [vp]),
             "pint_cuda_binary_host": (i, [i, LP, vp, vp, vp, sz]),

@@ -222,6 +222,55 @@ int pint_cuda_sharded_binary(int op, const pint_layout* layout, int ngpu, const 
     return rc;
 }
 
+int pint_cuda_sharded_fused_unpack_arith_repack(int op, const pint_layout* layout, int ngpu, const int* devices,
+                                                const void* const* a, const void* const* b, void* const* out,
+                                                const size_t* counts, const pint_stream_t* streams)
+{
+    if (ngpu < 1 || !devices || !a || !b || !out || !counts) return PINT_E_ARG;
+    int prev = 0;
+    if (cudaError_t e = cudaGetDevice(&prev)) return (int)e;
+    int rc = PINT_OK;
+    for (int k = 0; k < ngpu && rc == PINT_OK; ++k) {
+        if (cudaError_t e = cudaSetDevice(devices[k])) { rc = (int)e; break; }
+        rc = binary_impl(op, true, layout, a[k], b[k], out[k], counts[k], streams ? (cudaStream_t)streams[k] : nullptr);
+    }
+    cudaSetDevice(prev);
+    return rc;
+}
+
+int pint_cuda_sharded_unpack(const pint_layout* layout, int is_signed, int ngpu, const int* devices,
+                             const void* const* packed, void* const* planes, int plane_bytes,
+                             const size_t* counts, const pint_stream_t* streams)
+{
+    if (ngpu < 1 || !devices || !packed || !planes || !counts || !layout) return PINT_E_ARG;
+    int prev = 0;
+    if (cudaError_t e = cudaGetDevice(&prev)) return (int)e;
+    int rc = PINT_OK;
+    for (int k = 0; k < ngpu && rc == PINT_OK; ++k) {
+        if (cudaError_t e = cudaSetDevice(devices[k])) { rc = (int)e; break; }
+        rc = pint_cuda_unpack(layout, is_signed, packed[k], planes + (size_t)k * layout->nfields, plane_bytes, counts[k],
+                              streams ? streams[k] : nullptr);
+    }
+    cudaSetDevice(prev);
+    return rc;
+}
+
+int pint_cuda_sharded_repack(const pint_layout* layout, int ngpu, const int* devices, const void* const* planes,
+                             int plane_bytes, void* const* packed, const size_t* counts, const pint_stream_t* streams)
+{
+    if (ngpu < 1 || !devices || !packed || !planes || !counts || !layout) return PINT_E_ARG;
+    int prev = 0;
+    if (cudaError_t e = cudaGetDevice(&prev)) return (int)e;
+    int rc = PINT_OK;
+    for (int k = 0; k < ngpu && rc == PINT_OK; ++k) {
+        if (cudaError_t e = cudaSetDevice(devices[k])) { rc = (int)e; break; }
+        rc = pint_cuda_repack(layout, planes + (size_t)k * layout->nfields, plane_bytes, packed[k], counts[k],
+                              streams ? streams[k] : nullptr);
+    }
+    cudaSetDevice(prev);
+    return rc;
+}
+
 int pint_cuda_host_alloc(void** ptr, size_t bytes)
 {
     if (!ptr) return PINT_E_NULL;

@@ -28,9 +28,10 @@ def shard_range(n, elem_bytes, world_size, rank):
     return plan_shards(n, elem_bytes, world_size)[rank]
 
 
-def sharded_binary(op, layout, a_shards, b_shards, out_shards, streams=None):
+def sharded_binary(op, layout, a_shards, b_shards, out_shards, streams=None, fused=False):
     """Launch `op` on every device's shard (tensors already resident on their devices).
-    Asynchronous; synchronise the devices (or streams) afterwards."""
+    Asynchronous; synchronise the devices (or streams) afterwards.  fused=True runs the
+    fused unpack->arith->repack kernel (config C4)."""
     k = len(a_shards)
     devices = (C.c_int * k)(*[t.device.index for t in a_shards])
     counts = (C.c_size_t * k)()
@@ -43,6 +44,45 @@ def sharded_binary(op, layout, a_shards, b_shards, out_shards, streams=None):
             ps[i] = streams[i].cuda_stream
         else:
             ps[i] = torch.cuda.current_stream(a_shards[i].device).cuda_stream
-    _lib.check(_lib.lib().pint_cuda_sharded_binary(OP_CODE[op], layout.ref, k, devices, pa, pb, po, counts, ps),
-               "pint_cuda_sharded_binary")
+    f = _lib.lib().pint_cuda_sharded_fused_unpack_arith_repack if fused else _lib.lib().pint_cuda_sharded_binary
+    _lib.check(f(OP_CODE[op], layout.ref, k, devices, pa, pb, po, counts, ps), "pint_cuda_sharded_binary")
     return out_shards
+
+
+def _stream_array(tensors, streams):
+    ps = (C.c_void_p * len(tensors))()
+    for i, t in enumerate(tensors):
+        ps[i] = streams[i].cuda_stream if streams is not None else torch.cuda.current_stream(t.device).cuda_stream
+    return ps
+
+
+def sharded_unpack(layout, packed_shards, plane_shards, signed=True, streams=None):
+    """plane_shards[k][f] (on packed_shards[k]'s device) = field f of shard k; same element ranges."""
+    k, nf = len(packed_shards), layout.nfields
+    pb = plane_shards[0][0].element_size()
+    devices = (C.c_int * k)(*[t.device.index for t in packed_shards])
+    counts = (C.c_size_t * k)(*[_check(layout, t) for t in packed_shards])
+    pp = (C.c_void_p * k)(*[t.data_ptr() for t in packed_shards])
+    planes = (C.c_void_p * (k * nf))()
+    for i in range(k):
+        for f in range(nf):
+            p = plane_shards[i][f]
+            planes[i * nf + f] = None if p is None else p.data_ptr()
+    _lib.check(_lib.lib().pint_cuda_sharded_unpack(layout.ref, int(bool(signed)), k, devices, pp, planes, pb, counts,
+                                                   _stream_array(packed_shards, streams)), "pint_cuda_sharded_unpack")
+    return plane_shards
+
+
+def sharded_repack(layout, plane_shards, packed_shards, streams=None):
+    k, nf = len(packed_shards), layout.nfields
+    pb = plane_shards[0][0].element_size()
+    devices = (C.c_int * k)(*[t.device.index for t in packed_shards])
+    counts = (C.c_size_t * k)(*[_check(layout, t) for t in packed_shards])
+    pp = (C.c_void_p * k)(*[t.data_ptr() for t in packed_shards])
+    planes = (C.c_void_p * (k * nf))()
+    for i in range(k):
+        for f in range(nf):
+            planes[i * nf + f] = plane_shards[i][f].data_ptr()
+    _lib.check(_lib.lib().pint_cuda_sharded_repack(layout.ref, k, devices, planes, pb, pp, counts,
+                                                   _stream_array(packed_shards, streams)), "pint_cuda_sharded_repack")
+    return packed_shards

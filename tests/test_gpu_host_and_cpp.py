@@ -78,6 +78,38 @@ def test_sharded_binary_single_process(oracle):
     np.testing.assert_array_equal(got, oracle.binary("sub_signed_saturate", 8, (16, 16, 16, 16), a_h, b_h))
 
 
+def test_sharded_fused_unpack_repack(oracle):
+    """C4's shape: the fused kernel and unpack/repack over per-device shards (round-robin over the visible devices)."""
+    import pint_b200
+    from pint_b200 import sharded
+    bits = (3, 7, 11, 13, 17, 13)
+    L = pint_b200.Layout(8, *bits)
+    n = (1 << 19) + 77
+    ndev = torch.cuda.device_count()
+    k = max(3, ndev)
+    plan = sharded.plan_shards(n, 8, k)
+    a_h, b_h = oracle.fill(8, n, 51), oracle.fill(8, n, 52)
+    a_s, b_s, o_s, p_s = [], [], [], []
+    for i, (beg, cnt) in enumerate(plan):
+        dev = f"cuda:{i % ndev}"
+        a_s.append(to_dev(a_h[beg:beg + cnt]).to(dev))
+        b_s.append(to_dev(b_h[beg:beg + cnt]).to(dev))
+        o_s.append(torch.empty_like(a_s[-1]))
+        p_s.append([torch.empty(cnt, dtype=torch.int32, device=dev) for _ in bits])
+    sharded.sharded_binary("add_signed_saturate", L, a_s, b_s, o_s, fused=True)
+    sharded.sharded_unpack(L, o_s, p_s, signed=True)
+    back = [torch.empty_like(o) for o in o_s]
+    sharded.sharded_repack(L, p_s, back)
+    for d in range(ndev):
+        torch.cuda.synchronize(d)
+    want = oracle.binary("add_signed_saturate", 8, bits, a_h, b_h)
+    np.testing.assert_array_equal(np.concatenate([to_np(o) for o in o_s]), want)
+    np.testing.assert_array_equal(np.concatenate([to_np(o) for o in back]), want)
+    wp = oracle.unpack(8, bits, want, True, 4)
+    for f in range(len(bits)):
+        np.testing.assert_array_equal(np.concatenate([to_np(p[f], np.int32) for p in p_s]), wp[f])
+
+
 def test_persistent_grid_option_gives_same_results(oracle):
     import pint_b200
     from pint_b200 import ops
