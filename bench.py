@@ -4,8 +4,10 @@
 Workload (config C1, the one BASELINE.json's target is quoted on for 1 GPU):
   add_unsigned_saturate + add_signed_saturate over 2^30
   packed_int<uint32_t,8,8,8,8> (RGBA8) per GPU.  One "step" = one pass of each
-  op over the batch = 2 kernel launches, 2 * 2^30 packed elements processed,
-  2 * 12 * 2^30 algorithmic bytes (two 4-byte reads + one 4-byte write per element).
+  op over the batch, 2 * 2^30 packed elements processed.  The step is ONE launch of
+  pint_cuda_binary_multi: a and b are read once and both results are written
+  (16 algorithmic bytes per element instead of 2 * 12); the two-launch form is
+  timed beside it and reported as "separate_passes".
   N > 1: every rank owns an independent contiguous shard of the same size (weak
   scaling, no collective on the data path -- nothing reduces).
 
@@ -166,7 +168,7 @@ def run_reference_arm(args, rank):
 def workload_config(args, world, sample_log2=None):
     cfg = {
         "workload": "C1: add_unsigned_saturate + add_signed_saturate over 2^%d packed_int<uint32_t,8,8,8,8> per GPU, "
-                    "one pass of each op per step" % args.log2,
+                    "both ops per step (one pint_cuda_binary_multi launch: a,b read once, two outputs)" % args.log2,
         "layout": "packed_int<uint32_t,8,8,8,8>", "elements_per_gpu": 1 << args.log2,
         "elements_per_step": len(OPS) * (1 << args.log2) * world, "bytes_per_element": BYTES_PER_ELEM,
         "parallelism": "%d independent contiguous shard(s), no collective" % world,
@@ -230,13 +232,33 @@ def main():
     begin, count = sharded.shard_range(n * world, ELEM_BYTES, world, rank)
     a = torch.empty(count, dtype=torch.uint32, device=dev)
     b = torch.empty(count, dtype=torch.uint32, device=dev)
-    out = torch.empty(count, dtype=torch.uint32, device=dev)
+    outs = [torch.empty(count, dtype=torch.uint32, device=dev) for _ in OPS]
+    out = outs[-1]
     ops.fill_splitmix(a, 0x5EED0001, start=begin)
     ops.fill_splitmix(b, 0x5EED0002, start=begin)
 
+    def step_separate():
+        for op, o in zip(OPS, outs):
+            ops.binary(op, L, a, b, out=o)
+
     def step():
-        for op in OPS:
-            ops.binary(op, L, a, b, out=out)
+        # both ops of the step in ONE pass over a and b (pint_cuda_binary_multi): 2 reads + 2 writes per element
+        ops.binary_multi(OPS, L, a, b, outs=outs)
+
+    def timed_region(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        return max_over_ranks(e0.elapsed_time(e1))
+
+    # reference point: the same step as two separate kernel passes (3W bytes per element each)
+    for _ in range(args.warmup):
+        step_separate()
+    ms_separate = timed_region(step_separate, args.steps)
 
     for _ in range(args.warmup):
         step()
@@ -255,14 +277,17 @@ def main():
     ms = max_over_ranks(ev0.elapsed_time(ev1))
     total_elems = len(OPS) * args.steps * n * world
     value = total_elems / (ms * 1e-3)
-    # dominant (only) kernel in the timed region: binary_stream_kernel, one launch per op pass
-    per_launch_s = (ms * 1e-3) / (args.steps * len(OPS))
-    achieved = BYTES_PER_ELEM * count / per_launch_s / 1e9
+    # dominant (only) kernel in the timed region: binary_multi_stream_kernel, one launch per step;
+    # algorithmic bytes per launch: read a and b once, write one result per op
+    per_launch_s = (ms * 1e-3) / args.steps
+    multi_bytes_per_elem = (2 + len(OPS)) * ELEM_BYTES
+    achieved = multi_bytes_per_elem * count / per_launch_s / 1e9
+    separate_gbs = len(OPS) * BYTES_PER_ELEM * count / (ms_separate * 1e-3 / args.steps) / 1e9
     peak, peak_src = measured_peak()
     traffic = None
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            traffic = json.load(f).get("binary_stream_kernel_dram_bytes_per_launch")
+            traffic = json.load(f).get("binary_multi_stream_kernel_dram_bytes_per_launch")
     except Exception:
         pass
 
@@ -313,7 +338,8 @@ def main():
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         v, kind, cores, best = cpu_reference_run(1 << args.cpu_log2, reps=5)
-        cpu = {"value": v, "unit": "elements/s", "cores": cores, "kind": kind,
+        v1, _, _, best1 = cpu_reference_run(1 << max(args.cpu_log2 - 2, 20), reps=3, threads=1)
+        cpu = {"value": v, "unit": "elements/s", "cores": cores, "kind": kind, "single_thread_value": v1,
                "sample": f"{'+'.join(OPS)} over 2^{args.cpu_log2} elements (best of 5, {best:.3f} s per pass pair), "
                          f"out[i]=op(a[i],b[i]) loop of tests/pint_bench.cpp:90-94 over SoA arrays"}
 
@@ -324,9 +350,14 @@ def main():
             "vs_baseline": None, "dtype": "u32", "data": "synthetic",
             "config": workload_config(args, world),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "kernel": "binary_stream_kernel<swar_fn<op, static RGBA8 masks>>",
+                         "traffic": traffic, "kernel": "binary_multi_stream_kernel<static RGBA8 masks> (both ops, one pass)",
                          "peak_source": peak_src, "frac_of_spec_8000": achieved / 8000.0,
-                         "algorithmic_bytes_per_launch": BYTES_PER_ELEM * count},
+                         "algorithmic_bytes_per_launch": multi_bytes_per_elem * count,
+                         "algorithmic_bytes_per_element": multi_bytes_per_elem},
+            "separate_passes": {"value": len(OPS) * args.steps * n * world / (ms_separate * 1e-3), "unit": "elements/s",
+                                "ms_per_step": ms_separate / args.steps, "achieved_gbs": separate_gbs,
+                                "frac": separate_gbs / peak,
+                                "note": "same step as two pint_cuda_binary launches (12 B/element each)"},
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches) * world, "clocks": clocks,
             "hbm_gbs_whole_job": achieved * world, "out_checksum": list(chk),
         }

@@ -235,6 +235,21 @@ inline void binary(pint_op op, int ngpu, const int* devices, const packed_int<In
           "pint::cuda::sharded::binary");
 }
 
+// config C4's shape: the fused unpack -> arithmetic -> repack kernel on every device's shard
+template <class Integer, size_t Bits0, size_t... Bits>
+inline void fused_unpack_arith_repack(pint_op op, int ngpu, const int* devices,
+                                      const packed_int<Integer, Bits0, Bits...>* const* a,
+                                      const packed_int<Integer, Bits0, Bits...>* const* b,
+                                      packed_int<Integer, Bits0, Bits...>* const* out, const size_t* counts,
+                                      const stream_t* streams = nullptr)
+{
+    const pint_layout l = detail::layout_of<Integer, Bits0, Bits...>::get();
+    check(pint_cuda_sharded_fused_unpack_arith_repack(op, &l, ngpu, devices, reinterpret_cast<const void* const*>(a),
+                                                      reinterpret_cast<const void* const*>(b),
+                                                      reinterpret_cast<void* const*>(out), counts, streams),
+          "pint::cuda::sharded::fused_unpack_arith_repack");
+}
+
 }  // namespace sharded
 
 }  // namespace cuda

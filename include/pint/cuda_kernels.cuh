@@ -264,4 +264,5 @@ __device__ __forceinline__ Word apply_unary(Word v, const unary_params<Word>& u)
 }  // namespace pint
 
 #include "cuda_kernels_stream.cuh"
+#include "cuda_kernels_multi.cuh"
 #include "cuda_kernels_planes.cuh"

@@ -110,6 +110,13 @@ int pint_cuda_slice_layout(const pint_layout* layout, uint32_t start, uint32_t e
 /* out[i] = OP(a[i], b[i]); array form of the pint_op templates above. */
 int pint_cuda_binary(int op, const pint_layout* layout, const void* a, const void* b, void* out,
                      size_t n, pint_stream_t stream);
+/* outs[j][i] = ops[j](a[i], b[i]) for nops (1..PINT_MAX_MULTI_OPS) operations on the SAME
+ * operands in ONE pass: a and b are read once, every result is written
+ * ((2 + nops) * sizeof(Integer) bytes per element instead of nops * 3).  `outs` is a HOST
+ * array of device pointers; outputs must not overlap the inputs or each other. */
+#define PINT_MAX_MULTI_OPS 4
+int pint_cuda_binary_multi(int nops, const int* ops, const pint_layout* layout, const void* a, const void* b,
+                           void* const* outs, size_t n, pint_stream_t stream);
 /* Same function computed as unpack -> per-field arithmetic -> repack inside one
  * kernel (planes in registers); bit-identical to pint_cuda_binary. */
 int pint_cuda_fused_unpack_arith_repack(int op, const pint_layout* layout, const void* a, const void* b,

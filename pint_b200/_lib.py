@@ -50,6 +50,7 @@ def lib():
             "pint_cuda_slice_layout": (i, [LP, u32, u32, LP]),
             "pint_cuda_binary": (i, [i, LP, vp, vp, vp, sz, vp]),
             "pint_cuda_fused_unpack_arith_repack": (i, [i, LP, vp, vp, vp, sz, vp]),
+            "pint_cuda_binary_multi": (i, [i, C.POINTER(i), LP, vp, vp, C.POINTER(vp), sz, vp]),
             "pint_cuda_shift": (i, [i, LP, u64, vp, vp, sz, vp]),
             "pint_cuda_slice": (i, [LP, u32, u32, vp, vp, sz, vp]),
             "pint_cuda_unpack": (i, [LP, i, vp, C.POINTER(vp), i, sz, vp]),

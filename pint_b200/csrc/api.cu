@@ -111,6 +111,41 @@ int binary_impl(int op, bool fused, const pint_layout* layout, const void* a, co
     return (int)generic_binary(op, fused, d, a, b, out, n, s, g);
 }
 
+int binary_multi_impl(int nops, const int* ops, const pint_layout* layout, const void* a, const void* b,
+                      void* const* outs, size_t n, cudaStream_t s)
+{
+    layout_desc d;
+    if (int rc = check_layout(layout, &d)) return rc;
+    if (nops < 1 || nops > pint::cuda::kernels::kMaxMultiOps || !ops || !outs) return PINT_E_ARG;
+    pint::cuda::kernels::multi_ops m{};
+    m.nops = nops;
+    for (int j = 0; j < nops; ++j) {
+        if (ops[j] < 0 || ops[j] >= PINT_NUM_BINARY_OPS) return PINT_E_OP;
+        m.op[j] = ops[j];
+        m.out[j] = outs[j];
+    }
+    if (n == 0) return PINT_OK;
+    if (!a || !b) return PINT_E_NULL;
+    const size_t bytes = n * d.elem_bytes;
+    for (int j = 0; j < nops; ++j) {
+        if (!outs[j]) return PINT_E_NULL;
+        if ((uintptr_t)outs[j] % d.elem_bytes) return PINT_E_ARG;
+        // every input vector is read once and then each output is written: outputs must not
+        // overlap the inputs or each other at all
+        auto overlaps = [&](const void* x) {
+            const uintptr_t i = (uintptr_t)x, o = (uintptr_t)outs[j];
+            return i < o + bytes && o < i + bytes;
+        };
+        if (overlaps(a) || overlaps(b)) return PINT_E_ALIAS;
+        for (int k = 0; k < j; ++k)
+            if (overlaps(outs[k])) return PINT_E_ALIAS;
+    }
+    if (((uintptr_t)a | (uintptr_t)b) % d.elem_bytes) return PINT_E_ARG;
+    const launch_geom g = geom();
+    if (const layout_kernels* k = find_static(d)) return (int)k->multi(a, b, m, n, s, g);
+    return (int)generic_binary_multi(d, a, b, m, n, s, g);
+}
+
 template <class Elem>
 cudaError_t unary_launch(const void* in, void* out, size_t n, uint64_t pre, uint64_t post, uint32_t amount, bool left,
                          cudaStream_t s)
@@ -240,6 +275,12 @@ int pint_cuda_binary(int op, const pint_layout* layout, const void* a, const voi
                      pint_stream_t stream)
 {
     return binary_impl(op, false, layout, a, b, out, n, (cudaStream_t)stream);
+}
+
+int pint_cuda_binary_multi(int nops, const int* ops, const pint_layout* layout, const void* a, const void* b,
+                           void* const* outs, size_t n, pint_stream_t stream)
+{
+    return binary_multi_impl(nops, ops, layout, a, b, outs, n, (cudaStream_t)stream);
 }
 
 int pint_cuda_fused_unpack_arith_repack(int op, const pint_layout* layout, const void* a, const void* b, void* out,

@@ -364,11 +364,13 @@ extern "C" int pint_cuda_binary_multi_host(int nops, const int* ops, const pint_
         // stream order makes the slot's previous D2H copies finish before its buffers are overwritten
         if (cudaError_t e = cudaMemcpyAsync(r->buf[slot][0], pa + off, bytes, cudaMemcpyHostToDevice, s)) { rc = (int)e; break; }
         if (cudaError_t e = cudaMemcpyAsync(r->buf[slot][1], pb + off, bytes, cudaMemcpyHostToDevice, s)) { rc = (int)e; break; }
-        for (int j = 0; j < nops && rc == PINT_OK; ++j) {
-            rc = binary_impl(ops[j], false, layout, r->buf[slot][0], r->buf[slot][1], r->buf[slot][2 + j], cnt, s);
-            if (rc != PINT_OK) break;
-            if (cudaError_t e = cudaMemcpyAsync((char*)outs_host[j] + off, r->buf[slot][2 + j], bytes, cudaMemcpyDeviceToHost, s)) rc = (int)e;
+        {
+            void* douts[PINT_MAX_HOST_OPS];
+            for (int j = 0; j < nops; ++j) douts[j] = r->buf[slot][2 + j];
+            rc = binary_multi_impl(nops, ops, layout, r->buf[slot][0], r->buf[slot][1], douts, cnt, s);  // one pass for all ops
         }
+        for (int j = 0; j < nops && rc == PINT_OK; ++j)
+            if (cudaError_t e = cudaMemcpyAsync((char*)outs_host[j] + off, r->buf[slot][2 + j], bytes, cudaMemcpyDeviceToHost, s)) rc = (int)e;
         done += cnt;
     }
     for (int i = 0; i < r->slots; ++i) {

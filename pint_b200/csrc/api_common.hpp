@@ -24,6 +24,8 @@ int check_layout(const pint_layout* l, layout_desc* d);
 int current_sms();
 launch_geom geom();
 const layout_kernels* find_static(const layout_desc& d);
+int binary_multi_impl(int nops, const int* ops, const pint_layout* layout, const void* a, const void* b,
+                      void* const* outs, size_t n, cudaStream_t s);
 int binary_impl(int op, bool fused, const pint_layout* layout, const void* a, const void* b, void* out, size_t n,
                 cudaStream_t s);
 

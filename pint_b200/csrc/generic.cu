@@ -71,6 +71,17 @@ cudaError_t generic_binary(int op, bool fused, const layout_desc& d, const void*
     }
 }
 
+cudaError_t generic_binary_multi(const layout_desc& d, const void* a, const void* b, const multi_ops& m, size_t n,
+                                 cudaStream_t s, const launch_geom& g)
+{
+    switch (d.elem_bytes) {
+    case 1: return launch_binary_multi<uint8_t>(a, b, m, n, runtime_masks<uint32_t>(make_word_masks<uint32_t>(d)), s, g);
+    case 2: return launch_binary_multi<uint16_t>(a, b, m, n, runtime_masks<uint32_t>(make_word_masks<uint32_t>(d)), s, g);
+    case 4: return launch_binary_multi<uint32_t>(a, b, m, n, runtime_masks<uint32_t>(make_word_masks<uint32_t>(d)), s, g);
+    default: return launch_binary_multi<uint64_t>(a, b, m, n, runtime_masks<uint64_t>(make_word_masks<uint64_t>(d)), s, g);
+    }
+}
+
 cudaError_t generic_unpack(const layout_desc& d, bool is_signed, int plane_bytes, const void* packed,
                            const plane_ptrs& planes, size_t n, cudaStream_t s, const launch_geom& g)
 {

@@ -26,6 +26,12 @@ cudaError_t fused_entry(const void* a, const void* b, void* out, size_t n, cudaS
     return launch_binary<typename SL::integer, Fn>(a, b, out, n, Fn{}, s, g);
 }
 
+template <class SL>
+cudaError_t multi_entry(const void* a, const void* b, const multi_ops& m, size_t n, cudaStream_t s, const launch_geom& g)
+{
+    return launch_binary_multi<typename SL::integer>(a, b, m, n, static_masks<SL>{}, s, g);
+}
+
 template <class SL, bool Signed, int PB>
 cudaError_t unpack_entry(const void* packed, const plane_ptrs& planes, size_t n, cudaStream_t s, const launch_geom& g)
 {
@@ -45,6 +51,7 @@ layout_kernels make_kernels(std::integer_sequence<int, Ops...>)
     k.desc = SL::desc;
     ((k.binary[Ops] = &binary_entry<SL, Ops>), ...);
     ((k.fused[Ops] = &fused_entry<SL, Ops>), ...);
+    k.multi = &multi_entry<SL>;
     k.unpack[0][0] = &unpack_entry<SL, false, 4>;
     k.unpack[0][1] = &unpack_entry<SL, false, 8>;
     k.unpack[1][0] = &unpack_entry<SL, true, 4>;

@@ -69,6 +69,21 @@ def binary(op, layout, a, b, out=None, stream=None, fused=False):
     return out
 
 
+def binary_multi(op_list, layout, a, b, outs=None, stream=None):
+    """outs[j] = op_list[j](a, b) for up to 4 ops in ONE pass over a and b (pint_cuda_binary_multi)."""
+    if outs is None:
+        outs = [torch.empty_like(a) for _ in op_list]
+    n = _check(layout, a, b, *outs)
+    if len(outs) != len(op_list):
+        raise ValueError("need one output per op")
+    codes = (C.c_int * len(op_list))(*[OP_CODE[o] if isinstance(o, str) else int(o) for o in op_list])
+    ptrs = _plane_array([o.data_ptr() for o in outs])
+    with torch.cuda.device(a.device):
+        _lib.check(_lib.lib().pint_cuda_binary_multi(len(op_list), codes, layout.ref, a.data_ptr(), b.data_ptr(), ptrs, n,
+                                                     _stream(stream)), "pint_cuda_binary_multi")
+    return outs
+
+
 def _make_binary(name):
     def fn(layout, a, b, out=None, stream=None):
         return binary(name, layout, a, b, out=out, stream=stream)

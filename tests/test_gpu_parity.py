@@ -200,6 +200,32 @@ def test_oracle_differential_ragged(P, oracle, eb, bits, mode):
         np.testing.assert_array_equal(to_np(ops.shift_right_unsigned(L, x, amt)), oracle.shift(0, eb, bits, amt, a_h))
 
 
+def test_binary_multi_one_pass(P, oracle, mode):
+    """Several ops on the same operands in one kernel == the ops run one by one."""
+    import ctypes as C
+    pint_b200, ops = P
+    for eb, bits in [(4, (8, 8, 8, 8)), (2, (5, 6, 5)), (8, (3, 7, 11, 13, 17, 13)), (1, (2, 3, 3)), (4, (7, 9, 3))]:
+        L = pint_b200.Layout(eb, *bits)
+        for n, off in ((1 << 20) + 13, 0), (4099, 1), (3, 0):
+            a_h, b_h = oracle.fill(eb, n, 61), oracle.fill(eb, n, 62)
+            a, b = to_dev(a_h, off), to_dev(b_h, off)
+            for op_list in (["add_unsigned_saturate", "add_signed_saturate"], list(OPS[:4]), ["max_signed"], ["bit_xor", "sub_signed_saturate", "min_unsigned"]):
+                outs = [to_dev(np.zeros(n, dtype=a_h.dtype), off) for _ in op_list]
+                ops.binary_multi(op_list, L, a, b, outs=outs)
+                for op, o in zip(op_list, outs):
+                    np.testing.assert_array_equal(to_np(o), oracle.binary(op, eb, bits, a_h, b_h), err_msg=f"{L} {op} n={n} {mode}")
+    L = pint_b200.Layout(4, 8, 8, 8, 8)
+    x = torch.zeros(64, dtype=torch.int32, device="cuda")
+    y = torch.zeros(64, dtype=torch.int32, device="cuda")
+    from pint_b200 import _lib
+    codes = (C.c_int * 2)(1, 2)
+    outs = (C.c_void_p * 2)(x.data_ptr(), y.data_ptr())
+    # an output may not overlap an input or another output
+    assert _lib.lib().pint_cuda_binary_multi(2, codes, L.ref, x.data_ptr(), y.data_ptr(), outs, 64, None) == -14
+    codes5 = (C.c_int * 5)(0, 1, 2, 3, 4)
+    assert _lib.lib().pint_cuda_binary_multi(5, codes5, L.ref, x.data_ptr(), y.data_ptr(), outs, 64, None) == -15
+
+
 def test_small_sizes_and_empty(P, oracle):
     pint_b200, ops = P
     L = pint_b200.Layout(4, 8, 8, 8, 8)
