@@ -1,12 +1,17 @@
-// pint/cuda_kernels_multi.cuh -- several binary ops on the SAME operands in one pass.
+// pint/cuda_kernels_multi.cuh -- two binary ops on the SAME operands in one pass.
 //
-// out_j[i] = op_j(a[i], b[i]) for j < nops (nops <= 4): a and b are read once and
-// every result is written, so a step such as BASELINE.json's C1
+// out0[i] = Op0(a[i], b[i]), out1[i] = Op1(a[i], b[i]): a and b are read once and
+// both results are written, so a step such as BASELINE.json's C1
 // (add_unsigned_saturate + add_signed_saturate over the same arrays) moves
-// (2 + nops) * W bytes per element instead of nops * 3W -- 16 instead of 24 bytes
-// for two ops on uint32 packs.  Same per-element functions as apply_op (the op
-// code is a warp-uniform switch per 16-byte vector), same streaming structure as
-// binary_stream_kernel.  Included by cuda_kernels.cuh.
+// 4W bytes per element instead of 2 * 3W -- 16 instead of 24 bytes on uint32 packs.
+//
+// Both op codes are TEMPLATE parameters.  The first version of this kernel took
+// the op codes at run time (a warp-uniform switch per vector): ptxas kept all 13
+// op bodies live, 115 registers per thread, 21 % of the warps resident, 3.2 TB/s
+// (profiles/r01b_ncu_multi_runtime_switch.txt).  With compile-time ops the kernel
+// is binary_stream_kernel with a second store.  libpint_cuda.so instantiates the
+// pairs of kOpPairs below; pint_cuda_binary_multi decomposes any op list into
+// those pairs plus single-op passes.  Included by cuda_kernels.cuh.
 #pragma once
 
 namespace pint {
@@ -15,69 +20,52 @@ namespace kernels {
 
 constexpr int kMaxMultiOps = 4;
 
-struct multi_ops {
-    int nops;
-    int op[kMaxMultiOps];
-    void* out[kMaxMultiOps];  // device pointers (vector-aligned part is passed separately)
+// op pairs with a one-pass kernel (unordered; the dispatcher swaps the outputs)
+constexpr int kNumOpPairs = 7;
+constexpr int kOpPairs[kNumOpPairs][2] = {
+    {OP_ADD_UNSIGNED_SATURATE, OP_ADD_SIGNED_SATURATE},  // BASELINE.json C1
+    {OP_SUB_UNSIGNED_SATURATE, OP_SUB_SIGNED_SATURATE},
+    {OP_ADD_SIGNED_SATURATE, OP_SUB_SIGNED_SATURATE},    // BASELINE.json C2
+    {OP_ADD_UNSIGNED_SATURATE, OP_SUB_UNSIGNED_SATURATE},
+    {OP_ADD_WRAP, OP_SUB_WRAP},
+    {OP_MIN_UNSIGNED, OP_MAX_UNSIGNED},
+    {OP_MIN_SIGNED, OP_MAX_SIGNED},
 };
 
-// one 16-byte vector through op code `op` (uniform across the grid)
-template <class P>
-__device__ __forceinline__ uint4 apply_op_vec(int op, const uint4& a, const uint4& b, const P& p)
+// index into kOpPairs and whether (x, y) is stored there as (y, x); -1 if the pair has no kernel
+inline int find_op_pair(int x, int y, bool* swapped)
 {
-    using W = typename P::word;
-    switch (op) {
-#define PINT_MULTI_CASE(OP) \
-    case OP: return map_words2<W>(a, b, [&](W x, W y) { return apply_op<OP>(x, y, p); });
-        PINT_MULTI_CASE(OP_ADD_WRAP)
-        PINT_MULTI_CASE(OP_ADD_UNSIGNED_SATURATE)
-        PINT_MULTI_CASE(OP_ADD_SIGNED_SATURATE)
-        PINT_MULTI_CASE(OP_SUB_WRAP)
-        PINT_MULTI_CASE(OP_SUB_UNSIGNED_SATURATE)
-        PINT_MULTI_CASE(OP_SUB_SIGNED_SATURATE)
-        PINT_MULTI_CASE(OP_OR)
-        PINT_MULTI_CASE(OP_AND)
-        PINT_MULTI_CASE(OP_XOR)
-        PINT_MULTI_CASE(OP_MIN_UNSIGNED)
-        PINT_MULTI_CASE(OP_MAX_UNSIGNED)
-        PINT_MULTI_CASE(OP_MIN_SIGNED)
-    default:
-        PINT_MULTI_CASE(OP_MAX_SIGNED)
-#undef PINT_MULTI_CASE
+    for (int i = 0; i < kNumOpPairs; ++i) {
+        if (kOpPairs[i][0] == x && kOpPairs[i][1] == y) { *swapped = false; return i; }
+        if (kOpPairs[i][0] == y && kOpPairs[i][1] == x) { *swapped = true; return i; }
     }
+    return -1;
 }
 
-template <class P>
-__device__ __forceinline__ typename P::word apply_op_word(int op, typename P::word a, typename P::word b, const P& p)
-{
-    switch (op) {
-    case OP_ADD_WRAP: return apply_op<OP_ADD_WRAP>(a, b, p);
-    case OP_ADD_UNSIGNED_SATURATE: return apply_op<OP_ADD_UNSIGNED_SATURATE>(a, b, p);
-    case OP_ADD_SIGNED_SATURATE: return apply_op<OP_ADD_SIGNED_SATURATE>(a, b, p);
-    case OP_SUB_WRAP: return apply_op<OP_SUB_WRAP>(a, b, p);
-    case OP_SUB_UNSIGNED_SATURATE: return apply_op<OP_SUB_UNSIGNED_SATURATE>(a, b, p);
-    case OP_SUB_SIGNED_SATURATE: return apply_op<OP_SUB_SIGNED_SATURATE>(a, b, p);
-    case OP_OR: return a | b;
-    case OP_AND: return a & b;
-    case OP_XOR: return a ^ b;
-    case OP_MIN_UNSIGNED: return apply_op<OP_MIN_UNSIGNED>(a, b, p);
-    case OP_MAX_UNSIGNED: return apply_op<OP_MAX_UNSIGNED>(a, b, p);
-    case OP_MIN_SIGNED: return apply_op<OP_MIN_SIGNED>(a, b, p);
-    default: return apply_op<OP_MAX_SIGNED>(a, b, p);
-    }
-}
+template <int Op0, int Op1, class P>
+struct pair_fn {
+    using word = typename P::word;
+    static constexpr bool heavy = swar_fn<Op0, P>::heavy || swar_fn<Op1, P>::heavy;
+    P p;
+    __device__ __forceinline__ word first(word a, word b) const { return apply_op<Op0>(a, b, p); }
+    __device__ __forceinline__ word second(word a, word b) const { return apply_op<Op1>(a, b, p); }
+};
 
-// One CTA per tile (or grid stride when the grid is capped), UNROLL vectors per
-// operand per thread; the outputs of one vector are produced one op at a time so
-// that only the inputs stay live in registers.
-template <class P, class Cfg>
+// Same structure as binary_stream_kernel: one CTA per tile (grid stride when the
+// grid is capped), all 2 * UNROLL loads issued before the first use, two
+// streaming stores per input vector pair.
+template <class Fn, class Cfg>
 __global__ void __launch_bounds__(Cfg::BLOCK)
-binary_multi_stream_kernel(const uint4* a, const uint4* b, size_t nvec, const __grid_constant__ multi_ops m,
-                           const __grid_constant__ P p)
+binary_pair_stream_kernel(const uint4* a, const uint4* b, uint4* out0, uint4* out1, size_t nvec,
+                          const __grid_constant__ Fn fn)
 {
+    using W = typename Fn::word;
     constexpr int U = Cfg::UNROLL, B = Cfg::BLOCK;
     constexpr size_t tile = size_t(U) * B;
     const size_t nfull = nvec / tile;
+    auto f0 = [&](W x, W y) { return fn.first(x, y); };
+    auto f1 = [&](W x, W y) { return fn.second(x, y); };
+
     for (size_t t = blockIdx.x; t < nfull; t += gridDim.x) {
         const size_t base = t * tile + threadIdx.x;
         uint4 va[U], vb[U];
@@ -85,71 +73,54 @@ binary_multi_stream_kernel(const uint4* a, const uint4* b, size_t nvec, const __
         for (int u = 0; u < U; ++u) va[u] = ld16<Cfg::LD>(a + base + size_t(u) * B);
 #pragma unroll
         for (int u = 0; u < U; ++u) vb[u] = ld16<Cfg::LD>(b + base + size_t(u) * B);
-        for (int j = 0; j < m.nops; ++j) {
-            uint4* out = static_cast<uint4*>(m.out[j]);
-            const int op = m.op[j];
 #pragma unroll
-            for (int u = 0; u < U; ++u) st16<Cfg::ST>(out + base + size_t(u) * B, apply_op_vec(op, va[u], vb[u], p));
+        for (int u = 0; u < U; ++u) {
+            st16<Cfg::ST>(out0 + base + size_t(u) * B, map_words2<W>(va[u], vb[u], f0));
+            st16<Cfg::ST>(out1 + base + size_t(u) * B, map_words2<W>(va[u], vb[u], f1));
         }
     }
     if (blockIdx.x == nfull % gridDim.x) {
         for (size_t i = nfull * tile + threadIdx.x; i < nvec; i += B) {
             const uint4 x = ld16<Cfg::LD>(a + i), y = ld16<Cfg::LD>(b + i);
-            for (int j = 0; j < m.nops; ++j)
-                st16<Cfg::ST>(static_cast<uint4*>(m.out[j]) + i, apply_op_vec(m.op[j], x, y, p));
+            st16<Cfg::ST>(out0 + i, map_words2<W>(x, y, f0));
+            st16<Cfg::ST>(out1 + i, map_words2<W>(x, y, f1));
         }
     }
 }
 
-template <class Elem, class P>
-__global__ void __launch_bounds__(256)
-binary_multi_elem_kernel(const Elem* a, const Elem* b, size_t n, const __grid_constant__ multi_ops m,
-                         const __grid_constant__ P p)
+// The vector body runs the pair kernel; heads, tails and operands with different
+// misalignments go through the single-op launcher (element-granular kernels that
+// the library instantiates anyway).  Outputs must not overlap the inputs or each
+// other (checked at the C ABI).
+template <class Elem, int Op0, int Op1, class P, class Cfg = stream_cfg_for<pair_fn<Op0, Op1, P>>>
+cudaError_t launch_binary_pair(const void* a, const void* b, void* out0, void* out1, size_t n, const P& p,
+                               cudaStream_t stream, const launch_geom& g)
 {
-    using W = typename P::word;
-    for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) {
-        const W x = W(a[i]), y = W(b[i]);
-        for (int j = 0; j < m.nops; ++j) static_cast<Elem*>(m.out[j])[i] = Elem(apply_op_word(m.op[j], x, y, p));
-    }
-}
-
-// outs[j] may alias a or b only for the LAST op that reads them... to keep the
-// contract simple the C ABI forbids any overlap between outputs and inputs here.
-template <class Elem, class P, class Cfg = default_stream_cfg>
-cudaError_t launch_binary_multi(const void* a, const void* b, const multi_ops& m, size_t n, const P& p,
-                                cudaStream_t stream, const launch_geom& g)
-{
-    if (n == 0 || m.nops == 0) return cudaSuccess;
+    if (n == 0) return cudaSuccess;
+    using Fn = pair_fn<Op0, Op1, P>;
     const Elem* ea = static_cast<const Elem*>(a);
     const Elem* eb = static_cast<const Elem*>(b);
-    const void* ptrs[2 + kMaxMultiOps] = {a, b};
-    for (int j = 0; j < m.nops; ++j) ptrs[2 + j] = m.out[j];
+    Elem* e0 = static_cast<Elem*>(out0);
+    Elem* e1 = static_cast<Elem*>(out1);
+    auto single = [&](size_t first, size_t count) -> cudaError_t {
+        if (!count) return cudaSuccess;
+        cudaError_t rc = launch_binary<Elem, swar_fn<Op0, P>>(ea + first, eb + first, e0 + first, count, swar_fn<Op0, P>{p}, stream, g);
+        if (rc != cudaSuccess) return rc;
+        return launch_binary<Elem, swar_fn<Op1, P>>(ea + first, eb + first, e1 + first, count, swar_fn<Op1, P>{p}, stream, g);
+    };
+    const void* ptrs[4] = {a, b, out0, out1};
     size_t head = 0, nvec = 0, tail = 0;
-    const bool vec_ok = split_aligned(sizeof(Elem), n, ptrs, 2 + m.nops, &head, &nvec, &tail);
-    auto shifted = [&](size_t first) {
-        multi_ops s = m;
-        for (int j = 0; j < m.nops; ++j) s.out[j] = static_cast<Elem*>(m.out[j]) + first;
-        return s;
-    };
-    auto elems = [&](size_t first, size_t count) {
-        if (!count) return;
-        const unsigned grid = grid_for((count + 255) / 256, g);
-        binary_multi_elem_kernel<Elem, P><<<grid, 256, 0, stream>>>(ea + first, eb + first, count, shifted(first), p);
-        count_launch(g);
-    };
-    if (!vec_ok) {
-        elems(0, n);
-        return cudaGetLastError();
-    }
-    elems(0, head);
+    if (!split_aligned(sizeof(Elem), n, ptrs, 4, &head, &nvec, &tail)) return single(0, n);
+    if (cudaError_t rc = single(0, head)) return rc;
     if (nvec) {
         constexpr size_t tile = size_t(Cfg::UNROLL) * Cfg::BLOCK;
         const size_t ntiles = (nvec + tile - 1) / tile;
-        binary_multi_stream_kernel<P, Cfg><<<grid_for(ntiles, g), Cfg::BLOCK, 0, stream>>>(
-            reinterpret_cast<const uint4*>(ea + head), reinterpret_cast<const uint4*>(eb + head), nvec, shifted(head), p);
+        binary_pair_stream_kernel<Fn, Cfg><<<grid_for(ntiles, g), Cfg::BLOCK, 0, stream>>>(
+            reinterpret_cast<const uint4*>(ea + head), reinterpret_cast<const uint4*>(eb + head),
+            reinterpret_cast<uint4*>(e0 + head), reinterpret_cast<uint4*>(e1 + head), nvec, Fn{p});
         count_launch(g);
     }
-    elems(n - tail, tail);
+    if (cudaError_t rc = single(n - tail, tail)) return rc;
     return cudaGetLastError();
 }
 

@@ -111,8 +111,11 @@ int pint_cuda_slice_layout(const pint_layout* layout, uint32_t start, uint32_t e
 int pint_cuda_binary(int op, const pint_layout* layout, const void* a, const void* b, void* out,
                      size_t n, pint_stream_t stream);
 /* outs[j][i] = ops[j](a[i], b[i]) for nops (1..PINT_MAX_MULTI_OPS) operations on the SAME
- * operands in ONE pass: a and b are read once, every result is written
- * ((2 + nops) * sizeof(Integer) bytes per element instead of nops * 3).  `outs` is a HOST
+ * operands.  Op pairs that have a one-pass kernel (add_unsigned+add_signed saturate,
+ * sub_unsigned+sub_signed saturate, add_signed+sub_signed saturate, add_unsigned+sub_unsigned
+ * saturate, add_wrap+sub_wrap, min+max unsigned, min+max signed; either order) read a and b
+ * once and write both results: 4 * sizeof(Integer) bytes per element instead of 6.  Other
+ * ops of the list run as single passes; results are identical either way.  `outs` is a HOST
  * array of device pointers; outputs must not overlap the inputs or each other. */
 #define PINT_MAX_MULTI_OPS 4
 int pint_cuda_binary_multi(int nops, const int* ops, const pint_layout* layout, const void* a, const void* b,

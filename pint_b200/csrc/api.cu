@@ -117,8 +117,7 @@ int binary_multi_impl(int nops, const int* ops, const pint_layout* layout, const
     layout_desc d;
     if (int rc = check_layout(layout, &d)) return rc;
     if (nops < 1 || nops > pint::cuda::kernels::kMaxMultiOps || !ops || !outs) return PINT_E_ARG;
-    pint::cuda::kernels::multi_ops m{};
-    m.nops = nops;
+    struct { int op[pint::cuda::kernels::kMaxMultiOps]; void* out[pint::cuda::kernels::kMaxMultiOps]; } m{};
     for (int j = 0; j < nops; ++j) {
         if (ops[j] < 0 || ops[j] >= PINT_NUM_BINARY_OPS) return PINT_E_OP;
         m.op[j] = ops[j];
@@ -141,9 +140,29 @@ int binary_multi_impl(int nops, const int* ops, const pint_layout* layout, const
             if (overlaps(outs[k])) return PINT_E_ALIAS;
     }
     if (((uintptr_t)a | (uintptr_t)b) % d.elem_bytes) return PINT_E_ARG;
+    // Decompose the op list into pairs that have a one-pass kernel (kOpPairs) and single-op passes.
     const launch_geom g = geom();
-    if (const layout_kernels* k = find_static(d)) return (int)k->multi(a, b, m, n, s, g);
-    return (int)generic_binary_multi(d, a, b, m, n, s, g);
+    const layout_kernels* k = find_static(d);
+    bool done[pint::cuda::kernels::kMaxMultiOps] = {};
+    for (int j = 0; j < nops; ++j) {
+        if (done[j]) continue;
+        done[j] = true;
+        int rc = -1;
+        for (int i = j + 1; i < nops && rc < 0; ++i) {
+            bool swapped = false;
+            const int pi = done[i] ? -1 : pint::cuda::kernels::find_op_pair(m.op[j], m.op[i], &swapped);
+            if (pi < 0) continue;
+            done[i] = true;
+            void* o0 = swapped ? m.out[i] : m.out[j];
+            void* o1 = swapped ? m.out[j] : m.out[i];
+            rc = k ? (int)k->pair[pi](a, b, o0, o1, n, s, g) : (int)generic_binary_pair(pi, d, a, b, o0, o1, n, s, g);
+        }
+        if (rc < 0)
+            rc = k ? (int)k->binary[m.op[j]](a, b, m.out[j], n, s, g)
+                   : (int)generic_binary(m.op[j], false, d, a, b, m.out[j], n, s, g);
+        if (rc) return rc;
+    }
+    return PINT_OK;
 }
 
 template <class Elem>

@@ -34,6 +34,17 @@ cudaError_t binary_ops(int op, bool fused, const layout_desc& d, const void* a, 
     return rc;
 }
 
+template <class Elem, int... Pairs>
+cudaError_t pair_ops(int pair, const layout_desc& d, const void* a, const void* b, void* out0, void* out1, size_t n,
+                     cudaStream_t s, const launch_geom& g, std::integer_sequence<int, Pairs...>)
+{
+    using W = word_of<Elem>;
+    const runtime_masks<W> p(make_word_masks<W>(d));
+    cudaError_t rc = cudaErrorInvalidValue;
+    ((pair == Pairs ? (rc = launch_binary_pair<Elem, kOpPairs[Pairs][0], kOpPairs[Pairs][1]>(a, b, out0, out1, n, p, s, g), 0) : 0), ...);
+    return rc;
+}
+
 template <class Elem>
 cudaError_t unpack_elem(const layout_desc& d, bool is_signed, int pb, const void* packed, const plane_ptrs& planes,
                         size_t n, cudaStream_t s, const launch_geom& g)
@@ -71,14 +82,15 @@ cudaError_t generic_binary(int op, bool fused, const layout_desc& d, const void*
     }
 }
 
-cudaError_t generic_binary_multi(const layout_desc& d, const void* a, const void* b, const multi_ops& m, size_t n,
-                                 cudaStream_t s, const launch_geom& g)
+cudaError_t generic_binary_pair(int pair, const layout_desc& d, const void* a, const void* b, void* out0, void* out1,
+                                size_t n, cudaStream_t s, const launch_geom& g)
 {
+    auto pairs = std::make_integer_sequence<int, kNumOpPairs>();
     switch (d.elem_bytes) {
-    case 1: return launch_binary_multi<uint8_t>(a, b, m, n, runtime_masks<uint32_t>(make_word_masks<uint32_t>(d)), s, g);
-    case 2: return launch_binary_multi<uint16_t>(a, b, m, n, runtime_masks<uint32_t>(make_word_masks<uint32_t>(d)), s, g);
-    case 4: return launch_binary_multi<uint32_t>(a, b, m, n, runtime_masks<uint32_t>(make_word_masks<uint32_t>(d)), s, g);
-    default: return launch_binary_multi<uint64_t>(a, b, m, n, runtime_masks<uint64_t>(make_word_masks<uint64_t>(d)), s, g);
+    case 1: return pair_ops<uint8_t>(pair, d, a, b, out0, out1, n, s, g, pairs);
+    case 2: return pair_ops<uint16_t>(pair, d, a, b, out0, out1, n, s, g, pairs);
+    case 4: return pair_ops<uint32_t>(pair, d, a, b, out0, out1, n, s, g, pairs);
+    default: return pair_ops<uint64_t>(pair, d, a, b, out0, out1, n, s, g, pairs);
     }
 }
 

@@ -12,7 +12,7 @@ using pint::cuda::kernels::plane_ptrs;
 using pint::cuda::layout_desc;
 
 using binary_launch_t = cudaError_t (*)(const void* a, const void* b, void* out, size_t n, cudaStream_t, const launch_geom&);
-using multi_launch_t = cudaError_t (*)(const void* a, const void* b, const pint::cuda::kernels::multi_ops&, size_t n, cudaStream_t, const launch_geom&);
+using pair_launch_t = cudaError_t (*)(const void* a, const void* b, void* out0, void* out1, size_t n, cudaStream_t, const launch_geom&);
 using unpack_launch_t = cudaError_t (*)(const void* packed, const plane_ptrs&, size_t n, cudaStream_t, const launch_geom&);
 using repack_launch_t = cudaError_t (*)(const plane_ptrs&, void* packed, size_t n, cudaStream_t, const launch_geom&);
 
@@ -20,7 +20,7 @@ struct layout_kernels {
     layout_desc desc;
     binary_launch_t binary[pint::cuda::OP_NUM_BINARY];
     binary_launch_t fused[pint::cuda::OP_NUM_BINARY];
-    multi_launch_t multi;
+    pair_launch_t pair[pint::cuda::kernels::kNumOpPairs];  // one-pass kernels for kOpPairs
     unpack_launch_t unpack[2][2];  // [is_signed][plane_bytes == 8]
     repack_launch_t repack[2];     // [plane_bytes == 8]
 };
@@ -39,8 +39,8 @@ const layout_kernels* registry_part3(int* count);
 // runtime-mask kernels (generic.cu)
 cudaError_t generic_binary(int op, bool fused, const layout_desc& d, const void* a, const void* b, void* out,
                            size_t n, cudaStream_t s, const launch_geom& g);
-cudaError_t generic_binary_multi(const layout_desc& d, const void* a, const void* b,
-                                 const pint::cuda::kernels::multi_ops& m, size_t n, cudaStream_t s, const launch_geom& g);
+cudaError_t generic_binary_pair(int pair, const layout_desc& d, const void* a, const void* b, void* out0, void* out1,
+                                size_t n, cudaStream_t s, const launch_geom& g);
 cudaError_t generic_unpack(const layout_desc& d, bool is_signed, int plane_bytes, const void* packed,
                            const plane_ptrs& planes, size_t n, cudaStream_t s, const launch_geom& g);
 cudaError_t generic_repack(const layout_desc& d, int plane_bytes, const plane_ptrs& planes, void* packed,

@@ -26,10 +26,16 @@ cudaError_t fused_entry(const void* a, const void* b, void* out, size_t n, cudaS
     return launch_binary<typename SL::integer, Fn>(a, b, out, n, Fn{}, s, g);
 }
 
-template <class SL>
-cudaError_t multi_entry(const void* a, const void* b, const multi_ops& m, size_t n, cudaStream_t s, const launch_geom& g)
+template <class SL, int Pair>
+cudaError_t pair_entry(const void* a, const void* b, void* out0, void* out1, size_t n, cudaStream_t s, const launch_geom& g)
 {
-    return launch_binary_multi<typename SL::integer>(a, b, m, n, static_masks<SL>{}, s, g);
+    return launch_binary_pair<typename SL::integer, kOpPairs[Pair][0], kOpPairs[Pair][1]>(a, b, out0, out1, n, static_masks<SL>{}, s, g);
+}
+
+template <class SL, int... Pairs>
+void add_pairs(layout_kernels& k, std::integer_sequence<int, Pairs...>)
+{
+    ((k.pair[Pairs] = &pair_entry<SL, Pairs>), ...);
 }
 
 template <class SL, bool Signed, int PB>
@@ -51,7 +57,7 @@ layout_kernels make_kernels(std::integer_sequence<int, Ops...>)
     k.desc = SL::desc;
     ((k.binary[Ops] = &binary_entry<SL, Ops>), ...);
     ((k.fused[Ops] = &fused_entry<SL, Ops>), ...);
-    k.multi = &multi_entry<SL>;
+    add_pairs<SL>(k, std::make_integer_sequence<int, kNumOpPairs>());
     k.unpack[0][0] = &unpack_entry<SL, false, 4>;
     k.unpack[0][1] = &unpack_entry<SL, false, 8>;
     k.unpack[1][0] = &unpack_entry<SL, true, 4>;

@@ -209,7 +209,15 @@ def test_binary_multi_one_pass(P, oracle, mode):
         for n, off in ((1 << 20) + 13, 0), (4099, 1), (3, 0):
             a_h, b_h = oracle.fill(eb, n, 61), oracle.fill(eb, n, 62)
             a, b = to_dev(a_h, off), to_dev(b_h, off)
-            for op_list in (["add_unsigned_saturate", "add_signed_saturate"], list(OPS[:4]), ["max_signed"], ["bit_xor", "sub_signed_saturate", "min_unsigned"]):
+            op_lists = [["add_unsigned_saturate", "add_signed_saturate"], list(OPS[:4]), ["max_signed"],
+                        ["bit_xor", "sub_signed_saturate", "min_unsigned"],
+                        # every pair that has a one-pass kernel, in the swapped order too, and lists that mix pairs and singles
+                        ["sub_signed_saturate", "sub_unsigned_saturate"], ["add_signed_saturate", "sub_signed_saturate"],
+                        ["sub_unsigned_saturate", "add_unsigned_saturate"], ["add_wrap", "sub_wrap"],
+                        ["max_unsigned", "min_unsigned"], ["min_signed", "max_signed"],
+                        ["add_signed_saturate", "bit_and", "add_unsigned_saturate", "sub_signed_saturate"],
+                        ["min_signed", "min_unsigned", "max_signed", "max_unsigned"]]
+            for op_list in op_lists:
                 outs = [to_dev(np.zeros(n, dtype=a_h.dtype), off) for _ in op_list]
                 ops.binary_multi(op_list, L, a, b, outs=outs)
                 for op, o in zip(op_list, outs):

@@ -69,6 +69,20 @@ static void run_bulk(const char* tag, const void* a, const void* b, void* out, s
     });
 }
 
+template <class Fn, int U, int B, int LD, int ST>
+static void run_pair(const char* tag, const void* a, const void* b, void* o0, void* o1, size_t nvec, int ctas_per_sm)
+{
+    using Cfg = stream_cfg<U, B, LD, ST>;
+    constexpr size_t tile = size_t(U) * B;
+    const size_t ntiles = (nvec + tile - 1) / tile;
+    const size_t grid = ctas_per_sm > 0 ? std::min(ntiles, size_t(g_sms) * ctas_per_sm) : ntiles;
+    char name[128];
+    std::snprintf(name, sizeof name, "%s pair U%d B%d ld%d st%d ctas/sm %d", tag, U, B, LD, ST, ctas_per_sm);
+    time_it(name, double(nvec) * 64, [&] {
+        binary_pair_stream_kernel<Fn, Cfg><<<unsigned(grid), B>>>((const uint4*)a, (const uint4*)b, (uint4*)o0, (uint4*)o1, nvec, Fn{});
+    });
+}
+
 // persistent CTAs that take tiles in address order from a global counter (instead of a grid stride)
 template <class Fn, class Cfg>
 __global__ void __launch_bounds__(Cfg::BLOCK)
@@ -154,6 +168,30 @@ int main(int argc, char** argv)
     using FnIF = fused_fn<OP_ADD_SIGNED_SATURATE, static_fields<IRR>>;
     using FnX = swar_fn<OP_XOR, static_masks<RGBA>>;
 
+    if (argc > 3 && std::atoi(argv[3]) == 8) {
+        // two ops in one pass (2 reads + 2 writes, 16 B per uint32 element): unroll / block / cache policy
+        using Pu = pair_fn<OP_ADD_UNSIGNED_SATURATE, OP_ADD_SIGNED_SATURATE, static_masks<RGBA>>;
+        using C16 = static_layout<uint64_t, 16, 16, 16, 16>;
+        using Pc2 = pair_fn<OP_ADD_SIGNED_SATURATE, OP_SUB_SIGNED_SATURATE, static_masks<C16>>;
+        for (int rep = 0; rep < 2; ++rep) {
+            run_stream<FnU, 2, 256, 2, 2>("usat rgba8 single op (12 B/elem)", a, b, out, nvec, 0);
+            run_pair<Pu, 1, 256, 2, 2>("usat+ssat rgba8", a, b, out, out2, nvec, 0);
+            run_pair<Pu, 2, 256, 2, 2>("usat+ssat rgba8", a, b, out, out2, nvec, 0);
+            run_pair<Pu, 4, 256, 2, 2>("usat+ssat rgba8", a, b, out, out2, nvec, 0);
+            run_pair<Pu, 2, 128, 2, 2>("usat+ssat rgba8", a, b, out, out2, nvec, 0);
+            run_pair<Pu, 2, 512, 2, 2>("usat+ssat rgba8", a, b, out, out2, nvec, 0);
+            run_pair<Pu, 1, 512, 2, 2>("usat+ssat rgba8", a, b, out, out2, nvec, 0);
+            run_pair<Pu, 2, 256, 2, 0>("usat+ssat rgba8", a, b, out, out2, nvec, 0);
+            run_pair<Pu, 2, 256, 0, 0>("usat+ssat rgba8", a, b, out, out2, nvec, 0);
+            run_pair<Pu, 2, 256, 1, 2>("usat+ssat rgba8", a, b, out, out2, nvec, 0);
+            run_pair<Pu, 2, 256, 2, 2>("usat+ssat rgba8", a, b, out, out2, nvec, 4);
+            run_pair<Pu, 2, 256, 2, 2>("usat+ssat rgba8", a, b, out, out2, nvec, 8);
+            run_pair<Pc2, 2, 256, 2, 2>("ssat add+sub u64 16x4", a, b, out, out2, nvec, 0);
+            run_pair<Pc2, 4, 256, 2, 2>("ssat add+sub u64 16x4", a, b, out, out2, nvec, 0);
+        }
+        std::printf("done\n");
+        return 0;
+    }
     if (argc > 3 && std::atoi(argv[3]) == 7) {
         // library ordered kernel (self re-arming counter ring) vs the tune-local dyn kernel (memset per launch)
         tile_counter* ring;
