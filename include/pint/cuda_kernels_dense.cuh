@@ -1,0 +1,289 @@
+// pint/cuda_kernels_dense.cuh -- kernels for the DENSE bit-stream storage format
+// (SURVEY.md 8(f)4): element i of a layout with S = sum(Bits) bits occupies bits
+// [i*S, (i+1)*S) of a little-endian bit stream, with no padding to
+// find_appropriate_int (pint.hpp:724-734).  Elements -- and fields -- straddle
+// word boundaries here, and a packed array costs S/8 bytes per element instead
+// of sizeof(Integer): 3 instead of 4 bytes for <8,8,8>, 2.375 instead of 4 for
+// <5,6,5,3>.  Per-element semantics are unchanged: a dense op is
+// pack(op(unpack(a), unpack(b))) with op the SWAR functor of cuda_kernels.cuh.
+//
+// Data movement.  A straddling layout has no fixed relation between threads and
+// 16-byte vectors, so tiles are staged through shared memory by the TMA engine
+// (1-D bulk copies, cp.async.bulk + mbarrier complete_tx; the result tile goes
+// back with cp.async.bulk.global.shared::cta).  Global traffic is therefore
+// fully coalesced whatever S is, and costs no per-thread address arithmetic.
+//
+// Thread mapping for dense -> dense ops ("chunk" mapping).  The bit pattern of a
+// layout repeats every lcm(S, WB) bits (WB = bits of the processing word): a
+// CHUNK of Cw = S / gcd(S, WB) words holds exactly G = WB / gcd(S, WB) whole
+// elements.  One thread owns a chunk: it walks the chunk's words with a sliding
+// two-word window, extracts each element with a funnel shift, applies the SWAR
+// functor, and deposits the result into a two-word output window that is flushed
+// word by word over the input tile.  No element is shared between threads, so
+// there are no shuffles and no atomics; all shifts are the same for every thread
+// (immediates when the layout is compiled in).  Cw is odd for every S that is
+// not 8, 16, 32 or 64 (those ARE the padded format), so the chunk stride is
+// conflict-free in shared memory.
+//
+// Thread mapping for format conversions ("element" mapping): one thread per
+// element extracts (funnel shift at a per-lane offset) or deposits (shared-memory
+// atomicOr into a zeroed tile) so that the padded / plane side stays coalesced.
+#pragma once
+
+#include "cuda_kernels.cuh"
+#include "cuda_kernels_bulk.cuh"
+
+namespace pint {
+namespace cuda {
+namespace kernels {
+namespace dense {
+
+using bulk::bulk_load;
+using bulk::bulk_store;
+using bulk::bulk_wait_read;
+using bulk::evict_first_policy;
+using bulk::mbar_expect_tx;
+using bulk::mbar_init;
+using bulk::mbar_wait;
+
+constexpr uint32_t gcd_u32(uint32_t a, uint32_t b) { return b == 0 ? a : gcd_u32(b, a % b); }
+
+template <class W>
+__host__ __device__ __forceinline__ constexpr W ones_w(uint32_t n)
+{
+    return n >= 8 * sizeof(W) ? ~W(0) : W((W(1) << n) - 1);
+}
+
+// low word of (hi:lo) >> sh, sh in [0, WB)
+template <class W>
+__device__ __forceinline__ W funnel_r(W lo, W hi, uint32_t sh)
+{
+    if constexpr (sizeof(W) == 4) return __funnelshift_r(lo, hi, sh);
+    else return (lo >> sh) | ((hi << 1) << (63u - sh));
+}
+
+// the bits of (r << sh) that leave the word: r >> (WB - sh), 0 when sh == 0
+template <class W>
+__device__ __forceinline__ W spill_l(W r, uint32_t sh)
+{
+    if constexpr (sizeof(W) == 4) return __funnelshift_l(r, 0u, sh);
+    else return (r >> 1) >> (63u - sh);
+}
+
+// ---------------------------------------------------------------------------
+// Chunk geometry: compile-time (static layouts) or run-time (constant bank).
+
+template <class W, uint32_t S_>
+struct static_geom {
+    static constexpr bool is_static = true;
+    static constexpr uint32_t WB = 8 * sizeof(W);
+    static constexpr uint32_t kS = S_, kCw = S_ / gcd_u32(S_, WB), kG = WB / gcd_u32(S_, WB);
+    uint32_t chunks_per_thread;
+    __host__ __device__ static constexpr uint32_t S() { return kS; }
+    __host__ __device__ static constexpr uint32_t Cw() { return kCw; }
+    __host__ __device__ static constexpr uint32_t G() { return kG; }
+};
+
+template <class W>
+struct runtime_geom {
+    static constexpr bool is_static = false;
+    static constexpr uint32_t WB = 8 * sizeof(W);
+    uint32_t s, cw, g;
+    uint32_t chunks_per_thread;
+    runtime_geom() = default;
+    explicit runtime_geom(uint32_t S_) : s(S_), cw(S_ / gcd_u32(S_, WB)), g(WB / gcd_u32(S_, WB)), chunks_per_thread(1) {}
+    __host__ __device__ uint32_t S() const { return s; }
+    __host__ __device__ uint32_t Cw() const { return cw; }
+    __host__ __device__ uint32_t G() const { return g; }
+};
+
+// One chunk, in place: A[0..Cw) <- op(A, B) element by element.  A and B are
+// shared-memory pointers to the same chunk of the two operand tiles.
+template <class Fn, class Geo>
+__device__ __forceinline__ void process_chunk(typename Fn::word* A, const typename Fn::word* B, const Fn& fn, const Geo& geo)
+{
+    using W = typename Fn::word;
+    constexpr uint32_t WB = 8 * sizeof(W);
+    const uint32_t S = geo.S(), Cw = geo.Cw();
+    const W SM = ones_w<W>(S);
+    W ca = A[0], cb = B[0];
+    W na = Cw > 1 ? A[1] : W(0), nb = Cw > 1 ? B[1] : W(0);
+    W ocur = 0, onxt = 0;
+    uint32_t sh = 0, w = 0;
+    auto element = [&]() {
+        const W xa = funnel_r(ca, na, sh), xb = funnel_r(cb, nb, sh);
+        // Bits above S of xa / xb belong to the next element.  The functors ignore them for
+        // add/sub (M1 and H cover field bits only), pass them through for | & ^ and take them
+        // from b for min/max, so masking the RESULT is enough.
+        const W r = fn(xa, xb) & SM;
+        ocur |= r << sh;
+        onxt |= spill_l(r, sh);
+        sh += S;
+        if (sh >= WB) {  // the window moves on by one word (S <= WB: never by more)
+            sh -= WB;
+            A[w] = ocur;  // every element that touches word w has been read: in place is safe
+            ocur = onxt;
+            onxt = 0;
+            ++w;
+            ca = na;
+            cb = nb;
+            na = w + 1 < Cw ? A[w + 1] : W(0);
+            nb = w + 1 < Cw ? B[w + 1] : W(0);
+        }
+    };
+    if constexpr (Geo::is_static) {
+#pragma unroll
+        for (uint32_t e = 0; e < Geo::kG; ++e) element();
+    } else {
+        const uint32_t G = geo.G();
+        for (uint32_t e = 0; e < G; ++e) element();
+    }
+    // G * S == Cw * WB: the last element ends exactly on the chunk's last bit, so the last
+    // word was flushed by the branch above and sh is back at 0.
+}
+
+// zero the bits of `word` (which starts at bit `start` of the tile) at or above bit `limit`
+template <class W>
+__device__ __forceinline__ W clip_word(W word, uint64_t start, uint64_t limit)
+{
+    constexpr uint32_t WB = 8 * sizeof(W);
+    if (start >= limit) return 0;
+    if (start + WB > limit) return word & ones_w<W>(uint32_t(limit - start));
+    return word;
+}
+
+__device__ __forceinline__ uint4 clip_vec(uint4 v, uint64_t start_bit, uint64_t limit)
+{
+    v.x = clip_word<uint32_t>(v.x, start_bit, limit);
+    v.y = clip_word<uint32_t>(v.y, start_bit + 32, limit);
+    v.z = clip_word<uint32_t>(v.z, start_bit + 64, limit);
+    v.w = clip_word<uint32_t>(v.w, start_bit + 96, limit);
+    return v;
+}
+
+// ---------------------------------------------------------------------------
+// out = op(a, b) on dense streams.  One tile per CTA (tiles are handed out in
+// address order by the block scheduler, as in binary_stream_kernel); a tile is
+// blockDim.x * chunks_per_thread chunks.  Tiles that lie entirely below bit
+// n*S travel by TMA; the one tile that contains the end of the data is loaded
+// and stored with guarded 16-byte vectors, with the bits at or above n*S
+// forced to zero (op(0, 0) == 0 for every op, so the output tail is zero too).
+// `out` may alias a or b: the tile is complete in shared memory before any
+// store.  Dynamic shared memory: 2 * tile bytes.
+template <class Fn, class Geo>
+__global__ void dense_binary_kernel(const uint4* a, const uint4* b, uint4* out, size_t total_vec, uint64_t valid_bits,
+                                    const __grid_constant__ Fn fn, const __grid_constant__ Geo geo)
+{
+    using W = typename Fn::word;
+    extern __shared__ __align__(128) unsigned char dense_smem[];
+    __shared__ __align__(8) uint64_t full;
+    const uint32_t T = blockDim.x, R = geo.chunks_per_thread, Cw = geo.Cw();
+    const uint32_t tile_words = T * R * Cw;
+    const uint32_t tile_bytes = tile_words * uint32_t(sizeof(W));
+    const uint32_t tile_vecs = tile_bytes / 16;
+    W* A = reinterpret_cast<W*>(dense_smem);
+    W* B = reinterpret_cast<W*>(dense_smem + tile_bytes);
+    const size_t t = blockIdx.x;
+    const uint64_t tile_bits = uint64_t(tile_bytes) * 8;
+    const bool whole = (t + 1) * tile_bits <= valid_bits;
+    uint64_t pol = 0;
+
+    if (whole) {
+        if (threadIdx.x == 0) {
+            pol = evict_first_policy();
+            mbar_init(&full, 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            mbar_expect_tx(&full, 2 * tile_bytes);
+            bulk_load(A, a + t * tile_vecs, tile_bytes, &full, pol);
+            bulk_load(B, b + t * tile_vecs, tile_bytes, &full, pol);
+        }
+        __syncthreads();  // the barrier is initialised before anyone polls it
+        mbar_wait(&full, 0);
+    } else {
+        const uint64_t limit = valid_bits - t * tile_bits;  // first invalid bit, relative to the tile
+        for (uint32_t v = threadIdx.x; v < tile_vecs; v += T) {
+            const size_t gv = t * tile_vecs + v;
+            uint4 x = make_uint4(0, 0, 0, 0), y = x;
+            if (gv < total_vec) {
+                x = clip_vec(ld16<CACHE_STREAMING>(a + gv), uint64_t(v) * 128, limit);
+                y = clip_vec(ld16<CACHE_STREAMING>(b + gv), uint64_t(v) * 128, limit);
+            }
+            reinterpret_cast<uint4*>(A)[v] = x;
+            reinterpret_cast<uint4*>(B)[v] = y;
+        }
+        __syncthreads();
+    }
+
+    for (uint32_t r = 0; r < R; ++r) {
+        const uint32_t c = (r * T + threadIdx.x) * Cw;
+        process_chunk(A + c, B + c, fn, geo);
+    }
+
+    if (whole) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> async proxy
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            bulk_store(out + t * tile_vecs, A, tile_bytes, pol);
+            bulk_wait_read<0>();  // shared memory must stay valid until the TMA engine has read it
+        }
+    } else {
+        __syncthreads();
+        for (uint32_t v = threadIdx.x; v < tile_vecs; v += T) {
+            const size_t gv = t * tile_vecs + v;
+            if (gv < total_vec) st16<CACHE_STREAMING>(out + gv, reinterpret_cast<const uint4*>(A)[v]);
+        }
+    }
+}
+
+struct dense_tuning {
+    int threads = 0;     // 0 = choose from the chunk size
+    int tile_bytes = 0;  // per operand; 0 = default target
+};
+
+template <class W>
+inline void choose_tile(uint32_t cw, const dense_tuning& tune, uint32_t* threads, uint32_t* chunks_per_thread)
+{
+    const uint32_t chunk_bytes = cw * uint32_t(sizeof(W));
+    uint32_t T = tune.threads > 0 ? uint32_t(tune.threads) : (chunk_bytes > 256 ? 64u : 128u);
+    const uint32_t target = tune.tile_bytes > 0 ? uint32_t(tune.tile_bytes) : 16384u;
+    uint32_t R = target / (T * chunk_bytes);
+    if (R < 1) R = 1;
+    // 2 operand tiles must fit in 227 KB
+    while (R > 1 && 2ull * T * R * chunk_bytes > 200u * 1024u) --R;
+    while (T > 32 && 2ull * T * R * chunk_bytes > 200u * 1024u) T -= 32;
+    *threads = T;
+    *chunks_per_thread = R;
+}
+
+// a, b, out: 16-byte aligned dense streams of n elements (ceil(n*S/128)*16 bytes each)
+template <class Fn, class Geo>
+cudaError_t launch_dense_binary(const void* a, const void* b, void* out, size_t n, const Fn& fn, Geo geo,
+                                cudaStream_t stream, const launch_geom& g, const dense_tuning& tune = dense_tuning())
+{
+    using W = typename Fn::word;
+    if (n == 0) return cudaSuccess;
+    uint32_t T = 0, R = 0;
+    choose_tile<W>(geo.Cw(), tune, &T, &R);
+    geo.chunks_per_thread = R;
+    const uint64_t valid_bits = uint64_t(n) * geo.S();
+    const size_t total_vec = size_t((valid_bits + 127) / 128);
+    const size_t tile_bytes = size_t(T) * R * geo.Cw() * sizeof(W);
+    const size_t ntiles = (total_vec * 16 + tile_bytes - 1) / tile_bytes;
+    const size_t smem = 2 * tile_bytes;
+    auto kernel = dense_binary_kernel<Fn, Geo>;
+    if (smem > 48 * 1024) {
+        cudaError_t rc = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+        if (rc != cudaSuccess) return rc;
+    }
+    if (ntiles > 0x7FFFFFFFull) return cudaErrorInvalidValue;
+    kernel<<<unsigned(ntiles), T, smem, stream>>>(static_cast<const uint4*>(a), static_cast<const uint4*>(b),
+                                                  static_cast<uint4*>(out), total_vec, valid_bits, fn, geo);
+    count_launch(g);
+    return cudaGetLastError();
+}
+
+}  // namespace dense
+}  // namespace kernels
+}  // namespace cuda
+}  // namespace pint

@@ -90,7 +90,9 @@ unsigned long long pint_cuda_launch_count(void);
  * "ctas_per_sm" (0 = one CTA per tile, the default; k > 0 = persistent grid of SMs * k CTAs),
  * "ordered_ctas_per_sm" (k > 0: bandwidth-bound ops on large arrays run a persistent grid of
  * SMs * k CTAs that draw tiles in address order; default 0 = always one CTA per tile),
- * "host_chunk_bytes" / "host_slots" (staging ring of the host-buffer path).  Returns 0 or PINT_E_ARG. */
+ * "host_chunk_bytes" / "host_slots" (staging ring of the host-buffer path),
+ * "dense_threads" / "dense_tile_bytes" (CTA size and per-operand tile of the dense bit-stream
+ * kernels; 0 = chosen from the layout).  Returns 0 or PINT_E_ARG. */
 int pint_cuda_set_option(const char* key, long value);
 long pint_cuda_get_option(const char* key);
 
@@ -144,6 +146,30 @@ int pint_cuda_unpack(const pint_layout* layout, int is_signed, const void* packe
  * field constructor = make_truncate (pint.hpp:770-774, 592-601, 390-407). */
 int pint_cuda_repack(const pint_layout* layout, const void* const* planes, int plane_bytes, void* packed,
                      size_t n, pint_stream_t stream);
+
+/* ---- dense bit-stream storage (a storage format of THIS library) ----
+ * The reference always pads an element to find_appropriate_int (pint.hpp:724-734).  A dense
+ * stream stores element i in bits [i*S, (i+1)*S), S = sum(Bits), of a little-endian bit stream
+ * (bit k of the stream is bit k % 8 of byte k / 8): S/8 bytes per element instead of
+ * sizeof(Integer), elements and fields straddle word boundaries.  Per-element semantics are
+ * the reference's: a dense op equals pack(OP(unpack(a), unpack(b))).
+ *   - Dense buffers are DEVICE pointers, 16-byte aligned, pint_cuda_dense_bytes(layout, n)
+ *     bytes long (= ceil(n*S/128)*16).  Bits at or above n*S are written as zero and are
+ *     ignored on input.
+ *   - layout->elem_bytes describes the PADDED side of pack/unpack only. */
+size_t pint_cuda_dense_bytes(const pint_layout* layout, size_t n);
+/* out = OP(a, b) on dense streams (3*S/8 bytes per element); out may be a or b exactly. */
+int pint_cuda_dense_binary(int op, const pint_layout* layout, const void* a, const void* b, void* out, size_t n,
+                           pint_stream_t stream);
+/* dense[i] = low S bits of padded[i]  /  padded[i] = dense[i] zero-extended to Integer. */
+int pint_cuda_dense_pack(const pint_layout* layout, const void* padded, void* dense, size_t n, pint_stream_t stream);
+int pint_cuda_dense_unpack(const pint_layout* layout, const void* dense, void* padded, size_t n, pint_stream_t stream);
+/* get / get_signed (pint.hpp:799-822) of every field straight from a dense stream, and the
+ * truncating field constructor (pint.hpp:770-774) straight into one; planes as in pint_cuda_unpack. */
+int pint_cuda_dense_to_planes(const pint_layout* layout, int is_signed, const void* dense, void* const* planes,
+                              int plane_bytes, size_t n, pint_stream_t stream);
+int pint_cuda_dense_from_planes(const pint_layout* layout, const void* const* planes, int plane_bytes, void* dense,
+                                size_t n, pint_stream_t stream);
 
 /* ---- the benchmark's exact loop shape (tests/pint_bench.cpp:90-94) ---- */
 /* *sum_dev (device uint64_t) = sum_i OP(pairs[2i], pairs[2i+1]) mod 2^64 over an

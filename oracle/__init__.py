@@ -102,6 +102,11 @@ class Oracle:
         L.pint_oracle_fill.argtypes = [C.c_void_p, C.c_uint32, C.c_size_t, C.c_uint64, C.c_uint64]
         L.pint_oracle_checksum.argtypes = [C.c_void_p, C.c_uint32, C.c_size_t, C.c_void_p, C.c_void_p]
         L.pint_oracle_pairs_reduce.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+        L.pint_oracle_dense_bytes.restype = C.c_size_t
+        L.pint_oracle_dense_bytes.argtypes = [C.c_uint32, C.c_size_t]
+        L.pint_oracle_dense_pack.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
+        L.pint_oracle_dense_unpack.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
+        L.pint_oracle_dense_binary.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
 
     # -- layout helpers
     def validate(self, elem_bytes, bits):
@@ -222,6 +227,40 @@ class Oracle:
         if rc:
             raise ValueError(f"pint_oracle_pairs_reduce rc={rc}")
         return s.value
+
+    # -- dense bit-stream storage (our format; element i at bits [i*S, (i+1)*S))
+    def dense_bytes(self, bits, n):
+        return self.lib.pint_oracle_dense_bytes(sum(bits), n)
+
+    def dense_pack(self, elem_bytes, bits, x):
+        l = clayout(elem_bytes, bits)
+        x = np.ascontiguousarray(x, dtype=_DT[elem_bytes])
+        out = np.empty(self.dense_bytes(bits, x.size), dtype=np.uint8)
+        rc = self.lib.pint_oracle_dense_pack(C.byref(l), _ptr(x), _ptr(out), x.size)
+        if rc:
+            raise ValueError(f"pint_oracle_dense_pack rc={rc}")
+        return out
+
+    def dense_unpack(self, elem_bytes, bits, dense, n):
+        l = clayout(elem_bytes, bits)
+        dense = np.ascontiguousarray(dense, dtype=np.uint8)
+        assert dense.size >= self.dense_bytes(bits, n)
+        out = np.empty(n, dtype=_DT[elem_bytes])
+        rc = self.lib.pint_oracle_dense_unpack(C.byref(l), _ptr(dense), _ptr(out), n)
+        if rc:
+            raise ValueError(f"pint_oracle_dense_unpack rc={rc}")
+        return out
+
+    def dense_binary(self, op, elem_bytes, bits, a, b, n):
+        l = clayout(elem_bytes, bits)
+        a = np.ascontiguousarray(a, dtype=np.uint8)
+        b = np.ascontiguousarray(b, dtype=np.uint8)
+        out = np.empty(self.dense_bytes(bits, n), dtype=np.uint8)
+        rc = self.lib.pint_oracle_dense_binary(OP_CODE[op] if isinstance(op, str) else op, C.byref(l),
+                                               _ptr(a), _ptr(b), _ptr(out), n)
+        if rc:
+            raise ValueError(f"pint_oracle_dense_binary rc={rc}")
+        return out
 
 
 class Ref:

@@ -550,3 +550,101 @@ int pint_oracle_pairs_reduce(int op, const pint_oracle_layout* l, const void* pa
     if (sum) *sum = s;
     return 0;
 }
+
+/* ---------------------------------------------------------------------------
+ * Dense bit-stream storage.  NOT a reference format: the
+ * reference always pads an element to find_appropriate_int (pint.hpp:724-734).
+ * Spec (ours): element i of a layout with S = sum(Bits) occupies bits
+ * [i*S, (i+1)*S) of a little-endian bit stream (bit k of the stream is bit
+ * k % 8 of byte k / 8); the buffer is ceil(n*S / 128) * 16 bytes and every bit
+ * at or above n*S is zero on output.  The per-element SEMANTICS stay the
+ * reference's: a dense op is pack(op(unpack(a), unpack(b))) with `op` the
+ * restatement above (pinned against the reference), so only the bit layout is
+ * new.  tests/test_oracle_golden.py checks pack/unpack against an independent
+ * big-integer model of this spec. */
+
+size_t pint_oracle_dense_bytes(uint32_t total_bits, size_t n)
+{
+    /* n * S can exceed 64 bits only for absurd n; sizes here are test sizes */
+    const unsigned __int128 bits = (unsigned __int128)n * total_bits;
+    return (size_t)((bits + 127) / 128) * 16;
+}
+
+static uint64_t dense_get(const uint64_t* w, size_t nwords, uint32_t S, size_t i)
+{
+    const unsigned __int128 p = (unsigned __int128)i * S;
+    const size_t k = (size_t)(p >> 6);
+    const uint32_t sh = (uint32_t)(p & 63);
+    uint64_t x = w[k] >> sh;
+    if (sh && sh + S > 64 && k + 1 < nwords) x |= w[k + 1] << (64 - sh);
+    return S >= 64 ? x : (x & ((UINT64_C(1) << S) - 1));
+}
+
+static void dense_put(uint64_t* w, size_t nwords, uint32_t S, size_t i, uint64_t v)
+{
+    const unsigned __int128 p = (unsigned __int128)i * S;
+    const size_t k = (size_t)(p >> 6);
+    const uint32_t sh = (uint32_t)(p & 63);
+    if (S < 64) v &= (UINT64_C(1) << S) - 1;
+    w[k] |= v << sh;
+    if (sh && sh + S > 64 && k + 1 < nwords) w[k + 1] |= v >> (64 - sh);
+}
+
+int pint_oracle_dense_pack(const pint_oracle_layout* l, const void* padded, void* dense, size_t n)
+{
+    pint_oracle_masks m;
+    int rc = pint_oracle_make_masks(l, &m);
+    if (rc) return rc;
+    const size_t nwords = pint_oracle_dense_bytes(m.total, n) / 8;
+    uint64_t* w = (uint64_t*)dense;
+    memset(w, 0, nwords * 8);
+    for (size_t i = 0; i < n; ++i) dense_put(w, nwords, m.total, i, load_elem(padded, l->elem_bytes, i));
+    return 0;
+}
+
+int pint_oracle_dense_unpack(const pint_oracle_layout* l, const void* dense, void* padded, size_t n)
+{
+    pint_oracle_masks m;
+    int rc = pint_oracle_make_masks(l, &m);
+    if (rc) return rc;
+    const size_t nwords = pint_oracle_dense_bytes(m.total, n) / 8;
+    for (size_t i = 0; i < n; ++i)
+        store_elem(padded, l->elem_bytes, i, dense_get((const uint64_t*)dense, nwords, m.total, i));
+    return 0;
+}
+
+int pint_oracle_dense_binary(int op, const pint_oracle_layout* l, const void* a, const void* b, void* out, size_t n)
+{
+    pint_oracle_masks m;
+    int rc = pint_oracle_make_masks(l, &m);
+    if (rc) return rc;
+    if (op < 0 || op >= PINT_O_NUM_BINARY) return -10;
+    const size_t nwords = pint_oracle_dense_bytes(m.total, n) / 8;
+    uint64_t* w = (uint64_t*)out;
+    /* out may be a or b: element i of the result is written after element i of both inputs was
+     * read, and it only touches bits [i*S, (i+1)*S) -- but dense_put ORs, so clear as we go */
+    for (size_t i = 0; i < n; ++i) {
+        const uint64_t x = dense_get((const uint64_t*)a, nwords, m.total, i);
+        const uint64_t y = dense_get((const uint64_t*)b, nwords, m.total, i);
+        const uint64_t r = binary1(op, &m, x, y);
+        /* clear the destination bits, then deposit */
+        const unsigned __int128 p = (unsigned __int128)i * m.total;
+        const size_t k = (size_t)(p >> 6);
+        const uint32_t sh = (uint32_t)(p & 63);
+        const uint64_t ones = m.total >= 64 ? ~UINT64_C(0) : ((UINT64_C(1) << m.total) - 1);
+        w[k] &= ~(ones << sh);
+        if (sh && sh + m.total > 64 && k + 1 < nwords) w[k + 1] &= ~(ones >> (64 - sh));
+        dense_put(w, nwords, m.total, i, r);
+    }
+    /* zero the tail bits */
+    {
+        const unsigned __int128 end = (unsigned __int128)n * m.total;
+        size_t k = (size_t)(end >> 6);
+        const uint32_t sh = (uint32_t)(end & 63);
+        if (k < nwords) {
+            if (sh) { w[k] &= (UINT64_C(1) << sh) - 1; ++k; }
+            for (; k < nwords; ++k) w[k] = 0;
+        }
+    }
+    return 0;
+}

@@ -126,6 +126,15 @@ int pint_oracle_checksum(const void* x, uint32_t elem_bytes, size_t n, uint64_t*
  * over (first, second) pairs of Integer, accumulated in the Integer's width. */
 int pint_oracle_pairs_reduce(int op, const pint_oracle_layout* l, const void* pairs, size_t n, uint64_t* sum);
 
+/* ---- dense bit-stream storage (OUR format, see pint_oracle.c) ----
+ * element i occupies bits [i*S, (i+1)*S) of a little-endian bit stream, S = sum(Bits);
+ * buffers are ceil(n*S/128)*16 bytes, bits at or above n*S are zero on output.
+ * dense_binary = pack(op(unpack(a), unpack(b))) with op the restatement above. */
+size_t pint_oracle_dense_bytes(uint32_t total_bits, size_t n);
+int pint_oracle_dense_pack(const pint_oracle_layout* l, const void* padded, void* dense, size_t n);
+int pint_oracle_dense_unpack(const pint_oracle_layout* l, const void* dense, void* padded, size_t n);
+int pint_oracle_dense_binary(int op, const pint_oracle_layout* l, const void* a, const void* b, void* out, size_t n);
+
 #ifdef __cplusplus
 }
 #endif

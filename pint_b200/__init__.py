@@ -8,11 +8,11 @@ package is the Python mirror of that layer, used by the tests and bench.py:
 from . import _lib  # noqa: F401
 from .layout import Layout, storage_bytes  # noqa: F401
 
-__all__ = ["Layout", "storage_bytes", "ops", "sharded"]
+__all__ = ["Layout", "storage_bytes", "ops", "sharded", "dense"]
 
 
 def __getattr__(name):
-    if name in ("ops", "sharded"):
+    if name in ("ops", "sharded", "dense"):
         import importlib
         return importlib.import_module(f".{name}", __name__)
     raise AttributeError(name)

@@ -55,6 +55,12 @@ def lib():
             "pint_cuda_slice": (i, [LP, u32, u32, vp, vp, sz, vp]),
             "pint_cuda_unpack": (i, [LP, i, vp, C.POINTER(vp), i, sz, vp]),
             "pint_cuda_repack": (i, [LP, C.POINTER(vp), i, vp, sz, vp]),
+            "pint_cuda_dense_bytes": (sz, [LP, sz]),
+            "pint_cuda_dense_binary": (i, [i, LP, vp, vp, vp, sz, vp]),
+            "pint_cuda_dense_pack": (i, [LP, vp, vp, sz, vp]),
+            "pint_cuda_dense_unpack": (i, [LP, vp, vp, sz, vp]),
+            "pint_cuda_dense_to_planes": (i, [LP, i, vp, C.POINTER(vp), i, sz, vp]),
+            "pint_cuda_dense_from_planes": (i, [LP, C.POINTER(vp), i, vp, sz, vp]),
             "pint_cuda_pairs_reduce": (i, [i, LP, vp, sz, vp, vp]),
             "pint_cuda_fill_splitmix": (i, [vp, u32, sz, u64, u64, vp]),
             "pint_cuda_checksum": (i, [vp, u32, sz, vp, vp]),

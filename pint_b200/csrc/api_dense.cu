@@ -1,0 +1,206 @@
+// api_dense.cu -- C ABI of the dense bit-stream storage format (include/pint_cuda.h,
+// "dense" section): argument checking, kernel selection, launches.
+#include "api_common.hpp"
+#include "dense_registry.hpp"
+#include "pint/cuda_kernels_dense_convert.cuh"
+
+namespace pint_cuda_impl {
+namespace {
+
+using namespace pint::cuda;
+using namespace pint::cuda::kernels;
+
+uint32_t total_bits(const layout_desc& d)
+{
+    uint32_t s = 0;
+    for (uint32_t i = 0; i < d.nfields; ++i) s += d.bits[i];
+    return s;
+}
+
+size_t dense_bytes(uint32_t S, size_t n)
+{
+    const unsigned __int128 bits = (unsigned __int128)n * S;
+    return size_t((bits + 127) / 128) * 16;
+}
+
+// the dense stream seen as packed_int<Word, Bits...>: one element per processing word
+template <class W>
+layout_desc word_desc(const layout_desc& d)
+{
+    layout_desc e = d;
+    e.elem_bytes = sizeof(W);
+    return e;
+}
+
+dense_tuning tuning()
+{
+    dense_tuning t;
+    t.threads = (int)opts().dense_threads;
+    t.tile_bytes = (int)opts().dense_tile_bytes;
+    return t;
+}
+
+template <class W, int... Ops>
+cudaError_t dense_generic(int op, const layout_desc& d, uint32_t S, const void* a, const void* b, void* out, size_t n,
+                          cudaStream_t s, const launch_geom& g, std::integer_sequence<int, Ops...>)
+{
+    const runtime_masks<W> p(make_word_masks<W>(word_desc<W>(d)));
+    cudaError_t rc = cudaErrorInvalidValue;
+    ((op == Ops ? (rc = dense::launch_dense_binary(a, b, out, n, swar_fn<Ops, runtime_masks<W>>{p},
+                                                   dense::runtime_geom<W>(S), s, g, tuning()), 0) : 0), ...);
+    return rc;
+}
+
+dense::dense_fields make_fields(const layout_desc& d)
+{
+    dense::dense_fields f{};
+    layout_desc e = d;
+    e.elem_bytes = 8;  // offsets within one element, nothing replicated
+    f.t = make_field_table<uint64_t>(e);
+    return f;
+}
+
+template <class W, class Elem>
+cudaError_t pack_unpack(bool to_dense, const void* padded, void* dense, size_t n, uint32_t S, cudaStream_t s)
+{
+    const dense::dense_fields f{};
+    if (to_dense) return dense::launch_dense_insert<W, Elem, dense::SIDE_PADDED, 4>(padded, dense, n, S, f, s, geom());
+    return dense::launch_dense_extract<W, Elem, dense::SIDE_PADDED, 4, false>(dense, const_cast<void*>(padded), n, S, f, s, geom());
+}
+
+template <class W>
+cudaError_t pack_unpack_w(bool to_dense, uint32_t elem_bytes, const void* padded, void* dense, size_t n, uint32_t S,
+                          cudaStream_t s)
+{
+    switch (elem_bytes) {
+    case 1: return pack_unpack<W, uint8_t>(to_dense, padded, dense, n, S, s);
+    case 2: return pack_unpack<W, uint16_t>(to_dense, padded, dense, n, S, s);
+    case 4: return pack_unpack<W, uint32_t>(to_dense, padded, dense, n, S, s);
+    default: return pack_unpack<W, uint64_t>(to_dense, padded, dense, n, S, s);
+    }
+}
+
+int convert_impl(bool to_dense, const pint_layout* layout, const void* padded, void* dense, size_t n, cudaStream_t s)
+{
+    layout_desc d;
+    if (int rc = check_layout(layout, &d)) return rc;
+    if (n == 0) return PINT_OK;
+    if (!padded || !dense) return PINT_E_NULL;
+    if ((uintptr_t)dense % 16 || (uintptr_t)padded % d.elem_bytes) return PINT_E_ARG;
+    const uint32_t S = total_bits(d);
+    const uintptr_t p0 = (uintptr_t)padded, d0 = (uintptr_t)dense;
+    if (p0 < d0 + dense_bytes(S, n) && d0 < p0 + n * d.elem_bytes) return PINT_E_ALIAS;  // no in-place conversion
+    return (int)(S <= 32 ? pack_unpack_w<uint32_t>(to_dense, d.elem_bytes, padded, dense, n, S, s)
+                         : pack_unpack_w<uint64_t>(to_dense, d.elem_bytes, padded, dense, n, S, s));
+}
+
+template <class W>
+cudaError_t planes_launch(bool to_dense, bool is_signed, int pb, const void* dense, const dense::dense_fields& f, size_t n,
+                          uint32_t S, cudaStream_t s)
+{
+    const launch_geom g = geom();
+    void* dn = const_cast<void*>(dense);
+    if (to_dense)
+        return pb == 4 ? dense::launch_dense_insert<W, W, dense::SIDE_PLANES, 4>(nullptr, dn, n, S, f, s, g)
+                       : dense::launch_dense_insert<W, W, dense::SIDE_PLANES, 8>(nullptr, dn, n, S, f, s, g);
+    if (is_signed)
+        return pb == 4 ? dense::launch_dense_extract<W, W, dense::SIDE_PLANES, 4, true>(dense, nullptr, n, S, f, s, g)
+                       : dense::launch_dense_extract<W, W, dense::SIDE_PLANES, 8, true>(dense, nullptr, n, S, f, s, g);
+    return pb == 4 ? dense::launch_dense_extract<W, W, dense::SIDE_PLANES, 4, false>(dense, nullptr, n, S, f, s, g)
+                   : dense::launch_dense_extract<W, W, dense::SIDE_PLANES, 8, false>(dense, nullptr, n, S, f, s, g);
+}
+
+int planes_impl(bool to_dense, const pint_layout* layout, int is_signed, const void* dense, const void* const* planes,
+                int plane_bytes, size_t n, cudaStream_t s)
+{
+    layout_desc d;
+    if (int rc = check_layout(layout, &d)) return rc;
+    if (plane_bytes != 4 && plane_bytes != 8) return PINT_E_PLANE_BYTES;
+    if (n == 0) return PINT_OK;
+    if (!dense || !planes) return PINT_E_NULL;
+    if ((uintptr_t)dense % 16) return PINT_E_ARG;
+    dense::dense_fields f = make_fields(d);
+    for (uint32_t i = 0; i < d.nfields; ++i) {
+        if (!planes[i] && to_dense) return PINT_E_NULL;
+        if ((uintptr_t)planes[i] % plane_bytes) return PINT_E_ARG;
+        f.planes.p[i] = const_cast<void*>(planes[i]);
+    }
+    const uint32_t S = total_bits(d);
+    return (int)(S <= 32 ? planes_launch<uint32_t>(to_dense, is_signed != 0, plane_bytes, dense, f, n, S, s)
+                         : planes_launch<uint64_t>(to_dense, is_signed != 0, plane_bytes, dense, f, n, S, s));
+}
+
+}  // namespace
+}  // namespace pint_cuda_impl
+
+using namespace pint_cuda_impl;
+
+extern "C" {
+
+size_t pint_cuda_dense_bytes(const pint_layout* layout, size_t n)
+{
+    layout_desc d;
+    if (check_layout(layout, &d)) return 0;
+    return dense_bytes(total_bits(d), n);
+}
+
+int pint_cuda_dense_binary(int op, const pint_layout* layout, const void* a, const void* b, void* out, size_t n,
+                           pint_stream_t stream)
+{
+    layout_desc d;
+    if (int rc = check_layout(layout, &d)) return rc;
+    if (op < 0 || op >= PINT_NUM_BINARY_OPS) return PINT_E_OP;
+    if (n == 0) return PINT_OK;
+    if (!a || !b || !out) return PINT_E_NULL;
+    if (((uintptr_t)a | (uintptr_t)b | (uintptr_t)out) % 16) return PINT_E_ARG;
+    const uint32_t S = total_bits(d);
+    const size_t bytes = dense_bytes(S, n);
+    auto partial = [&](const void* in) {
+        const uintptr_t i = (uintptr_t)in, o = (uintptr_t)out;
+        return in != out && i < o + bytes && o < i + bytes;
+    };
+    if (partial(a) || partial(b)) return PINT_E_ALIAS;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (S == 8 || S == 16 || S == 32 || S == 64) {
+        // no padding to remove: the dense stream IS the padded array of make_packed_int's Integer;
+        // run the vector kernels over the whole buffer (the zero tail stays zero: op(0, 0) == 0)
+        pint_layout p = *layout;
+        p.elem_bytes = S / 8;
+        const size_t total = bytes / p.elem_bytes;
+        // inputs may carry garbage above n*S in the last vector: the padded kernels would keep it
+        // for | & ^; only whole elements exist here (S divides 128), so process n and zero the rest
+        if (int rc = binary_impl(op, false, &p, a, b, out, n, s)) return rc;
+        if (total > n) return (int)cudaMemsetAsync((char*)out + n * p.elem_bytes, 0, (total - n) * p.elem_bytes, s);
+        return PINT_OK;
+    }
+    const launch_geom g = geom();
+    if (!opts().force_generic)
+        if (const dense_layout_kernels* k = find_dense_static(d)) return (int)k->binary[op](a, b, out, n, s, g, tuning());
+    auto ops = std::make_integer_sequence<int, pint::cuda::OP_NUM_BINARY>();
+    return (int)(S <= 32 ? dense_generic<uint32_t>(op, d, S, a, b, out, n, s, g, ops)
+                         : dense_generic<uint64_t>(op, d, S, a, b, out, n, s, g, ops));
+}
+
+int pint_cuda_dense_pack(const pint_layout* layout, const void* padded, void* dense, size_t n, pint_stream_t stream)
+{
+    return convert_impl(true, layout, padded, dense, n, (cudaStream_t)stream);
+}
+
+int pint_cuda_dense_unpack(const pint_layout* layout, const void* dense, void* padded, size_t n, pint_stream_t stream)
+{
+    return convert_impl(false, layout, padded, const_cast<void*>(dense), n, (cudaStream_t)stream);
+}
+
+int pint_cuda_dense_to_planes(const pint_layout* layout, int is_signed, const void* dense, void* const* planes,
+                              int plane_bytes, size_t n, pint_stream_t stream)
+{
+    return planes_impl(false, layout, is_signed, dense, planes, plane_bytes, n, (cudaStream_t)stream);
+}
+
+int pint_cuda_dense_from_planes(const pint_layout* layout, const void* const* planes, int plane_bytes, void* dense,
+                                size_t n, pint_stream_t stream)
+{
+    return planes_impl(true, layout, 0, dense, planes, plane_bytes, n, (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,44 @@
+// dense_static.cu -- instantiates the dense bit-stream kernels for the layouts of dense_layouts.def.
+#include "dense_registry.hpp"
+
+namespace pint_cuda_impl {
+namespace {
+
+using namespace pint::cuda;
+using namespace pint::cuda::kernels;
+
+template <class SL, int Op>
+cudaError_t dense_entry(const void* a, const void* b, void* out, size_t n, cudaStream_t s, const launch_geom& g,
+                        const dense_tuning& tune)
+{
+    using W = typename SL::word;
+    using Fn = swar_fn<Op, static_masks<SL>>;
+    using Geo = dense::static_geom<W, SL::masks.total_bits>;
+    return dense::launch_dense_binary(a, b, out, n, Fn{}, Geo{1}, s, g, tune);
+}
+
+template <class SL, int... Ops>
+dense_layout_kernels make_dense(std::integer_sequence<int, Ops...>)
+{
+    dense_layout_kernels k{};
+    k.nfields = SL::desc.nfields;
+    for (uint32_t i = 0; i < k.nfields; ++i) k.bits[i] = SL::desc.bits[i];
+    ((k.binary[Ops] = &dense_entry<SL, Ops>), ...);
+    return k;
+}
+
+}  // namespace
+
+const dense_layout_kernels* find_dense_static(const layout_desc& d)
+{
+    static const dense_layout_kernels tab[] = {
+#define X(W, ...) make_dense<static_layout<W, __VA_ARGS__>>(std::make_integer_sequence<int, OP_NUM_BINARY>()),
+#include "dense_layouts.def"
+#undef X
+    };
+    for (const dense_layout_kernels& k : tab)
+        if (k.nfields == d.nfields && std::memcmp(k.bits, d.bits, d.nfields) == 0) return &k;
+    return nullptr;
+}
+
+}  // namespace pint_cuda_impl

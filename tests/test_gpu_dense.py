@@ -1,0 +1,150 @@
+"""GPU parity of the dense bit-stream format (pint_cuda_dense_*), through the C ABI, against the
+oracle (dense op == pack(op(unpack)) with the reference-pinned per-element op).  Bit-exact."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import OPS
+
+pytestmark = pytest.mark.gpu
+
+from gpu_util import to_dev, to_np  # noqa: E402
+
+# static dense kernels exist for the first five (pint_b200/csrc/dense_layouts.def); the rest run the
+# run-time-geometry kernel; S in {8,16,32,64} is the padded format itself
+LAYOUTS = [(4, (8, 8, 8)), (4, (10, 10, 10)), (2, (12,)), (4, (7, 9, 3)), (8, (16, 16, 16)),
+           (4, (5, 6, 5, 3)), (8, (10, 10, 10, 10)), (8, (21, 21, 21)), (1, (3,)), (4, (1,)), (8, (31, 2)), (8, (1, 62)),
+           (8, (3, 7, 11, 13, 17, 12)), (4, (11, 11, 9)), (2, (5, 6, 5)), (8, (64,)), (4, (8, 8, 8, 8)), (1, (2, 3, 3))]
+SIZES = [1, 2, 5, 127, 128, 129, 4096, (1 << 18) + 77]
+
+
+@pytest.fixture(scope="module")
+def P():
+    import pint_b200
+    from pint_b200 import dense, ops
+    assert torch.cuda.is_available()
+    return pint_b200, ops, dense
+
+
+@pytest.fixture(params=["static_or_generic", "force_generic"])
+def mode(request, P):
+    _, ops, _ = P
+    ops.set_option("force_generic", 1 if request.param == "force_generic" else 0)
+    yield request.param
+    ops.set_option("force_generic", 0)
+
+
+def dev_bytes(x):
+    return torch.from_numpy(np.ascontiguousarray(x).copy()).cuda()
+
+
+@pytest.mark.parametrize("eb,bits", LAYOUTS)
+def test_dense_binary_vs_oracle(P, oracle, eb, bits, mode):
+    pint_b200, ops, dense = P
+    L = pint_b200.Layout(eb, *bits)
+    for n in SIZES:
+        x, y = oracle.fill(eb, n, 0xD0 + n), oracle.fill(eb, n, 0xE0 + n)
+        dx_h, dy_h = oracle.dense_pack(eb, bits, x), oracle.dense_pack(eb, bits, y)
+        assert dense.nbytes(L, n) == dx_h.size
+        if (n * sum(bits)) % 128:
+            dx_h[-1] |= 0x80  # garbage above n*S must not reach the output
+        dx, dy = dev_bytes(dx_h), dev_bytes(dy_h)
+        for op in OPS:
+            got = dense.binary(op, L, dx, dy, n).cpu().numpy()
+            np.testing.assert_array_equal(got, oracle.dense_binary(op, eb, bits, dx_h, dy_h, n),
+                                          err_msg=f"{L} {op} n={n} {mode}")
+
+
+@pytest.mark.parametrize("eb,bits", LAYOUTS[:8])
+def test_dense_in_place_and_tiles(P, oracle, eb, bits):
+    """In place on either operand; every tile geometry option gives the same stream."""
+    pint_b200, ops, dense = P
+    L = pint_b200.Layout(eb, *bits)
+    n = (1 << 19) + 3
+    x, y = oracle.fill(eb, n, 21), oracle.fill(eb, n, 22)
+    dx_h, dy_h = oracle.dense_pack(eb, bits, x), oracle.dense_pack(eb, bits, y)
+    want = oracle.dense_binary("sub_signed_saturate", eb, bits, dx_h, dy_h, n)
+    for threads, tile in ((0, 0), (32, 4096), (64, 0), (256, 32768), (128, 65536)):
+        ops.set_option("dense_threads", threads)
+        ops.set_option("dense_tile_bytes", tile)
+        try:
+            dx, dy = dev_bytes(dx_h), dev_bytes(dy_h)
+            dense.binary("sub_signed_saturate", L, dx, dy, n, out=dx)
+            np.testing.assert_array_equal(dx.cpu().numpy(), want, err_msg=f"{L} threads={threads} tile={tile}")
+            dx = dev_bytes(dx_h)
+            dense.binary("sub_signed_saturate", L, dx, dy, n, out=dy)
+            np.testing.assert_array_equal(dy.cpu().numpy(), want)
+        finally:
+            ops.set_option("dense_threads", 0)
+            ops.set_option("dense_tile_bytes", 0)
+
+
+@pytest.mark.parametrize("eb,bits", LAYOUTS)
+def test_dense_pack_unpack_planes(P, oracle, eb, bits):
+    pint_b200, ops, dense = P
+    L = pint_b200.Layout(eb, *bits)
+    S = sum(bits)
+    for n in SIZES:
+        x = oracle.fill(eb, n, 0xF0 + n)
+        want = oracle.dense_pack(eb, bits, x)
+        xd = to_dev(x)
+        d = dense.pack(L, xd)
+        np.testing.assert_array_equal(d.cpu().numpy(), want, err_msg=f"pack {L} n={n}")
+        back = to_np(dense.unpack(L, d, n))
+        np.testing.assert_array_equal(back, x & np.array((1 << S) - 1, dtype=x.dtype), err_msg=f"unpack {L} n={n}")
+        masked = x & np.array((1 << S) - 1, dtype=x.dtype)
+        for signed in (False, True):
+            for pb in (4, 8):
+                planes = dense.to_planes(L, d, n, signed=signed, plane_bytes=pb)
+                ref_planes = oracle.unpack(eb, bits, masked, signed, pb)
+                for f in range(len(bits)):
+                    np.testing.assert_array_equal(to_np(planes[f], ref_planes[f].dtype), ref_planes[f],
+                                                  err_msg=f"to_planes {L} f={f} signed={signed} pb={pb} n={n}")
+        # planes -> dense (truncating constructor): arbitrary int32 plane values, not just in-range ones
+        rng = np.random.default_rng(n)
+        raw = [rng.integers(-2**31, 2**31, n, dtype=np.int64).astype(np.int32) for _ in bits]
+        want2 = oracle.dense_pack(eb, bits, oracle.repack(eb, bits, raw, 4))
+        got2 = dense.from_planes(L, [to_dev(p) for p in raw])
+        np.testing.assert_array_equal(got2.cpu().numpy(), want2, err_msg=f"from_planes {L} n={n}")
+
+
+def test_dense_round_trip_properties_large(P):
+    """2^27 RGB24 elements (384 MiB per stream): pack/unpack round trip, op identities."""
+    pint_b200, ops, dense = P
+    L = pint_b200.Layout(4, 8, 8, 8)
+    n = 1 << 27
+    x = torch.empty(n, dtype=torch.uint32, device="cuda")
+    y = torch.empty(n, dtype=torch.uint32, device="cuda")
+    ops.fill_splitmix(x, 1)
+    ops.fill_splitmix(y, 2)
+    dx, dy = dense.pack(L, x), dense.pack(L, y)
+    mask = torch.tensor(0xFFFFFF, dtype=torch.int64, device="cuda")
+    assert torch.equal(dense.unpack(L, dx, n).view(torch.int32) , (x.view(torch.int32) & 0xFFFFFF))
+    # dense op == padded op then pack
+    for op in ("add_unsigned_saturate", "sub_signed_saturate", "max_signed"):
+        got = dense.binary(op, L, dx, dy, n)
+        want = dense.pack(L, ops.binary(op, L, x, y))
+        assert torch.equal(got, want), op
+    # (a - b) + b == a wherever nothing wraps differently: wrap ops are exact inverses
+    d = dense.binary("sub_wrap", L, dx, dy, n)
+    assert torch.equal(dense.binary("add_wrap", L, d, dy, n), dx)
+    del mask
+
+
+def test_dense_error_codes(P):
+    pint_b200, ops, dense = P
+    from pint_b200 import _lib
+    lib = _lib.lib()
+    L = pint_b200.Layout(4, 8, 8, 8)
+    buf = torch.zeros(4096, dtype=torch.uint8, device="cuda")
+    p = buf.data_ptr()
+    assert lib.pint_cuda_dense_binary(0, L.ref, p + 4, p + 1024, p + 2048, 10, None) == -15   # misaligned stream
+    assert lib.pint_cuda_dense_binary(99, L.ref, p, p + 1024, p + 2048, 10, None) == -10
+    assert lib.pint_cuda_dense_binary(0, L.ref, p, p + 1024, p + 16, 100, None) == -14       # partial overlap
+    assert lib.pint_cuda_dense_binary(0, L.ref, None, p, p, 10, None) == -1
+    assert lib.pint_cuda_dense_binary(0, L.ref, p, p, p, 0, None) == 0
+    assert lib.pint_cuda_dense_bytes(L.ref, 5) == 16 and lib.pint_cuda_dense_bytes(L.ref, 6) == 32
+    planes = (C.c_void_p * 3)(p, p + 1024, p + 2048)
+    assert lib.pint_cuda_dense_to_planes(L.ref, 0, p + 3072, planes, 3, 4, None) == -13
