@@ -25,9 +25,10 @@
 // not 8, 16, 32 or 64 (those ARE the padded format), so the chunk stride is
 // conflict-free in shared memory.
 //
-// Thread mapping for format conversions ("element" mapping): one thread per
-// element extracts (funnel shift at a per-lane offset) or deposits (shared-memory
-// atomicOr into a zeroed tile) so that the padded / plane side stays coalesced.
+// Thread mapping for format conversions (cuda_kernels_dense_convert.cuh): dense ->
+// padded/planes takes one thread per ELEMENT (funnel shift at a per-lane offset out
+// of the staged tile); padded/planes -> dense takes one thread per OUTPUT WORD, so
+// both sides stay coalesced and nothing needs atomics.
 #pragma once
 
 #include "cuda_kernels.cuh"
@@ -72,74 +73,143 @@ __device__ __forceinline__ W spill_l(W r, uint32_t sh)
 
 // ---------------------------------------------------------------------------
 // Chunk geometry: compile-time (static layouts) or run-time (constant bank).
+// EB = bits of one SLOT of the processing word: elements narrower than 17 (9) bits
+// are gathered two (four) to a 32-bit word at slot boundaries, which is exactly the
+// replicated-mask form the SWAR functors use for uint16_t (uint8_t) packs, so one
+// functor call serves 2 (4) elements.
 
-template <class W, uint32_t S_>
+template <class W, uint32_t S_, uint32_t EB_ = 8 * sizeof(W)>
 struct static_geom {
     static constexpr bool is_static = true;
     static constexpr uint32_t WB = 8 * sizeof(W);
-    static constexpr uint32_t kS = S_, kCw = S_ / gcd_u32(S_, WB), kG = WB / gcd_u32(S_, WB);
+    static constexpr uint32_t kS = S_, kCw = S_ / gcd_u32(S_, WB), kG = WB / gcd_u32(S_, WB), kEB = EB_, kEPW = WB / EB_;
+    static_assert(kG % kEPW == 0, "a chunk holds a whole number of gathered words");
     uint32_t chunks_per_thread;
     __host__ __device__ static constexpr uint32_t S() { return kS; }
     __host__ __device__ static constexpr uint32_t Cw() { return kCw; }
     __host__ __device__ static constexpr uint32_t G() { return kG; }
+    __host__ __device__ static constexpr uint32_t EB() { return kEB; }
 };
 
 template <class W>
 struct runtime_geom {
     static constexpr bool is_static = false;
     static constexpr uint32_t WB = 8 * sizeof(W);
-    uint32_t s, cw, g;
+    uint32_t s, cw, g, eb;
     uint32_t chunks_per_thread;
     runtime_geom() = default;
-    explicit runtime_geom(uint32_t S_) : s(S_), cw(S_ / gcd_u32(S_, WB)), g(WB / gcd_u32(S_, WB)), chunks_per_thread(1) {}
+    // slot_bits: 8 * sizeof(Integer) of the layout the masks were generated for
+    runtime_geom(uint32_t S_, uint32_t slot_bits)
+        : s(S_), cw(S_ / gcd_u32(S_, WB)), g(WB / gcd_u32(S_, WB)), eb(slot_bits), chunks_per_thread(1) {}
     __host__ __device__ uint32_t S() const { return s; }
     __host__ __device__ uint32_t Cw() const { return cw; }
     __host__ __device__ uint32_t G() const { return g; }
+    __host__ __device__ uint32_t EB() const { return eb; }
 };
 
 // One chunk, in place: A[0..Cw) <- op(A, B) element by element.  A and B are
-// shared-memory pointers to the same chunk of the two operand tiles.
+// shared-memory pointers to the same chunk of the two operand tiles.  An input
+// window (two words per operand) and an output window (two words) slide over the
+// chunk; the output never runs ahead of the input, and a word is written only
+// after every element that touches it has been read, so in place is safe.
 template <class Fn, class Geo>
 __device__ __forceinline__ void process_chunk(typename Fn::word* A, const typename Fn::word* B, const Fn& fn, const Geo& geo)
 {
     using W = typename Fn::word;
     constexpr uint32_t WB = 8 * sizeof(W);
-    const uint32_t S = geo.S(), Cw = geo.Cw();
+    const uint32_t S = geo.S(), Cw = geo.Cw(), EB = geo.EB();
     const W SM = ones_w<W>(S);
     W ca = A[0], cb = B[0];
     W na = Cw > 1 ? A[1] : W(0), nb = Cw > 1 ? B[1] : W(0);
     W ocur = 0, onxt = 0;
-    uint32_t sh = 0, w = 0;
-    auto element = [&]() {
-        const W xa = funnel_r(ca, na, sh), xb = funnel_r(cb, nb, sh);
-        // Bits above S of xa / xb belong to the next element.  The functors ignore them for
-        // add/sub (M1 and H cover field bits only), pass them through for | & ^ and take them
-        // from b for min/max, so masking the RESULT is enough.
-        const W r = fn(xa, xb) & SM;
-        ocur |= r << sh;
-        onxt |= spill_l(r, sh);
-        sh += S;
-        if (sh >= WB) {  // the window moves on by one word (S <= WB: never by more)
-            sh -= WB;
-            A[w] = ocur;  // every element that touches word w has been read: in place is safe
-            ocur = onxt;
-            onxt = 0;
-            ++w;
+    uint32_t shi = 0, wi = 0, sho = 0, wo = 0;
+    auto take = [&](W& xa, W& xb) {
+        xa = funnel_r(ca, na, shi);
+        xb = funnel_r(cb, nb, shi);
+        shi += S;
+        if (shi >= WB) {  // the window moves on by one word (S <= WB: never by more)
+            shi -= WB;
+            ++wi;
             ca = na;
             cb = nb;
-            na = w + 1 < Cw ? A[w + 1] : W(0);
-            nb = w + 1 < Cw ? B[w + 1] : W(0);
+            na = wi + 1 < Cw ? A[wi + 1] : W(0);
+            nb = wi + 1 < Cw ? B[wi + 1] : W(0);
         }
+    };
+    auto put = [&](W r) {
+        ocur |= r << sho;
+        onxt |= spill_l(r, sho);
+        sho += S;
+        if (sho >= WB) {
+            sho -= WB;
+            A[wo] = ocur;
+            ocur = onxt;
+            onxt = 0;
+            ++wo;
+        }
+    };
+    auto group = [&]() {  // run-time slots: 2 or 4 elements per functor call
+        W xa = 0, xb = 0;
+        for (uint32_t k = 0; k < WB; k += EB) {
+            W ta, tb;
+            take(ta, tb);
+            xa |= (ta & SM) << k;
+            xb |= (tb & SM) << k;
+        }
+        const W r = fn(xa, xb);
+        for (uint32_t k = 0; k < WB; k += EB) put((r >> k) & SM);
     };
     if constexpr (Geo::is_static) {
 #pragma unroll
-        for (uint32_t e = 0; e < Geo::kG; ++e) element();
-    } else {
+        for (uint32_t e = 0; e < Geo::kG; e += Geo::kEPW) {
+            if constexpr (Geo::kEPW == 1) {
+                // Bits above S of xa / xb belong to the next element.  The functors ignore them for
+                // add/sub (M1 and H cover field bits only), pass them through for | & ^ and take them
+                // from b for min/max, so masking the RESULT is enough.
+                W xa, xb;
+                take(xa, xb);
+                put(fn(xa, xb) & SM);
+            } else {
+                W xa = 0, xb = 0;
+#pragma unroll
+                for (uint32_t k = 0; k < Geo::kEPW; ++k) {
+                    W ta, tb;
+                    take(ta, tb);
+                    xa |= (ta & SM) << (k * Geo::kEB);
+                    xb |= (tb & SM) << (k * Geo::kEB);
+                }
+                const W r = fn(xa, xb);
+#pragma unroll
+                for (uint32_t k = 0; k < Geo::kEPW; ++k) put((r >> (k * Geo::kEB)) & SM);
+            }
+        }
+    } else if (EB == WB) {
+        // one element per word: input and output windows move together -- one shift, one branch
         const uint32_t G = geo.G();
-        for (uint32_t e = 0; e < G; ++e) element();
+        uint32_t sh = 0, w = 0;
+        for (uint32_t e = 0; e < G; ++e) {
+            const W r = fn(funnel_r(ca, na, sh), funnel_r(cb, nb, sh)) & SM;
+            ocur |= r << sh;
+            onxt |= spill_l(r, sh);
+            sh += S;
+            if (sh >= WB) {
+                sh -= WB;
+                A[w] = ocur;
+                ocur = onxt;
+                onxt = 0;
+                ++w;
+                ca = na;
+                cb = nb;
+                na = w + 1 < Cw ? A[w + 1] : W(0);
+                nb = w + 1 < Cw ? B[w + 1] : W(0);
+            }
+        }
+    } else {
+        const uint32_t G = geo.G(), step = WB / EB;
+        for (uint32_t e = 0; e < G; e += step) group();
     }
     // G * S == Cw * WB: the last element ends exactly on the chunk's last bit, so the last
-    // word was flushed by the branch above and sh is back at 0.
+    // word was flushed by put() and both windows are back at shift 0.
 }
 
 // zero the bits of `word` (which starts at bit `start` of the tile) at or above bit `limit`

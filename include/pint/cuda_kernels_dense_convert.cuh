@@ -5,10 +5,9 @@
 //     tiles), thread e takes element e with a funnel shift at its own bit offset and
 //     writes the padded element (or its fields: get / get_signed, pint.hpp:799-822)
 //     with coalesced stores.
-//   dense_insert_kernel: thread e reads the padded element (or builds it from the
-//     planes: truncating field constructor, pint.hpp:770-774, 592-601) with
-//     coalesced loads and ORs it into a zeroed shared tile with shared-memory
-//     atomics (neighbouring elements share words); the tile leaves by TMA.
+//   dense_insert_kernel: one thread per output word gathers the padded elements (or
+//     builds them from the planes: truncating field constructor, pint.hpp:770-774,
+//     592-601) that overlap its word and stores it; no shared memory, no atomics.
 // Bytes per element: S/8 on the dense side + sizeof(Integer) (or P*F) on the other.
 #pragma once
 
@@ -86,63 +85,71 @@ __global__ void dense_extract_kernel(const uint4* dense, Elem* padded, size_t n,
     }
 }
 
-template <class W>
-__device__ __forceinline__ void smem_or(W* p, W v)
-{
-    if constexpr (sizeof(W) == 4) atomicOr(reinterpret_cast<unsigned int*>(p), (unsigned int)v);
-    else atomicOr(reinterpret_cast<unsigned long long*>(p), (unsigned long long)v);
-}
-
+// Insert ("word-owner" mapping): the padded elements (or the F planes) of a tile are
+// staged in shared memory with coalesced, independent loads; then one thread per
+// OUTPUT word gathers the elements that overlap its word -- word j of the tile holds
+// (parts of) elements floor(j*WB/S) .. floor(((j+1)*WB-1)/S) -- shifts each into place
+// and stores the finished word (consecutive threads, consecutive words).  No atomics.
+// History (profiles/r01e_dense_sweep.jsonl, r01g_dense.jsonl): OR-ing elements into a
+// zeroed shared tile with atomicOr ran at 3.1-3.9 TB/s; gathering straight from global
+// memory (dependent loads in a data-dependent loop, one word per thread) at 1.7-3.2.
 template <class W, class Elem, int Side, int PlaneBytes>
-__global__ void dense_insert_kernel(const Elem* padded, uint4* dense, size_t n, uint32_t S, uint32_t tile_elems,
-                                    size_t total_vec, const __grid_constant__ dense_fields f)
+__global__ void __launch_bounds__(256)
+dense_insert_kernel(const Elem* padded, W* dense, size_t n, uint32_t S, uint32_t tile_elems, size_t total_words,
+                    const __grid_constant__ dense_fields f)
 {
     constexpr uint32_t WB = 8 * sizeof(W);
+    using ST = typename std::conditional<PlaneBytes == 8, int64_t, int32_t>::type;
+    using Staged = typename std::conditional<Side == SIDE_PADDED, Elem, ST>::type;
     extern __shared__ __align__(128) unsigned char dense_smem[];
-    W* D = reinterpret_cast<W*>(dense_smem);
+    Staged* tile = reinterpret_cast<Staged*>(dense_smem);
     const uint32_t T = blockDim.x;
-    const uint32_t tile_vecs = uint32_t(uint64_t(tile_elems) * S / 128);
-    const uint32_t tile_bytes = tile_vecs * 16;
     const size_t t = blockIdx.x;
     const size_t first = t * tile_elems;
     const uint32_t cnt = uint32_t(n - first < tile_elems ? n - first : tile_elems);
-    const bool whole = (t + 1) * size_t(tile_vecs) <= total_vec;
-    for (uint32_t v = threadIdx.x; v <= tile_vecs; v += T)  // one vector more: spill target of the last element
-        reinterpret_cast<uint4*>(D)[v] = make_uint4(0, 0, 0, 0);
+    const uint32_t nsrc = Side == SIDE_PADDED ? 1u : f.t.nfields;
+    for (uint32_t k = 0; k < nsrc; ++k) {
+        const Staged* src = (Side == SIDE_PADDED ? reinterpret_cast<const Staged*>(padded)
+                                                 : static_cast<const Staged*>(f.planes.p[k])) + first;
+        Staged* dst = tile + size_t(k) * tile_elems;
+        if (cnt == tile_elems && (reinterpret_cast<uintptr_t>(src) & 15u) == 0) {
+            const uint32_t nv = tile_elems * uint32_t(sizeof(Staged)) / 16;  // tile_elems is a multiple of 128
+#pragma unroll 4
+            for (uint32_t v = threadIdx.x; v < nv; v += T)
+                reinterpret_cast<uint4*>(dst)[v] = ld16<CACHE_STREAMING>(reinterpret_cast<const uint4*>(src) + v);
+        } else {
+#pragma unroll 4
+            for (uint32_t i = threadIdx.x; i < tile_elems; i += T) dst[i] = i < cnt ? src[i] : Staged(0);
+        }
+    }
     __syncthreads();
     const W SM = ones_w<W>(S);
-    for (uint32_t e = threadIdx.x; e < cnt; e += T) {
-        W x;
-        if constexpr (Side == SIDE_PADDED) {
-            x = W(padded[first + e]) & SM;
-        } else {
-            x = 0;
-            for (uint32_t i = 0; i < f.t.nfields; ++i) {
-                // 4-byte planes are int32_t values converted to Integer (the field constructor's
-                // parameters are value_type, pint.hpp:771-772): sign-extend before truncating
-                using ST = typename std::conditional<PlaneBytes == 8, int64_t, int32_t>::type;
-                const ST v = static_cast<const ST*>(f.planes.p[i])[first + e];
-                x |= (W(int64_t(v)) & ones_w<W>(f.t.bits[i])) << f.t.off[i];  // make_truncated_int, pint.hpp:390-407
+    const uint32_t tile_words = uint32_t(uint64_t(tile_elems) * S / WB);
+    for (uint32_t j = threadIdx.x; j < tile_words; j += T) {
+        const size_t gj = t * size_t(tile_words) + j;
+        if (gj >= total_words) break;
+        const uint32_t bit0 = j * WB;
+        uint32_t e = bit0 / S;
+        int32_t rel = int32_t(e * S) - int32_t(bit0);  // in (-S, 0]
+        W acc = 0;
+        while (rel < int32_t(WB) && e < tile_elems) {
+            W x;
+            if constexpr (Side == SIDE_PADDED) {
+                x = W(tile[e]) & SM;
+            } else {
+                x = 0;
+                for (uint32_t i = 0; i < f.t.nfields; ++i) {
+                    // plane values are signed integers converted to Integer (the field constructor's
+                    // parameters are value_type, pint.hpp:771-772): sign-extend, then truncate to the field
+                    const ST v = tile[size_t(i) * tile_elems + e];
+                    x |= (W(int64_t(v)) & ones_w<W>(f.t.bits[i])) << f.t.off[i];  // make_truncated_int, pint.hpp:390-407
+                }
             }
+            acc |= rel >= 0 ? W(x << rel) : W(x >> (-rel));
+            ++e;
+            rel += int32_t(S);
         }
-        const uint64_t p = uint64_t(e) * S;
-        const uint32_t w = uint32_t(p / WB), sh = uint32_t(p % WB);
-        smem_or(D + w, W(x << sh));
-        if (sh + S > WB) smem_or(D + w + 1, spill_l(x, sh));
-    }
-    if (whole) {
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            bulk_store(dense + t * tile_vecs, D, tile_bytes, evict_first_policy());
-            bulk_wait_read<0>();
-        }
-    } else {
-        __syncthreads();
-        for (uint32_t v = threadIdx.x; v < tile_vecs; v += T) {
-            const size_t gv = t * tile_vecs + v;
-            if (gv < total_vec) st16<CACHE_STREAMING>(dense + gv, reinterpret_cast<const uint4*>(D)[v]);
-        }
+        dense[gj] = acc;
     }
 }
 
@@ -175,13 +182,22 @@ cudaError_t launch_dense_insert(const void* other, void* dense, size_t n, uint32
                                 cudaStream_t stream, const launch_geom& g)
 {
     if (n == 0) return cudaSuccess;
-    const uint32_t te = convert_tile_elems(S);
-    const size_t total_vec = size_t((uint64_t(n) * S + 127) / 128);
+    const size_t total_words = size_t((uint64_t(n) * S + 127) / 128) * (16 / sizeof(W));
+    // staged bytes per element: the padded element, or one value per plane
+    const uint32_t per_elem = Side == SIDE_PADDED ? uint32_t(sizeof(Elem)) : uint32_t(PlaneBytes) * f.t.nfields;
+    uint32_t te = (32768u / per_elem) & ~127u;
+    if (te < 128) te = 128;
+    if (te > 8192) te = 8192;
+    const size_t smem = size_t(te) * per_elem;
     const size_t ntiles = (n + te - 1) / te;
-    const size_t smem = size_t(te) * S / 8 + 16;
     if (ntiles > 0x7FFFFFFFull) return cudaErrorInvalidValue;
-    dense_insert_kernel<W, Elem, Side, PlaneBytes><<<unsigned(ntiles), 256, smem, stream>>>(
-        static_cast<const Elem*>(other), static_cast<uint4*>(dense), n, S, te, total_vec, f);
+    auto kernel = dense_insert_kernel<W, Elem, Side, PlaneBytes>;
+    if (smem > 48 * 1024) {
+        cudaError_t rc = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+        if (rc != cudaSuccess) return rc;
+    }
+    kernel<<<unsigned(ntiles), 256, smem, stream>>>(static_cast<const Elem*>(other), static_cast<W*>(dense), n, S, te,
+                                                    total_words, f);
     count_launch(g);
     return cudaGetLastError();
 }

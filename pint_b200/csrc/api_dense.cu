@@ -23,12 +23,12 @@ size_t dense_bytes(uint32_t S, size_t n)
     return size_t((bits + 127) / 128) * 16;
 }
 
-// the dense stream seen as packed_int<Word, Bits...>: one element per processing word
-template <class W>
-layout_desc word_desc(const layout_desc& d)
+// The dense stream's elements as packed_int<make_packed_int's Integer, Bits...>: narrow
+// elements are processed several to a word, one per Integer-sized slot (replicated masks).
+layout_desc slot_desc(const layout_desc& d, uint32_t S)
 {
     layout_desc e = d;
-    e.elem_bytes = sizeof(W);
+    e.elem_bytes = storage_bytes(S);
     return e;
 }
 
@@ -44,10 +44,11 @@ template <class W, int... Ops>
 cudaError_t dense_generic(int op, const layout_desc& d, uint32_t S, const void* a, const void* b, void* out, size_t n,
                           cudaStream_t s, const launch_geom& g, std::integer_sequence<int, Ops...>)
 {
-    const runtime_masks<W> p(make_word_masks<W>(word_desc<W>(d)));
+    const layout_desc e = slot_desc(d, S);
+    const runtime_masks<W> p(make_word_masks<W>(e));
     cudaError_t rc = cudaErrorInvalidValue;
     ((op == Ops ? (rc = dense::launch_dense_binary(a, b, out, n, swar_fn<Ops, runtime_masks<W>>{p},
-                                                   dense::runtime_geom<W>(S), s, g, tuning()), 0) : 0), ...);
+                                                   dense::runtime_geom<W>(S, 8 * e.elem_bytes), s, g, tuning()), 0) : 0), ...);
     return rc;
 }
 

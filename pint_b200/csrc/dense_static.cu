@@ -13,7 +13,7 @@ cudaError_t dense_entry(const void* a, const void* b, void* out, size_t n, cudaS
 {
     using W = typename SL::word;
     using Fn = swar_fn<Op, static_masks<SL>>;
-    using Geo = dense::static_geom<W, SL::masks.total_bits>;
+    using Geo = dense::static_geom<W, SL::masks.total_bits, 8 * sizeof(typename SL::integer)>;
     return dense::launch_dense_binary(a, b, out, n, Fn{}, Geo{1}, s, g, tune);
 }
 

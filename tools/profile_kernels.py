@@ -34,5 +34,23 @@ for rep in range(2):
     ops.binary("add_signed_saturate", rt, a32, b32, out=o32)
     ops.shift_left(rt, a32, 3, out=o32)
     ops.pairs_reduce("add_signed_saturate", rt, a32)
+# dense bit-stream kernels: static RGB24 / 19-bit / 12-bit chunk kernels, run-time geometry, conversions
+from pint_b200 import dense  # noqa: E402
+nd = n
+for eb, bits in ((4, (8, 8, 8)), (4, (7, 9, 3)), (2, (12,)), (4, (5, 6, 5, 3))):
+    L = pint_b200.Layout(eb, *bits)
+    x = torch.empty(nd, dtype={2: torch.uint16, 4: torch.uint32}[eb], device="cuda")
+    ops.fill_splitmix(x, 5)
+    da = dense.pack(L, x)
+    ops.fill_splitmix(x, 6)
+    db = dense.pack(L, x)
+    do = torch.empty_like(da)
+    for rep in range(2):
+        dense.binary("add_signed_saturate", L, da, db, nd, out=do)
+        dense.binary("add_unsigned_saturate", L, da, db, nd, out=do)
+    dense.unpack(L, do, nd, out=x)
+    pl = dense.to_planes(L, do, nd, signed=True)
+    dense.from_planes(L, pl, out=do)
+    del x, da, db, do, pl
 torch.cuda.synchronize()
 print("ok", ops.launch_count())
