@@ -170,7 +170,8 @@ def workload_config(args, world, sample_log2=None):
         "workload": "C1: add_unsigned_saturate + add_signed_saturate over 2^%d packed_int<uint32_t,8,8,8,8> per GPU, "
                     "both ops per step (one pint_cuda_binary_multi launch: a,b read once, two outputs)" % args.log2,
         "layout": "packed_int<uint32_t,8,8,8,8>", "elements_per_gpu": 1 << args.log2,
-        "elements_per_step": len(OPS) * (1 << args.log2) * world, "bytes_per_element": BYTES_PER_ELEM,
+        "elements_per_step": len(OPS) * (1 << args.log2) * world,
+        "bytes_per_element": (2 + len(OPS)) * ELEM_BYTES, "bytes_per_element_single_op_pass": BYTES_PER_ELEM,
         "parallelism": "%d independent contiguous shard(s), no collective" % world,
         "l2": "inputs (2 x %.1f GiB per GPU) far larger than the 126 MB L2; no flush needed" % ((1 << args.log2) * 4 / 2 ** 30),
     }

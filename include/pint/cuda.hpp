@@ -150,6 +150,22 @@ PINT_CUDA_BINARY(min_signed, PINT_MIN_SIGNED)                        // pint.hpp
 PINT_CUDA_BINARY(max_signed, PINT_MAX_SIGNED)                        // pint.hpp:987-1004
 #undef PINT_CUDA_BINARY
 
+// Two (up to PINT_MAX_MULTI_OPS) operations on the SAME operands: pairs such as
+// add_unsigned_saturate + add_signed_saturate run as ONE pass that reads a and b once
+// (pint_cuda_binary_multi); outs[j][i] = ops[j](a[i], b[i]).  Outputs may not alias inputs.
+template <size_t NOps, class Integer, size_t Bits0, size_t... Bits>
+inline void binary_multi(const pint_op (&ops)[NOps], const packed_int<Integer, Bits0, Bits...>* a,
+                         const packed_int<Integer, Bits0, Bits...>* b,
+                         packed_int<Integer, Bits0, Bits...>* const (&outs)[NOps], size_t n, stream_t stream = nullptr)
+{
+    static_assert(NOps >= 1 && NOps <= PINT_MAX_MULTI_OPS, "1..PINT_MAX_MULTI_OPS operations");
+    const pint_layout l = detail::layout_of<Integer, Bits0, Bits...>::get();
+    int codes[NOps];
+    void* o[NOps];
+    for (size_t j = 0; j < NOps; ++j) { codes[j] = ops[j]; o[j] = outs[j]; }
+    check(pint_cuda_binary_multi((int)NOps, codes, &l, a, b, o, n, stream), "pint::cuda::binary_multi");
+}
+
 // Any of the above, computed as unpack -> per-field arithmetic -> repack in one kernel.
 template <class Integer, size_t Bits0, size_t... Bits>
 inline void fused_unpack_arith_repack(pint_op op, const packed_int<Integer, Bits0, Bits...>* a,
@@ -215,6 +231,103 @@ inline void repack(const Plane* const (&planes)[sizeof...(Bits) + 1], packed_int
     check(pint_cuda_repack(&l, p, (int)sizeof(Plane), packed, n, stream), "pint::cuda::repack");
 }
 
+// Dense bit-stream storage (include/pint_cuda.h, "dense" section): element i of
+// packed_int<Integer, Bits...> in bits [i*S, (i+1)*S) of a byte stream, S = sum(Bits).
+// The layout is a template argument (a stream has no element type): e.g.
+//     pint::cuda::dense::add_signed_saturate<rgb>(a, b, out, n, stream);
+namespace dense {
+
+typedef unsigned char stream_byte;
+
+template <class P> struct layout_from;
+template <class Integer, size_t Bits0, size_t... Bits>
+struct layout_from<packed_int<Integer, Bits0, Bits...> > {
+    static pint_layout get() { return detail::layout_of<Integer, Bits0, Bits...>::get(); }
+    typedef Integer integer;
+    static const size_t nfields = sizeof...(Bits) + 1;
+};
+
+// bytes of a dense stream of n elements (16-byte granular)
+template <class P>
+inline size_t bytes(size_t n)
+{
+    const pint_layout l = layout_from<P>::get();
+    return pint_cuda_dense_bytes(&l, n);
+}
+
+template <class P>
+inline void binary(pint_op op, const stream_byte* a, const stream_byte* b, stream_byte* out, size_t n,
+                   stream_t stream = nullptr)
+{
+    const pint_layout l = layout_from<P>::get();
+    check(pint_cuda_dense_binary(op, &l, a, b, out, n, stream), "pint::cuda::dense::binary");
+}
+
+#define PINT_CUDA_DENSE_BINARY(NAME, CODE)                                                                   \
+    template <class P>                                                                                       \
+    inline void NAME(const stream_byte* a, const stream_byte* b, stream_byte* out, size_t n, stream_t stream = nullptr) \
+    {                                                                                                        \
+        binary<P>(CODE, a, b, out, n, stream);                                                               \
+    }
+PINT_CUDA_DENSE_BINARY(add_wrap, PINT_ADD_WRAP)
+PINT_CUDA_DENSE_BINARY(add_unsigned_saturate, PINT_ADD_UNSIGNED_SATURATE)
+PINT_CUDA_DENSE_BINARY(add_signed_saturate, PINT_ADD_SIGNED_SATURATE)
+PINT_CUDA_DENSE_BINARY(sub_wrap, PINT_SUB_WRAP)
+PINT_CUDA_DENSE_BINARY(sub_unsigned_saturate, PINT_SUB_UNSIGNED_SATURATE)
+PINT_CUDA_DENSE_BINARY(sub_signed_saturate, PINT_SUB_SIGNED_SATURATE)
+PINT_CUDA_DENSE_BINARY(bit_or, PINT_OR)
+PINT_CUDA_DENSE_BINARY(bit_and, PINT_AND)
+PINT_CUDA_DENSE_BINARY(bit_xor, PINT_XOR)
+PINT_CUDA_DENSE_BINARY(min_unsigned, PINT_MIN_UNSIGNED)
+PINT_CUDA_DENSE_BINARY(max_unsigned, PINT_MAX_UNSIGNED)
+PINT_CUDA_DENSE_BINARY(min_signed, PINT_MIN_SIGNED)
+PINT_CUDA_DENSE_BINARY(max_signed, PINT_MAX_SIGNED)
+#undef PINT_CUDA_DENSE_BINARY
+
+// padded packed_int array <-> dense stream
+template <class Integer, size_t Bits0, size_t... Bits>
+inline void pack(const packed_int<Integer, Bits0, Bits...>* padded, stream_byte* dense_out, size_t n, stream_t stream = nullptr)
+{
+    const pint_layout l = detail::layout_of<Integer, Bits0, Bits...>::get();
+    check(pint_cuda_dense_pack(&l, padded, dense_out, n, stream), "pint::cuda::dense::pack");
+}
+
+template <class Integer, size_t Bits0, size_t... Bits>
+inline void unpack(const stream_byte* dense_in, packed_int<Integer, Bits0, Bits...>* padded, size_t n, stream_t stream = nullptr)
+{
+    const pint_layout l = detail::layout_of<Integer, Bits0, Bits...>::get();
+    check(pint_cuda_dense_unpack(&l, dense_in, padded, n, stream), "pint::cuda::dense::unpack");
+}
+
+// get<I> / get_signed<I> of every field straight from a dense stream, and the truncating
+// field constructor straight into one
+template <class P, class Plane>
+inline void to_planes(const stream_byte* dense_in, Plane* const (&planes)[layout_from<P>::nfields], size_t n,
+                      stream_t stream = nullptr)
+{
+    static_assert(std::is_integral<Plane>::value && (sizeof(Plane) == 4 || sizeof(Plane) == 8),
+                  "planes are 32- or 64-bit integers");
+    const pint_layout l = layout_from<P>::get();
+    void* p[layout_from<P>::nfields];
+    for (size_t i = 0; i < layout_from<P>::nfields; ++i) p[i] = planes[i];
+    check(pint_cuda_dense_to_planes(&l, std::is_signed<Plane>::value ? 1 : 0, dense_in, p, (int)sizeof(Plane), n, stream),
+          "pint::cuda::dense::to_planes");
+}
+
+template <class P, class Plane>
+inline void from_planes(const Plane* const (&planes)[layout_from<P>::nfields], stream_byte* dense_out, size_t n,
+                        stream_t stream = nullptr)
+{
+    static_assert(std::is_integral<Plane>::value && (sizeof(Plane) == 4 || sizeof(Plane) == 8),
+                  "planes are 32- or 64-bit integers");
+    const pint_layout l = layout_from<P>::get();
+    const void* p[layout_from<P>::nfields];
+    for (size_t i = 0; i < layout_from<P>::nfields; ++i) p[i] = planes[i];
+    check(pint_cuda_dense_from_planes(&l, p, (int)sizeof(Plane), dense_out, n, stream), "pint::cuda::dense::from_planes");
+}
+
+}  // namespace dense
+
 // multi-GPU: independent contiguous shards, one per device, no collective
 namespace sharded {
 
@@ -248,6 +361,24 @@ inline void fused_unpack_arith_repack(pint_op op, int ngpu, const int* devices,
                                                       reinterpret_cast<const void* const*>(b),
                                                       reinterpret_cast<void* const*>(out), counts, streams),
           "pint::cuda::sharded::fused_unpack_arith_repack");
+}
+
+// dense streams: shard starts are multiples of 128 elements (16-byte boundaries of the stream)
+inline void dense_plan(size_t n, int nshards, size_t* begin, size_t* count)
+{
+    check(pint_cuda_dense_plan_shards(n, nshards, begin, count), "pint::cuda::sharded::dense_plan");
+}
+
+template <class P>
+inline void dense_binary(pint_op op, int ngpu, const int* devices, const unsigned char* const* a,
+                         const unsigned char* const* b, unsigned char* const* out, const size_t* counts,
+                         const stream_t* streams = nullptr)
+{
+    const pint_layout l = dense::layout_from<P>::get();
+    check(pint_cuda_sharded_dense_binary(op, &l, ngpu, devices, reinterpret_cast<const void* const*>(a),
+                                         reinterpret_cast<const void* const*>(b), reinterpret_cast<void* const*>(out),
+                                         counts, streams),
+          "pint::cuda::sharded::dense_binary");
 }
 
 }  // namespace sharded

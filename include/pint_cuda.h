@@ -171,6 +171,15 @@ int pint_cuda_dense_to_planes(const pint_layout* layout, int is_signed, const vo
 int pint_cuda_dense_from_planes(const pint_layout* layout, const void* const* planes, int plane_bytes, void* dense,
                                 size_t n, pint_stream_t stream);
 
+/* Multi-GPU for dense streams: contiguous shards whose starts are multiples of 128 ELEMENTS, so
+ * that every shard's stream starts on a 16-byte boundary of the global stream (byte offset
+ * begin[k] * S / 8) and is a valid dense stream of count[k] elements on its own; remainder to the
+ * last shard.  No collective. */
+int pint_cuda_dense_plan_shards(size_t n, int nshards, size_t* begin, size_t* count);
+int pint_cuda_sharded_dense_binary(int op, const pint_layout* layout, int ngpu, const int* devices,
+                                   const void* const* a, const void* const* b, void* const* out,
+                                   const size_t* counts, const pint_stream_t* streams);
+
 /* ---- the benchmark's exact loop shape (tests/pint_bench.cpp:90-94) ---- */
 /* *sum_dev (device uint64_t) = sum_i OP(pairs[2i], pairs[2i+1]) mod 2^64 over an
  * AoS array of (first, second) Integer pairs; the benchmark's uint32_t `sum`

@@ -61,6 +61,9 @@ def lib():
             "pint_cuda_dense_unpack": (i, [LP, vp, vp, sz, vp]),
             "pint_cuda_dense_to_planes": (i, [LP, i, vp, C.POINTER(vp), i, sz, vp]),
             "pint_cuda_dense_from_planes": (i, [LP, C.POINTER(vp), i, vp, sz, vp]),
+            "pint_cuda_dense_plan_shards": (i, [sz, i, C.POINTER(sz), C.POINTER(sz)]),
+            "pint_cuda_sharded_dense_binary": (i, [i, LP, i, C.POINTER(i), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp),
+                                                  C.POINTER(sz), C.POINTER(vp)]),
             "pint_cuda_pairs_reduce": (i, [i, LP, vp, sz, vp, vp]),
             "pint_cuda_fill_splitmix": (i, [vp, u32, sz, u64, u64, vp]),
             "pint_cuda_checksum": (i, [vp, u32, sz, vp, vp]),

@@ -204,4 +204,33 @@ int pint_cuda_dense_from_planes(const pint_layout* layout, const void* const* pl
     return planes_impl(true, layout, 0, dense, planes, plane_bytes, n, (cudaStream_t)stream);
 }
 
+int pint_cuda_dense_plan_shards(size_t n, int nshards, size_t* begin, size_t* count)
+{
+    if (nshards < 1 || !begin || !count) return PINT_E_ARG;
+    const size_t base = (n / (size_t)nshards) / 128 * 128;  // shard length rounded down to 128 elements
+    size_t pos = 0;
+    for (int k = 0; k < nshards; ++k) {
+        begin[k] = pos;
+        count[k] = (k == nshards - 1) ? n - pos : base;
+        pos += count[k];
+    }
+    return PINT_OK;
+}
+
+int pint_cuda_sharded_dense_binary(int op, const pint_layout* layout, int ngpu, const int* devices,
+                                   const void* const* a, const void* const* b, void* const* out,
+                                   const size_t* counts, const pint_stream_t* streams)
+{
+    if (ngpu < 1 || !devices || !a || !b || !out || !counts) return PINT_E_ARG;
+    int prev = 0;
+    if (cudaError_t e = cudaGetDevice(&prev)) return (int)e;
+    int rc = PINT_OK;
+    for (int k = 0; k < ngpu && rc == PINT_OK; ++k) {
+        if (cudaError_t e = cudaSetDevice(devices[k])) { rc = (int)e; break; }
+        rc = pint_cuda_dense_binary(op, layout, a[k], b[k], out[k], counts[k], streams ? streams[k] : nullptr);
+    }
+    cudaSetDevice(prev);
+    return rc;
+}
+
 }  // extern "C"

@@ -86,3 +86,35 @@ def sharded_repack(layout, plane_shards, packed_shards, streams=None):
     _lib.check(_lib.lib().pint_cuda_sharded_repack(layout.ref, k, devices, planes, pb, pp, counts,
                                                    _stream_array(packed_shards, streams)), "pint_cuda_sharded_repack")
     return packed_shards
+
+
+# ---- dense bit streams (pint_b200.dense): shard starts are multiples of 128 elements ----
+
+def dense_plan_shards(n, nshards):
+    """[(begin, count)] in ELEMENTS; every begin is a multiple of 128 elements, so shard k's stream
+    starts at byte begin * S / 8 of the global stream (a 16-byte boundary) and is a valid dense
+    stream of count elements on its own."""
+    if nshards < 1:
+        raise ValueError("nshards must be >= 1")
+    begin = (C.c_size_t * nshards)()
+    count = (C.c_size_t * nshards)()
+    _lib.check(_lib.lib().pint_cuda_dense_plan_shards(n, nshards, begin, count), "pint_cuda_dense_plan_shards")
+    return [(begin[k], count[k]) for k in range(nshards)]
+
+
+def dense_shard_range(n, world_size, rank):
+    return dense_plan_shards(n, world_size)[rank]
+
+
+def sharded_dense_binary(op, layout, a_shards, b_shards, out_shards, counts, streams=None):
+    """Launch the dense op on every device's shard (uint8 streams resident on their devices)."""
+    k = len(a_shards)
+    devices = (C.c_int * k)(*[t.device.index for t in a_shards])
+    cnt = (C.c_size_t * k)(*counts)
+    pa = (C.c_void_p * k)(*[t.data_ptr() for t in a_shards])
+    pb = (C.c_void_p * k)(*[t.data_ptr() for t in b_shards])
+    po = (C.c_void_p * k)(*[t.data_ptr() for t in out_shards])
+    _lib.check(_lib.lib().pint_cuda_sharded_dense_binary(OP_CODE[op], layout.ref, k, devices, pa, pb, po, cnt,
+                                                         _stream_array(a_shards, streams)),
+               "pint_cuda_sharded_dense_binary")
+    return out_shards

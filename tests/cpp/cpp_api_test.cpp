@@ -120,6 +120,51 @@ int main()
         CK(cudaMemcpy(hr.data(), sr, n * 2, cudaMemcpyDeviceToHost));
         for (size_t i = 0; i < n; ++i) if (hr[i] != ((hs[i] >> 3) & 0x7F)) { ++fails; if (fails < 5) std::printf("slice mismatch at %zu\n", i); }
 
+        // ---- two ops in one pass (pint_cuda_binary_multi) ----
+        {
+            rgba *o0, *o1;
+            CK(cudaMalloc((void**)&o0, n * 4)); CK(cudaMalloc((void**)&o1, n * 4));
+            const pint_op two[2] = {PINT_ADD_UNSIGNED_SATURATE, PINT_ADD_SIGNED_SATURATE};
+            rgba* const outs[2] = {o0, o1};
+            pint::cuda::binary_multi(two, a, b, outs, n, s);
+            CK(cudaStreamSynchronize(s));
+            CK(cudaMemcpy(ho.data(), o0, n * 4, cudaMemcpyDeviceToHost));
+            for (size_t i = 0; i < n; ++i) if (ho[i] != rgba_add_usat(ha[i], hb[i])) { ++fails; if (fails < 5) std::printf("multi usat mismatch at %zu\n", i); }
+            CK(cudaMemcpy(ho.data(), o1, n * 4, cudaMemcpyDeviceToHost));
+            for (size_t i = 0; i < n; ++i) if (ho[i] != rgba_add_ssat(ha[i], hb[i])) { ++fails; if (fails < 5) std::printf("multi ssat mismatch at %zu\n", i); }
+        }
+
+        // ---- dense bit streams: RGB24 = packed_int<uint32_t,8,8,8> at 3 bytes per element ----
+        {
+            typedef pint::packed_int<uint32_t, 8, 8, 8> rgb;
+            namespace pd = pint::cuda::dense;
+            const size_t nb = pd::bytes<rgb>(n);
+            if (nb != ((n * 24 + 127) / 128) * 16) { ++fails; std::printf("dense::bytes\n"); }
+            unsigned char *da, *db, *dout;
+            CK(cudaMalloc((void**)&da, nb)); CK(cudaMalloc((void**)&db, nb)); CK(cudaMalloc((void**)&dout, nb));
+            pd::pack((const rgb*)a, da, n, s);   // the RGBA8 arrays reinterpreted: the top byte is dropped
+            pd::pack((const rgb*)b, db, n, s);
+            pd::add_unsigned_saturate<rgb>(da, db, dout, n, s);
+            std::vector<unsigned char> hd(nb);
+            CK(cudaStreamSynchronize(s));
+            CK(cudaMemcpy(hd.data(), dout, nb, cudaMemcpyDeviceToHost));
+            for (size_t i = 0; i < n; ++i) {
+                const uint32_t want = rgba_add_usat(ha[i], hb[i]) & 0xFFFFFFu;
+                const uint32_t got = hd[3 * i] | (hd[3 * i + 1] << 8) | ((uint32_t)hd[3 * i + 2] << 16);
+                if (got != want) { ++fails; if (fails < 5) std::printf("dense usat mismatch at %zu\n", i); }
+            }
+            for (size_t i = 3 * n; i < nb; ++i) if (hd[i]) { ++fails; std::printf("dense tail not zero\n"); break; }
+            int32_t* dpl[3];
+            for (int f = 0; f < 3; ++f) CK(cudaMalloc((void**)&dpl[f], n * 4));
+            pd::to_planes<rgb>(dout, dpl, n, s);
+            const int32_t* cdpl[3] = {dpl[0], dpl[1], dpl[2]};
+            pd::from_planes<rgb>(cdpl, da, n, s);
+            pd::unpack(da, (rgb*)out, n, s);
+            CK(cudaStreamSynchronize(s));
+            CK(cudaMemcpy(ho.data(), out, n * 4, cudaMemcpyDeviceToHost));
+            for (size_t i = 0; i < n; ++i) if (ho[i] != (rgba_add_usat(ha[i], hb[i]) & 0xFFFFFFu)) { ++fails; if (fails < 5) std::printf("dense planes round trip mismatch at %zu\n", i); }
+        }
+
         // ---- runtime errors throw ----
         bool threw = false;
         try { pint::cuda::add_wrap(a, b, (rgba*)((char*)a + 4), n - 1, s); } catch (const pint::cuda::error& e) { threw = e.code == PINT_E_ALIAS; }

@@ -148,3 +148,32 @@ def test_dense_error_codes(P):
     assert lib.pint_cuda_dense_bytes(L.ref, 5) == 16 and lib.pint_cuda_dense_bytes(L.ref, 6) == 32
     planes = (C.c_void_p * 3)(p, p + 1024, p + 2048)
     assert lib.pint_cuda_dense_to_planes(L.ref, 0, p + 3072, planes, 3, 4, None) == -13
+
+
+def test_sharded_dense_binary_single_process(P, oracle):
+    """pint_cuda_sharded_dense_binary over the visible devices (the same device twice when there is one)."""
+    pint_b200, ops, dense = P
+    from pint_b200 import sharded
+    eb, bits = 4, (5, 6, 5, 3)
+    L = pint_b200.Layout(eb, *bits)
+    S = sum(bits)
+    n = 777_777
+    ndev = torch.cuda.device_count()
+    devs = [k % ndev for k in range(max(2, ndev))]
+    plan = sharded.dense_plan_shards(n, len(devs))
+    x, y = oracle.fill(eb, n, 31), oracle.fill(eb, n, 32)
+    dx, dy = oracle.dense_pack(eb, bits, x), oracle.dense_pack(eb, bits, y)
+    want = oracle.dense_binary("add_signed_saturate", eb, bits, dx, dy, n)
+    a_sh, b_sh, o_sh = [], [], []
+    for (beg, cnt), d in zip(plan, devs):
+        lo, nb = beg * S // 8, dense.nbytes(L, cnt)
+        pad = lambda v: np.concatenate([v[lo:lo + nb], np.zeros(max(0, lo + nb - v.size), dtype=np.uint8)])  # noqa: E731
+        a_sh.append(torch.from_numpy(pad(dx)).to(f"cuda:{d}"))
+        b_sh.append(torch.from_numpy(pad(dy)).to(f"cuda:{d}"))
+        o_sh.append(torch.empty(nb, dtype=torch.uint8, device=f"cuda:{d}"))
+    sharded.sharded_dense_binary("add_signed_saturate", L, a_sh, b_sh, o_sh, [c for _, c in plan])
+    for d in set(devs):
+        torch.cuda.synchronize(d)
+    for (beg, cnt), o in zip(plan, o_sh):
+        lo, valid = beg * S // 8, (cnt * S) // 8  # whole bytes of the shard (its last partial byte shares bits only with padding)
+        np.testing.assert_array_equal(o.cpu().numpy()[:valid], want[lo:lo + valid])
