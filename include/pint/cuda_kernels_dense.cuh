@@ -26,9 +26,10 @@
 // conflict-free in shared memory.
 //
 // Thread mapping for format conversions (cuda_kernels_dense_convert.cuh): dense ->
-// padded/planes takes one thread per ELEMENT (funnel shift at a per-lane offset out
-// of the staged tile); padded/planes -> dense takes one thread per OUTPUT WORD, so
-// both sides stay coalesced and nothing needs atomics.
+// padded/planes takes one thread per four ELEMENTS (funnel shifts at per-lane offsets
+// out of the staged tile, 16-byte stores); padded/planes -> dense stages the inputs in
+// shared memory and uses the chunk mapping again, so both sides stay coalesced and
+// nothing needs atomics.
 #pragma once
 
 #include "cuda_kernels.cuh"

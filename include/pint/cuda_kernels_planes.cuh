@@ -110,10 +110,12 @@ template <class Elem, class Word>
 __device__ __forceinline__ void store_quad(Elem* p, const Word (&e)[4])
 {
     if constexpr (sizeof(Elem) == 8) {
+        // (a 32-bit Word under a 64-bit Integer happens in the dense kernels: sum(Bits) <= 32)
+        const uint64_t w0 = e[0], w1 = e[1], w2 = e[2], w3 = e[3];
         st16<CACHE_STREAMING>(reinterpret_cast<uint4*>(p),
-                              make_uint4(uint32_t(e[0]), uint32_t(e[0] >> 32), uint32_t(e[1]), uint32_t(e[1] >> 32)));
+                              make_uint4(uint32_t(w0), uint32_t(w0 >> 32), uint32_t(w1), uint32_t(w1 >> 32)));
         st16<CACHE_STREAMING>(reinterpret_cast<uint4*>(p) + 1,
-                              make_uint4(uint32_t(e[2]), uint32_t(e[2] >> 32), uint32_t(e[3]), uint32_t(e[3] >> 32)));
+                              make_uint4(uint32_t(w2), uint32_t(w2 >> 32), uint32_t(w3), uint32_t(w3 >> 32)));
     } else if constexpr (sizeof(Elem) == 4) {
         st16<CACHE_STREAMING>(reinterpret_cast<uint4*>(p), make_uint4(e[0], e[1], e[2], e[3]));
     } else if constexpr (sizeof(Elem) == 2) {
