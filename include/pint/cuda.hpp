@@ -284,6 +284,19 @@ PINT_CUDA_DENSE_BINARY(min_signed, PINT_MIN_SIGNED)
 PINT_CUDA_DENSE_BINARY(max_signed, PINT_MAX_SIGNED)
 #undef PINT_CUDA_DENSE_BINARY
 
+// several ops on the same dense operands; pairs such as add_unsigned_saturate + add_signed_saturate in one pass
+template <class P, size_t NOps>
+inline void binary_multi(const pint_op (&ops)[NOps], const stream_byte* a, const stream_byte* b,
+                         stream_byte* const (&outs)[NOps], size_t n, stream_t stream = nullptr)
+{
+    static_assert(NOps >= 1 && NOps <= PINT_MAX_MULTI_OPS, "1..PINT_MAX_MULTI_OPS operations");
+    const pint_layout l = layout_from<P>::get();
+    int codes[NOps];
+    void* o[NOps];
+    for (size_t j = 0; j < NOps; ++j) { codes[j] = ops[j]; o[j] = outs[j]; }
+    check(pint_cuda_dense_binary_multi((int)NOps, codes, &l, a, b, o, n, stream), "pint::cuda::dense::binary_multi");
+}
+
 // padded packed_int array <-> dense stream
 template <class Integer, size_t Bits0, size_t... Bits>
 inline void pack(const packed_int<Integer, Bits0, Bits...>* padded, stream_byte* dense_out, size_t n, stream_t stream = nullptr)

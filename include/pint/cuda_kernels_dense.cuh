@@ -213,6 +213,81 @@ __device__ __forceinline__ void process_chunk(typename Fn::word* A, const typena
     // word was flushed by put() and both windows are back at shift 0.
 }
 
+// Two results per element (pair_fn, cuda_kernels_multi.cuh): A <- Op0(A, B), B <- Op1(A, B), both in
+// place.  Same windows as process_chunk with a second output window that moves in step with
+// the first; B[wo] is written only after the input window has moved past word wo, as for A.
+template <class PFn, class Geo>
+__device__ __forceinline__ void process_chunk_pair(typename PFn::word* A, typename PFn::word* B, const PFn& fn, const Geo& geo)
+{
+    using W = typename PFn::word;
+    constexpr uint32_t WB = 8 * sizeof(W);
+    const uint32_t S = geo.S(), Cw = geo.Cw(), EB = geo.EB();
+    const W SM = ones_w<W>(S);
+    W ca = A[0], cb = B[0];
+    W na = Cw > 1 ? A[1] : W(0), nb = Cw > 1 ? B[1] : W(0);
+    W o0cur = 0, o0nxt = 0, o1cur = 0, o1nxt = 0;
+    uint32_t shi = 0, wi = 0, sho = 0, wo = 0;
+    auto take = [&](W& xa, W& xb) {
+        xa = funnel_r(ca, na, shi);
+        xb = funnel_r(cb, nb, shi);
+        shi += S;
+        if (shi >= WB) {
+            shi -= WB;
+            ++wi;
+            ca = na;
+            cb = nb;
+            na = wi + 1 < Cw ? A[wi + 1] : W(0);
+            nb = wi + 1 < Cw ? B[wi + 1] : W(0);
+        }
+    };
+    auto put = [&](W r0, W r1) {
+        o0cur |= r0 << sho;
+        o0nxt |= spill_l(r0, sho);
+        o1cur |= r1 << sho;
+        o1nxt |= spill_l(r1, sho);
+        sho += S;
+        if (sho >= WB) {
+            sho -= WB;
+            A[wo] = o0cur;
+            B[wo] = o1cur;
+            o0cur = o0nxt;
+            o1cur = o1nxt;
+            o0nxt = 0;
+            o1nxt = 0;
+            ++wo;
+        }
+    };
+    if constexpr (Geo::is_static) {
+#pragma unroll
+        for (uint32_t e = 0; e < Geo::kG; e += Geo::kEPW) {
+            W xa = 0, xb = 0;
+#pragma unroll
+            for (uint32_t k = 0; k < Geo::kEPW; ++k) {
+                W ta, tb;
+                take(ta, tb);
+                xa |= (Geo::kEPW == 1 ? ta : W(ta & SM)) << (k * Geo::kEB);
+                xb |= (Geo::kEPW == 1 ? tb : W(tb & SM)) << (k * Geo::kEB);
+            }
+            const W r0 = fn.first(xa, xb), r1 = fn.second(xa, xb);
+#pragma unroll
+            for (uint32_t k = 0; k < Geo::kEPW; ++k) put((r0 >> (k * Geo::kEB)) & SM, (r1 >> (k * Geo::kEB)) & SM);
+        }
+    } else {
+        const uint32_t G = geo.G(), step = WB / EB;
+        for (uint32_t e = 0; e < G; e += step) {
+            W xa = 0, xb = 0;
+            for (uint32_t k = 0; k < WB; k += EB) {
+                W ta, tb;
+                take(ta, tb);
+                xa |= (ta & SM) << k;
+                xb |= (tb & SM) << k;
+            }
+            const W r0 = fn.first(xa, xb), r1 = fn.second(xa, xb);
+            for (uint32_t k = 0; k < WB; k += EB) put((r0 >> k) & SM, (r1 >> k) & SM);
+        }
+    }
+}
+
 // zero the bits of `word` (which starts at bit `start` of the tile) at or above bit `limit`
 template <class W>
 __device__ __forceinline__ W clip_word(W word, uint64_t start, uint64_t limit)
@@ -241,9 +316,10 @@ __device__ __forceinline__ uint4 clip_vec(uint4 v, uint64_t start_bit, uint64_t 
 // forced to zero (op(0, 0) == 0 for every op, so the output tail is zero too).
 // `out` may alias a or b: the tile is complete in shared memory before any
 // store.  Dynamic shared memory: 2 * tile bytes.
-template <class Fn, class Geo>
-__global__ void dense_binary_kernel(const uint4* a, const uint4* b, uint4* out, size_t total_vec, uint64_t valid_bits,
-                                    const __grid_constant__ Fn fn, const __grid_constant__ Geo geo)
+// Pair = true: Fn is a pair_fn; the second result is produced in place over the b tile and stored to out1.
+template <class Fn, class Geo, bool Pair = false>
+__global__ void dense_binary_kernel(const uint4* a, const uint4* b, uint4* out, uint4* out1, size_t total_vec,
+                                    uint64_t valid_bits, const __grid_constant__ Fn fn, const __grid_constant__ Geo geo)
 {
     using W = typename Fn::word;
     extern __shared__ __align__(128) unsigned char dense_smem[];
@@ -288,7 +364,8 @@ __global__ void dense_binary_kernel(const uint4* a, const uint4* b, uint4* out, 
 
     for (uint32_t r = 0; r < R; ++r) {
         const uint32_t c = (r * T + threadIdx.x) * Cw;
-        process_chunk(A + c, B + c, fn, geo);
+        if constexpr (Pair) process_chunk_pair(A + c, B + c, fn, geo);
+        else process_chunk(A + c, B + c, fn, geo);
     }
 
     if (whole) {
@@ -296,13 +373,17 @@ __global__ void dense_binary_kernel(const uint4* a, const uint4* b, uint4* out, 
         __syncthreads();
         if (threadIdx.x == 0) {
             bulk_store(out + t * tile_vecs, A, tile_bytes, pol);
+            if constexpr (Pair) bulk_store(out1 + t * tile_vecs, B, tile_bytes, pol);
             bulk_wait_read<0>();  // shared memory must stay valid until the TMA engine has read it
         }
     } else {
         __syncthreads();
         for (uint32_t v = threadIdx.x; v < tile_vecs; v += T) {
             const size_t gv = t * tile_vecs + v;
-            if (gv < total_vec) st16<CACHE_STREAMING>(out + gv, reinterpret_cast<const uint4*>(A)[v]);
+            if (gv < total_vec) {
+                st16<CACHE_STREAMING>(out + gv, reinterpret_cast<const uint4*>(A)[v]);
+                if constexpr (Pair) st16<CACHE_STREAMING>(out1 + gv, reinterpret_cast<const uint4*>(B)[v]);
+            }
         }
     }
 }
@@ -328,9 +409,10 @@ inline void choose_tile(uint32_t cw, const dense_tuning& tune, uint32_t* threads
 }
 
 // a, b, out: 16-byte aligned dense streams of n elements (ceil(n*S/128)*16 bytes each)
-template <class Fn, class Geo>
+template <class Fn, class Geo, bool Pair = false>
 cudaError_t launch_dense_binary(const void* a, const void* b, void* out, size_t n, const Fn& fn, Geo geo,
-                                cudaStream_t stream, const launch_geom& g, const dense_tuning& tune = dense_tuning())
+                                cudaStream_t stream, const launch_geom& g, const dense_tuning& tune = dense_tuning(),
+                                void* out1 = nullptr)
 {
     using W = typename Fn::word;
     if (n == 0) return cudaSuccess;
@@ -342,14 +424,15 @@ cudaError_t launch_dense_binary(const void* a, const void* b, void* out, size_t 
     const size_t tile_bytes = size_t(T) * R * geo.Cw() * sizeof(W);
     const size_t ntiles = (total_vec * 16 + tile_bytes - 1) / tile_bytes;
     const size_t smem = 2 * tile_bytes;
-    auto kernel = dense_binary_kernel<Fn, Geo>;
+    auto kernel = dense_binary_kernel<Fn, Geo, Pair>;
     if (smem > 48 * 1024) {
         cudaError_t rc = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
         if (rc != cudaSuccess) return rc;
     }
     if (ntiles > 0x7FFFFFFFull) return cudaErrorInvalidValue;
     kernel<<<unsigned(ntiles), T, smem, stream>>>(static_cast<const uint4*>(a), static_cast<const uint4*>(b),
-                                                  static_cast<uint4*>(out), total_vec, valid_bits, fn, geo);
+                                                  static_cast<uint4*>(out), static_cast<uint4*>(out1), total_vec,
+                                                  valid_bits, fn, geo);
     count_launch(g);
     return cudaGetLastError();
 }

@@ -161,6 +161,11 @@ size_t pint_cuda_dense_bytes(const pint_layout* layout, size_t n);
 /* out = OP(a, b) on dense streams (3*S/8 bytes per element); out may be a or b exactly. */
 int pint_cuda_dense_binary(int op, const pint_layout* layout, const void* a, const void* b, void* out, size_t n,
                            pint_stream_t stream);
+/* outs[j] = ops[j](a, b) on dense streams, as pint_cuda_binary_multi: op pairs that have a one-pass
+ * kernel read a and b once and write both results (4*S/8 bytes per element instead of 6*S/8);
+ * outputs must not overlap the inputs or each other. */
+int pint_cuda_dense_binary_multi(int nops, const int* ops, const pint_layout* layout, const void* a, const void* b,
+                                 void* const* outs, size_t n, pint_stream_t stream);
 /* dense[i] = low S bits of padded[i]  /  padded[i] = dense[i] zero-extended to Integer. */
 int pint_cuda_dense_pack(const pint_layout* layout, const void* padded, void* dense, size_t n, pint_stream_t stream);
 int pint_cuda_dense_unpack(const pint_layout* layout, const void* dense, void* padded, size_t n, pint_stream_t stream);

@@ -57,6 +57,7 @@ def lib():
             "pint_cuda_repack": (i, [LP, C.POINTER(vp), i, vp, sz, vp]),
             "pint_cuda_dense_bytes": (sz, [LP, sz]),
             "pint_cuda_dense_binary": (i, [i, LP, vp, vp, vp, sz, vp]),
+            "pint_cuda_dense_binary_multi": (i, [i, C.POINTER(i), LP, vp, vp, C.POINTER(vp), sz, vp]),
             "pint_cuda_dense_pack": (i, [LP, vp, vp, sz, vp]),
             "pint_cuda_dense_unpack": (i, [LP, vp, vp, sz, vp]),
             "pint_cuda_dense_to_planes": (i, [LP, i, vp, C.POINTER(vp), i, sz, vp]),

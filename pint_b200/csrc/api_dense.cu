@@ -52,6 +52,21 @@ cudaError_t dense_generic(int op, const layout_desc& d, uint32_t S, const void* 
     return rc;
 }
 
+template <class W, int... Pairs>
+cudaError_t dense_generic_pair(int pair, const layout_desc& d, uint32_t S, const void* a, const void* b, void* out0,
+                               void* out1, size_t n, cudaStream_t s, const launch_geom& g,
+                               std::integer_sequence<int, Pairs...>)
+{
+    const layout_desc e = slot_desc(d, S);
+    const runtime_masks<W> p(make_word_masks<W>(e));
+    cudaError_t rc = cudaErrorInvalidValue;
+    ((pair == Pairs ? (rc = dense::launch_dense_binary<pair_fn<kOpPairs[Pairs][0], kOpPairs[Pairs][1], runtime_masks<W>>,
+                                                       dense::runtime_geom<W>, true>(
+                                a, b, out0, n, pair_fn<kOpPairs[Pairs][0], kOpPairs[Pairs][1], runtime_masks<W>>{p},
+                                dense::runtime_geom<W>(S, 8 * e.elem_bytes), s, g, tuning(), out1), 0) : 0), ...);
+    return rc;
+}
+
 dense::dense_fields make_fields(const layout_desc& d)
 {
     dense::dense_fields f{};
@@ -143,6 +158,57 @@ size_t pint_cuda_dense_bytes(const pint_layout* layout, size_t n)
     layout_desc d;
     if (check_layout(layout, &d)) return 0;
     return dense_bytes(total_bits(d), n);
+}
+
+int pint_cuda_dense_binary_multi(int nops, const int* ops, const pint_layout* layout, const void* a, const void* b,
+                                 void* const* outs, size_t n, pint_stream_t stream)
+{
+    layout_desc d;
+    if (int rc = check_layout(layout, &d)) return rc;
+    if (nops < 1 || nops > PINT_MAX_MULTI_OPS || !ops || !outs) return PINT_E_ARG;
+    for (int j = 0; j < nops; ++j)
+        if (ops[j] < 0 || ops[j] >= PINT_NUM_BINARY_OPS) return PINT_E_OP;
+    if (n == 0) return PINT_OK;
+    if (!a || !b) return PINT_E_NULL;
+    const uint32_t S = total_bits(d);
+    const size_t bytes = dense_bytes(S, n);
+    if (((uintptr_t)a | (uintptr_t)b) % 16) return PINT_E_ARG;
+    for (int j = 0; j < nops; ++j) {
+        if (!outs[j]) return PINT_E_NULL;
+        if ((uintptr_t)outs[j] % 16) return PINT_E_ARG;
+        auto overlaps = [&](const void* x) {
+            const uintptr_t i = (uintptr_t)x, o = (uintptr_t)outs[j];
+            return i < o + bytes && o < i + bytes;
+        };
+        if (overlaps(a) || overlaps(b)) return PINT_E_ALIAS;
+        for (int k = 0; k < j; ++k)
+            if (overlaps(outs[k])) return PINT_E_ALIAS;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    const bool padded_format = S == 8 || S == 16 || S == 32 || S == 64;
+    const launch_geom g = geom();
+    const dense_layout_kernels* k = opts().force_generic ? nullptr : find_dense_static(d);
+    bool done[PINT_MAX_MULTI_OPS] = {};
+    for (int j = 0; j < nops; ++j) {
+        if (done[j]) continue;
+        done[j] = true;
+        int rc = -1;
+        for (int i = j + 1; i < nops && rc < 0 && !padded_format; ++i) {
+            bool swapped = false;
+            const int pi = done[i] ? -1 : find_op_pair(ops[j], ops[i], &swapped);
+            if (pi < 0) continue;
+            done[i] = true;
+            void* o0 = swapped ? outs[i] : outs[j];
+            void* o1 = swapped ? outs[j] : outs[i];
+            auto pairs = std::make_integer_sequence<int, kNumOpPairs>();
+            rc = k ? (int)k->pair[pi](a, b, o0, o1, n, s, g, tuning())
+                   : (int)(S <= 32 ? dense_generic_pair<uint32_t>(pi, d, S, a, b, o0, o1, n, s, g, pairs)
+                                   : dense_generic_pair<uint64_t>(pi, d, S, a, b, o0, o1, n, s, g, pairs));
+        }
+        if (rc < 0) rc = pint_cuda_dense_binary(ops[j], layout, a, b, outs[j], n, stream);
+        if (rc) return rc;
+    }
+    return PINT_OK;
 }
 
 int pint_cuda_dense_binary(int op, const pint_layout* layout, const void* a, const void* b, void* out, size_t n,

@@ -17,6 +17,22 @@ cudaError_t dense_entry(const void* a, const void* b, void* out, size_t n, cudaS
     return dense::launch_dense_binary(a, b, out, n, Fn{}, Geo{1}, s, g, tune);
 }
 
+template <class SL, int Pair>
+cudaError_t dense_pair_entry(const void* a, const void* b, void* out0, void* out1, size_t n, cudaStream_t s,
+                             const launch_geom& g, const dense_tuning& tune)
+{
+    using W = typename SL::word;
+    using Fn = pair_fn<kOpPairs[Pair][0], kOpPairs[Pair][1], static_masks<SL>>;
+    using Geo = dense::static_geom<W, SL::masks.total_bits, 8 * sizeof(typename SL::integer)>;
+    return dense::launch_dense_binary<Fn, Geo, true>(a, b, out0, n, Fn{}, Geo{1}, s, g, tune, out1);
+}
+
+template <class SL, int... Pairs>
+void add_dense_pairs(dense_layout_kernels& k, std::integer_sequence<int, Pairs...>)
+{
+    ((k.pair[Pairs] = &dense_pair_entry<SL, Pairs>), ...);
+}
+
 template <class SL, int... Ops>
 dense_layout_kernels make_dense(std::integer_sequence<int, Ops...>)
 {
@@ -24,6 +40,7 @@ dense_layout_kernels make_dense(std::integer_sequence<int, Ops...>)
     k.nfields = SL::desc.nfields;
     for (uint32_t i = 0; i < k.nfields; ++i) k.bits[i] = SL::desc.bits[i];
     ((k.binary[Ops] = &dense_entry<SL, Ops>), ...);
+    add_dense_pairs<SL>(k, std::make_integer_sequence<int, kNumOpPairs>());
     return k;
 }
 

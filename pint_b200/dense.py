@@ -40,6 +40,20 @@ def binary(op, layout, a, b, n, out=None, stream=None):
     return out
 
 
+def binary_multi(op_list, layout, a, b, n, outs=None, stream=None):
+    """outs[j] = op_list[j](a, b) on dense streams; op pairs with a one-pass kernel read a and b once."""
+    import ctypes as C
+    if outs is None:
+        outs = [torch.empty_like(a) for _ in op_list]
+    _check_dense(layout, n, a, b, *outs)
+    codes = (C.c_int * len(op_list))(*[OP_CODE[o] if isinstance(o, str) else int(o) for o in op_list])
+    ptrs = (C.c_void_p * len(op_list))(*[o.data_ptr() for o in outs])
+    with torch.cuda.device(a.device):
+        _lib.check(_lib.lib().pint_cuda_dense_binary_multi(len(op_list), codes, layout.ref, a.data_ptr(), b.data_ptr(), ptrs,
+                                                           n, _stream(stream)), "pint_cuda_dense_binary_multi")
+    return outs
+
+
 def pack(layout, padded, out=None, stream=None):
     """Padded packed_int array -> dense stream (drops the bits above sum(Bits))."""
     n = _check(layout, padded)

@@ -177,3 +177,54 @@ def test_sharded_dense_binary_single_process(P, oracle):
     for (beg, cnt), o in zip(plan, o_sh):
         lo, valid = beg * S // 8, (cnt * S) // 8  # whole bytes of the shard (its last partial byte shares bits only with padding)
         np.testing.assert_array_equal(o.cpu().numpy()[:valid], want[lo:lo + valid])
+
+
+@pytest.mark.parametrize("eb,bits", [(4, (8, 8, 8)), (4, (7, 9, 3)), (8, (21, 21, 21)), (2, (12,))])
+def test_dense_conversions_misaligned_other_side(P, oracle, eb, bits):
+    """The padded array / the planes at addresses that are not 16-byte aligned (element-granular
+    fallback of the quad paths) give the same streams and values."""
+    pint_b200, ops, dense = P
+    L = pint_b200.Layout(eb, *bits)
+    S = sum(bits)
+    n = 70_001
+    x = oracle.fill(eb, n, 0xAB)
+    masked = x & np.array((1 << S) - 1, dtype=x.dtype)
+    want = oracle.dense_pack(eb, bits, x)
+    for off in (1, 3):
+        xd = to_dev(x, off)
+        assert xd.data_ptr() % 16 != 0
+        d = dense.pack(L, xd)
+        np.testing.assert_array_equal(d.cpu().numpy(), want)
+        out = to_dev(np.zeros(n, dtype=x.dtype), off)
+        dense.unpack(L, d, n, out=out)
+        np.testing.assert_array_equal(to_np(out), masked)
+        ref_planes = oracle.unpack(eb, bits, masked, True, 4)
+        planes = [to_dev(np.zeros(n, dtype=np.int32), off) for _ in bits]
+        assert planes[0].data_ptr() % 16 != 0
+        dense.to_planes(L, d, n, signed=True, out=planes)
+        for f in range(len(bits)):
+            np.testing.assert_array_equal(to_np(planes[f], np.int32), ref_planes[f])
+        got = dense.from_planes(L, planes)
+        np.testing.assert_array_equal(got.cpu().numpy(), want)
+
+
+@pytest.mark.parametrize("eb,bits", [(4, (8, 8, 8)), (2, (12,)), (4, (5, 6, 5, 3)), (8, (10, 10, 10, 10)), (4, (8, 8, 8, 8))])
+def test_dense_binary_multi(P, oracle, eb, bits, mode):
+    """Op pairs in one pass over dense streams == the ops run one by one; lists mixing pairs and singles."""
+    pint_b200, ops, dense = P
+    L = pint_b200.Layout(eb, *bits)
+    for n in (3, 4099, (1 << 18) + 5):
+        x, y = oracle.fill(eb, n, 71), oracle.fill(eb, n, 72)
+        dx_h, dy_h = oracle.dense_pack(eb, bits, x), oracle.dense_pack(eb, bits, y)
+        dx, dy = dev_bytes(dx_h), dev_bytes(dy_h)
+        for op_list in (["add_unsigned_saturate", "add_signed_saturate"], ["sub_signed_saturate", "add_signed_saturate"],
+                        ["max_unsigned", "min_unsigned"], ["add_wrap", "bit_xor", "sub_wrap", "min_signed"], ["sub_unsigned_saturate"]):
+            outs = dense.binary_multi(op_list, L, dx, dy, n)
+            for op, o in zip(op_list, outs):
+                np.testing.assert_array_equal(o.cpu().numpy(), oracle.dense_binary(op, eb, bits, dx_h, dy_h, n),
+                                              err_msg=f"{L} {op} n={n} {mode}")
+    import ctypes as C
+    from pint_b200 import _lib
+    codes = (C.c_int * 2)(1, 2)
+    outs = (C.c_void_p * 2)(dx.data_ptr(), dy.data_ptr())
+    assert _lib.lib().pint_cuda_dense_binary_multi(2, codes, L.ref, dx.data_ptr(), dy.data_ptr(), outs, n, None) == -14

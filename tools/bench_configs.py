@@ -82,6 +82,16 @@ def main():
         binary_case("C1-runtime-masks", L, 1 << 30, ["add_unsigned_saturate", "add_signed_saturate"], generic=True)
     if "C2" in which:
         binary_case("C2", pint_b200.Layout(8, 16, 16, 16, 16), 1 << 31, ["sub_signed_saturate", "add_signed_saturate"])
+        # both C2 ops in one pass (a, b read once): 4W bytes per element for two results
+        L = pint_b200.Layout(8, 16, 16, 16, 16)
+        n = 1 << 30
+        a, b = alloc(L, n, 1), alloc(L, n, 2)
+        o0, o1 = torch.empty_like(a), torch.empty_like(a)
+        pair = ["sub_signed_saturate", "add_signed_saturate"]
+        best, med = timed(lambda i: ops.binary_multi(pair, L, a, b, outs=[o0, o1]))
+        report("C2-pair (2^30, both ops in one pass)", n, 4 * 8, best, med, op="+".join(pair), layout=repr(L), kernel="pair/static-masks")
+        del a, b, o0, o1
+        torch.cuda.empty_cache()
     if "C3" in which:
         L = pint_b200.Layout(8, 3, 7, 11, 13, 17, 13)
         n = 1 << 28

@@ -67,6 +67,13 @@ def main():
                      gbs_median=bytes_ / med / 1e6, gbs_best=bytes_ / best / 1e6, gelem_s=n / med / 1e6, ms=med)
         ops.set_option("dense_threads", 0)
         ops.set_option("dense_tile_bytes", 0)
+        # two ops in one pass: 4*S/8 bytes per element for two results
+        do2 = torch.empty_like(da)
+        pair = ["add_unsigned_saturate", "add_signed_saturate"]
+        best, med = timed(lambda: dense.binary_multi(pair, L, da, db, n, outs=[do, do2]))
+        emit(what="dense_binary_pair", layout=str(L), S=S, kernel=kind, op="+".join(pair), gbs_median=4 * n * S / 8 / med / 1e6,
+             gelem_s=2 * n / med / 1e6, ms=med)
+        del do2
         # same op on the padded format, for the elements/s comparison
         y = torch.empty_like(x)
         out = torch.empty_like(x)
