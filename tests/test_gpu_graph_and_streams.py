@@ -76,3 +76,61 @@ def test_concurrent_streams(oracle):
         # one round is enough to pin the arithmetic; the loop above only stresses concurrency:
         # every round recomputes o = (a + b) + b from the same a, b
         np.testing.assert_array_equal(to_np(outs[k]), w)
+
+
+def test_dense_kernels_in_graph_and_host_threads(oracle):
+    """Dense (TMA-staged) kernels captured in a CUDA graph, and the C ABI called from several
+    host threads at once, each on its own stream."""
+    import threading
+    import pint_b200
+    from pint_b200 import dense
+    eb, bits = 4, (7, 9, 3)
+    L = pint_b200.Layout(eb, *bits)
+    n = (1 << 18) + 9
+    x, y = oracle.fill(eb, n, 3), oracle.fill(eb, n, 4)
+    dx_h, dy_h = oracle.dense_pack(eb, bits, x), oracle.dense_pack(eb, bits, y)
+    dx, dy = torch.from_numpy(dx_h.copy()).cuda(), torch.from_numpy(dy_h.copy()).cuda()
+    t1, out = torch.empty_like(dx), torch.empty_like(dx)
+    planes = [torch.empty(n, dtype=torch.int32, device="cuda") for _ in bits]
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(s):
+        dense.binary("add_wrap", L, dx, dy, n, out=t1)  # warm-up outside capture
+        dense.to_planes(L, t1, n, signed=True, out=planes)
+        dense.from_planes(L, planes, out=out)
+        torch.cuda.synchronize()
+        with torch.cuda.graph(g, stream=s):
+            dense.binary("add_signed_saturate", L, dx, dy, n, out=t1)
+            dense.to_planes(L, t1, n, signed=True, out=planes)
+            dense.from_planes(L, planes, out=out)
+    want = oracle.dense_binary("add_signed_saturate", eb, bits, dx_h, dy_h, n)
+    for _ in range(2):
+        out.zero_()
+        g.replay()
+        torch.cuda.synchronize()
+        np.testing.assert_array_equal(out.cpu().numpy(), want)
+
+    results, errors = {}, []
+
+    def worker(k):
+        try:
+            st = torch.cuda.Stream()
+            o = torch.empty_like(dx)
+            with torch.cuda.stream(st):
+                for _ in range(20):
+                    dense.binary("sub_signed_saturate" if k % 2 else "add_unsigned_saturate", L, dx, dy, n, out=o, stream=st)
+            st.synchronize()
+            results[k] = o.cpu().numpy()
+        except Exception as e:  # noqa: BLE001
+            errors.append(e)
+
+    threads = [threading.Thread(target=worker, args=(k,)) for k in range(4)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
+    for k in range(4):
+        op = "sub_signed_saturate" if k % 2 else "add_unsigned_saturate"
+        np.testing.assert_array_equal(results[k], oracle.dense_binary(op, eb, bits, dx_h, dy_h, n))
