@@ -135,7 +135,9 @@ struct runtime_masks {
     __device__ __forceinline__ word fill(word c) const
     {
         if (nsmear == 0) return c | (c - (c >> shift0));
-        // all steps, unconditionally: keep[k] is 0 for the steps a layout does not need
+        // all steps, unconditionally: keep[k] is 0 for the steps a layout does not need.  Skipping
+        // them with warp-uniform branches on nsmear was measured and is slower where it matters
+        // (padded <7,9,3> add_signed_saturate 6226 -> 5181 GB/s, profiles/r01q_extra.jsonl).
         word x = c;
         x |= (x >> 1) & keep[0];
         x |= (x >> 2) & keep[1];

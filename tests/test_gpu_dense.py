@@ -12,9 +12,10 @@ pytestmark = pytest.mark.gpu
 
 from gpu_util import to_dev, to_np  # noqa: E402
 
-# static dense kernels exist for the first five (pint_b200/csrc/dense_layouts.def); the rest run the
+# static dense kernels exist for the first nine (pint_b200/csrc/dense_layouts.def); the rest run the
 # run-time-geometry kernel; S in {8,16,32,64} is the padded format itself
 LAYOUTS = [(4, (8, 8, 8)), (4, (10, 10, 10)), (2, (12,)), (4, (7, 9, 3)), (8, (16, 16, 16)),
+           (2, (14,)), (2, (5, 5, 5)), (4, (6, 6, 6)), (2, (10,)),
            (4, (5, 6, 5, 3)), (8, (10, 10, 10, 10)), (8, (21, 21, 21)), (1, (3,)), (4, (1,)), (8, (31, 2)), (8, (1, 62)),
            (8, (3, 7, 11, 13, 17, 12)), (4, (11, 11, 9)), (2, (5, 6, 5)), (8, (64,)), (4, (8, 8, 8, 8)), (1, (2, 3, 3))]
 SIZES = [1, 2, 5, 127, 128, 129, 4096, (1 << 18) + 77]
@@ -57,7 +58,7 @@ def test_dense_binary_vs_oracle(P, oracle, eb, bits, mode):
                                           err_msg=f"{L} {op} n={n} {mode}")
 
 
-@pytest.mark.parametrize("eb,bits", LAYOUTS[:8])
+@pytest.mark.parametrize("eb,bits", LAYOUTS[:12])
 def test_dense_in_place_and_tiles(P, oracle, eb, bits):
     """In place on either operand; every tile geometry option gives the same stream."""
     pint_b200, ops, dense = P
