@@ -86,10 +86,18 @@ struct static_masks {
     {
         return lsb_impl(c, std::make_index_sequence<SL::masks.nsh>());
     }
+    // (a local constexpr copy: a class-type mask -- the multi-word chunks of the dense kernels --
+    // must not be odr-used from device code)
+    template <std::size_t K>
+    __device__ __forceinline__ static constexpr word keep_k()
+    {
+        constexpr word m = SL::masks.keep[K];
+        return m;
+    }
     template <std::size_t... Ks>
     __device__ __forceinline__ static constexpr word smear_impl(word x, std::index_sequence<Ks...>)
     {
-        ((x |= word((x >> (1u << Ks)) & SL::masks.keep[Ks])), ...);
+        ((x |= word((x >> (1u << Ks)) & keep_k<Ks>())), ...);
         return x;
     }
     // all bits of every field whose MSB flag is set in c (c subset of H): the

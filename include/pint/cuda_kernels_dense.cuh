@@ -82,6 +82,8 @@ __device__ __forceinline__ W spill_l(W r, uint32_t sh)
 template <class W, uint32_t S_, uint32_t EB_ = 8 * sizeof(W)>
 struct static_geom {
     static constexpr bool is_static = true;
+    static constexpr bool whole_chunk = false;
+    using unit = W;  // the tile is handled in words of this type
     static constexpr uint32_t WB = 8 * sizeof(W);
     static constexpr uint32_t kS = S_, kCw = S_ / gcd_u32(S_, WB), kG = WB / gcd_u32(S_, WB), kEB = EB_, kEPW = WB / EB_;
     static_assert(kG % kEPW == 0, "a chunk holds a whole number of gathered words");
@@ -95,6 +97,8 @@ struct static_geom {
 template <class W>
 struct runtime_geom {
     static constexpr bool is_static = false;
+    static constexpr bool whole_chunk = false;
+    using unit = W;
     static constexpr uint32_t WB = 8 * sizeof(W);
     uint32_t s, cw, g, eb;
     uint32_t chunks_per_thread;
@@ -107,6 +111,18 @@ struct runtime_geom {
     __host__ __device__ uint32_t G() const { return g; }
     __host__ __device__ uint32_t EB() const { return eb; }
 };
+
+}  // namespace dense
+}  // namespace kernels
+}  // namespace cuda
+}  // namespace pint
+
+#include "cuda_kernels_dense_mw.cuh"  // whole-chunk SWAR for compiled-in layouts with small chunks
+
+namespace pint {
+namespace cuda {
+namespace kernels {
+namespace dense {
 
 // One chunk, in place: A[0..Cw) <- op(A, B) element by element.  A and B are
 // shared-memory pointers to the same chunk of the two operand tiles.  An input
@@ -321,7 +337,7 @@ template <class Fn, class Geo, bool Pair = false>
 __global__ void dense_binary_kernel(const uint4* a, const uint4* b, uint4* out, uint4* out1, size_t total_vec,
                                     uint64_t valid_bits, const __grid_constant__ Fn fn, const __grid_constant__ Geo geo)
 {
-    using W = typename Fn::word;
+    using W = typename Geo::unit;
     extern __shared__ __align__(128) unsigned char dense_smem[];
     __shared__ __align__(8) uint64_t full;
     const uint32_t T = blockDim.x, R = geo.chunks_per_thread, Cw = geo.Cw();
@@ -364,8 +380,13 @@ __global__ void dense_binary_kernel(const uint4* a, const uint4* b, uint4* out, 
 
     for (uint32_t r = 0; r < R; ++r) {
         const uint32_t c = (r * T + threadIdx.x) * Cw;
-        if constexpr (Pair) process_chunk_pair(A + c, B + c, fn, geo);
-        else process_chunk(A + c, B + c, fn, geo);
+        if constexpr (Geo::whole_chunk) {
+            if constexpr (Pair) process_chunk_mw_pair<Fn, int(Geo::kCw)>(A + c, B + c, fn);
+            else process_chunk_mw<Fn, int(Geo::kCw)>(A + c, B + c, fn);
+        } else {
+            if constexpr (Pair) process_chunk_pair(A + c, B + c, fn, geo);
+            else process_chunk(A + c, B + c, fn, geo);
+        }
     }
 
     if (whole) {
@@ -414,7 +435,7 @@ cudaError_t launch_dense_binary(const void* a, const void* b, void* out, size_t 
                                 cudaStream_t stream, const launch_geom& g, const dense_tuning& tune = dense_tuning(),
                                 void* out1 = nullptr)
 {
-    using W = typename Fn::word;
+    using W = typename Geo::unit;
     if (n == 0) return cudaSuccess;
     uint32_t T = 0, R = 0;
     choose_tile<W>(geo.Cw(), tune, &T, &R);

@@ -201,8 +201,17 @@ int pint_cuda_dense_binary_multi(int nops, const int* ops, const pint_layout* la
             void* o0 = swapped ? outs[i] : outs[j];
             void* o1 = swapped ? outs[j] : outs[i];
             auto pairs = std::make_integer_sequence<int, kNumOpPairs>();
-            rc = k ? (int)k->pair[pi](a, b, o0, o1, n, s, g, tuning())
-                   : (int)(S <= 32 ? dense_generic_pair<uint32_t>(pi, d, S, a, b, o0, o1, n, s, g, pairs)
+            const int N = int(S / dense::gcd_u32(S, 32));
+            cudaError_t mrc = cudaSuccess;
+            if (k)
+                rc = (int)k->pair[pi](a, b, o0, o1, n, s, g, tuning());
+            else if (!opts().dense_windows &&
+                     (dense_mw_pair_part0(N, pi, d, S, a, b, o0, o1, n, s, g, tuning(), &mrc) ||
+                      dense_mw_pair_part1(N, pi, d, S, a, b, o0, o1, n, s, g, tuning(), &mrc) ||
+                      dense_mw_pair_part2(N, pi, d, S, a, b, o0, o1, n, s, g, tuning(), &mrc)))
+                rc = (int)mrc;
+            else
+                rc = (int)(S <= 32 ? dense_generic_pair<uint32_t>(pi, d, S, a, b, o0, o1, n, s, g, pairs)
                                    : dense_generic_pair<uint64_t>(pi, d, S, a, b, o0, o1, n, s, g, pairs));
         }
         if (rc < 0) rc = pint_cuda_dense_binary(ops[j], layout, a, b, outs[j], n, stream);
@@ -243,6 +252,16 @@ int pint_cuda_dense_binary(int op, const pint_layout* layout, const void* a, con
     const launch_geom g = geom();
     if (!opts().force_generic)
         if (const dense_layout_kernels* k = find_dense_static(d)) return (int)k->binary[op](a, b, out, n, s, g, tuning());
+    // any layout whose chunk is short enough computes whole chunks with run-time masks ...
+    const int N = int(S / dense::gcd_u32(S, 32));
+    if (!opts().dense_windows) {
+        cudaError_t rc = cudaSuccess;
+        if (dense_mw_binary_part0(N, op, d, S, a, b, out, n, s, g, tuning(), &rc) ||
+            dense_mw_binary_part1(N, op, d, S, a, b, out, n, s, g, tuning(), &rc) ||
+            dense_mw_binary_part2(N, op, d, S, a, b, out, n, s, g, tuning(), &rc))
+            return (int)rc;
+    }
+    // ... the rest slides windows over the chunk element by element
     auto ops = std::make_integer_sequence<int, pint::cuda::OP_NUM_BINARY>();
     return (int)(S <= 32 ? dense_generic<uint32_t>(op, d, S, a, b, out, n, s, g, ops)
                          : dense_generic<uint64_t>(op, d, S, a, b, out, n, s, g, ops));

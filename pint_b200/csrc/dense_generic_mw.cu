@@ -1,0 +1,73 @@
+// dense_generic_mw.cu -- whole-chunk dense kernels with RUN-TIME masks (cuda_kernels_dense_mw.cuh),
+// instantiated per chunk length N (32-bit words).  Compile with -DPINT_MW_PART=<0..2>; each part
+// covers three values of N.
+#include "dense_registry.hpp"
+
+#ifndef PINT_MW_PART
+#error "compile with -DPINT_MW_PART=n"
+#endif
+
+namespace pint_cuda_impl {
+namespace {
+
+using namespace pint::cuda;
+using namespace pint::cuda::kernels;
+
+template <int N, int... Ops>
+cudaError_t binary_n(int op, const layout_desc& d, uint32_t S, const void* a, const void* b, void* out, size_t n,
+                     cudaStream_t s, const launch_geom& g, const dense_tuning& tune, std::integer_sequence<int, Ops...>)
+{
+    using P = dense::runtime_chunk_masks<N>;
+    const P p(dense::make_chunk_masks<N>(d));
+    cudaError_t rc = cudaErrorInvalidValue;
+    ((op == Ops ? (rc = dense::launch_dense_binary(a, b, out, n, swar_fn<Ops, P>{p}, dense::mw_geom<N>{S, 1}, s, g, tune), 0) : 0), ...);
+    return rc;
+}
+
+template <int N, int... Pairs>
+cudaError_t pair_n(int pair, const layout_desc& d, uint32_t S, const void* a, const void* b, void* out0, void* out1,
+                   size_t n, cudaStream_t s, const launch_geom& g, const dense_tuning& tune,
+                   std::integer_sequence<int, Pairs...>)
+{
+    using P = dense::runtime_chunk_masks<N>;
+    const P p(dense::make_chunk_masks<N>(d));
+    cudaError_t rc = cudaErrorInvalidValue;
+    ((pair == Pairs ? (rc = dense::launch_dense_binary<pair_fn<kOpPairs[Pairs][0], kOpPairs[Pairs][1], P>, dense::mw_geom<N>, true>(
+                                a, b, out0, n, pair_fn<kOpPairs[Pairs][0], kOpPairs[Pairs][1], P>{p}, dense::mw_geom<N>{S, 1}, s,
+                                g, tune, out1), 0) : 0), ...);
+    return rc;
+}
+
+constexpr int kFirst = 3 + 6 * PINT_MW_PART;  // N = kFirst, kFirst + 2, kFirst + 4
+
+}  // namespace
+
+#define PINT_CAT2(a, b) a##b
+#define PINT_CAT(a, b) PINT_CAT2(a, b)
+
+// false when this part does not cover N
+bool PINT_CAT(dense_mw_binary_part, PINT_MW_PART)(int N, int op, const layout_desc& d, uint32_t S, const void* a,
+                                                   const void* b, void* out, size_t n, cudaStream_t s,
+                                                   const launch_geom& g, const dense_tuning& tune, cudaError_t* rc)
+{
+    auto ops = std::make_integer_sequence<int, OP_NUM_BINARY>();
+    if (N == kFirst) *rc = binary_n<kFirst>(op, d, S, a, b, out, n, s, g, tune, ops);
+    else if (N == kFirst + 2) *rc = binary_n<kFirst + 2>(op, d, S, a, b, out, n, s, g, tune, ops);
+    else if (N == kFirst + 4) *rc = binary_n<kFirst + 4>(op, d, S, a, b, out, n, s, g, tune, ops);
+    else return false;
+    return true;
+}
+
+bool PINT_CAT(dense_mw_pair_part, PINT_MW_PART)(int N, int pair, const layout_desc& d, uint32_t S, const void* a,
+                                                 const void* b, void* out0, void* out1, size_t n, cudaStream_t s,
+                                                 const launch_geom& g, const dense_tuning& tune, cudaError_t* rc)
+{
+    auto pairs = std::make_integer_sequence<int, kNumOpPairs>();
+    if (N == kFirst) *rc = pair_n<kFirst>(pair, d, S, a, b, out0, out1, n, s, g, tune, pairs);
+    else if (N == kFirst + 2) *rc = pair_n<kFirst + 2>(pair, d, S, a, b, out0, out1, n, s, g, tune, pairs);
+    else if (N == kFirst + 4) *rc = pair_n<kFirst + 4>(pair, d, S, a, b, out0, out1, n, s, g, tune, pairs);
+    else return false;
+    return true;
+}
+
+}  // namespace pint_cuda_impl

@@ -23,4 +23,18 @@ struct dense_layout_kernels {
 // the element side's Integer does not matter for a dense stream: lookup is by Bits... only
 const dense_layout_kernels* find_dense_static(const layout_desc& d);
 
+// whole-chunk kernels with run-time masks, chunk length N = 3, 5, ..., 19 words (dense_generic_mw.cu,
+// one translation unit per three values of N); false when the part does not cover N
+#define PINT_MW_PART_DECL(P)                                                                                          \
+    bool dense_mw_binary_part##P(int N, int op, const layout_desc& d, uint32_t S, const void* a, const void* b,       \
+                                 void* out, size_t n, cudaStream_t s, const launch_geom& g, const dense_tuning& tune, \
+                                 cudaError_t* rc);                                                                    \
+    bool dense_mw_pair_part##P(int N, int pair, const layout_desc& d, uint32_t S, const void* a, const void* b,       \
+                               void* out0, void* out1, size_t n, cudaStream_t s, const launch_geom& g,                \
+                               const dense_tuning& tune, cudaError_t* rc);
+PINT_MW_PART_DECL(0)
+PINT_MW_PART_DECL(1)
+PINT_MW_PART_DECL(2)
+#undef PINT_MW_PART_DECL
+
 }  // namespace pint_cuda_impl

@@ -29,12 +29,16 @@ def P():
     return pint_b200, ops, dense
 
 
-@pytest.fixture(params=["static_or_generic", "force_generic"])
+# compiled-in kernels where they exist / run-time masks (whole-chunk kernels where the chunk is short
+# enough) / run-time masks with the element-by-element window kernels forced
+@pytest.fixture(params=["static_or_generic", "force_generic", "force_generic_windows"])
 def mode(request, P):
     _, ops, _ = P
-    ops.set_option("force_generic", 1 if request.param == "force_generic" else 0)
+    ops.set_option("force_generic", 0 if request.param == "static_or_generic" else 1)
+    ops.set_option("dense_windows", 1 if request.param == "force_generic_windows" else 0)
     yield request.param
     ops.set_option("force_generic", 0)
+    ops.set_option("dense_windows", 0)
 
 
 def dev_bytes(x):

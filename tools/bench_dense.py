@@ -43,6 +43,7 @@ def main():
     torch.cuda.set_device(0)
     n = 1 << LOG2
     layouts = [(4, (8, 8, 8)), (4, (10, 10, 10)), (2, (12,)), (4, (7, 9, 3)), (8, (16, 16, 16)),
+               (2, (10,)), (2, (14,)), (2, (5, 5, 5)), (4, (6, 6, 6)),
                (4, (5, 6, 5, 3)), (8, (10, 10, 10, 10)), (8, (21, 21, 21))]
     for eb, bits in layouts:
         L = pint_b200.Layout(eb, *bits)
@@ -53,7 +54,7 @@ def main():
         ops.fill_splitmix(x, 2)
         db = dense.pack(L, x)
         do = torch.empty_like(da)
-        kind = "static" if eb * 8 >= S and (bits in [(8, 8, 8), (10, 10, 10), (12,), (7, 9, 3), (16, 16, 16)]) else "runtime-geometry"
+        kind = "static" if eb * 8 >= S and (bits in [(8, 8, 8), (10, 10, 10), (12,), (7, 9, 3), (16, 16, 16), (10,), (14,), (5, 5, 5), (6, 6, 6)]) else "runtime-geometry"
         configs = [(0, 0)]
         if SWEEP:
             configs += [(64, 8192), (64, 16384), (128, 8192), (128, 32768), (256, 16384), (256, 32768), (256, 65536), (512, 32768)]
