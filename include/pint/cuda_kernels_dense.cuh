@@ -16,14 +16,18 @@
 // Thread mapping for dense -> dense ops ("chunk" mapping).  The bit pattern of a
 // layout repeats every lcm(S, WB) bits (WB = bits of the processing word): a
 // CHUNK of Cw = S / gcd(S, WB) words holds exactly G = WB / gcd(S, WB) whole
-// elements.  One thread owns a chunk: it walks the chunk's words with a sliding
-// two-word window, extracts each element with a funnel shift, applies the SWAR
-// functor, and deposits the result into a two-word output window that is flushed
-// word by word over the input tile.  No element is shared between threads, so
-// there are no shuffles and no atomics; all shifts are the same for every thread
-// (immediates when the layout is compiled in).  Cw is odd for every S that is
-// not 8, 16, 32 or 64 (those ARE the padded format), so the chunk stride is
-// conflict-free in shared memory.
+// elements.  One thread owns a chunk, so no element is shared between threads:
+// no shuffles, no atomics.  Cw is odd for every S that is not 8, 16, 32 or 64
+// (those ARE the padded format), so the chunk stride is conflict-free in shared
+// memory.  Two ways to compute a chunk:
+//   * whole-chunk SWAR (cuda_kernels_dense_mw.cuh; chunks of up to 19 32-bit
+//     words): the chunk is treated as ONE wide packed_int and the SWAR functor
+//     runs on it directly with multi-word carries and shifts;
+//   * sliding windows (below; longer chunks): the thread walks the chunk with a
+//     two-word window, extracts each element with a funnel shift, applies the
+//     functor, and deposits the result into a two-word output window flushed word
+//     by word over the input tile; all shifts are the same for every thread
+//     (immediates when the layout is compiled in).
 //
 // Thread mapping for format conversions (cuda_kernels_dense_convert.cuh): dense ->
 // padded/planes takes one thread per four ELEMENTS (funnel shifts at per-lane offsets

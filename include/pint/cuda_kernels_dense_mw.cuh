@@ -12,7 +12,8 @@
 // operator+ propagates exactly those; flag moves are multi-word shifts.  No per-element
 // extract / deposit at all: 12-bit samples cost ~6 ALU ops per element instead of ~15 with the
 // sliding windows, which turns the narrow layouts from ALU-bound into HBM-bound.
-// Used for compiled-in layouts with N <= kMaxMwWords (the chunk must live in registers).
+// Used for chunks of N <= kMaxMwWords words (the chunk must live in registers), with compiled-in
+// masks (static_masks<chunk_layout<Bits...>>) or run-time masks (runtime_chunk_masks<N>).
 // Included by cuda_kernels_dense.cuh (after its helpers, before its kernels).
 #pragma once
 
