@@ -88,6 +88,42 @@ binary_pair_stream_kernel(const uint4* a, const uint4* b, uint4* out0, uint4* ou
     }
 }
 
+// 32-byte-vector form (see vec32 in cuda_kernels_stream.cuh)
+template <class Fn, class Cfg>
+__global__ void __launch_bounds__(Cfg::BLOCK)
+binary_pair_stream256_kernel(const vec32* a, const vec32* b, vec32* out0, vec32* out1, size_t nvec,
+                             const __grid_constant__ Fn fn)
+{
+    using W = typename Fn::word;
+    constexpr int U = Cfg::UNROLL / 2 > 0 ? Cfg::UNROLL / 2 : 1, B = Cfg::BLOCK;
+    constexpr size_t tile = size_t(U) * B;
+    const size_t nfull = nvec / tile;
+    auto f0 = [&](W x, W y) { return fn.first(x, y); };
+    auto f1 = [&](W x, W y) { return fn.second(x, y); };
+    auto emit = [&](size_t i, const vec32& x, const vec32& y) {
+        vec32 r;
+        r.lo = map_words2<W>(x.lo, y.lo, f0);
+        r.hi = map_words2<W>(x.hi, y.hi, f0);
+        st32(out0 + i, r);
+        r.lo = map_words2<W>(x.lo, y.lo, f1);
+        r.hi = map_words2<W>(x.hi, y.hi, f1);
+        st32(out1 + i, r);
+    };
+    for (size_t t = blockIdx.x; t < nfull; t += gridDim.x) {
+        const size_t base = t * tile + threadIdx.x;
+        vec32 va[U], vb[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) va[u] = ld32(a + base + size_t(u) * B);
+#pragma unroll
+        for (int u = 0; u < U; ++u) vb[u] = ld32(b + base + size_t(u) * B);
+#pragma unroll
+        for (int u = 0; u < U; ++u) emit(base + size_t(u) * B, va[u], vb[u]);
+    }
+    if (blockIdx.x == nfull % gridDim.x) {
+        for (size_t i = nfull * tile + threadIdx.x; i < nvec; i += B) emit(i, ld32(a + i), ld32(b + i));
+    }
+}
+
 // The vector body runs the pair kernel; heads, tails and operands with different
 // misalignments go through the single-op launcher (element-granular kernels that
 // the library instantiates anyway).  Outputs must not overlap the inputs or each
@@ -110,6 +146,18 @@ cudaError_t launch_binary_pair(const void* a, const void* b, void* out0, void* o
     };
     const void* ptrs[4] = {a, b, out0, out1};
     size_t head = 0, nvec = 0, tail = 0;
+    if (Cfg::LD == CACHE_STREAMING && Cfg::ST == CACHE_STREAMING &&
+        split_aligned(sizeof(Elem), n, ptrs, 4, &head, &nvec, &tail, 32) && nvec) {
+        if (cudaError_t rc = single(0, head)) return rc;
+        constexpr size_t tile = size_t(Cfg::UNROLL / 2 > 0 ? Cfg::UNROLL / 2 : 1) * Cfg::BLOCK;
+        const size_t ntiles = (nvec + tile - 1) / tile;
+        binary_pair_stream256_kernel<Fn, Cfg><<<grid_for(ntiles, g), Cfg::BLOCK, 0, stream>>>(
+            reinterpret_cast<const vec32*>(ea + head), reinterpret_cast<const vec32*>(eb + head),
+            reinterpret_cast<vec32*>(e0 + head), reinterpret_cast<vec32*>(e1 + head), nvec, Fn{p});
+        count_launch(g);
+        if (cudaError_t rc = single(n - tail, tail)) return rc;
+        return cudaGetLastError();
+    }
     if (!split_aligned(sizeof(Elem), n, ptrs, 4, &head, &nvec, &tail)) return single(0, n);
     if (cudaError_t rc = single(0, head)) return rc;
     if (nvec) {

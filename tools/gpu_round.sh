@@ -23,6 +23,6 @@ timeout 900 ncu --set full --clock-control none --import-source on -k regex:bina
 echo "ncu pair rc=$?"
 PK="python tools/profile_kernels.py 26"
 timeout 300 $PK > $out/${tag}_profile_kernels.log 2>&1 && \
-timeout 1200 ncu --set full --clock-control none --import-source on -k regex:dense_ -c 40 -o $out/${tag}_ncu_full_dense $PK > $out/${tag}_ncu_full_dense.log 2>&1
+timeout 1200 ncu --set full --clock-control none --import-source on -k regex:dense_binary -c 14 -o $out/${tag}_ncu_full_dense $PK > $out/${tag}_ncu_full_dense.log 2>&1
 echo "ncu dense rc=$?"
 ls -la $out | tail -24

@@ -83,6 +83,55 @@ static void run_pair(const char* tag, const void* a, const void* b, void* o0, vo
     });
 }
 
+// 256-bit global accesses (LDG.E.256 / STG.E.256, sm_100a): half the memory instructions per byte
+struct u8v { uint32_t v[8]; };
+__device__ __forceinline__ u8v ld32cs(const void* p)
+{
+    u8v r;
+    asm volatile("ld.global.cs.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r.v[0]), "=r"(r.v[1]), "=r"(r.v[2]), "=r"(r.v[3]), "=r"(r.v[4]), "=r"(r.v[5]), "=r"(r.v[6]), "=r"(r.v[7]) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ void st32cs(void* p, const u8v& r)
+{
+    asm volatile("st.global.cs.v8.u32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+                 :: "l"(p), "r"(r.v[0]), "r"(r.v[1]), "r"(r.v[2]), "r"(r.v[3]), "r"(r.v[4]), "r"(r.v[5]), "r"(r.v[6]), "r"(r.v[7]) : "memory");
+}
+template <class Fn, int U, int B, bool Pair>
+__global__ void __launch_bounds__(B)
+stream256_kernel(const char* a, const char* b, char* o0, char* o1, size_t nv32, const __grid_constant__ Fn fn)
+{
+    const size_t base = (size_t(blockIdx.x) * U * B + threadIdx.x);
+    u8v va[U], vb[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) if (base + size_t(u) * B < nv32) va[u] = ld32cs(a + (base + size_t(u) * B) * 32);
+#pragma unroll
+    for (int u = 0; u < U; ++u) if (base + size_t(u) * B < nv32) vb[u] = ld32cs(b + (base + size_t(u) * B) * 32);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        if (base + size_t(u) * B >= nv32) continue;
+        u8v r0, r1;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            if constexpr (Pair) { r0.v[j] = fn.first(va[u].v[j], vb[u].v[j]); r1.v[j] = fn.second(va[u].v[j], vb[u].v[j]); }
+            else r0.v[j] = fn(va[u].v[j], vb[u].v[j]);
+        }
+        st32cs(o0 + (base + size_t(u) * B) * 32, r0);
+        if constexpr (Pair) st32cs(o1 + (base + size_t(u) * B) * 32, r1);
+    }
+}
+template <class Fn, int U, int B, bool Pair>
+static void run256(const char* tag, const void* a, const void* b, void* o0, void* o1, size_t nvec)
+{
+    const size_t nv32 = nvec / 2;
+    const size_t grid = (nv32 + size_t(U) * B - 1) / (size_t(U) * B);
+    char name[128];
+    std::snprintf(name, sizeof name, "%s 256-bit accesses U%d B%d", tag, U, B);
+    time_it(name, double(nvec) * (Pair ? 64 : 48), [&] {
+        stream256_kernel<Fn, U, B, Pair><<<unsigned(grid), B>>>((const char*)a, (const char*)b, (char*)o0, (char*)o1, nv32, Fn{});
+    });
+}
+
 // persistent CTAs that take tiles in address order from a global counter (instead of a grid stride)
 template <class Fn, class Cfg>
 __global__ void __launch_bounds__(Cfg::BLOCK)
@@ -168,6 +217,23 @@ int main(int argc, char** argv)
     using FnIF = fused_fn<OP_ADD_SIGNED_SATURATE, static_fields<IRR>>;
     using FnX = swar_fn<OP_XOR, static_masks<RGBA>>;
 
+    if (argc > 3 && std::atoi(argv[3]) == 9) {
+        using Pu = pair_fn<OP_ADD_UNSIGNED_SATURATE, OP_ADD_SIGNED_SATURATE, static_masks<RGBA>>;
+        for (int rep = 0; rep < 2; ++rep) {
+            run_stream<FnU, 2, 256, 2, 2>("usat rgba8 128-bit", a, b, out, nvec, 0);
+            run256<FnU, 1, 256, false>("usat rgba8", a, b, out, out2, nvec);
+            run256<FnU, 2, 256, false>("usat rgba8", a, b, out, out2, nvec);
+            run256<FnU, 1, 128, false>("usat rgba8", a, b, out, out2, nvec);
+            run256<FnU, 1, 512, false>("usat rgba8", a, b, out, out2, nvec);
+            run_pair<Pu, 2, 256, 2, 2>("usat+ssat rgba8 128-bit", a, b, out, out2, nvec, 0);
+            run256<Pu, 1, 256, true>("usat+ssat rgba8 pair", a, b, out, out2, nvec);
+            run256<Pu, 2, 256, true>("usat+ssat rgba8 pair", a, b, out, out2, nvec);
+            run256<Pu, 1, 128, true>("usat+ssat rgba8 pair", a, b, out, out2, nvec);
+            run256<Pu, 1, 512, true>("usat+ssat rgba8 pair", a, b, out, out2, nvec);
+        }
+        std::printf("done\n");
+        return 0;
+    }
     if (argc > 3 && std::atoi(argv[3]) == 8) {
         // two ops in one pass (2 reads + 2 writes, 16 B per uint32 element): unroll / block / cache policy
         using Pu = pair_fn<OP_ADD_UNSIGNED_SATURATE, OP_ADD_SIGNED_SATURATE, static_masks<RGBA>>;
