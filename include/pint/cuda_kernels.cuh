@@ -59,6 +59,7 @@ struct static_masks {
     using word = typename SL::word;
     // many distinct widths make the saturating ops ALU-heavy: their kernels run with a deeper unroll
     static constexpr bool heavy_fill = SL::masks.nsh >= 3;
+    static constexpr bool compiled_in = true;
     __device__ __forceinline__ static constexpr word H() { return SL::masks.H; }
     __device__ __forceinline__ static constexpr word L() { return SL::masks.L; }
     __device__ __forceinline__ static constexpr word A() { return SL::masks.A; }
@@ -124,6 +125,7 @@ template <class Word>
 struct runtime_masks {
     using word = Word;
     static constexpr bool heavy_fill = true;
+    static constexpr bool compiled_in = false;
     Word mH, mL, mA, mM1, mHL, mLM1;
     Word keep[6];
     uint32_t shift0;   // w - 1 when all fields have the same width

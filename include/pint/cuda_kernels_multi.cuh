@@ -146,7 +146,10 @@ cudaError_t launch_binary_pair(const void* a, const void* b, void* out0, void* o
     };
     const void* ptrs[4] = {a, b, out0, out1};
     size_t head = 0, nvec = 0, tail = 0;
-    if (Cfg::LD == CACHE_STREAMING && Cfg::ST == CACHE_STREAMING &&
+    // 32-byte vectors for light functors on 32-bit words only (a 64-bit pair is 5-10 % slower with
+    // them, RGBA8 pair 1 % faster: same-box A/B in profiles/r01z_ab_vec256.log)
+    if ((g.vec256 == 2 || (g.vec256 == 1 && !Fn::heavy && sizeof(typename Fn::word) == 4)) &&
+        Cfg::LD == CACHE_STREAMING && Cfg::ST == CACHE_STREAMING &&
         split_aligned(sizeof(Elem), n, ptrs, 4, &head, &nvec, &tail, 32) && nvec) {
         if (cudaError_t rc = single(0, head)) return rc;
         constexpr size_t tile = size_t(Cfg::UNROLL / 2 > 0 ? Cfg::UNROLL / 2 : 1) * Cfg::BLOCK;

@@ -120,6 +120,10 @@ template <int Op, class P>
 struct swar_fn {
     using word = typename P::word;
     static constexpr bool heavy = P::heavy_fill && !(Op == OP_ADD_WRAP || Op == OP_SUB_WRAP || Op == OP_OR || Op == OP_AND || Op == OP_XOR);
+    // 32-byte global accesses: faster for light functors and for heavy compiled-in ones on 32-bit
+    // words, slower for heavy 64-bit ones (registers), neutral to slower for heavy run-time-mask
+    // ones; same-box A/B in profiles/r01z_ab_vec256.log
+    static constexpr bool vec256 = !heavy || (sizeof(word) == 4 && P::compiled_in);
     P p;
     __device__ __forceinline__ word operator()(word a, word b) const { return apply_op<Op>(a, b, p); }
 };
@@ -340,6 +344,7 @@ struct launch_geom {
     tile_counter* counters = nullptr;
     unsigned* counter_cursor = nullptr;
     int ordered_ctas_per_sm = 0;  // 0 = off
+    int vec256 = 1;               // 32-byte vectors: 0 never, 1 where measured faster (light functors), 2 wherever aligned
 };
 
 inline tile_counter* next_tile_counter(const launch_geom& g)
@@ -401,7 +406,8 @@ cudaError_t launch_binary(const void* a, const void* b, void* out, size_t n, con
         count_launch(g);
     };
     // 32-byte vectors when the operands allow it (and the ordered persistent mode is not asked for)
-    if (Cfg::LD == CACHE_STREAMING && Cfg::ST == CACHE_STREAMING && g.ordered_ctas_per_sm <= 0 &&
+    if ((g.vec256 == 2 || (g.vec256 == 1 && Fn::vec256)) && Cfg::LD == CACHE_STREAMING && Cfg::ST == CACHE_STREAMING &&
+        g.ordered_ctas_per_sm <= 0 &&
         split_aligned(sizeof(Elem), n, ptrs, 3, &head, &nvec, &tail, 32) && nvec) {
         elems(0, head);
         constexpr size_t tile = size_t(Cfg::UNROLL / 2 > 0 ? Cfg::UNROLL / 2 : 1) * Cfg::BLOCK;

@@ -92,7 +92,8 @@ unsigned long long pint_cuda_launch_count(void);
  * SMs * k CTAs that draw tiles in address order; default 0 = always one CTA per tile),
  * "host_chunk_bytes" / "host_slots" (staging ring of the host-buffer path),
  * "dense_threads" / "dense_tile_bytes" (CTA size and per-operand tile of the dense bit-stream
- * kernels; 0 = chosen from the layout), "dense_windows" (1 = layouts without compiled-in dense
+ * kernels; 0 = chosen from the layout), "vec256" (32-byte global accesses in the stream kernels:
+ * 0 never, 1 = default, where measured faster, 2 wherever the operands are 32-byte congruent), "dense_windows" (1 = layouts without compiled-in dense
  * kernels always use the element-by-element window kernels; testing).  Returns 0 or PINT_E_ARG. */
 int pint_cuda_set_option(const char* key, long value);
 long pint_cuda_get_option(const char* key);

@@ -65,6 +65,7 @@ launch_geom geom()
     g.ctas_per_sm = (int)opts().ctas_per_sm;
     g.launch_counter = &g_launches;
     g.ordered_ctas_per_sm = (int)opts().ordered_ctas_per_sm;
+    g.vec256 = (int)opts().vec256;
     if (g.ordered_ctas_per_sm > 0) {
         g.counters = current_counters();
         g.counter_cursor = &g_counter_cursor;
@@ -233,6 +234,7 @@ int pint_cuda_set_option(const char* key, long value)
     if (!std::strcmp(key, "ordered_ctas_per_sm")) { if (value < 0 || value > 32) return PINT_E_ARG; opts().ordered_ctas_per_sm = value; return PINT_OK; }
     if (!std::strcmp(key, "host_chunk_bytes")) { if (value < 4096) return PINT_E_ARG; opts().host_chunk_bytes = value; return PINT_OK; }
     if (!std::strcmp(key, "host_slots")) { if (value < 1 || value > 8) return PINT_E_ARG; opts().host_slots = value; return PINT_OK; }
+    if (!std::strcmp(key, "vec256")) { if (value < 0 || value > 2) return PINT_E_ARG; opts().vec256 = value; return PINT_OK; }
     if (!std::strcmp(key, "dense_windows")) { opts().dense_windows = value != 0; return PINT_OK; }
     if (!std::strcmp(key, "dense_threads")) { if (value < 0 || value > 1024 || value % 32) return PINT_E_ARG; opts().dense_threads = value; return PINT_OK; }
     if (!std::strcmp(key, "dense_tile_bytes")) { if (value < 0 || value > 100 * 1024) return PINT_E_ARG; opts().dense_tile_bytes = value; return PINT_OK; }
@@ -247,6 +249,7 @@ long pint_cuda_get_option(const char* key)
     if (!std::strcmp(key, "ordered_ctas_per_sm")) return opts().ordered_ctas_per_sm;
     if (!std::strcmp(key, "host_chunk_bytes")) return opts().host_chunk_bytes;
     if (!std::strcmp(key, "host_slots")) return opts().host_slots;
+    if (!std::strcmp(key, "vec256")) return opts().vec256;
     if (!std::strcmp(key, "dense_windows")) return opts().dense_windows;
     if (!std::strcmp(key, "dense_threads")) return opts().dense_threads;
     if (!std::strcmp(key, "dense_tile_bytes")) return opts().dense_tile_bytes;

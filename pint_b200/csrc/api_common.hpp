@@ -14,6 +14,7 @@ struct options {
     long ctas_per_sm = 0;  // 0 = one CTA per tile (fastest, see launch_geom)
     long host_chunk_bytes = 32L << 20;  // per operand per pipeline slot
     long host_slots = 3;
+    long vec256 = 1;            // 32-byte vector kernels: 0 never, 1 auto (light functors), 2 wherever aligned
     long dense_windows = 0;     // 1 = run-time dense layouts always use the element-by-element window kernels (testing)
     long dense_threads = 0;     // dense bit-stream kernels: threads per CTA (0 = from the chunk size)
     long dense_tile_bytes = 0;  // ... and tile bytes per operand (0 = 16 KB target)

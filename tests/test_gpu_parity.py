@@ -284,3 +284,29 @@ def test_fill_and_checksum_match_oracle(P, oracle):
         np.testing.assert_array_equal(to_np(x), want)
         assert ops.checksum(x) == oracle.checksum(want)
         assert ops.checksum(x[1:]) == oracle.checksum(want[1:])  # misaligned start
+
+
+@pytest.mark.parametrize("vec256", [0, 2])
+def test_vector_width_option_same_results(P, oracle, vec256):
+    """16-byte-only and 32-byte-everywhere kernel selection (option "vec256") are bit-identical to the
+    oracle: single ops, op pairs and the fused kernel, aligned and 16-byte-but-not-32-byte-aligned operands."""
+    pint_b200, ops = P
+    ops.set_option("vec256", vec256)
+    try:
+        for eb, bits in [(4, (8, 8, 8, 8)), (8, (3, 7, 11, 13, 17, 13)), (2, (5, 6, 5)), (4, (1, 2, 3, 4, 5, 6, 11))]:
+            L = pint_b200.Layout(eb, *bits)
+            n = (1 << 19) + 11
+            a_h, b_h = oracle.fill(eb, n, 91), oracle.fill(eb, n, 92)
+            for off in (0, 16 // eb, 1):
+                a, b = to_dev(a_h, off), to_dev(b_h, off)
+                for op in ("add_unsigned_saturate", "sub_signed_saturate", "min_signed"):
+                    want = oracle.binary(op, eb, bits, a_h, b_h)
+                    np.testing.assert_array_equal(to_np(ops.binary(op, L, a, b)), want, err_msg=f"{L} {op} off{off}")
+                    np.testing.assert_array_equal(to_np(ops.fused_unpack_arith_repack(op, L, a, b)), want)
+                pair = ["add_unsigned_saturate", "add_signed_saturate"]
+                outs = [to_dev(np.zeros(n, dtype=a_h.dtype), off) for _ in pair]
+                ops.binary_multi(pair, L, a, b, outs=outs)
+                for op, o in zip(pair, outs):
+                    np.testing.assert_array_equal(to_np(o), oracle.binary(op, eb, bits, a_h, b_h))
+    finally:
+        ops.set_option("vec256", 1)
