@@ -89,12 +89,25 @@ pairs_reduce_kernel(const Elem* pairs, size_t n, uint64_t* sum, const __grid_con
     uint64_t s = 0;
     const bool vec_ok = (reinterpret_cast<uintptr_t>(pairs) & 15u) == 0;
     const size_t nvec = vec_ok ? n / PER : 0;
-    for (size_t v = size_t(blockIdx.x) * blockDim.x + threadIdx.x; v < nvec; v += size_t(gridDim.x) * blockDim.x) {
+    // tiles of U * blockDim vectors, U independent loads per thread issued before the first use
+    constexpr int U = 4;
+    const uint4* vec = reinterpret_cast<const uint4*>(pairs);
+    const size_t tile = size_t(U) * blockDim.x, nfull = nvec / tile;
+    auto add_vec = [&](const uint4& q) {
         union { uint4 q; Elem e[2 * PER]; } u;
-        u.q = ld16<CACHE_STREAMING>(reinterpret_cast<const uint4*>(pairs) + v);
+        u.q = q;
 #pragma unroll
         for (int j = 0; j < PER; ++j) s += Elem(apply_op<Op>(W(u.e[2 * j]), W(u.e[2 * j + 1]), p));
+    };
+    for (size_t t = blockIdx.x; t < nfull; t += gridDim.x) {
+        uint4 q[U];
+#pragma unroll
+        for (int k = 0; k < U; ++k) q[k] = ld16<CACHE_STREAMING>(vec + t * tile + size_t(k) * blockDim.x + threadIdx.x);
+#pragma unroll
+        for (int k = 0; k < U; ++k) add_vec(q[k]);
     }
+    for (size_t v = nfull * tile + size_t(blockIdx.x) * blockDim.x + threadIdx.x; v < nvec; v += size_t(gridDim.x) * blockDim.x)
+        add_vec(ld16<CACHE_STREAMING>(vec + v));
     for (size_t i = nvec * PER + size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x)
         s += Elem(apply_op<Op>(W(pairs[2 * i]), W(pairs[2 * i + 1]), p));
     block_reduce_sum_xor(s, 0, sum);
