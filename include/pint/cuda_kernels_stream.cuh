@@ -320,6 +320,33 @@ unary_stream_kernel(const uint4* in, uint4* out, size_t nvec, const __grid_const
     }
 }
 
+template <class Word, class Cfg>
+__global__ void __launch_bounds__(Cfg::BLOCK)
+unary_stream256_kernel(const vec32* in, vec32* out, size_t nvec, const __grid_constant__ unary_params<Word> u)
+{
+    constexpr int U = Cfg::UNROLL, B = Cfg::BLOCK;  // twice the bytes per thread of the 16-byte kernel: one stream only
+    constexpr size_t tile = size_t(U) * B;
+    const size_t nfull = nvec / tile;
+    auto f = [&](Word x) { return apply_unary(x, u); };
+    auto apply = [&](const vec32& x) {
+        vec32 r;
+        r.lo = map_words1<Word>(x.lo, f);
+        r.hi = map_words1<Word>(x.hi, f);
+        return r;
+    };
+    for (size_t t = blockIdx.x; t < nfull; t += gridDim.x) {
+        const size_t base = t * tile + threadIdx.x;
+        vec32 v[U];
+#pragma unroll
+        for (int k = 0; k < U; ++k) v[k] = ld32(in + base + size_t(k) * B);
+#pragma unroll
+        for (int k = 0; k < U; ++k) st32(out + base + size_t(k) * B, apply(v[k]));
+    }
+    if (blockIdx.x == nfull % gridDim.x) {
+        for (size_t i = nfull * tile + threadIdx.x; i < nvec; i += B) st32(out + i, apply(ld32(in + i)));
+    }
+}
+
 template <class Elem, class Word>
 __global__ void __launch_bounds__(256)
 unary_elem_kernel(const Elem* in, Elem* out, size_t n, const __grid_constant__ unary_params<Word> u)
@@ -453,13 +480,24 @@ cudaError_t launch_unary(const void* in, void* out, size_t n, const unary_params
     Elem* eo = static_cast<Elem*>(out);
     const void* ptrs[2] = {in, out};
     size_t head = 0, nvec = 0, tail = 0;
-    const bool vec_ok = split_aligned(sizeof(Elem), n, ptrs, 2, &head, &nvec, &tail);
     auto elems = [&](size_t first, size_t count) {
         if (!count) return;
         const unsigned grid = grid_for((count + 255) / 256, g);
         unary_elem_kernel<Elem, Word><<<grid, 256, 0, stream>>>(ei + first, eo + first, count, u);
         count_launch(g);
     };
+    if (g.vec256 != 0 && Cfg::LD == CACHE_STREAMING && Cfg::ST == CACHE_STREAMING && g.ordered_ctas_per_sm <= 0 &&
+        split_aligned(sizeof(Elem), n, ptrs, 2, &head, &nvec, &tail, 32) && nvec) {
+        elems(0, head);
+        constexpr size_t tile = size_t(Cfg::UNROLL) * Cfg::BLOCK;
+        const size_t ntiles = (nvec + tile - 1) / tile;
+        unary_stream256_kernel<Word, Cfg><<<grid_for(ntiles, g), Cfg::BLOCK, 0, stream>>>(
+            reinterpret_cast<const vec32*>(ei + head), reinterpret_cast<vec32*>(eo + head), nvec, u);
+        count_launch(g);
+        elems(n - tail, tail);
+        return cudaGetLastError();
+    }
+    const bool vec_ok = split_aligned(sizeof(Elem), n, ptrs, 2, &head, &nvec, &tail);
     if (!vec_ok) {
         elems(0, n);
         return cudaGetLastError();
