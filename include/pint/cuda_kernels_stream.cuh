@@ -486,7 +486,9 @@ cudaError_t launch_unary(const void* in, void* out, size_t n, const unary_params
         unary_elem_kernel<Elem, Word><<<grid, 256, 0, stream>>>(ei + first, eo + first, count, u);
         count_launch(g);
     };
-    if (g.vec256 != 0 && Cfg::LD == CACHE_STREAMING && Cfg::ST == CACHE_STREAMING && g.ordered_ctas_per_sm <= 0 &&
+    // 32-byte accesses measured 0.5 % SLOWER for the one-in/one-out maps (profiles/r02f_ab_vec256_unary.log):
+    // only when forced (option "vec256" = 2, kept for parity tests and re-measurement)
+    if (g.vec256 == 2 && Cfg::LD == CACHE_STREAMING && Cfg::ST == CACHE_STREAMING && g.ordered_ctas_per_sm <= 0 &&
         split_aligned(sizeof(Elem), n, ptrs, 2, &head, &nvec, &tail, 32) && nvec) {
         elems(0, head);
         constexpr size_t tile = size_t(Cfg::UNROLL) * Cfg::BLOCK;

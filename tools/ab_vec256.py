@@ -43,6 +43,21 @@ cases = [
 ]
 UDT[2] = torch.uint16
 n = 1 << 29
+if len(sys.argv) > 1 and sys.argv[1] == "unary":
+    for name, eb, bits in (("RGBA8 shift_left 3", 4, (8, 8, 8, 8)), ("irregular u64 slice<1,4>", 8, (3, 7, 11, 13, 17, 13))):
+        L = pint_b200.Layout(eb, *bits)
+        a = torch.empty(n, dtype=UDT[eb], device="cuda")
+        out = torch.empty_like(a)
+        ops.fill_splitmix(a, 1)
+        res = []
+        for rep in range(3):
+            for mode in (0, 2):
+                ops.set_option("vec256", mode)
+                ms = timed((lambda: ops.shift_left(L, a, 3, out=out)) if eb == 4 else (lambda: ops.slice(L, 1, 4, a, out=out)))
+                res.append(2 * eb * n / ms / 1e6)
+        ops.set_option("vec256", 1)
+        print("%-36s 16B: %6.0f %6.0f %6.0f   32B: %6.0f %6.0f %6.0f GB/s" % (name, res[0], res[2], res[4], res[1], res[3], res[5]), flush=True)
+    sys.exit(0)
 for name, eb, bits, op_list, fused in cases:
     L = pint_b200.Layout(eb, *bits)
     a = torch.empty(n, dtype=UDT[eb], device="cuda")
