@@ -297,6 +297,21 @@ inline void binary_multi(const pint_op (&ops)[NOps], const stream_byte* a, const
     check(pint_cuda_dense_binary_multi((int)NOps, codes, &l, a, b, o, n, stream), "pint::cuda::dense::binary_multi");
 }
 
+// shift_left / shift_right_unsigned of every field by one uniform amount (pint.hpp:1006-1029)
+template <class P>
+inline void shift_left(const stream_byte* in, stream_byte* out, size_t n, size_t amount, stream_t stream = nullptr)
+{
+    const pint_layout l = layout_from<P>::get();
+    check(pint_cuda_dense_shift(1, &l, amount, in, out, n, stream), "pint::cuda::dense::shift_left");
+}
+
+template <class P>
+inline void shift_right_unsigned(const stream_byte* in, stream_byte* out, size_t n, size_t amount, stream_t stream = nullptr)
+{
+    const pint_layout l = layout_from<P>::get();
+    check(pint_cuda_dense_shift(0, &l, amount, in, out, n, stream), "pint::cuda::dense::shift_right_unsigned");
+}
+
 // padded packed_int array <-> dense stream
 template <class Integer, size_t Bits0, size_t... Bits>
 inline void pack(const packed_int<Integer, Bits0, Bits...>* padded, stream_byte* dense_out, size_t n, stream_t stream = nullptr)

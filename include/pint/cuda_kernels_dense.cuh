@@ -308,6 +308,42 @@ __device__ __forceinline__ void process_chunk_pair(typename PFn::word* A, typena
     }
 }
 
+// One-in/one-out maps (shift_left / shift_right_unsigned) element by element: one input window,
+// one output window, in place.
+template <class W>
+struct window_unary_fn {
+    using word = W;
+    unary_params<W> u;
+    __device__ __forceinline__ W operator()(W v) const { return apply_unary(v, u); }
+};
+
+template <class Fn, class Geo>
+__device__ __forceinline__ void process_chunk_unary(typename Fn::word* A, const Fn& fn, const Geo& geo)
+{
+    using W = typename Fn::word;
+    constexpr uint32_t WB = 8 * sizeof(W);
+    const uint32_t S = geo.S(), Cw = geo.Cw(), G = geo.G();
+    const W SM = ones_w<W>(S);
+    W ca = A[0], na = Cw > 1 ? A[1] : W(0);
+    W ocur = 0, onxt = 0;
+    uint32_t sh = 0, w = 0;
+    for (uint32_t e = 0; e < G; ++e) {
+        const W r = fn(funnel_r(ca, na, sh) & SM) & SM;
+        ocur |= r << sh;
+        onxt |= spill_l(r, sh);
+        sh += S;
+        if (sh >= WB) {
+            sh -= WB;
+            A[w] = ocur;
+            ocur = onxt;
+            onxt = 0;
+            ++w;
+            ca = na;
+            na = w + 1 < Cw ? A[w + 1] : W(0);
+        }
+    }
+}
+
 // zero the bits of `word` (which starts at bit `start` of the tile) at or above bit `limit`
 template <class W>
 __device__ __forceinline__ W clip_word(W word, uint64_t start, uint64_t limit)
@@ -336,8 +372,9 @@ __device__ __forceinline__ uint4 clip_vec(uint4 v, uint64_t start_bit, uint64_t 
 // forced to zero (op(0, 0) == 0 for every op, so the output tail is zero too).
 // `out` may alias a or b: the tile is complete in shared memory before any
 // store.  Dynamic shared memory: 2 * tile bytes.
-// Pair = true: Fn is a pair_fn; the second result is produced in place over the b tile and stored to out1.
-template <class Fn, class Geo, bool Pair = false>
+// Mode 0: out = fn(a, b).  Mode 1 (pair): Fn is a pair_fn; the second result is produced in place over the
+// b tile and stored to out1.  Mode 2 (unary): out = fn(a); b is not read and has no tile.
+template <class Fn, class Geo, int Mode = 0>
 __global__ void dense_binary_kernel(const uint4* a, const uint4* b, uint4* out, uint4* out1, size_t total_vec,
                                     uint64_t valid_bits, const __grid_constant__ Fn fn, const __grid_constant__ Geo geo)
 {
@@ -354,6 +391,7 @@ __global__ void dense_binary_kernel(const uint4* a, const uint4* b, uint4* out, 
     const uint64_t tile_bits = uint64_t(tile_bytes) * 8;
     const bool whole = (t + 1) * tile_bits <= valid_bits;
     uint64_t pol = 0;
+    constexpr bool Pair = Mode == 1, Unary = Mode == 2;
 
     if (whole) {
         if (threadIdx.x == 0) {
@@ -361,9 +399,9 @@ __global__ void dense_binary_kernel(const uint4* a, const uint4* b, uint4* out, 
             mbar_init(&full, 1);
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            mbar_expect_tx(&full, 2 * tile_bytes);
+            mbar_expect_tx(&full, (Unary ? 1 : 2) * tile_bytes);
             bulk_load(A, a + t * tile_vecs, tile_bytes, &full, pol);
-            bulk_load(B, b + t * tile_vecs, tile_bytes, &full, pol);
+            if constexpr (!Unary) bulk_load(B, b + t * tile_vecs, tile_bytes, &full, pol);
         }
         __syncthreads();  // the barrier is initialised before anyone polls it
         mbar_wait(&full, 0);
@@ -374,17 +412,20 @@ __global__ void dense_binary_kernel(const uint4* a, const uint4* b, uint4* out, 
             uint4 x = make_uint4(0, 0, 0, 0), y = x;
             if (gv < total_vec) {
                 x = clip_vec(ld16<CACHE_STREAMING>(a + gv), uint64_t(v) * 128, limit);
-                y = clip_vec(ld16<CACHE_STREAMING>(b + gv), uint64_t(v) * 128, limit);
+                if constexpr (!Unary) y = clip_vec(ld16<CACHE_STREAMING>(b + gv), uint64_t(v) * 128, limit);
             }
             reinterpret_cast<uint4*>(A)[v] = x;
-            reinterpret_cast<uint4*>(B)[v] = y;
+            if constexpr (!Unary) reinterpret_cast<uint4*>(B)[v] = y;
         }
         __syncthreads();
     }
 
     for (uint32_t r = 0; r < R; ++r) {
         const uint32_t c = (r * T + threadIdx.x) * Cw;
-        if constexpr (Geo::whole_chunk) {
+        if constexpr (Unary) {
+            if constexpr (Geo::whole_chunk) process_chunk_mw_unary<Fn, int(Geo::kCw)>(A + c, fn);
+            else process_chunk_unary(A + c, fn, geo);
+        } else if constexpr (Geo::whole_chunk) {
             if constexpr (Pair) process_chunk_mw_pair<Fn, int(Geo::kCw)>(A + c, B + c, fn);
             else process_chunk_mw<Fn, int(Geo::kCw)>(A + c, B + c, fn);
         } else {
@@ -434,7 +475,7 @@ inline void choose_tile(uint32_t cw, const dense_tuning& tune, uint32_t* threads
 }
 
 // a, b, out: 16-byte aligned dense streams of n elements (ceil(n*S/128)*16 bytes each)
-template <class Fn, class Geo, bool Pair = false>
+template <class Fn, class Geo, int Mode = 0>
 cudaError_t launch_dense_binary(const void* a, const void* b, void* out, size_t n, const Fn& fn, Geo geo,
                                 cudaStream_t stream, const launch_geom& g, const dense_tuning& tune = dense_tuning(),
                                 void* out1 = nullptr)
@@ -448,8 +489,8 @@ cudaError_t launch_dense_binary(const void* a, const void* b, void* out, size_t 
     const size_t total_vec = size_t((valid_bits + 127) / 128);
     const size_t tile_bytes = size_t(T) * R * geo.Cw() * sizeof(W);
     const size_t ntiles = (total_vec * 16 + tile_bytes - 1) / tile_bytes;
-    const size_t smem = 2 * tile_bytes;
-    auto kernel = dense_binary_kernel<Fn, Geo, Pair>;
+    const size_t smem = (Mode == 2 ? 1 : 2) * tile_bytes;
+    auto kernel = dense_binary_kernel<Fn, Geo, Mode>;
     if (smem > 48 * 1024) {
         cudaError_t rc = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
         if (rc != cudaSuccess) return rc;

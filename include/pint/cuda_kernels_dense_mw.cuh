@@ -74,6 +74,19 @@ struct mw {
         }
         return r;
     }
+    // logical shift left by s < 32 * N bits
+    PINT_HD friend constexpr mw operator<<(const mw& x, uint32_t s)
+    {
+        mw r;
+        const int ws = int(s / 32);
+        const uint32_t bs = s % 32;
+        for (int j = 0; j < N; ++j) {
+            const uint32_t hi = j - ws >= 0 ? x.w[j - ws] : 0u;
+            const uint32_t lo = j - ws - 1 >= 0 ? x.w[j - ws - 1] : 0u;
+            r.w[j] = bs ? ((hi << bs) | (lo >> (32 - bs))) : hi;
+        }
+        return r;
+    }
     PINT_HD friend constexpr bool operator==(const mw& x, const mw& y)
     {
         for (int j = 0; j < N; ++j)
@@ -244,6 +257,45 @@ __device__ __forceinline__ void process_chunk_mw(uint32_t* A, const uint32_t* B,
 #pragma unroll
     for (int j = 0; j < N; ++j) { a.w[j] = A[j]; b.w[j] = B[j]; }
     const mw<N> r = fn(a, b);
+#pragma unroll
+    for (int j = 0; j < N; ++j) A[j] = r.w[j];
+}
+
+// shift_left / shift_right_unsigned with a uniform amount (pint.hpp:1006-1029) on a whole chunk:
+// "mask, shift" with the per-field keep mask replicated over the chunk's elements (the shift
+// cannot move a kept bit out of its field, so multi-word shifts are exact).
+template <int N>
+struct mw_unary_fn {
+    using word = mw<N>;
+    mw<N> pre;
+    uint32_t amount;  // < max(Bits)
+    uint32_t left;
+    __device__ __forceinline__ mw<N> operator()(const mw<N>& v) const
+    {
+        const mw<N> t = v & pre;
+        return left ? (t << amount) : (t >> amount);
+    }
+};
+
+// element mask (S bits) replicated over the G elements of a chunk
+template <int N>
+inline mw<N> replicate_element_mask(uint64_t elem_mask, uint32_t S)
+{
+    mw<N> r;
+    const uint32_t G = 32u * N / S;
+    for (uint32_t e = 0; e < G; ++e)
+        for (uint32_t b = 0; b < S; ++b)
+            if ((elem_mask >> b) & 1) r.set_bit(e * S + b);
+    return r;
+}
+
+template <class Fn, int N>
+__device__ __forceinline__ void process_chunk_mw_unary(uint32_t* A, const Fn& fn)
+{
+    mw<N> a;
+#pragma unroll
+    for (int j = 0; j < N; ++j) a.w[j] = A[j];
+    const mw<N> r = fn(a);
 #pragma unroll
     for (int j = 0; j < N; ++j) A[j] = r.w[j];
 }

@@ -168,6 +168,10 @@ int pint_cuda_dense_binary(int op, const pint_layout* layout, const void* a, con
  * outputs must not overlap the inputs or each other. */
 int pint_cuda_dense_binary_multi(int nops, const int* ops, const pint_layout* layout, const void* a, const void* b,
                                  void* const* outs, size_t n, pint_stream_t stream);
+/* out = shift_left(in, amount) (pint.hpp:1006-1017) or shift_right_unsigned (pint.hpp:1019-1029) when
+ * left == 0, on a dense stream (2*S/8 bytes per element); uniform amount; out may be in exactly. */
+int pint_cuda_dense_shift(int left, const pint_layout* layout, uint64_t amount, const void* in, void* out, size_t n,
+                          pint_stream_t stream);
 /* dense[i] = low S bits of padded[i]  /  padded[i] = dense[i] zero-extended to Integer. */
 int pint_cuda_dense_pack(const pint_layout* layout, const void* padded, void* dense, size_t n, pint_stream_t stream);
 int pint_cuda_dense_unpack(const pint_layout* layout, const void* dense, void* padded, size_t n, pint_stream_t stream);

@@ -58,6 +58,7 @@ def lib():
             "pint_cuda_dense_bytes": (sz, [LP, sz]),
             "pint_cuda_dense_binary": (i, [i, LP, vp, vp, vp, sz, vp]),
             "pint_cuda_dense_binary_multi": (i, [i, C.POINTER(i), LP, vp, vp, C.POINTER(vp), sz, vp]),
+            "pint_cuda_dense_shift": (i, [i, LP, u64, vp, vp, sz, vp]),
             "pint_cuda_dense_pack": (i, [LP, vp, vp, sz, vp]),
             "pint_cuda_dense_unpack": (i, [LP, vp, vp, sz, vp]),
             "pint_cuda_dense_to_planes": (i, [LP, i, vp, C.POINTER(vp), i, sz, vp]),

@@ -267,6 +267,67 @@ int pint_cuda_dense_binary(int op, const pint_layout* layout, const void* a, con
                          : dense_generic<uint64_t>(op, d, S, a, b, out, n, s, g, ops));
 }
 
+int pint_cuda_dense_shift(int left, const pint_layout* layout, uint64_t amount, const void* in, void* out, size_t n,
+                          pint_stream_t stream)
+{
+    layout_desc d;
+    if (int rc = check_layout(layout, &d)) return rc;
+    if (n == 0) return PINT_OK;
+    if (!in || !out) return PINT_E_NULL;
+    if (((uintptr_t)in | (uintptr_t)out) % 16) return PINT_E_ARG;
+    const uint32_t S = total_bits(d);
+    const size_t bytes = dense_bytes(S, n);
+    {
+        const uintptr_t i = (uintptr_t)in, o = (uintptr_t)out;
+        if (in != out && i < o + bytes && o < i + bytes) return PINT_E_ALIAS;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    if (S == 8 || S == 16 || S == 32 || S == 64) {
+        pint_layout p = *layout;
+        p.elem_bytes = S / 8;
+        const size_t total = bytes / p.elem_bytes;
+        if (int rc = pint_cuda_shift(left, &p, amount, in, out, n, stream)) return rc;
+        if (total > n) return (int)cudaMemsetAsync((char*)out + n * p.elem_bytes, 0, (total - n) * p.elem_bytes, s);
+        return PINT_OK;
+    }
+    // per-field keep mask of ONE element, as pint_cuda_shift builds it (pint.hpp:630-705, 1006-1029):
+    // shift_left keeps the low (w - amount) bits of every field, shift_right_unsigned drops the low
+    // min(w, amount) bits; amount >= max(Bits) gives 0
+    layout_desc e = d;
+    e.elem_bytes = 8;
+    const auto m = make_word_masks<uint64_t>(e);
+    uint64_t pre = 0;
+    uint32_t amt = 0;
+    if (amount < m.max_bits) {
+        amt = (uint32_t)amount;
+        uint64_t mask = 0;
+        for (uint32_t k = 0; k < m.nuniq; ++k) {
+            const uint64_t lo = m.ulo[k];
+            const uint32_t w = m.uw[k];
+            const uint32_t sh = left ? (w > amt ? w - amt : 0) : (w < amt ? w : amt);
+            mask |= (sh >= 64 ? 0 : (lo << sh)) - lo;
+        }
+        pre = (left ? mask : ~mask) & m.A;
+    }
+    const launch_geom g = geom();
+    const int N = int(S / dense::gcd_u32(S, 32));
+    if (!opts().dense_windows) {
+        cudaError_t rc = cudaSuccess;
+        if (dense_mw_unary_part0(N, pre, amt, left != 0, S, in, out, n, s, g, tuning(), &rc) ||
+            dense_mw_unary_part1(N, pre, amt, left != 0, S, in, out, n, s, g, tuning(), &rc) ||
+            dense_mw_unary_part2(N, pre, amt, left != 0, S, in, out, n, s, g, tuning(), &rc))
+            return (int)rc;
+    }
+    if (S <= 32) {
+        dense::window_unary_fn<uint32_t> fn{{uint32_t(pre), ~0u, amt, left ? 1u : 0u}};
+        return (int)dense::launch_dense_binary<dense::window_unary_fn<uint32_t>, dense::runtime_geom<uint32_t>, 2>(
+            in, nullptr, out, n, fn, dense::runtime_geom<uint32_t>(S, 32), s, g, tuning());
+    }
+    dense::window_unary_fn<uint64_t> fn{{pre, ~0ULL, amt, left ? 1u : 0u}};
+    return (int)dense::launch_dense_binary<dense::window_unary_fn<uint64_t>, dense::runtime_geom<uint64_t>, 2>(
+        in, nullptr, out, n, fn, dense::runtime_geom<uint64_t>(S, 64), s, g, tuning());
+}
+
 int pint_cuda_dense_pack(const pint_layout* layout, const void* padded, void* dense, size_t n, pint_stream_t stream)
 {
     return convert_impl(true, layout, padded, dense, n, (cudaStream_t)stream);

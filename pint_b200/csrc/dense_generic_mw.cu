@@ -38,6 +38,15 @@ cudaError_t pair_n(int pair, const layout_desc& d, uint32_t S, const void* a, co
     return rc;
 }
 
+template <int N>
+cudaError_t unary_n(uint64_t elem_pre, uint32_t amount, bool left, uint32_t S, const void* in, void* out, size_t n,
+                    cudaStream_t s, const launch_geom& g, const dense_tuning& tune)
+{
+    dense::mw_unary_fn<N> fn{dense::replicate_element_mask<N>(elem_pre, S), amount, left ? 1u : 0u};
+    return dense::launch_dense_binary<dense::mw_unary_fn<N>, dense::mw_geom<N>, 2>(in, nullptr, out, n, fn, dense::mw_geom<N>{S, 1},
+                                                                                    s, g, tune);
+}
+
 constexpr int kFirst = 3 + 6 * PINT_MW_PART;  // N = kFirst, kFirst + 2, kFirst + 4
 
 }  // namespace
@@ -66,6 +75,17 @@ bool PINT_CAT(dense_mw_pair_part, PINT_MW_PART)(int N, int pair, const layout_de
     if (N == kFirst) *rc = pair_n<kFirst>(pair, d, S, a, b, out0, out1, n, s, g, tune, pairs);
     else if (N == kFirst + 2) *rc = pair_n<kFirst + 2>(pair, d, S, a, b, out0, out1, n, s, g, tune, pairs);
     else if (N == kFirst + 4) *rc = pair_n<kFirst + 4>(pair, d, S, a, b, out0, out1, n, s, g, tune, pairs);
+    else return false;
+    return true;
+}
+
+bool PINT_CAT(dense_mw_unary_part, PINT_MW_PART)(int N, uint64_t elem_pre, uint32_t amount, bool left, uint32_t S,
+                                                  const void* in, void* out, size_t n, cudaStream_t s,
+                                                  const launch_geom& g, const dense_tuning& tune, cudaError_t* rc)
+{
+    if (N == kFirst) *rc = unary_n<kFirst>(elem_pre, amount, left, S, in, out, n, s, g, tune);
+    else if (N == kFirst + 2) *rc = unary_n<kFirst + 2>(elem_pre, amount, left, S, in, out, n, s, g, tune);
+    else if (N == kFirst + 4) *rc = unary_n<kFirst + 4>(elem_pre, amount, left, S, in, out, n, s, g, tune);
     else return false;
     return true;
 }

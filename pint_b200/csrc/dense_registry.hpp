@@ -31,7 +31,10 @@ const dense_layout_kernels* find_dense_static(const layout_desc& d);
                                  cudaError_t* rc);                                                                    \
     bool dense_mw_pair_part##P(int N, int pair, const layout_desc& d, uint32_t S, const void* a, const void* b,       \
                                void* out0, void* out1, size_t n, cudaStream_t s, const launch_geom& g,                \
-                               const dense_tuning& tune, cudaError_t* rc);
+                               const dense_tuning& tune, cudaError_t* rc);                                            \
+    bool dense_mw_unary_part##P(int N, uint64_t elem_pre, uint32_t amount, bool left, uint32_t S, const void* in,     \
+                                void* out, size_t n, cudaStream_t s, const launch_geom& g, const dense_tuning& tune,  \
+                                cudaError_t* rc);
 PINT_MW_PART_DECL(0)
 PINT_MW_PART_DECL(1)
 PINT_MW_PART_DECL(2)

@@ -54,6 +54,17 @@ def binary_multi(op_list, layout, a, b, n, outs=None, stream=None):
     return outs
 
 
+def shift(left, layout, dense_in, amount, n, out=None, stream=None):
+    """out = shift_left (left=True) / shift_right_unsigned of every field by a uniform amount."""
+    if out is None:
+        out = torch.empty_like(dense_in)
+    _check_dense(layout, n, dense_in, out)
+    with torch.cuda.device(dense_in.device):
+        _lib.check(_lib.lib().pint_cuda_dense_shift(int(bool(left)), layout.ref, int(amount), dense_in.data_ptr(), out.data_ptr(),
+                                                    n, _stream(stream)), "pint_cuda_dense_shift")
+    return out
+
+
 def pack(layout, padded, out=None, stream=None):
     """Padded packed_int array -> dense stream (drops the bits above sum(Bits))."""
     n = _check(layout, padded)

@@ -163,6 +163,15 @@ int main()
             CK(cudaStreamSynchronize(s));
             CK(cudaMemcpy(ho.data(), out, n * 4, cudaMemcpyDeviceToHost));
             for (size_t i = 0; i < n; ++i) if (ho[i] != (rgba_add_usat(ha[i], hb[i]) & 0xFFFFFFu)) { ++fails; if (fails < 5) std::printf("dense planes round trip mismatch at %zu\n", i); }
+            // uniform shift of every 8-bit field on the stream: (x >> 3) per byte
+            pd::pack((const rgb*)a, da, n, s);
+            pd::shift_right_unsigned<rgb>(da, dout, n, 3, s);
+            CK(cudaStreamSynchronize(s));
+            CK(cudaMemcpy(hd.data(), dout, nb, cudaMemcpyDeviceToHost));
+            for (size_t i = 0; i < 3 * n; ++i) {
+                const unsigned char want = (unsigned char)(((ha[i / 3] >> (8 * (i % 3))) & 0xFF) >> 3);
+                if (hd[i] != want) { ++fails; if (fails < 5) std::printf("dense shift mismatch at byte %zu\n", i); }
+            }
         }
 
         // ---- runtime errors throw ----

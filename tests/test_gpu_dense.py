@@ -62,6 +62,31 @@ def test_dense_binary_vs_oracle(P, oracle, eb, bits, mode):
                                           err_msg=f"{L} {op} n={n} {mode}")
 
 
+@pytest.mark.parametrize("eb,bits", LAYOUTS)
+def test_dense_shift_vs_oracle(P, oracle, eb, bits, mode):
+    """shift_left / shift_right_unsigned on a dense stream == pack(shift(unpack)), every amount class:
+    0, inside the narrowest field, between field widths, >= the widest field, beyond the word."""
+    pint_b200, ops, dense = P
+    L = pint_b200.Layout(eb, *bits)
+    S = sum(bits)
+    amounts = sorted({0, 1, 2, min(bits) - 1, min(bits), max(bits) - 1, max(bits), max(bits) + 1, 8 * eb, 8 * eb + 5} - {-1})
+    for n in (1, 5, 129, 4096, (1 << 17) + 77):
+        x = oracle.fill(eb, n, 0xA5 + n)
+        x = x & np.array((1 << S) - 1, dtype=x.dtype)
+        dx_h = oracle.dense_pack(eb, bits, x)
+        if (n * S) % 128:
+            dx_h[-1] |= 0x80
+        dx = dev_bytes(dx_h)
+        for left in (True, False):
+            for amt in amounts:
+                got = dense.shift(left, L, dx, amt, n).cpu().numpy()
+                want = oracle.dense_pack(eb, bits, oracle.shift(left, eb, bits, amt, x))
+                np.testing.assert_array_equal(got, want, err_msg=f"{L} left={left} amount={amt} n={n} {mode}")
+        inplace = dev_bytes(dx_h)
+        dense.shift(True, L, inplace, 1, n, out=inplace)
+        np.testing.assert_array_equal(inplace.cpu().numpy(), oracle.dense_pack(eb, bits, oracle.shift(True, eb, bits, 1, x)))
+
+
 @pytest.mark.parametrize("eb,bits", LAYOUTS[:12])
 def test_dense_in_place_and_tiles(P, oracle, eb, bits):
     """In place on either operand; every tile geometry option gives the same stream."""

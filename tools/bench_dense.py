@@ -75,6 +75,11 @@ def main():
         emit(what="dense_binary_pair", layout=str(L), S=S, kernel=kind, op="+".join(pair), gbs_median=4 * n * S / 8 / med / 1e6,
              gelem_s=2 * n / med / 1e6, ms=med)
         del do2
+        # uniform shifts: 2*S/8 bytes per element
+        for left in (1, 0):
+            best, med = timed(lambda: dense.shift(left, L, da, 3, n, out=do))
+            emit(what="dense_shift", layout=str(L), S=S, op="shift_left" if left else "shift_right_unsigned",
+                 gbs_median=2 * n * S / 8 / med / 1e6, gelem_s=n / med / 1e6, ms=med)
         # same op on the padded format, for the elements/s comparison
         y = torch.empty_like(x)
         out = torch.empty_like(x)
