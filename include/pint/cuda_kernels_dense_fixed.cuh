@@ -1,0 +1,311 @@
+// pint/cuda_kernels_dense_fixed.cuh -- padded elements / planes -> dense stream with the
+// element width S known at COMPILE time.
+//
+// The run-time-geometry insert kernel (cuda_kernels_dense_convert.cuh) spends ~40
+// instructions per element on staging, index arithmetic and data-dependent shifts and is
+// issue-bound at 3.4-4.7 TB/s (profiles/r03b_ncu_insert_summary.txt).  Here everything that
+// depends on S is a compile-time constant:
+//   * a thread owns whole UNITS: GE consecutive elements = CW whole words of the stream
+//     (GE = WB / gcd(S, WB) elements, times K when that is less than 16 bytes of input), so
+//     no word is shared between threads and there is nothing to stage on the input side;
+//   * it reads them with 16-byte loads straight from global memory (consecutive lanes read
+//     consecutive units; several loads in flight), deposits each element with immediate
+//     shifts and writes every finished word into the CTA's output tile in shared memory
+//     (unit stride CW words, odd: conflict-free);
+//   * the tile leaves by one TMA bulk store.
+// Only whole tiles; the launcher hands the remainder to the run-time-geometry kernel.
+#pragma once
+
+#include "cuda_kernels_dense_convert.cuh"
+
+namespace pint {
+namespace cuda {
+namespace kernels {
+namespace dense {
+
+constexpr uint32_t cgcd(uint32_t a, uint32_t b) { return b == 0 ? a : cgcd(b, a % b); }
+
+// Src: the type read from memory (the padded Integer, or the plane value type)
+template <uint32_t S, uint32_t SrcBytes>
+struct fixed_geom {
+    using W = typename std::conditional<(S <= 32), uint32_t, uint64_t>::type;
+    static constexpr uint32_t WB = 8 * sizeof(W);
+    static constexpr uint32_t gc = cgcd(S, WB);
+    static constexpr uint32_t G0 = WB / gc, Cw0 = S / gc;                                  // one chunk
+    static constexpr uint32_t K = G0 * SrcBytes >= 16 ? 1 : 16 / (G0 * SrcBytes);          // chunks per unit
+    static constexpr uint32_t GE = K * G0, CW = K * Cw0;                                   // one unit
+    static constexpr uint32_t unit_in_bytes = GE * SrcBytes;                               // a multiple of 16
+    static constexpr uint32_t unit_out_bytes = CW * uint32_t(sizeof(W));
+    // elements a thread has in flight: at least 16 and at least 64 bytes of input
+    static constexpr uint32_t want = SrcBytes >= 4 ? 16 : 64 / SrcBytes;
+    static constexpr uint32_t UB = GE >= want ? 1 : want / GE;                             // units per iteration
+    static constexpr uint32_t BEL = GE >= want ? want : GE;                                // elements per load batch
+};
+
+// deposit of the E-th element of a unit; folds to immediates once the callers' loops are unrolled
+template <class W, uint32_t S>
+__device__ __forceinline__ void deposit(W x, uint32_t e, W& cur, W* o)
+{
+    constexpr uint32_t WB = 8 * sizeof(W);
+    const uint32_t p = e * S, sh = p % WB, w = p / WB;
+    x &= ones_w<W>(S);
+    cur |= W(x << sh);
+    if (sh + S >= WB) {
+        o[w] = cur;
+        cur = sh + S > WB ? W(x >> (WB - sh)) : W(0);
+    }
+}
+
+template <class Elem, uint32_t S, int Side, int PlaneBytes>
+__global__ void __launch_bounds__(256)
+dense_insert_fixed_kernel(const Elem* padded, uint4* dense, uint32_t units_per_thread, const __grid_constant__ dense_fields f)
+{
+    using Geo = fixed_geom<S, (Side == SIDE_PADDED ? uint32_t(sizeof(Elem)) : uint32_t(PlaneBytes))>;
+    using W = typename Geo::W;
+    constexpr uint32_t GE = Geo::GE, CW = Geo::CW, UB = Geo::UB, BEL = Geo::BEL;
+    extern __shared__ __align__(128) unsigned char dense_smem[];
+    W* out = reinterpret_cast<W*>(dense_smem);
+    const uint32_t T = blockDim.x;
+    const uint32_t units_per_tile = T * units_per_thread;
+    const size_t unit0 = size_t(blockIdx.x) * units_per_tile;
+    for (uint32_t it = 0; it < units_per_thread; it += UB) {
+        if constexpr (Side == SIDE_PADDED) {
+            constexpr uint32_t PV = 16 / sizeof(Elem);  // elements per 16-byte load
+            constexpr uint32_t NVB = BEL / PV;          // loads per batch
+            // UB > 1: one batch holds UB whole units; else the unit is cut into GE / BEL batches and the
+            // word under construction (`cur`) carries over from one batch to the next
+            constexpr uint32_t NU = UB;
+            static_assert(UB == 1 || GE == BEL, "a multi-unit batch holds whole units");
+            W cur[NU];
+#pragma unroll
+            for (uint32_t j = 0; j < NU; ++j) cur[j] = 0;
+#pragma unroll
+            for (uint32_t b0 = 0; b0 < GE; b0 += BEL) {
+                union { uint4 q; Elem x[PV]; } v[NU][NVB];
+#pragma unroll
+                for (uint32_t j = 0; j < NU; ++j) {
+                    const uint32_t u = (it + j) * T + threadIdx.x;
+                    const uint4* src = reinterpret_cast<const uint4*>(padded + (unit0 + u) * GE + b0);
+#pragma unroll
+                    for (uint32_t k = 0; k < NVB; ++k) v[j][k].q = ld16<CACHE_STREAMING>(src + k);
+                }
+#pragma unroll
+                for (uint32_t j = 0; j < NU; ++j) {
+                    const uint32_t u = (it + j) * T + threadIdx.x;
+                    W* o = out + size_t(u) * CW;
+#pragma unroll
+                    for (uint32_t k = 0; k < NVB; ++k)
+#pragma unroll
+                        for (uint32_t i = 0; i < PV; ++i) deposit<W, S>(W(v[j][k].x[i]), b0 + k * PV + i, cur[j], o);
+                }
+            }
+        } else {
+            // the truncating field constructor (pint.hpp:770-774, 592-601, 390-407), four elements per
+            // plane load; plane values are signed integers converted to Integer: sign-extend, then truncate
+            constexpr uint32_t NQ = BEL / 4;
+            constexpr uint32_t NU = UB;
+            static_assert(UB == 1 || GE == BEL, "a multi-unit batch holds whole units");
+            W cur[NU];
+#pragma unroll
+            for (uint32_t j = 0; j < NU; ++j) cur[j] = 0;
+#pragma unroll
+            for (uint32_t b0 = 0; b0 < GE; b0 += BEL) {
+                W e[NU][BEL];
+#pragma unroll
+                for (uint32_t j = 0; j < NU; ++j)
+#pragma unroll
+                    for (uint32_t i = 0; i < BEL; ++i) e[j][i] = 0;
+                for (uint32_t fi = 0; fi < f.t.nfields; ++fi) {
+                    const W m = ones_w<W>(f.t.bits[fi]);
+                    const uint32_t off = f.t.off[fi];
+                    const void* plane = f.planes.p[fi];
+                    uint64_t pv[NU][NQ][4];
+#pragma unroll
+                    for (uint32_t j = 0; j < NU; ++j) {
+                        const uint32_t u = (it + j) * T + threadIdx.x;
+                        const size_t q0 = ((unit0 + u) * GE + b0) / 4;
+#pragma unroll
+                        for (uint32_t q = 0; q < NQ; ++q) load_plane_quad<PlaneBytes>(plane, q0 + q, pv[j][q]);
+                    }
+#pragma unroll
+                    for (uint32_t j = 0; j < NU; ++j)
+#pragma unroll
+                        for (uint32_t q = 0; q < NQ; ++q)
+#pragma unroll
+                            for (uint32_t i = 0; i < 4; ++i) e[j][4 * q + i] |= W(W(pv[j][q][i]) & m) << off;
+                }
+#pragma unroll
+                for (uint32_t j = 0; j < NU; ++j) {
+                    const uint32_t u = (it + j) * T + threadIdx.x;
+                    W* o = out + size_t(u) * CW;
+#pragma unroll
+                    for (uint32_t i = 0; i < BEL; ++i) deposit<W, S>(e[j][i], b0 + i, cur[j], o);
+                }
+            }
+        }
+    }
+    const uint32_t tile_bytes = units_per_tile * Geo::unit_out_bytes;  // a multiple of 128 (T is a multiple of 32)
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        bulk_store(reinterpret_cast<unsigned char*>(dense) + size_t(blockIdx.x) * tile_bytes, out, tile_bytes, evict_first_policy());
+        bulk_wait_read<0>();
+    }
+}
+
+// Units of more than 64 bytes of input (odd S: 32 or 64 elements per unit) make the direct form's
+// loads one whole 128-byte line per lane and instruction (measured 3.5-5.1 TB/s, r03c_dense.jsonl).
+// For those the tile's elements are first staged in shared memory with coalesced 16-byte loads
+// (assembled from the planes on the way for SIDE_PLANES), element i at index i + i / GE so that
+// the thread owning a unit walks a row of odd stride; the deposit is the compile-time one above.
+template <class Elem, uint32_t S, int Side, int PlaneBytes>
+__global__ void __launch_bounds__(128)
+dense_insert_fixed_staged_kernel(const Elem* padded, uint4* dense, uint32_t units_per_tile, const __grid_constant__ dense_fields f)
+{
+    using Geo = fixed_geom<S, (Side == SIDE_PADDED ? uint32_t(sizeof(Elem)) : uint32_t(PlaneBytes))>;
+    using W = typename Geo::W;
+    using Staged = typename std::conditional<Side == SIDE_PADDED, Elem, W>::type;
+    constexpr uint32_t GE = Geo::GE, CW = Geo::CW;
+    // 64-bit words: a unit is up to 64 elements and one thread per unit leaves most of the CTA idle
+    // (3.5 TB/s); there every thread assembles whole output WORDS instead (word w of the tile starts
+    // at element 64 w / S, a multiply-high), and the staged elements need no row padding
+    constexpr bool WordOwner = sizeof(W) == 8;
+    constexpr uint32_t PAD = WordOwner ? 0 : 1;
+    extern __shared__ __align__(128) unsigned char dense_smem[];
+    const uint32_t T = blockDim.x;
+    const uint32_t tile_elems = units_per_tile * GE;
+    const uint32_t tile_bytes = units_per_tile * Geo::unit_out_bytes;  // a multiple of 128 (units_per_tile is one of 32)
+    W* out = reinterpret_cast<W*>(dense_smem);
+    Staged* in = reinterpret_cast<Staged*>(dense_smem + tile_bytes);
+    const size_t first = size_t(blockIdx.x) * tile_elems;
+    // four independent 16-byte loads (per plane) in flight per thread; the launcher makes the tile a
+    // multiple of 4 * T vectors / quads
+    if constexpr (Side == SIDE_PADDED) {
+        constexpr uint32_t PV = 16 / sizeof(Elem);
+        const uint4* src = reinterpret_cast<const uint4*>(padded + first);
+        const uint32_t nv = tile_elems / PV;
+        for (uint32_t v0 = threadIdx.x; v0 < nv; v0 += 4 * T) {
+            union { uint4 q; Elem x[PV]; } u[4];
+#pragma unroll
+            for (uint32_t j = 0; j < 4; ++j) u[j].q = ld16<CACHE_STREAMING>(src + v0 + j * T);
+#pragma unroll
+            for (uint32_t j = 0; j < 4; ++j) {
+                const uint32_t i = (v0 + j * T) * PV;
+                Staged* dst = in + i + PAD * (i / GE);  // PV <= GE: the vector stays in one row
+#pragma unroll
+                for (uint32_t k = 0; k < PV; ++k) dst[k] = u[j].x[k];
+            }
+        }
+    } else {
+        // the truncating field constructor (pint.hpp:770-774, 592-601, 390-407) on four elements at a time
+        const uint32_t nq = tile_elems / 4;
+        for (uint32_t q0 = threadIdx.x; q0 < nq; q0 += 4 * T) {
+            W e[4][4];
+#pragma unroll
+            for (uint32_t j = 0; j < 4; ++j)
+#pragma unroll
+                for (uint32_t k = 0; k < 4; ++k) e[j][k] = 0;
+            for (uint32_t fi = 0; fi < f.t.nfields; ++fi) {
+                uint64_t v[4][4];
+#pragma unroll
+                for (uint32_t j = 0; j < 4; ++j) load_plane_quad<PlaneBytes>(f.planes.p[fi], first / 4 + q0 + j * T, v[j]);
+                const W m = ones_w<W>(f.t.bits[fi]);
+                const uint32_t off = f.t.off[fi];
+#pragma unroll
+                for (uint32_t j = 0; j < 4; ++j)
+#pragma unroll
+                    for (uint32_t k = 0; k < 4; ++k) e[j][k] |= W(W(v[j][k]) & m) << off;
+            }
+#pragma unroll
+            for (uint32_t j = 0; j < 4; ++j) {
+                const uint32_t i = 4 * (q0 + j * T);
+                Staged* dst = in + i + PAD * (i / GE);
+#pragma unroll
+                for (uint32_t k = 0; k < 4; ++k) dst[k] = e[j][k];
+            }
+        }
+    }
+    __syncthreads();
+    if constexpr (WordOwner) {
+        constexpr uint32_t WB = Geo::WB;
+        constexpr uint32_t MAXE = (WB - 1 + S - 1) / S;  // elements after the first that can reach into one word
+        const W SM = ones_w<W>(S);
+        const uint32_t nwords = units_per_tile * CW;
+        for (uint32_t w = threadIdx.x; w < nwords; w += T) {
+            const uint32_t p = w * WB;  // tile_elems * S < 2^32
+            const uint32_t i = p / S, off = p - i * S;
+            W r = W(W(in[i]) & SM) >> off;
+            uint32_t have = S - off;
+#pragma unroll
+            for (uint32_t k = 1; k <= MAXE; ++k)
+                if (have < WB) {  // the tile ends on a word boundary: never reads past its last element
+                    r |= W(W(in[i + k]) & SM) << have;
+                    have += S;
+                }
+            out[w] = r;
+        }
+    } else {
+        for (uint32_t u = threadIdx.x; u < units_per_tile; u += T) {
+            const Staged* row = in + size_t(u) * (GE + 1);
+            W* o = out + size_t(u) * CW;
+            W cur = 0;
+#pragma unroll
+            for (uint32_t e = 0; e < GE; ++e) deposit<W, S>(W(row[e]), e, cur, o);
+        }
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        bulk_store(reinterpret_cast<unsigned char*>(dense) + size_t(blockIdx.x) * tile_bytes, out, tile_bytes, evict_first_policy());
+        bulk_wait_read<0>();
+    }
+}
+
+// Whole tiles only: *done = the elements converted (a multiple of 128); the caller finishes
+// [*done, n) with the run-time-geometry kernel.  Needs 16-byte aligned inputs (checked by the caller).
+template <class Elem, uint32_t S, int Side, int PlaneBytes>
+cudaError_t launch_dense_insert_fixed(const void* other, void* dense, size_t n, const dense_fields& f, cudaStream_t stream,
+                                      const launch_geom& g, size_t* done)
+{
+    using Geo = fixed_geom<S, (Side == SIDE_PADDED ? uint32_t(sizeof(Elem)) : uint32_t(PlaneBytes))>;
+    if (Geo::unit_in_bytes > 64) {
+        using Staged = typename std::conditional<Side == SIDE_PADDED, Elem, typename Geo::W>::type;
+        // units per tile: ~8 KB of output, at most ~16 KB of staged input, a whole number of load rounds
+        // (4 vectors or quads per thread: 2048 elements cover every source width)
+        const uint32_t by_out = 8192 / Geo::unit_out_bytes, by_in = 16384 / ((Geo::GE + 1) * uint32_t(sizeof(Staged)));
+        const uint32_t round = 2048 / Geo::GE > 32 ? 2048 / Geo::GE : 32;
+        uint32_t U = (by_out < by_in ? by_out : by_in) / round * round;
+        if (U < round) U = round;
+        const size_t smem = size_t(U) * Geo::unit_out_bytes + size_t(U) * (Geo::GE + 1) * sizeof(Staged);
+        const size_t tile_elems = size_t(U) * Geo::GE;
+        const size_t ntiles = n / tile_elems;
+        *done = ntiles * tile_elems;
+        if (ntiles == 0) return cudaSuccess;
+        if (ntiles > 0x7FFFFFFFull) return cudaErrorInvalidValue;
+        dense_insert_fixed_staged_kernel<Elem, S, Side, PlaneBytes><<<unsigned(ntiles), 128, smem, stream>>>(
+            static_cast<const Elem*>(other), static_cast<uint4*>(dense), U, f);
+        count_launch(g);
+        return cudaGetLastError();
+    }
+    // CTA size: the largest whose one-unit-per-thread tile stays within 16 KB; then units per thread
+    // to bring the output tile to ~16 KB
+    unsigned T = 256;
+    while (T > 32 && T * Geo::unit_out_bytes > 16384) T >>= 1;
+    uint32_t upt = 16384 / (T * Geo::unit_out_bytes) / Geo::UB * Geo::UB;
+    if (upt < Geo::UB) upt = Geo::UB;
+    const size_t smem = size_t(T) * upt * Geo::unit_out_bytes;
+    const size_t tile_elems = size_t(T) * upt * Geo::GE;
+    const size_t ntiles = n / tile_elems;
+    *done = ntiles * tile_elems;
+    if (ntiles == 0) return cudaSuccess;
+    if (ntiles > 0x7FFFFFFFull) return cudaErrorInvalidValue;
+    dense_insert_fixed_kernel<Elem, S, Side, PlaneBytes><<<unsigned(ntiles), T, smem, stream>>>(
+        static_cast<const Elem*>(other), static_cast<uint4*>(dense), upt, f);
+    count_launch(g);
+    return cudaGetLastError();
+}
+
+}  // namespace dense
+}  // namespace kernels
+}  // namespace cuda
+}  // namespace pint

@@ -76,6 +76,28 @@ dense::dense_fields make_fields(const layout_desc& d)
     return f;
 }
 
+// Conversions INTO a dense stream: the kernels with S compiled in (dense_fixed.cu) take the whole
+// tiles when the inputs are 16-byte aligned and a kernel exists for (S, Integer); *done = elements
+// converted, the rest is left to the run-time-geometry kernel.  Option dense_windows = 1 turns them off.
+cudaError_t insert_fixed(uint32_t S, uint32_t elem_bytes, int plane_bytes, const void* other, void* dn, size_t n,
+                         const dense::dense_fields& f, cudaStream_t s, size_t* done)
+{
+    *done = 0;
+    if (opts().dense_windows) return cudaSuccess;
+    uintptr_t align = reinterpret_cast<uintptr_t>(other);
+    if (!elem_bytes)
+        for (uint32_t i = 0; i < f.t.nfields; ++i) align |= reinterpret_cast<uintptr_t>(f.planes.p[i]);
+    if (align % 16) return cudaSuccess;
+    const launch_geom g = geom();
+    cudaError_t rc = cudaSuccess;
+    if (dense_insert_fixed_part0(S, elem_bytes, plane_bytes, other, dn, n, f, s, g, done, &rc) ||
+        dense_insert_fixed_part1(S, elem_bytes, plane_bytes, other, dn, n, f, s, g, done, &rc) ||
+        dense_insert_fixed_part2(S, elem_bytes, plane_bytes, other, dn, n, f, s, g, done, &rc) ||
+        dense_insert_fixed_part3(S, elem_bytes, plane_bytes, other, dn, n, f, s, g, done, &rc))
+        return rc;
+    return cudaSuccess;
+}
+
 template <class W, class Elem>
 cudaError_t pack_unpack(bool to_dense, const void* padded, void* dense, size_t n, uint32_t S, cudaStream_t s)
 {
@@ -106,6 +128,14 @@ int convert_impl(bool to_dense, const pint_layout* layout, const void* padded, v
     const uint32_t S = total_bits(d);
     const uintptr_t p0 = (uintptr_t)padded, d0 = (uintptr_t)dense;
     if (p0 < d0 + dense_bytes(S, n) && d0 < p0 + n * d.elem_bytes) return PINT_E_ALIAS;  // no in-place conversion
+    if (to_dense) {
+        size_t done = 0;
+        if (cudaError_t rc = insert_fixed(S, d.elem_bytes, 0, padded, dense, n, dense::dense_fields{}, s, &done)) return (int)rc;
+        if (done == n) return PINT_OK;
+        padded = static_cast<const char*>(padded) + done * d.elem_bytes;  // done is a multiple of 128 elements
+        dense = static_cast<char*>(dense) + done / 8 * S;
+        n -= done;
+    }
     return (int)(S <= 32 ? pack_unpack_w<uint32_t>(to_dense, d.elem_bytes, padded, dense, n, S, s)
                          : pack_unpack_w<uint64_t>(to_dense, d.elem_bytes, padded, dense, n, S, s));
 }
@@ -142,6 +172,14 @@ int planes_impl(bool to_dense, const pint_layout* layout, int is_signed, const v
         f.planes.p[i] = const_cast<void*>(planes[i]);
     }
     const uint32_t S = total_bits(d);
+    if (to_dense) {
+        size_t done = 0;
+        if (cudaError_t rc = insert_fixed(S, 0, plane_bytes, nullptr, const_cast<void*>(dense), n, f, s, &done)) return (int)rc;
+        if (done == n) return PINT_OK;
+        for (uint32_t i = 0; i < d.nfields; ++i) f.planes.p[i] = static_cast<char*>(f.planes.p[i]) + done * plane_bytes;
+        dense = static_cast<const char*>(dense) + done / 8 * S;
+        n -= done;
+    }
     return (int)(S <= 32 ? planes_launch<uint32_t>(to_dense, is_signed != 0, plane_bytes, dense, f, n, S, s)
                          : planes_launch<uint64_t>(to_dense, is_signed != 0, plane_bytes, dense, f, n, S, s));
 }

@@ -1,7 +1,7 @@
 // dense_registry.hpp -- dense bit-stream kernels with the layout compiled in (dense_static.cu).
 #pragma once
 
-#include "pint/cuda_kernels_dense.cuh"
+#include "pint/cuda_kernels_dense_convert.cuh"
 #include "registry.hpp"
 
 namespace pint_cuda_impl {
@@ -39,5 +39,18 @@ PINT_MW_PART_DECL(0)
 PINT_MW_PART_DECL(1)
 PINT_MW_PART_DECL(2)
 #undef PINT_MW_PART_DECL
+
+// conversions into a dense stream with S compiled in (dense_fixed.cu, part p covers S in [16 p, 16 p + 16));
+// elem_bytes != 0: padded elements of that Integer, else planes of plane_bytes each.  false: no kernel for
+// this (S, Integer).  Converts whole tiles only: *done elements, the caller finishes the rest.
+#define PINT_FIXED_PART_DECL(P)                                                                                       \
+    bool dense_insert_fixed_part##P(uint32_t S, uint32_t elem_bytes, int plane_bytes, const void* other, void* dn,    \
+                                    size_t n, const pint::cuda::kernels::dense::dense_fields& f, cudaStream_t s,      \
+                                    const launch_geom& g, size_t* done, cudaError_t* rc);
+PINT_FIXED_PART_DECL(0)
+PINT_FIXED_PART_DECL(1)
+PINT_FIXED_PART_DECL(2)
+PINT_FIXED_PART_DECL(3)
+#undef PINT_FIXED_PART_DECL
 
 }  // namespace pint_cuda_impl
