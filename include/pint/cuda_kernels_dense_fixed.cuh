@@ -42,6 +42,9 @@ struct fixed_geom {
     static constexpr uint32_t BEL = GE >= want ? want : GE;                                // elements per load batch
 };
 
+__device__ __forceinline__ void st_stream(uint32_t* p, uint32_t v) { asm volatile("st.global.cs.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ void st_stream(uint64_t* p, uint64_t v) { asm volatile("st.global.cs.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory"); }
+
 // deposit of the E-th element of a unit; folds to immediates once the callers' loops are unrolled
 template <class W, uint32_t S>
 __device__ __forceinline__ void deposit(W x, uint32_t e, W& cur, W* o)
@@ -159,7 +162,7 @@ dense_insert_fixed_kernel(const Elem* padded, uint4* dense, uint32_t units_per_t
 // (assembled from the planes on the way for SIDE_PLANES), element i at index i + i / GE so that
 // the thread owning a unit walks a row of odd stride; the deposit is the compile-time one above.
 template <class Elem, uint32_t S, int Side, int PlaneBytes>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(256)
 dense_insert_fixed_staged_kernel(const Elem* padded, uint4* dense, uint32_t units_per_tile, const __grid_constant__ dense_fields f)
 {
     using Geo = fixed_geom<S, (Side == SIDE_PADDED ? uint32_t(sizeof(Elem)) : uint32_t(PlaneBytes))>;
@@ -175,8 +178,8 @@ dense_insert_fixed_staged_kernel(const Elem* padded, uint4* dense, uint32_t unit
     const uint32_t T = blockDim.x;
     const uint32_t tile_elems = units_per_tile * GE;
     const uint32_t tile_bytes = units_per_tile * Geo::unit_out_bytes;  // a multiple of 128 (units_per_tile is one of 32)
-    W* out = reinterpret_cast<W*>(dense_smem);
-    Staged* in = reinterpret_cast<Staged*>(dense_smem + tile_bytes);
+    W* out = reinterpret_cast<W*>(dense_smem);  // unit owners only; word owners store straight to global memory
+    Staged* in = reinterpret_cast<Staged*>(dense_smem + (WordOwner ? 0 : tile_bytes));
     const size_t first = size_t(blockIdx.x) * tile_elems;
     // four independent 16-byte loads (per plane) in flight per thread; the launcher makes the tile a
     // multiple of 4 * T vectors / quads
@@ -187,9 +190,11 @@ dense_insert_fixed_staged_kernel(const Elem* padded, uint4* dense, uint32_t unit
         for (uint32_t v0 = threadIdx.x; v0 < nv; v0 += 4 * T) {
             union { uint4 q; Elem x[PV]; } u[4];
 #pragma unroll
-            for (uint32_t j = 0; j < 4; ++j) u[j].q = ld16<CACHE_STREAMING>(src + v0 + j * T);
+            for (uint32_t j = 0; j < 4; ++j)
+                if (v0 + j * T < nv) u[j].q = ld16<CACHE_STREAMING>(src + v0 + j * T);
 #pragma unroll
             for (uint32_t j = 0; j < 4; ++j) {
+                if (v0 + j * T >= nv) break;
                 const uint32_t i = (v0 + j * T) * PV;
                 Staged* dst = in + i + PAD * (i / GE);  // PV <= GE: the vector stays in one row
 #pragma unroll
@@ -198,26 +203,30 @@ dense_insert_fixed_staged_kernel(const Elem* padded, uint4* dense, uint32_t unit
         }
     } else {
         // the truncating field constructor (pint.hpp:770-774, 592-601, 390-407) on four elements at a time
+        // quads in flight per thread: 64-bit words double the registers per value (89 registers with four)
+        constexpr uint32_t LIF = sizeof(W) == 8 ? 2 : 4;
         const uint32_t nq = tile_elems / 4;
-        for (uint32_t q0 = threadIdx.x; q0 < nq; q0 += 4 * T) {
-            W e[4][4];
+        for (uint32_t q0 = threadIdx.x; q0 < nq; q0 += LIF * T) {
+            W e[LIF][4];
 #pragma unroll
-            for (uint32_t j = 0; j < 4; ++j)
+            for (uint32_t j = 0; j < LIF; ++j)
 #pragma unroll
                 for (uint32_t k = 0; k < 4; ++k) e[j][k] = 0;
             for (uint32_t fi = 0; fi < f.t.nfields; ++fi) {
-                uint64_t v[4][4];
+                uint64_t v[LIF][4];
 #pragma unroll
-                for (uint32_t j = 0; j < 4; ++j) load_plane_quad<PlaneBytes>(f.planes.p[fi], first / 4 + q0 + j * T, v[j]);
+                for (uint32_t j = 0; j < LIF; ++j)
+                    if (q0 + j * T < nq) load_plane_quad<PlaneBytes>(f.planes.p[fi], first / 4 + q0 + j * T, v[j]);
                 const W m = ones_w<W>(f.t.bits[fi]);
                 const uint32_t off = f.t.off[fi];
 #pragma unroll
-                for (uint32_t j = 0; j < 4; ++j)
+                for (uint32_t j = 0; j < LIF; ++j)
 #pragma unroll
                     for (uint32_t k = 0; k < 4; ++k) e[j][k] |= W(W(v[j][k]) & m) << off;
             }
 #pragma unroll
-            for (uint32_t j = 0; j < 4; ++j) {
+            for (uint32_t j = 0; j < LIF; ++j) {
+                if (q0 + j * T >= nq) break;
                 const uint32_t i = 4 * (q0 + j * T);
                 Staged* dst = in + i + PAD * (i / GE);
 #pragma unroll
@@ -242,8 +251,9 @@ dense_insert_fixed_staged_kernel(const Elem* padded, uint4* dense, uint32_t unit
                     r |= W(W(in[i + k]) & SM) << have;
                     have += S;
                 }
-            out[w] = r;
+            st_stream(reinterpret_cast<W*>(dense) + size_t(blockIdx.x) * nwords + w, r);  // consecutive lanes, consecutive words
         }
+        return;
     } else {
         for (uint32_t u = threadIdx.x; u < units_per_tile; u += T) {
             const Staged* row = in + size_t(u) * (GE + 1);
@@ -276,13 +286,15 @@ cudaError_t launch_dense_insert_fixed(const void* other, void* dense, size_t n, 
         const uint32_t round = 2048 / Geo::GE > 32 ? 2048 / Geo::GE : 32;
         uint32_t U = (by_out < by_in ? by_out : by_in) / round * round;
         if (U < round) U = round;
-        const size_t smem = size_t(U) * Geo::unit_out_bytes + size_t(U) * (Geo::GE + 1) * sizeof(Staged);
+        const bool word_owner = sizeof(typename Geo::W) == 8;  // as in the kernel: no output tile, no row padding
+        const size_t smem = word_owner ? size_t(U) * Geo::GE * sizeof(Staged)
+                                       : size_t(U) * Geo::unit_out_bytes + size_t(U) * (Geo::GE + 1) * sizeof(Staged);
         const size_t tile_elems = size_t(U) * Geo::GE;
         const size_t ntiles = n / tile_elems;
         *done = ntiles * tile_elems;
         if (ntiles == 0) return cudaSuccess;
         if (ntiles > 0x7FFFFFFFull) return cudaErrorInvalidValue;
-        dense_insert_fixed_staged_kernel<Elem, S, Side, PlaneBytes><<<unsigned(ntiles), 128, smem, stream>>>(
+        dense_insert_fixed_staged_kernel<Elem, S, Side, PlaneBytes><<<unsigned(ntiles), word_owner ? 256 : 128, smem, stream>>>(
             static_cast<const Elem*>(other), static_cast<uint4*>(dense), U, f);
         count_launch(g);
         return cudaGetLastError();
