@@ -278,7 +278,7 @@ cudaError_t launch_dense_insert_fixed(const void* other, void* dense, size_t n, 
                                       const launch_geom& g, size_t* done)
 {
     using Geo = fixed_geom<S, (Side == SIDE_PADDED ? uint32_t(sizeof(Elem)) : uint32_t(PlaneBytes))>;
-    if (Geo::unit_in_bytes > 64) {
+    if constexpr (Geo::unit_in_bytes > 64) {
         using Staged = typename std::conditional<Side == SIDE_PADDED, Elem, typename Geo::W>::type;
         // units per tile: ~8 KB of output, at most ~16 KB of staged input, a whole number of load rounds
         // (4 vectors or quads per thread: 2048 elements cover every source width)
@@ -298,7 +298,7 @@ cudaError_t launch_dense_insert_fixed(const void* other, void* dense, size_t n, 
             static_cast<const Elem*>(other), static_cast<uint4*>(dense), U, f);
         count_launch(g);
         return cudaGetLastError();
-    }
+    } else {
     // CTA size: the largest whose one-unit-per-thread tile stays within 16 KB; then units per thread
     // to bring the output tile to ~16 KB
     unsigned T = 256;
@@ -313,6 +313,124 @@ cudaError_t launch_dense_insert_fixed(const void* other, void* dense, size_t n, 
     if (ntiles > 0x7FFFFFFFull) return cudaErrorInvalidValue;
     dense_insert_fixed_kernel<Elem, S, Side, PlaneBytes><<<unsigned(ntiles), T, smem, stream>>>(
         static_cast<const Elem*>(other), static_cast<uint4*>(dense), upt, f);
+    count_launch(g);
+    return cudaGetLastError();
+    }
+}
+
+// The other direction.  Owning whole units does not pay here: a lane's 16-byte stores would be
+// 32-128 bytes apart and partial-sector stores cost more than they save (measured: slower than the
+// run-time-geometry kernel for every unit above 16 bytes, profiles/r03k_dense_extract_unit_owner_experiment.jsonl).
+// Instead a thread owns a GROUP of GP consecutive elements -- 16 bytes of padded output (32 for
+// uint64_t), 4 values per plane -- so that consecutive lanes store consecutive vectors.  The group
+// starts at bit g * GP * S of the TMA-staged tile: the thread loads the NW words that cover it ONCE,
+// re-aligns them to the group start with NW - 1 funnel shifts by its own offset, and every element
+// is then cut out with IMMEDIATE shifts.  The run-time-geometry kernel loads two words per element
+// and costs 14 (padded) to 22 (one plane) instructions per element, 66-75 % issue-active on 12-bit
+// elements (profiles/r03j_ncu_convert_summary.txt).  Instantiated for dense -> padded with uint8_t /
+// uint16_t / uint64_t elements, where it wins on the same box (profiles/r03m_ab_dense_convert.log:
+// 7-bit 3662 -> 5454, 12-bit 5669 -> 6035, 63-bit 5277 -> 6785 GB/s; 32-byte stores for uint64_t);
+// for uint32_t elements and for planes the run-time-geometry kernel stays 0-2 % ahead and is kept.
+template <class Elem, uint32_t S, int Side>
+struct group_geom {
+    using W = typename std::conditional<(S <= 32), uint32_t, uint64_t>::type;
+    static constexpr uint32_t WB = 8 * sizeof(W);
+    static constexpr uint32_t GP = Side == SIDE_PADDED ? (sizeof(Elem) >= 4 ? 4u : 16u / uint32_t(sizeof(Elem))) : 4u;
+    static constexpr uint32_t NA = (GP * S + WB - 1) / WB;  // aligned words that hold the group
+    static constexpr uint32_t NW = NA + 1;                  // words loaded: the group may start anywhere in the first
+};
+
+template <class Elem, uint32_t S, int Side, int PlaneBytes, bool Signed>
+__global__ void __launch_bounds__(256)
+dense_extract_fixed_kernel(const uint4* dense, Elem* padded, uint32_t tile_elems, const __grid_constant__ dense_fields f)
+{
+    using Geo = group_geom<Elem, S, Side>;
+    using W = typename Geo::W;
+    constexpr uint32_t GP = Geo::GP, NA = Geo::NA, NW = Geo::NW, WB = Geo::WB;
+    extern __shared__ __align__(128) unsigned char dense_smem[];
+    __shared__ __align__(8) uint64_t full;
+    W* D = reinterpret_cast<W*>(dense_smem);
+    const uint32_t T = blockDim.x;
+    const uint32_t tile_bytes = tile_elems / 8 * S;  // tile_elems is a multiple of 128
+    const size_t first = size_t(blockIdx.x) * tile_elems;
+    if (threadIdx.x == 0) {
+        mbar_init(&full, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        mbar_expect_tx(&full, tile_bytes);
+        bulk_load(dense_smem, reinterpret_cast<const unsigned char*>(dense) + size_t(blockIdx.x) * tile_bytes, tile_bytes, &full,
+                  evict_first_policy());
+    }
+    // the last group's extra word lies past the tile (its bits are never used): keep it defined
+    if (threadIdx.x < 16 / sizeof(W)) D[tile_bytes / sizeof(W) + threadIdx.x] = 0;
+    __syncthreads();
+    mbar_wait(&full, 0);
+    const W SM = ones_w<W>(S);
+    const uint32_t ngroups = tile_elems / GP;
+    for (uint32_t g = threadIdx.x; g < ngroups; g += T) {
+        const uint32_t p0 = g * (GP * S);  // tile_elems * S < 2^32
+        const uint32_t w0 = p0 / WB, off = p0 % WB;
+        W wd[NW];
+#pragma unroll
+        for (uint32_t k = 0; k < NW; ++k) wd[k] = D[w0 + k];
+        W al[NA];
+#pragma unroll
+        for (uint32_t k = 0; k < NA; ++k) al[k] = funnel_r(wd[k], wd[k + 1], off);
+        W x[GP];
+#pragma unroll
+        for (uint32_t e = 0; e < GP; ++e) {
+            const uint32_t p = e * S, sh = p % WB, w = p / WB;  // immediates once unrolled
+            W v = al[w] >> sh;
+            if (sh + S > WB) v |= W(al[w + 1] << (WB - sh));
+            x[e] = v & SM;
+        }
+        const size_t e0 = first + size_t(g) * GP;
+        if constexpr (Side == SIDE_PADDED) {
+            if constexpr (sizeof(Elem) == 8) {
+                const uint64_t y0 = x[0], y1 = x[1], y2 = x[2], y3 = x[3];
+                vec32 v;
+                v.lo = make_uint4(uint32_t(y0), uint32_t(y0 >> 32), uint32_t(y1), uint32_t(y1 >> 32));
+                v.hi = make_uint4(uint32_t(y2), uint32_t(y2 >> 32), uint32_t(y3), uint32_t(y3 >> 32));
+                st32(reinterpret_cast<vec32*>(padded + e0), v);
+            } else {
+                constexpr uint32_t PV = 16 / sizeof(Elem);
+                static_assert(PV == GP, "one 16-byte store per group");
+                union { uint4 q; Elem x[PV]; } v;
+#pragma unroll
+                for (uint32_t i = 0; i < PV; ++i) v.x[i] = Elem(x[i]);
+                st16<CACHE_STREAMING>(reinterpret_cast<uint4*>(padded + e0), v.q);
+            }
+        } else {
+            for (uint32_t fi = 0; fi < f.t.nfields; ++fi) {
+                void* plane = f.planes.p[fi];
+                if (!plane) continue;
+                const uint32_t foff = f.t.off[fi], wdt = f.t.bits[fi];
+                uint64_t v[4];
+#pragma unroll
+                for (uint32_t i = 0; i < 4; ++i)
+                    v[i] = Signed ? uint64_t(int64_t(field_get_signed<W>(x[i], foff, wdt))) : uint64_t(field_get<W>(x[i], foff, wdt));
+                store_plane_quad<PlaneBytes>(plane, e0 / 4, v);
+            }
+        }
+    }
+}
+
+// Whole tiles only, as for the insert kernels.  The caller checks alignment: 16 bytes (32 for a
+// uint64_t padded array, which is stored with 32-byte vectors).
+template <class Elem, uint32_t S, int Side, int PlaneBytes, bool Signed>
+cudaError_t launch_dense_extract_fixed(const void* dense, void* other, size_t n, const dense_fields& f, cudaStream_t stream,
+                                       const launch_geom& g, size_t* done)
+{
+    using W = typename group_geom<Elem, S, Side>::W;
+    const uint32_t tile_elems = convert_tile_elems(S);  // ~16 KB of stream, a multiple of 128 elements
+    const size_t smem = size_t(tile_elems) / 8 * S + 16;
+    const size_t ntiles = n / tile_elems;
+    *done = ntiles * size_t(tile_elems);
+    if (ntiles == 0) return cudaSuccess;
+    if (ntiles > 0x7FFFFFFFull) return cudaErrorInvalidValue;
+    (void)sizeof(W);
+    dense_extract_fixed_kernel<Elem, S, Side, PlaneBytes, Signed><<<unsigned(ntiles), 256, smem, stream>>>(
+        static_cast<const uint4*>(dense), static_cast<Elem*>(other), tile_elems, f);
     count_launch(g);
     return cudaGetLastError();
 }

@@ -98,6 +98,22 @@ cudaError_t insert_fixed(uint32_t S, uint32_t elem_bytes, int plane_bytes, const
     return cudaSuccess;
 }
 
+// dense -> padded with S compiled in: uint8_t / uint16_t / uint64_t elements (dense_fixed.cu says why)
+cudaError_t extract_fixed(uint32_t S, uint32_t elem_bytes, const void* dn, void* other, size_t n, cudaStream_t s, size_t* done)
+{
+    *done = 0;
+    if (opts().dense_windows || reinterpret_cast<uintptr_t>(other) % 16) return cudaSuccess;
+    const launch_geom g = geom();
+    const dense::dense_fields f{};
+    cudaError_t rc = cudaSuccess;
+    if (dense_extract_fixed_part0(S, elem_bytes, dn, other, n, f, s, g, done, &rc) ||
+        dense_extract_fixed_part1(S, elem_bytes, dn, other, n, f, s, g, done, &rc) ||
+        dense_extract_fixed_part2(S, elem_bytes, dn, other, n, f, s, g, done, &rc) ||
+        dense_extract_fixed_part3(S, elem_bytes, dn, other, n, f, s, g, done, &rc))
+        return rc;
+    return cudaSuccess;
+}
+
 template <class W, class Elem>
 cudaError_t pack_unpack(bool to_dense, const void* padded, void* dense, size_t n, uint32_t S, cudaStream_t s)
 {
@@ -133,6 +149,13 @@ int convert_impl(bool to_dense, const pint_layout* layout, const void* padded, v
         if (cudaError_t rc = insert_fixed(S, d.elem_bytes, 0, padded, dense, n, dense::dense_fields{}, s, &done)) return (int)rc;
         if (done == n) return PINT_OK;
         padded = static_cast<const char*>(padded) + done * d.elem_bytes;  // done is a multiple of 128 elements
+        dense = static_cast<char*>(dense) + done / 8 * S;
+        n -= done;
+    } else {
+        size_t done = 0;
+        if (cudaError_t rc = extract_fixed(S, d.elem_bytes, dense, const_cast<void*>(padded), n, s, &done)) return (int)rc;
+        if (done == n) return PINT_OK;
+        padded = static_cast<const char*>(padded) + done * d.elem_bytes;
         dense = static_cast<char*>(dense) + done / 8 * S;
         n -= done;
     }

@@ -37,6 +37,37 @@ bool insert_s(uint32_t elem_bytes, int plane_bytes, const void* other, void* dn,
     return true;
 }
 
+// dense -> padded only, and not for uint32_t: same-box A/B (profiles/r03m_ab_dense_convert.log) has the
+// group-owner kernel ahead for uint8_t / uint16_t / uint64_t elements (5454 vs 3662, 6035 vs 5669,
+// 6785 vs 5277 GB/s) and 2 % behind the run-time-geometry kernel for uint32_t and for planes.
+template <uint32_t S>
+bool extract_s(uint32_t elem_bytes, const void* dn, void* other, size_t n, const dense::dense_fields& f, cudaStream_t s,
+               const launch_geom& g, size_t* done, cudaError_t* rc)
+{
+    using E = natural_int<S>;
+    if constexpr (sizeof(E) == 4) {
+        return false;
+    } else {
+        if (elem_bytes != sizeof(E)) return false;
+        if (sizeof(E) == 8 && reinterpret_cast<uintptr_t>(other) % 32) return false;  // 32-byte stores
+        *rc = dense::launch_dense_extract_fixed<E, S, dense::SIDE_PADDED, 4, false>(dn, other, n, f, s, g, done);
+        return true;
+    }
+}
+
+template <uint32_t Lo, uint32_t Hi>
+bool extract_range(uint32_t S, uint32_t elem_bytes, const void* dn, void* other, size_t n, const dense::dense_fields& f,
+                   cudaStream_t s, const launch_geom& g, size_t* done, cudaError_t* rc)
+{
+    if constexpr (Lo >= Hi) {
+        return false;
+    } else {
+        if constexpr (Lo != 0 && Lo != 8 && Lo != 16 && Lo != 32)
+            if (S == Lo) return extract_s<Lo>(elem_bytes, dn, other, n, f, s, g, done, rc);
+        return extract_range<Lo + 1, Hi>(S, elem_bytes, dn, other, n, f, s, g, done, rc);
+    }
+}
+
 template <uint32_t Lo, uint32_t Hi>
 bool insert_range(uint32_t S, uint32_t elem_bytes, int plane_bytes, const void* other, void* dn, size_t n,
                   const dense::dense_fields& f, cudaStream_t s, const launch_geom& g, size_t* done, cudaError_t* rc)
@@ -62,6 +93,13 @@ bool PINT_CAT(dense_insert_fixed_part, PINT_FIXED_PART)(uint32_t S, uint32_t ele
 {
     return insert_range<16 * PINT_FIXED_PART, 16 * PINT_FIXED_PART + 16>(S, elem_bytes, plane_bytes, other, dn, n, f, s, g,
                                                                           done, rc);
+}
+
+bool PINT_CAT(dense_extract_fixed_part, PINT_FIXED_PART)(uint32_t S, uint32_t elem_bytes, const void* dn, void* other, size_t n,
+                                                         const dense::dense_fields& f, cudaStream_t s, const launch_geom& g,
+                                                         size_t* done, cudaError_t* rc)
+{
+    return extract_range<16 * PINT_FIXED_PART, 16 * PINT_FIXED_PART + 16>(S, elem_bytes, dn, other, n, f, s, g, done, rc);
 }
 
 }  // namespace pint_cuda_impl

@@ -19,7 +19,7 @@ LAYOUTS = [(4, (8, 8, 8)), (4, (10, 10, 10)), (2, (12,)), (4, (7, 9, 3)), (8, (1
            (4, (5, 6, 5, 3)), (8, (10, 10, 10, 10)), (8, (21, 21, 21)), (1, (3,)), (4, (1,)), (8, (31, 2)), (8, (1, 62)),
            (8, (3, 7, 11, 13, 17, 12)), (4, (11, 11, 9)), (2, (5, 6, 5)), (8, (64,)), (4, (8, 8, 8, 8)), (1, (2, 3, 3)),
            (8, (12, 12, 12)), (8, (17, 17)), (1, (2, 2)), (2, (3, 4)), (4, (13, 13)), (8, (19, 19, 19))]
-SIZES = [1, 2, 5, 127, 128, 129, 4096, (1 << 18) + 77]
+SIZES = [1, 2, 5, 127, 128, 129, 4096, (1 << 18) + 77]  # the last: many whole tiles + a remainder
 
 
 @pytest.fixture(scope="module")
@@ -112,8 +112,17 @@ def test_dense_in_place_and_tiles(P, oracle, eb, bits):
             ops.set_option("dense_tile_bytes", 0)
 
 
+@pytest.fixture(params=["compiled_in_S", "runtime_geometry"])
+def convert_mode(request, P):
+    """Conversions: kernels with S compiled in (dense_fixed.cu) / the run-time-geometry kernels only."""
+    _, ops, _ = P
+    ops.set_option("dense_windows", 1 if request.param == "runtime_geometry" else 0)
+    yield request.param
+    ops.set_option("dense_windows", 0)
+
+
 @pytest.mark.parametrize("eb,bits", LAYOUTS)
-def test_dense_pack_unpack_planes(P, oracle, eb, bits):
+def test_dense_pack_unpack_planes(P, oracle, eb, bits, convert_mode):
     pint_b200, ops, dense = P
     L = pint_b200.Layout(eb, *bits)
     S = sum(bits)
@@ -211,7 +220,7 @@ def test_sharded_dense_binary_single_process(P, oracle):
 
 
 @pytest.mark.parametrize("eb,bits", [(4, (8, 8, 8)), (4, (7, 9, 3)), (8, (21, 21, 21)), (2, (12,))])
-def test_dense_conversions_misaligned_other_side(P, oracle, eb, bits):
+def test_dense_conversions_misaligned_other_side(P, oracle, eb, bits, convert_mode):
     """The padded array / the planes at addresses that are not 16-byte aligned (element-granular
     fallback of the quad paths) give the same streams and values."""
     pint_b200, ops, dense = P

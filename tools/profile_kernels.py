@@ -37,9 +37,9 @@ for rep in range(2):
 # dense bit-stream kernels: static RGB24 / 19-bit / 12-bit chunk kernels, run-time geometry, conversions
 from pint_b200 import dense  # noqa: E402
 nd = n
-for eb, bits in ((4, (8, 8, 8)), (4, (7, 9, 3)), (2, (12,)), (4, (5, 6, 5, 3))):
+for eb, bits in ((4, (8, 8, 8)), (4, (7, 9, 3)), (2, (12,)), (4, (5, 6, 5, 3)), (8, (16, 16, 16)), (8, (21, 21, 21))):
     L = pint_b200.Layout(eb, *bits)
-    x = torch.empty(nd, dtype={2: torch.uint16, 4: torch.uint32}[eb], device="cuda")
+    x = torch.empty(nd, dtype={2: torch.uint16, 4: torch.uint32, 8: torch.uint64}[eb], device="cuda")
     ops.fill_splitmix(x, 5)
     da = dense.pack(L, x)
     ops.fill_splitmix(x, 6)
