@@ -18,7 +18,8 @@ LAYOUTS = [(4, (8, 8, 8)), (4, (10, 10, 10)), (2, (12,)), (4, (7, 9, 3)), (8, (1
            (2, (14,)), (2, (5, 5, 5)), (4, (6, 6, 6)), (2, (10,)),
            (4, (5, 6, 5, 3)), (8, (10, 10, 10, 10)), (8, (21, 21, 21)), (1, (3,)), (4, (1,)), (8, (31, 2)), (8, (1, 62)),
            (8, (3, 7, 11, 13, 17, 12)), (4, (11, 11, 9)), (2, (5, 6, 5)), (8, (64,)), (4, (8, 8, 8, 8)), (1, (2, 3, 3)),
-           (8, (12, 12, 12)), (8, (17, 17)), (1, (2, 2)), (2, (3, 4)), (4, (13, 13)), (8, (19, 19, 19))]
+           (8, (12, 12, 12)), (8, (17, 17)), (1, (2, 2)), (2, (3, 4)), (4, (13, 13)), (8, (19, 19, 19)),
+           (4, (8, 8)), (8, (16, 16)), (8, (4, 4))]  # the last three: S = 16 / 32 / 8 inside a wider Integer
 SIZES = [1, 2, 5, 127, 128, 129, 4096, (1 << 18) + 77]  # the last: many whole tiles + a remainder
 
 
