@@ -233,80 +233,10 @@ __device__ __forceinline__ void process_chunk(typename Fn::word* A, const typena
     // word was flushed by put() and both windows are back at shift 0.
 }
 
-// Two results per element (pair_fn, cuda_kernels_multi.cuh): A <- Op0(A, B), B <- Op1(A, B), both in
-// place.  Same windows as process_chunk with a second output window that moves in step with
-// the first; B[wo] is written only after the input window has moved past word wo, as for A.
-template <class PFn, class Geo>
-__device__ __forceinline__ void process_chunk_pair(typename PFn::word* A, typename PFn::word* B, const PFn& fn, const Geo& geo)
-{
-    using W = typename PFn::word;
-    constexpr uint32_t WB = 8 * sizeof(W);
-    const uint32_t S = geo.S(), Cw = geo.Cw(), EB = geo.EB();
-    const W SM = ones_w<W>(S);
-    W ca = A[0], cb = B[0];
-    W na = Cw > 1 ? A[1] : W(0), nb = Cw > 1 ? B[1] : W(0);
-    W o0cur = 0, o0nxt = 0, o1cur = 0, o1nxt = 0;
-    uint32_t shi = 0, wi = 0, sho = 0, wo = 0;
-    auto take = [&](W& xa, W& xb) {
-        xa = funnel_r(ca, na, shi);
-        xb = funnel_r(cb, nb, shi);
-        shi += S;
-        if (shi >= WB) {
-            shi -= WB;
-            ++wi;
-            ca = na;
-            cb = nb;
-            na = wi + 1 < Cw ? A[wi + 1] : W(0);
-            nb = wi + 1 < Cw ? B[wi + 1] : W(0);
-        }
-    };
-    auto put = [&](W r0, W r1) {
-        o0cur |= r0 << sho;
-        o0nxt |= spill_l(r0, sho);
-        o1cur |= r1 << sho;
-        o1nxt |= spill_l(r1, sho);
-        sho += S;
-        if (sho >= WB) {
-            sho -= WB;
-            A[wo] = o0cur;
-            B[wo] = o1cur;
-            o0cur = o0nxt;
-            o1cur = o1nxt;
-            o0nxt = 0;
-            o1nxt = 0;
-            ++wo;
-        }
-    };
-    if constexpr (Geo::is_static) {
-#pragma unroll
-        for (uint32_t e = 0; e < Geo::kG; e += Geo::kEPW) {
-            W xa = 0, xb = 0;
-#pragma unroll
-            for (uint32_t k = 0; k < Geo::kEPW; ++k) {
-                W ta, tb;
-                take(ta, tb);
-                xa |= (Geo::kEPW == 1 ? ta : W(ta & SM)) << (k * Geo::kEB);
-                xb |= (Geo::kEPW == 1 ? tb : W(tb & SM)) << (k * Geo::kEB);
-            }
-            const W r0 = fn.first(xa, xb), r1 = fn.second(xa, xb);
-#pragma unroll
-            for (uint32_t k = 0; k < Geo::kEPW; ++k) put((r0 >> (k * Geo::kEB)) & SM, (r1 >> (k * Geo::kEB)) & SM);
-        }
-    } else {
-        const uint32_t G = geo.G(), step = WB / EB;
-        for (uint32_t e = 0; e < G; e += step) {
-            W xa = 0, xb = 0;
-            for (uint32_t k = 0; k < WB; k += EB) {
-                W ta, tb;
-                take(ta, tb);
-                xa |= (ta & SM) << k;
-                xb |= (tb & SM) << k;
-            }
-            const W r0 = fn.first(xa, xb), r1 = fn.second(xa, xb);
-            for (uint32_t k = 0; k < WB; k += EB) put((r0 >> k) & SM, (r1 >> k) & SM);
-        }
-    }
-}
+// Two results per element exist only for whole-chunk geometries (process_chunk_mw_pair): with the
+// sliding windows a second output window costs more than the second pass over a and b saves
+// (two launches 447 / 767 / 208 against one pass 411 / 660 / 179 Gelem-results/s for S = 31 / 21 / 63,
+// profiles/r03p_ab_dense_pair.log), so the C ABI runs such layouts as two launches.
 
 // One-in/one-out maps (shift_left / shift_right_unsigned) element by element: one input window,
 // one output window, in place.
@@ -429,8 +359,8 @@ __global__ void dense_binary_kernel(const uint4* a, const uint4* b, uint4* out, 
             if constexpr (Pair) process_chunk_mw_pair<Fn, int(Geo::kCw)>(A + c, B + c, fn);
             else process_chunk_mw<Fn, int(Geo::kCw)>(A + c, B + c, fn);
         } else {
-            if constexpr (Pair) process_chunk_pair(A + c, B + c, fn, geo);
-            else process_chunk(A + c, B + c, fn, geo);
+            static_assert(!Pair, "op pairs in one pass: whole-chunk geometries only");
+            process_chunk(A + c, B + c, fn, geo);
         }
     }
 

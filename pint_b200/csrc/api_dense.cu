@@ -52,21 +52,6 @@ cudaError_t dense_generic(int op, const layout_desc& d, uint32_t S, const void* 
     return rc;
 }
 
-template <class W, int... Pairs>
-cudaError_t dense_generic_pair(int pair, const layout_desc& d, uint32_t S, const void* a, const void* b, void* out0,
-                               void* out1, size_t n, cudaStream_t s, const launch_geom& g,
-                               std::integer_sequence<int, Pairs...>)
-{
-    const layout_desc e = slot_desc(d, S);
-    const runtime_masks<W> p(make_word_masks<W>(e));
-    cudaError_t rc = cudaErrorInvalidValue;
-    ((pair == Pairs ? (rc = dense::launch_dense_binary<pair_fn<kOpPairs[Pairs][0], kOpPairs[Pairs][1], runtime_masks<W>>,
-                                                       dense::runtime_geom<W>, true>(
-                                a, b, out0, n, pair_fn<kOpPairs[Pairs][0], kOpPairs[Pairs][1], runtime_masks<W>>{p},
-                                dense::runtime_geom<W>(S, 8 * e.elem_bytes), s, g, tuning(), out1), 0) : 0), ...);
-    return rc;
-}
-
 dense::dense_fields make_fields(const layout_desc& d)
 {
     dense::dense_fields f{};
@@ -261,19 +246,19 @@ int pint_cuda_dense_binary_multi(int nops, const int* ops, const pint_layout* la
             done[i] = true;
             void* o0 = swapped ? outs[i] : outs[j];
             void* o1 = swapped ? outs[j] : outs[i];
-            auto pairs = std::make_integer_sequence<int, kNumOpPairs>();
             const int N = int(S / dense::gcd_u32(S, 32));
             cudaError_t mrc = cudaSuccess;
-            if (k)
+            // one pass for whole-chunk kernels only; window kernels (chunks above 19 words, or the
+            // dense_windows option) run the two ops as two launches, which is faster there
+            if (k && k->pair[pi])
                 rc = (int)k->pair[pi](a, b, o0, o1, n, s, g, tuning());
-            else if (!opts().dense_windows &&
+            else if (!k && !opts().dense_windows &&
                      (dense_mw_pair_part0(N, pi, d, S, a, b, o0, o1, n, s, g, tuning(), &mrc) ||
                       dense_mw_pair_part1(N, pi, d, S, a, b, o0, o1, n, s, g, tuning(), &mrc) ||
                       dense_mw_pair_part2(N, pi, d, S, a, b, o0, o1, n, s, g, tuning(), &mrc)))
                 rc = (int)mrc;
             else
-                rc = (int)(S <= 32 ? dense_generic_pair<uint32_t>(pi, d, S, a, b, o0, o1, n, s, g, pairs)
-                                   : dense_generic_pair<uint64_t>(pi, d, S, a, b, o0, o1, n, s, g, pairs));
+                done[i] = false;  // not paired after all
         }
         if (rc < 0) rc = pint_cuda_dense_binary(ops[j], layout, a, b, outs[j], n, stream);
         if (rc) return rc;

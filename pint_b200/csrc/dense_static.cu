@@ -34,17 +34,14 @@ cudaError_t dense_pair_entry(const void* a, const void* b, void* out0, void* out
         using Geo = dense::mw_geom<CL::kN>;
         return dense::launch_dense_binary<Fn, Geo, true>(a, b, out0, n, Fn{}, Geo{CL::kS, 1}, s, g, tune, out1);
     } else {
-        using W = typename SL::word;
-        using Fn = pair_fn<kOpPairs[Pair][0], kOpPairs[Pair][1], static_masks<SL>>;
-        using Geo = dense::static_geom<W, SL::masks.total_bits, 8 * sizeof(typename SL::integer)>;
-        return dense::launch_dense_binary<Fn, Geo, true>(a, b, out0, n, Fn{}, Geo{1}, s, g, tune, out1);
+        return cudaErrorNotSupported;  // never installed (add_dense_pairs): window kernels run pairs as two launches
     }
 }
 
 template <class SL, class CL, int... Pairs>
 void add_dense_pairs(dense_layout_kernels& k, std::integer_sequence<int, Pairs...>)
 {
-    ((k.pair[Pairs] = &dense_pair_entry<SL, CL, Pairs>), ...);
+    if (CL::kN <= (int)dense::kMaxMwWords) ((k.pair[Pairs] = &dense_pair_entry<SL, CL, Pairs>), ...);
 }
 
 template <class SL, class CL, int... Ops>
