@@ -59,7 +59,35 @@ __device__ __forceinline__ void deposit(W x, uint32_t e, W& cur, W* o)
     }
 }
 
-template <class Elem, uint32_t S, int Side, int PlaneBytes>
+// NQ consecutive quads of one plane (sign-extended to 64 bits as load_plane_quad does); V32: 256-bit
+// loads where the run is a whole number of 32-byte sectors, so that a lane never leaves half a
+// sector to a second instruction
+template <int PlaneBytes, uint32_t NQ, bool V32>
+__device__ __forceinline__ void load_plane_quads(const void* plane, size_t q0, uint64_t (&v)[NQ][4])
+{
+    if constexpr (V32 && PlaneBytes == 8) {
+#pragma unroll
+        for (uint32_t q = 0; q < NQ; ++q) {
+            const vec32 x = ld32(reinterpret_cast<const vec32*>(plane) + q0 + q);
+            v[q][0] = (uint64_t(x.lo.y) << 32) | x.lo.x; v[q][1] = (uint64_t(x.lo.w) << 32) | x.lo.z;
+            v[q][2] = (uint64_t(x.hi.y) << 32) | x.hi.x; v[q][3] = (uint64_t(x.hi.w) << 32) | x.hi.z;
+        }
+    } else if constexpr (V32 && PlaneBytes == 4 && NQ % 2 == 0) {
+#pragma unroll
+        for (uint32_t q = 0; q < NQ; q += 2) {
+            const vec32 x = ld32(reinterpret_cast<const vec32*>(static_cast<const uint4*>(plane) + q0 + q));
+            v[q][0] = uint64_t(int64_t(int32_t(x.lo.x))); v[q][1] = uint64_t(int64_t(int32_t(x.lo.y)));
+            v[q][2] = uint64_t(int64_t(int32_t(x.lo.z))); v[q][3] = uint64_t(int64_t(int32_t(x.lo.w)));
+            v[q + 1][0] = uint64_t(int64_t(int32_t(x.hi.x))); v[q + 1][1] = uint64_t(int64_t(int32_t(x.hi.y)));
+            v[q + 1][2] = uint64_t(int64_t(int32_t(x.hi.z))); v[q + 1][3] = uint64_t(int64_t(int32_t(x.hi.w)));
+        }
+    } else {
+#pragma unroll
+        for (uint32_t q = 0; q < NQ; ++q) load_plane_quad<PlaneBytes>(plane, q0 + q, v[q]);
+    }
+}
+
+template <class Elem, uint32_t S, int Side, int PlaneBytes, bool V32 = false>
 __global__ void __launch_bounds__(256)
 dense_insert_fixed_kernel(const Elem* padded, uint4* dense, uint32_t units_per_thread, const __grid_constant__ dense_fields f)
 {
@@ -73,8 +101,11 @@ dense_insert_fixed_kernel(const Elem* padded, uint4* dense, uint32_t units_per_t
     const size_t unit0 = size_t(blockIdx.x) * units_per_tile;
     for (uint32_t it = 0; it < units_per_thread; it += UB) {
         if constexpr (Side == SIDE_PADDED) {
-            constexpr uint32_t PV = 16 / sizeof(Elem);  // elements per 16-byte load
-            constexpr uint32_t NVB = BEL / PV;          // loads per batch
+            // 16-byte loads, or 32-byte ones (V32) when a batch is a whole number of sectors
+            constexpr bool Wide = V32 && (BEL * sizeof(Elem)) % 32 == 0;
+            constexpr uint32_t PV = (Wide ? 32 : 16) / sizeof(Elem);  // elements per load
+            constexpr uint32_t NVB = BEL / PV;                        // loads per batch
+            using Vec = typename std::conditional<Wide, vec32, uint4>::type;
             // UB > 1: one batch holds UB whole units; else the unit is cut into GE / BEL batches and the
             // word under construction (`cur`) carries over from one batch to the next
             constexpr uint32_t NU = UB;
@@ -84,13 +115,16 @@ dense_insert_fixed_kernel(const Elem* padded, uint4* dense, uint32_t units_per_t
             for (uint32_t j = 0; j < NU; ++j) cur[j] = 0;
 #pragma unroll
             for (uint32_t b0 = 0; b0 < GE; b0 += BEL) {
-                union { uint4 q; Elem x[PV]; } v[NU][NVB];
+                union { Vec q; Elem x[PV]; } v[NU][NVB];
 #pragma unroll
                 for (uint32_t j = 0; j < NU; ++j) {
                     const uint32_t u = (it + j) * T + threadIdx.x;
-                    const uint4* src = reinterpret_cast<const uint4*>(padded + (unit0 + u) * GE + b0);
+                    const Vec* src = reinterpret_cast<const Vec*>(padded + (unit0 + u) * GE + b0);
 #pragma unroll
-                    for (uint32_t k = 0; k < NVB; ++k) v[j][k].q = ld16<CACHE_STREAMING>(src + k);
+                    for (uint32_t k = 0; k < NVB; ++k) {
+                        if constexpr (Wide) v[j][k].q = ld32(src + k);
+                        else v[j][k].q = ld16<CACHE_STREAMING>(src + k);
+                    }
                 }
 #pragma unroll
                 for (uint32_t j = 0; j < NU; ++j) {
@@ -127,8 +161,7 @@ dense_insert_fixed_kernel(const Elem* padded, uint4* dense, uint32_t units_per_t
                     for (uint32_t j = 0; j < NU; ++j) {
                         const uint32_t u = (it + j) * T + threadIdx.x;
                         const size_t q0 = ((unit0 + u) * GE + b0) / 4;
-#pragma unroll
-                        for (uint32_t q = 0; q < NQ; ++q) load_plane_quad<PlaneBytes>(plane, q0 + q, pv[j][q]);
+                        load_plane_quads<PlaneBytes, NQ, V32>(plane, q0, pv[j]);
                     }
 #pragma unroll
                     for (uint32_t j = 0; j < NU; ++j)
@@ -311,8 +344,24 @@ cudaError_t launch_dense_insert_fixed(const void* other, void* dense, size_t n, 
     *done = ntiles * tile_elems;
     if (ntiles == 0) return cudaSuccess;
     if (ntiles > 0x7FFFFFFFull) return cudaErrorInvalidValue;
-    dense_insert_fixed_kernel<Elem, S, Side, PlaneBytes><<<unsigned(ntiles), T, smem, stream>>>(
-        static_cast<const Elem*>(other), static_cast<uint4*>(dense), upt, f);
+    // 256-bit loads when every input is 32-byte aligned (and option vec256 != 0)
+    uintptr_t align = reinterpret_cast<uintptr_t>(other);
+    if (Side == SIDE_PLANES)
+        for (uint32_t i = 0; i < f.t.nfields; ++i) align |= reinterpret_cast<uintptr_t>(f.planes.p[i]);
+    constexpr uint32_t src_bytes = Side == SIDE_PADDED ? uint32_t(sizeof(Elem)) : uint32_t(PlaneBytes);
+    // same-box A/B (profiles/r03r_ab_insert_vec256.log): +10-15 % for 64-bit words (48-bit pack 6198 -> 6818,
+    // 40-bit from_planes 6105 -> 7014 GB/s), 0 to -3 % for 32-bit words: instantiated for the former only
+    bool wide = false;
+    if constexpr (sizeof(typename Geo::W) == 8 && (Geo::BEL * src_bytes) % 32 == 0) {
+        if (g.vec256 != 0 && align % 32 == 0) {
+            wide = true;
+            dense_insert_fixed_kernel<Elem, S, Side, PlaneBytes, true><<<unsigned(ntiles), T, smem, stream>>>(
+                static_cast<const Elem*>(other), static_cast<uint4*>(dense), upt, f);
+        }
+    }
+    if (!wide)
+        dense_insert_fixed_kernel<Elem, S, Side, PlaneBytes, false><<<unsigned(ntiles), T, smem, stream>>>(
+            static_cast<const Elem*>(other), static_cast<uint4*>(dense), upt, f);
     count_launch(g);
     return cudaGetLastError();
     }

@@ -13,6 +13,8 @@ from pint_b200 import dense, ops  # noqa: E402
 
 UDT = {1: torch.uint8, 2: torch.uint16, 4: torch.uint32, 8: torch.uint64}
 n = 1 << (int(sys.argv[1]) if len(sys.argv) > 1 else 28)
+# second argument "vec256": A/B the 256-bit loads of the compiled-in-S insert kernels instead (option vec256 0 / 1)
+OPTION, OFF, ON = ("vec256", 0, 1) if len(sys.argv) > 2 and sys.argv[2] == "vec256" else ("dense_windows", 1, 0)
 
 
 def timed(fn, reps=10):
@@ -44,12 +46,15 @@ for eb, bits in LAYOUTS:
                              ("to_planes", lambda: dense.to_planes(L, da, n, signed=True, out=planes), n * (S / 8 + 4 * len(bits))),
                              ("pack", lambda: dense.pack(L, x, out=da), n * (S / 8 + eb)),
                              ("from_planes", lambda: dense.from_planes(L, planes, out=da), n * (S / 8 + 4 * len(bits)))):
-        for mode in (0, 1, 0, 1):
-            ops.set_option("dense_windows", mode)
+        for mode in (ON, OFF, ON, OFF):
+            ops.set_option(OPTION, mode)
             gbs = round(bytes_ / timed(fn) / 1e6)
-            key = name + ("_runtime" if mode else "_fixed")
+            if OPTION == "vec256":
+                key = name + ("_256bit" if mode == ON else "_128bit")
+            else:
+                key = name + ("_runtime" if mode == OFF else "_fixed")
             row[key] = max(row.get(key, 0), gbs)
-    ops.set_option("dense_windows", 0)
+    ops.set_option(OPTION, ON)
     print(json.dumps(row), flush=True)
     del x, da, planes
     torch.cuda.empty_cache()
