@@ -106,6 +106,27 @@ def test_golden_pairs_reduce(P, refvec):
             assert ops.pairs_reduce(op, L, pairs) == int(want[i]), (L, op)
 
 
+@pytest.mark.parametrize("eb,bits", [(4, (8, 8, 8, 8)), (2, (5, 6, 5)), (8, (3, 7, 11, 13, 17, 13)), (1, (2, 3, 3))])
+def test_pairs_reduce_large_and_alignments(P, oracle, eb, bits):
+    """Whole 256-bit tiles, 16-byte tiles, vector and scalar tails; arrays starting 0 / 16 / eb bytes
+    past a 32-byte boundary; both load widths."""
+    pint_b200, ops = P
+    L = pint_b200.Layout(eb, *bits)
+    n = (1 << 19) + 13
+    flat = oracle.fill(eb, 2 * n + 64, 0xBEEF)
+    dev = to_dev(flat)
+    try:
+        for off in (0, 16 // eb, 1):
+            pairs_h = flat[off:off + 2 * n]
+            for op in ("add_signed_saturate", "sub_wrap", "max_unsigned"):
+                want = int(oracle.pairs_reduce(op, eb, bits, pairs_h))
+                for vec256 in (0, 1):
+                    ops.set_option("vec256", vec256)
+                    assert ops.pairs_reduce(op, L, dev[off:off + 2 * n]) == want, (L, op, off, vec256)
+    finally:
+        ops.set_option("vec256", 1)
+
+
 def test_reference_kats_through_cuda(P, oracle, kats):
     """The reference's own 61 unit tests (tests/pint_test.cpp), executed by the CUDA kernels."""
     pint_b200, ops = P
