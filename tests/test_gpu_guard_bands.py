@@ -52,3 +52,44 @@ def test_no_writes_outside_outputs(eb, bits):
             torch.cuda.synchronize()
             assert g.intact(), f"write outside `out`: {L} n={n} off={off_elems}"
             assert all(p.intact() for p in pg), f"write outside a plane: {L} n={n} off={off_elems}"
+
+
+@pytest.mark.parametrize("eb,bits", [(4, (8, 8, 8)), (2, (12,)), (4, (7, 9, 3)), (8, (21, 21, 21)), (1, (2, 3, 2)),
+                                     (8, (12, 12, 12)), (8, (16, 16, 16)), (4, (11, 11, 9))])
+def test_dense_no_writes_outside_outputs(eb, bits):
+    """Dense streams: binary ops, shifts, and the conversions in both kernel families (S compiled in:
+    direct / staged / word-owner insert, group-owner extract; run-time geometry) -- whole tiles plus a
+    remainder, outputs at 16-byte offsets, padded outputs and planes also at element offsets."""
+    import pint_b200
+    from pint_b200 import dense, ops
+    L = pint_b200.Layout(eb, *bits)
+    udt = {1: torch.uint8, 2: torch.uint16, 4: torch.uint32, 8: torch.uint64}[eb]
+    try:
+        for n in (1, 127, 4097, 70001):
+            nb = dense.nbytes(L, n)
+            x = torch.empty(n, dtype=udt, device="cuda")
+            ops.fill_splitmix(x, 3)
+            for windows in (0, 1):
+                ops.set_option("dense_windows", windows)
+                for off16 in (0, 16):
+                    g = Guarded(nb, off16)
+                    d = g.view(torch.uint8)
+                    dense.pack(L, x, out=d)
+                    g2 = Guarded(nb, off16)
+                    d2 = g2.view(torch.uint8)
+                    dense.binary("add_signed_saturate", L, d, d, n, out=d2)
+                    dense.shift(1, L, d, 1, n, out=d2)
+                    planes_g = [Guarded(n * 4, off16) for _ in bits]
+                    planes = [p.view(torch.int32) for p in planes_g]
+                    dense.to_planes(L, d, n, signed=True, out=planes)
+                    dense.from_planes(L, planes, out=d2)
+                    for off_elems in (0, 1):
+                        gp = Guarded(n * eb, off_elems * eb)
+                        dense.unpack(L, d, n, out=gp.view(udt))
+                        torch.cuda.synchronize()
+                        assert gp.intact(), f"write outside the padded array: {L} n={n} windows={windows} off={off_elems}"
+                    torch.cuda.synchronize()
+                    assert g.intact() and g2.intact(), f"write outside a dense stream: {L} n={n} windows={windows} off16={off16}"
+                    assert all(p.intact() for p in planes_g), f"write outside a plane: {L} n={n} windows={windows}"
+    finally:
+        ops.set_option("dense_windows", 0)
