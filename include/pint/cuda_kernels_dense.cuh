@@ -204,6 +204,38 @@ __device__ __forceinline__ void process_chunk(typename Fn::word* A, const typena
                 for (uint32_t k = 0; k < Geo::kEPW; ++k) put((r >> (k * Geo::kEB)) & SM);
             }
         }
+    } else if constexpr (sizeof(W) == 8) {
+        // 33..63-bit elements (EB == WB == 64).  64-bit funnel shifts by run-time amounts are 2-3
+        // instructions each on the 32-bit datapath and made this path ALU-bound at 4.1-4.9 TB/s
+        // (profiles/r03u_ncu_windows_summary.txt: 83-88 % ALU pipe).  Seen as 32-bit words, an element
+        // is two native funnel shifts over three words and its result three shifts into a three-word
+        // output window; an element always completes the word it starts in (S > 32) and sometimes the
+        // next.  Word w + 2 of the chunk's last element is the word after the chunk: read but never
+        // used (the launcher pads the tiles by 16 bytes).
+        uint32_t* A32 = reinterpret_cast<uint32_t*>(A);
+        const uint32_t* B32 = reinterpret_cast<const uint32_t*>(B);
+        const uint32_t G = geo.G();
+        uint32_t o0 = 0, o1 = 0, p = 0;
+        for (uint32_t e = 0; e < G; ++e) {
+            const uint32_t w = p >> 5, sh = p & 31u;
+            const uint32_t a0 = A32[w], a1 = A32[w + 1], a2 = A32[w + 2];
+            const uint32_t b0 = B32[w], b1 = B32[w + 1], b2 = B32[w + 2];
+            const uint64_t xa = (uint64_t(__funnelshift_r(a1, a2, sh)) << 32) | __funnelshift_r(a0, a1, sh);
+            const uint64_t xb = (uint64_t(__funnelshift_r(b1, b2, sh)) << 32) | __funnelshift_r(b0, b1, sh);
+            const uint64_t r = fn(xa, xb) & SM;
+            const uint32_t lo = uint32_t(r), hi = uint32_t(r >> 32);
+            A32[w] = o0 | (lo << sh);
+            const uint32_t m1 = o1 | __funnelshift_l(lo, hi, sh), m2 = __funnelshift_l(hi, 0u, sh);
+            if (sh + S >= 64) {
+                A32[w + 1] = m1;
+                o0 = m2;
+                o1 = 0;
+            } else {
+                o0 = m1;
+                o1 = m2;
+            }
+            p += S;
+        }
     } else if (EB == WB) {
         // one element per word: input and output windows move together -- one shift, one branch
         const uint32_t G = geo.G();
@@ -419,7 +451,7 @@ cudaError_t launch_dense_binary(const void* a, const void* b, void* out, size_t 
     const size_t total_vec = size_t((valid_bits + 127) / 128);
     const size_t tile_bytes = size_t(T) * R * geo.Cw() * sizeof(W);
     const size_t ntiles = (total_vec * 16 + tile_bytes - 1) / tile_bytes;
-    const size_t smem = (Mode == 2 ? 1 : 2) * tile_bytes;
+    const size_t smem = (Mode == 2 ? 1 : 2) * tile_bytes + 16;  // + 16: the 64-bit window form peeks one word past a chunk
     auto kernel = dense_binary_kernel<Fn, Geo, Mode>;
     if (smem > 48 * 1024) {
         cudaError_t rc = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
