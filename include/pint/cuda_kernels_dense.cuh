@@ -87,6 +87,7 @@ template <class W, uint32_t S_, uint32_t EB_ = 8 * sizeof(W)>
 struct static_geom {
     static constexpr bool is_static = true;
     static constexpr bool whole_chunk = false;
+    static constexpr bool wide64 = false;
     using unit = W;  // the tile is handled in words of this type
     static constexpr uint32_t WB = 8 * sizeof(W);
     static constexpr uint32_t kS = S_, kCw = S_ / gcd_u32(S_, WB), kG = WB / gcd_u32(S_, WB), kEB = EB_, kEPW = WB / EB_;
@@ -102,6 +103,7 @@ template <class W>
 struct runtime_geom {
     static constexpr bool is_static = false;
     static constexpr bool whole_chunk = false;
+    static constexpr bool wide64 = false;
     using unit = W;
     static constexpr uint32_t WB = 8 * sizeof(W);
     uint32_t s, cw, g, eb;
@@ -114,6 +116,23 @@ struct runtime_geom {
     __host__ __device__ uint32_t Cw() const { return cw; }
     __host__ __device__ uint32_t G() const { return g; }
     __host__ __device__ uint32_t EB() const { return eb; }
+};
+
+// 33..63-bit elements (64-bit functors) over a tile of 32-bit words: the bit pattern repeats every
+// lcm(S, 32) bits, half the 64-bit-word chunk for odd S, so twice as many threads fit beside the
+// staged tiles (S = 63: 252 instead of 504 bytes of each operand per thread).
+struct wide_geom {
+    static constexpr bool is_static = false;
+    static constexpr bool whole_chunk = false;
+    static constexpr bool wide64 = true;
+    using unit = uint32_t;
+    uint32_t s, cw, g;
+    uint32_t chunks_per_thread;
+    wide_geom() = default;
+    explicit wide_geom(uint32_t S_) : s(S_), cw(S_ / gcd_u32(S_, 32)), g(32 / gcd_u32(S_, 32)), chunks_per_thread(1) {}
+    __host__ __device__ uint32_t S() const { return s; }
+    __host__ __device__ uint32_t Cw() const { return cw; }  // 32-bit words
+    __host__ __device__ uint32_t G() const { return g; }
 };
 
 }  // namespace dense
@@ -204,38 +223,6 @@ __device__ __forceinline__ void process_chunk(typename Fn::word* A, const typena
                 for (uint32_t k = 0; k < Geo::kEPW; ++k) put((r >> (k * Geo::kEB)) & SM);
             }
         }
-    } else if constexpr (sizeof(W) == 8) {
-        // 33..63-bit elements (EB == WB == 64).  64-bit funnel shifts by run-time amounts are 2-3
-        // instructions each on the 32-bit datapath and made this path ALU-bound at 4.1-4.9 TB/s
-        // (profiles/r03u_ncu_windows_summary.txt: 83-88 % ALU pipe).  Seen as 32-bit words, an element
-        // is two native funnel shifts over three words and its result three shifts into a three-word
-        // output window; an element always completes the word it starts in (S > 32) and sometimes the
-        // next.  Word w + 2 of the chunk's last element is the word after the chunk: read but never
-        // used (the launcher pads the tiles by 16 bytes).
-        uint32_t* A32 = reinterpret_cast<uint32_t*>(A);
-        const uint32_t* B32 = reinterpret_cast<const uint32_t*>(B);
-        const uint32_t G = geo.G();
-        uint32_t o0 = 0, o1 = 0, p = 0;
-        for (uint32_t e = 0; e < G; ++e) {
-            const uint32_t w = p >> 5, sh = p & 31u;
-            const uint32_t a0 = A32[w], a1 = A32[w + 1], a2 = A32[w + 2];
-            const uint32_t b0 = B32[w], b1 = B32[w + 1], b2 = B32[w + 2];
-            const uint64_t xa = (uint64_t(__funnelshift_r(a1, a2, sh)) << 32) | __funnelshift_r(a0, a1, sh);
-            const uint64_t xb = (uint64_t(__funnelshift_r(b1, b2, sh)) << 32) | __funnelshift_r(b0, b1, sh);
-            const uint64_t r = fn(xa, xb) & SM;
-            const uint32_t lo = uint32_t(r), hi = uint32_t(r >> 32);
-            A32[w] = o0 | (lo << sh);
-            const uint32_t m1 = o1 | __funnelshift_l(lo, hi, sh), m2 = __funnelshift_l(hi, 0u, sh);
-            if (sh + S >= 64) {
-                A32[w + 1] = m1;
-                o0 = m2;
-                o1 = 0;
-            } else {
-                o0 = m1;
-                o1 = m2;
-            }
-            p += S;
-        }
     } else if (EB == WB) {
         // one element per word: input and output windows move together -- one shift, one branch
         const uint32_t G = geo.G();
@@ -263,6 +250,43 @@ __device__ __forceinline__ void process_chunk(typename Fn::word* A, const typena
     }
     // G * S == Cw * WB: the last element ends exactly on the chunk's last bit, so the last
     // word was flushed by put() and both windows are back at shift 0.
+}
+
+// 33..63-bit elements, tile seen as 32-bit words (wide_geom).  64-bit funnel shifts by run-time
+// amounts are 2-3 instructions each on the 32-bit datapath and made the 64-bit-word form of this
+// path ALU-bound at 4.1-4.9 TB/s (profiles/r03u_ncu_windows_summary.txt: 83-88 % ALU pipe).  On
+// 32-bit words an element is two native funnel shifts over three words and its result three shifts
+// into a three-word output window; an element always completes the word it starts in (S > 32) and
+// sometimes the next.  Word w + 2 of the chunk's last element is the word after the chunk: read
+// but never used (the launcher pads the tiles by 16 bytes).  In place as process_chunk: a word is
+// written only after every element that touches it has been read.
+template <class Fn>
+__device__ __forceinline__ void process_chunk_wide64(uint32_t* A32, const uint32_t* B32, const Fn& fn, const wide_geom& geo)
+{
+    static_assert(sizeof(typename Fn::word) == 8, "64-bit functor");
+    const uint32_t S = geo.S(), G = geo.G();
+    const uint64_t SM = ones_w<uint64_t>(S);
+    uint32_t o0 = 0, o1 = 0, p = 0;
+    for (uint32_t e = 0; e < G; ++e) {
+        const uint32_t w = p >> 5, sh = p & 31u;
+        const uint32_t a0 = A32[w], a1 = A32[w + 1], a2 = A32[w + 2];
+        const uint32_t b0 = B32[w], b1 = B32[w + 1], b2 = B32[w + 2];
+        const uint64_t xa = (uint64_t(__funnelshift_r(a1, a2, sh)) << 32) | __funnelshift_r(a0, a1, sh);
+        const uint64_t xb = (uint64_t(__funnelshift_r(b1, b2, sh)) << 32) | __funnelshift_r(b0, b1, sh);
+        const uint64_t r = fn(xa, xb) & SM;
+        const uint32_t lo = uint32_t(r), hi = uint32_t(r >> 32);
+        A32[w] = o0 | (lo << sh);
+        const uint32_t m1 = o1 | __funnelshift_l(lo, hi, sh), m2 = __funnelshift_l(hi, 0u, sh);
+        if (sh + S >= 64) {
+            A32[w + 1] = m1;
+            o0 = m2;
+            o1 = 0;
+        } else {
+            o0 = m1;
+            o1 = m2;
+        }
+        p += S;
+    }
 }
 
 // Two results per element exist only for whole-chunk geometries (process_chunk_mw_pair): with the
@@ -385,6 +409,7 @@ __global__ void dense_binary_kernel(const uint4* a, const uint4* b, uint4* out, 
     for (uint32_t r = 0; r < R; ++r) {
         const uint32_t c = (r * T + threadIdx.x) * Cw;
         if constexpr (Unary) {
+            static_assert(!Geo::wide64, "shifts use the 64-bit-word windows (HBM-bound as they are)");
             if constexpr (Geo::whole_chunk) process_chunk_mw_unary<Fn, int(Geo::kCw)>(A + c, fn);
             else process_chunk_unary(A + c, fn, geo);
         } else if constexpr (Geo::whole_chunk) {
@@ -392,7 +417,8 @@ __global__ void dense_binary_kernel(const uint4* a, const uint4* b, uint4* out, 
             else process_chunk_mw<Fn, int(Geo::kCw)>(A + c, B + c, fn);
         } else {
             static_assert(!Pair, "op pairs in one pass: whole-chunk geometries only");
-            process_chunk(A + c, B + c, fn, geo);
+            if constexpr (Geo::wide64) process_chunk_wide64(A + c, B + c, fn, geo);
+            else process_chunk(A + c, B + c, fn, geo);
         }
     }
 
@@ -425,7 +451,7 @@ template <class W>
 inline void choose_tile(uint32_t cw, const dense_tuning& tune, uint32_t* threads, uint32_t* chunks_per_thread)
 {
     const uint32_t chunk_bytes = cw * uint32_t(sizeof(W));
-    uint32_t T = tune.threads > 0 ? uint32_t(tune.threads) : (chunk_bytes > 256 ? 64u : 128u);
+    uint32_t T = tune.threads > 0 ? uint32_t(tune.threads) : (chunk_bytes > 192 ? 64u : 128u);
     const uint32_t target = tune.tile_bytes > 0 ? uint32_t(tune.tile_bytes) : 16384u;
     uint32_t R = target / (T * chunk_bytes);
     if (R < 1) R = 1;

@@ -242,6 +242,7 @@ template <int N>
 struct mw_geom {
     static constexpr bool is_static = true;
     static constexpr bool whole_chunk = true;
+    static constexpr bool wide64 = false;
     using unit = uint32_t;
     static constexpr uint32_t kCw = N;
     uint32_t s;  // sum(Bits)

@@ -47,8 +47,12 @@ cudaError_t dense_generic(int op, const layout_desc& d, uint32_t S, const void* 
     const layout_desc e = slot_desc(d, S);
     const runtime_masks<W> p(make_word_masks<W>(e));
     cudaError_t rc = cudaErrorInvalidValue;
-    ((op == Ops ? (rc = dense::launch_dense_binary(a, b, out, n, swar_fn<Ops, runtime_masks<W>>{p},
-                                                   dense::runtime_geom<W>(S, 8 * e.elem_bytes), s, g, tuning()), 0) : 0), ...);
+    if constexpr (sizeof(W) == 8)  // 33..63-bit elements: 64-bit functor over a tile of 32-bit words
+        ((op == Ops ? (rc = dense::launch_dense_binary(a, b, out, n, swar_fn<Ops, runtime_masks<W>>{p}, dense::wide_geom(S), s, g,
+                                                       tuning()), 0) : 0), ...);
+    else
+        ((op == Ops ? (rc = dense::launch_dense_binary(a, b, out, n, swar_fn<Ops, runtime_masks<W>>{p},
+                                                       dense::runtime_geom<W>(S, 8 * e.elem_bytes), s, g, tuning()), 0) : 0), ...);
     return rc;
 }
 
