@@ -10,7 +10,7 @@ OBJ := build/obj
 LIB := pint_b200/lib/libpint_cuda.so
 HDRS := $(wildcard include/pint/*.hpp include/pint/*.cuh include/*.h $(SRC)/*.hpp $(SRC)/*.def)
 PARTS := 0 1 2 3
-OBJS := $(OBJ)/api.o $(OBJ)/api_aux.o $(OBJ)/api_dense.o $(OBJ)/dense_static.o $(foreach p,0 1 2,$(OBJ)/dense_generic_mw$(p).o) $(foreach p,0 1 2 3,$(OBJ)/dense_fixed$(p).o) $(OBJ)/generic.o $(foreach p,$(PARTS),$(OBJ)/registry_part$(p).o)
+OBJS := $(OBJ)/api.o $(OBJ)/api_aux.o $(OBJ)/api_dense.o $(OBJ)/api_callers.o $(OBJ)/dense_static.o $(foreach p,0 1 2,$(OBJ)/dense_generic_mw$(p).o) $(foreach p,0 1 2 3,$(OBJ)/dense_fixed$(p).o) $(OBJ)/generic.o $(foreach p,$(PARTS),$(OBJ)/registry_part$(p).o)
 
 all: $(LIB)
 

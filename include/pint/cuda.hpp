@@ -32,6 +32,7 @@
 #include <stdexcept>
 #include <string>
 #include <type_traits>
+#include <utility>
 
 #include "../pint_cuda.h"
 
@@ -164,6 +165,47 @@ inline void binary_multi(const pint_op (&ops)[NOps], const packed_int<Integer, B
     void* o[NOps];
     for (size_t j = 0; j < NOps; ++j) { codes[j] = ops[j]; o[j] = outs[j]; }
     check(pint_cuda_binary_multi((int)NOps, codes, &l, a, b, o, n, stream), "pint::cuda::binary_multi");
+}
+
+// One operand the same packed_int for every element: out[i] = OP(a[i], k) (binary_scalar) or
+// OP(k, a[i]) (scalar_binary); 2 * sizeof(Integer) bytes per element.  out may be a.  k is given
+// as a packed_int (needs pint.hpp) or as its value() (pint.hpp:776).
+template <class Integer, size_t Bits0, size_t... Bits>
+inline void binary_scalar(pint_op op, const packed_int<Integer, Bits0, Bits...>* a, Integer k_value,
+                          packed_int<Integer, Bits0, Bits...>* out, size_t n, stream_t stream = nullptr)
+{
+    const pint_layout l = detail::layout_of<Integer, Bits0, Bits...>::get();
+    check(pint_cuda_binary_scalar(op, &l, a, k_value, 0, out, n, stream), "pint::cuda::binary_scalar");
+}
+template <class Integer, size_t Bits0, size_t... Bits>
+inline void scalar_binary(pint_op op, Integer k_value, const packed_int<Integer, Bits0, Bits...>* a,
+                          packed_int<Integer, Bits0, Bits...>* out, size_t n, stream_t stream = nullptr)
+{
+    const pint_layout l = detail::layout_of<Integer, Bits0, Bits...>::get();
+    check(pint_cuda_binary_scalar(op, &l, a, k_value, 1, out, n, stream), "pint::cuda::scalar_binary");
+}
+template <class Integer, size_t Bits0, size_t... Bits>
+inline void binary_scalar(pint_op op, const packed_int<Integer, Bits0, Bits...>* a, packed_int<Integer, Bits0, Bits...> k,
+                          packed_int<Integer, Bits0, Bits...>* out, size_t n, stream_t stream = nullptr)
+{
+    binary_scalar(op, a, k.value(), out, n, stream);
+}
+template <class Integer, size_t Bits0, size_t... Bits>
+inline void scalar_binary(pint_op op, packed_int<Integer, Bits0, Bits...> k, const packed_int<Integer, Bits0, Bits...>* a,
+                          packed_int<Integer, Bits0, Bits...>* out, size_t n, stream_t stream = nullptr)
+{
+    scalar_binary(op, k.value(), a, out, n, stream);
+}
+
+// Interleaved operands, as the reference benchmark stores them (std::pair<Integer, Integer>,
+// tests/pint_bench.cpp:22): out[i] = OP(packed_int(pairs[i].first), packed_int(pairs[i].second)).
+template <class Integer, size_t Bits0, size_t... Bits>
+inline void binary_pairs(pint_op op, const std::pair<Integer, Integer>* pairs, packed_int<Integer, Bits0, Bits...>* out,
+                         size_t n, stream_t stream = nullptr)
+{
+    static_assert(sizeof(std::pair<Integer, Integer>) == 2 * sizeof(Integer), "pairs are two Integers back to back");
+    const pint_layout l = detail::layout_of<Integer, Bits0, Bits...>::get();
+    check(pint_cuda_binary_pairs(op, &l, pairs, out, n, stream), "pint::cuda::binary_pairs");
 }
 
 // Any of the above, computed as unpack -> per-field arithmetic -> repack in one kernel.

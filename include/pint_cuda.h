@@ -197,6 +197,19 @@ int pint_cuda_sharded_dense_binary(int op, const pint_layout* layout, int ngpu, 
  * is the low 32 bits. */
 int pint_cuda_pairs_reduce(int op, const pint_layout* layout, const void* pairs, size_t n,
                            uint64_t* sum_dev, pint_stream_t stream);
+/* out[i] = OP(pairs[2i], pairs[2i+1]): the same interleaved operands (std::pair<Integer, Integer>
+ * array, tests/pint_bench.cpp:22), the results kept as a plain array instead of summed.
+ * 3 * sizeof(Integer) bytes per element; `out` must not overlap `pairs`. */
+int pint_cuda_binary_pairs(int op, const pint_layout* layout, const void* pairs, void* out, size_t n,
+                           pint_stream_t stream);
+
+/* ---- one operand the same for every element (2 * sizeof(Integer) bytes per element) ---- */
+/* out[i] = OP(a[i], packed_int(scalar)), or OP(packed_int(scalar), a[i]) when scalar_first != 0
+ * (the order matters for the sub_* ops and for the unused high bits of min / max, which come from
+ * the second operand).  `scalar` is a packed_int::value() (pint.hpp:768, 776) and must fit the
+ * Integer (else PINT_E_ARG); `out` may be `a`. */
+int pint_cuda_binary_scalar(int op, const pint_layout* layout, const void* a, uint64_t scalar, int scalar_first,
+                            void* out, size_t n, pint_stream_t stream);
 
 /* ---- synthetic inputs and checksums ---- */
 /* out[i] = (Integer) splitmix64(seed + start + i) */

@@ -67,6 +67,8 @@ def lib():
             "pint_cuda_sharded_dense_binary": (i, [i, LP, i, C.POINTER(i), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp),
                                                   C.POINTER(sz), C.POINTER(vp)]),
             "pint_cuda_pairs_reduce": (i, [i, LP, vp, sz, vp, vp]),
+            "pint_cuda_binary_pairs": (i, [i, LP, vp, vp, sz, vp]),
+            "pint_cuda_binary_scalar": (i, [i, LP, vp, u64, i, vp, sz, vp]),
             "pint_cuda_fill_splitmix": (i, [vp, u32, sz, u64, u64, vp]),
             "pint_cuda_checksum": (i, [vp, u32, sz, vp, vp]),
             "pint_cuda_plan_shards": (i, [sz, u32, i, C.POINTER(sz), C.POINTER(sz)]),

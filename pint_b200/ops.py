@@ -198,6 +198,36 @@ def pairs_reduce(op, layout, pairs, stream=None):
     return int(res.item()) & 0xFFFFFFFFFFFFFFFF
 
 
+def binary_pairs(op, layout, pairs, out=None, stream=None):
+    """out[i] = op(pairs[2i], pairs[2i+1]): interleaved operands (the benchmark's std::pair array,
+    tests/pint_bench.cpp:22) in, plain array out."""
+    _check(layout, pairs)
+    n = pairs.numel() // 2
+    if out is None:
+        out = torch.empty(n, dtype=pairs.dtype, device=pairs.device)
+    _check(layout, out)
+    if out.numel() != n:
+        raise ValueError("out must hold one element per pair")
+    with torch.cuda.device(pairs.device):
+        _lib.check(_lib.lib().pint_cuda_binary_pairs(OP_CODE[op] if isinstance(op, str) else int(op), layout.ref,
+                                                     pairs.data_ptr(), out.data_ptr(), n, _stream(stream)),
+                   "pint_cuda_binary_pairs")
+    return out
+
+
+def binary_scalar(op, layout, a, scalar, out=None, stream=None, scalar_first=False):
+    """out[i] = op(a[i], P(scalar)) -- or op(P(scalar), a[i]) with scalar_first -- for one packed_int
+    value `scalar` (an int, packed_int::value()); `out` may be `a`."""
+    if out is None:
+        out = torch.empty_like(a)
+    n = _check(layout, a, out)
+    with torch.cuda.device(a.device):
+        _lib.check(_lib.lib().pint_cuda_binary_scalar(OP_CODE[op] if isinstance(op, str) else int(op), layout.ref,
+                                                      a.data_ptr(), int(scalar), 1 if scalar_first else 0,
+                                                      out.data_ptr(), n, _stream(stream)), "pint_cuda_binary_scalar")
+    return out
+
+
 def fill_splitmix(out, seed, start=0, stream=None):
     """out[i] = (Integer) splitmix64(seed + start + i): the synthetic input of SURVEY.md 8(d)."""
     if not out.is_cuda or not out.is_contiguous():

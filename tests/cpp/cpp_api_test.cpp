@@ -134,6 +134,29 @@ int main()
             for (size_t i = 0; i < n; ++i) if (ho[i] != rgba_add_ssat(ha[i], hb[i])) { ++fails; if (fails < 5) std::printf("multi ssat mismatch at %zu\n", i); }
         }
 
+        // ---- one constant operand; interleaved std::pair operands (tests/pint_bench.cpp:22) ----
+        {
+            const uint32_t k = 0x7F80FF01u;
+            pint::cuda::binary_scalar(PINT_ADD_SIGNED_SATURATE, a, k, out, n, s);
+            CK(cudaStreamSynchronize(s));
+            CK(cudaMemcpy(ho.data(), out, n * 4, cudaMemcpyDeviceToHost));
+            for (size_t i = 0; i < n; ++i) if (ho[i] != rgba_add_ssat(ha[i], k)) { ++fails; if (fails < 5) std::printf("binary_scalar mismatch at %zu\n", i); }
+            pint::cuda::scalar_binary(PINT_ADD_UNSIGNED_SATURATE, k, a, out, n, s);
+            CK(cudaStreamSynchronize(s));
+            CK(cudaMemcpy(ho.data(), out, n * 4, cudaMemcpyDeviceToHost));
+            for (size_t i = 0; i < n; ++i) if (ho[i] != rgba_add_usat(k, ha[i])) { ++fails; if (fails < 5) std::printf("scalar_binary mismatch at %zu\n", i); }
+            std::vector<std::pair<uint32_t, uint32_t> > hpairs(n);
+            for (size_t i = 0; i < n; ++i) hpairs[i] = std::make_pair(ha[i], hb[i]);
+            std::pair<uint32_t, uint32_t>* dpairs;
+            CK(cudaMalloc((void**)&dpairs, n * 8));
+            CK(cudaMemcpy(dpairs, hpairs.data(), n * 8, cudaMemcpyHostToDevice));
+            pint::cuda::binary_pairs(PINT_ADD_SIGNED_SATURATE, dpairs, out, n, s);
+            CK(cudaStreamSynchronize(s));
+            CK(cudaMemcpy(ho.data(), out, n * 4, cudaMemcpyDeviceToHost));
+            for (size_t i = 0; i < n; ++i) if (ho[i] != rgba_add_ssat(ha[i], hb[i])) { ++fails; if (fails < 5) std::printf("binary_pairs mismatch at %zu\n", i); }
+            CK(cudaFree(dpairs));
+        }
+
         // ---- dense bit streams: RGB24 = packed_int<uint32_t,8,8,8> at 3 bytes per element ----
         {
             typedef pint::packed_int<uint32_t, 8, 8, 8> rgb;

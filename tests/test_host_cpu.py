@@ -44,6 +44,21 @@ def test_no_cpu_fallback():
         ops.add_wrap(L, torch.zeros(4, dtype=torch.int16), torch.zeros(4, dtype=torch.int16))
 
 
+def test_callers_argument_checks_need_no_device():
+    """pint_cuda_binary_scalar / _pairs reject bad arguments before any CUDA call."""
+    lib = _lib.lib()
+    L = pint_b200.Layout.make(5, 6, 5)
+    a = np.zeros(64, dtype=np.uint16)
+    p = a.ctypes.data
+    assert lib.pint_cuda_binary_scalar(0, L.ref, p, 1 << 16, 0, p, 16, None) == -15
+    assert lib.pint_cuda_binary_scalar(99, L.ref, p, 1, 0, p, 16, None) == -10
+    assert lib.pint_cuda_binary_scalar(0, L.ref, p, 1, 0, p + 2, 16, None) == -14
+    assert lib.pint_cuda_binary_scalar(0, L.ref, p, 1, 1, None, 16, None) == -1
+    assert lib.pint_cuda_binary_pairs(0, L.ref, p, p + 16, 16, None) == -14
+    assert lib.pint_cuda_binary_pairs(13, L.ref, p, p + 64, 16, None) == -10
+    assert lib.pint_cuda_binary_pairs(0, L.ref, p, p + 64, 0, None) == 0
+
+
 def test_layout_validation_matches_oracle(oracle):
     rng = np.random.default_rng(7)
     lib = _lib.lib()

@@ -128,6 +128,32 @@ def main():
         pairs = alloc(L, n, 21)
         best, med = timed(lambda i: ops.pairs_reduce("add_signed_saturate", L, pairs))
         report("pairs_reduce (tests/pint_bench.cpp:90-94 shape)", n // 2, 8, best, med, op="add_signed_saturate", layout=repr(L))
+        out2 = out[: n // 2]
+        for op in ("add_unsigned_saturate", "add_signed_saturate"):
+            best, med = timed(lambda i: ops.binary_pairs(op, L, pairs, out=out2))
+            report("binary_pairs (interleaved operands -> results)", n // 2, 12, best, med, op=op, layout=repr(L))
+        for op in ("add_unsigned_saturate", "add_signed_saturate", "sub_signed_saturate"):
+            best, med = timed(lambda i: ops.binary_scalar(op, L, x, 0x10203040, out=out))
+            report("binary_scalar (one operand constant)", n, 8, best, med, op=op, layout=repr(L))
+        L3 = pint_b200.Layout(8, 3, 7, 11, 13, 17, 13)
+        x3 = alloc(L3, 1 << 29, 31)
+        o3 = torch.empty_like(x3)
+        for op in ("add_signed_saturate",):
+            best, med = timed(lambda i: ops.binary_scalar(op, L3, x3, 0x0123456789ABCDEF, out=o3))
+            report("binary_scalar (one operand constant)", 1 << 29, 16, best, med, op=op, layout=repr(L3))
+            best, med = timed(lambda i: ops.binary_pairs(op, L3, x3, out=o3[: 1 << 28]))
+            report("binary_pairs (interleaved operands -> results)", 1 << 28, 24, best, med, op=op, layout=repr(L3))
+        del x3, o3
+        # directional ceilings of this box, for reading the write-heavy rows (unpack: 75 % writes):
+        # write-only (the generator kernel and cudaMemset), read-only (checksum), copy
+        best, med = timed(lambda i: ops.fill_splitmix(x, 5))
+        report("ceiling: write-only (fill_splitmix kernel)", n, 4, best, med)
+        best, med = timed(lambda i: x.zero_())
+        report("ceiling: write-only (cudaMemsetAsync via torch zero_)", n, 4, best, med)
+        best, med = timed(lambda i: ops.checksum(x))
+        report("ceiling: read-only (checksum kernel, includes the result read-back)", n, 4, best, med)
+        best, med = timed(lambda i: out.copy_(x))
+        report("ceiling: copy (torch copy_, read + write)", n, 8, best, med)
 
 
 if __name__ == "__main__":
