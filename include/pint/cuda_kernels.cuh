@@ -278,3 +278,4 @@ __device__ __forceinline__ Word apply_unary(Word v, const unary_params<Word>& u)
 #include "cuda_kernels_stream.cuh"
 #include "cuda_kernels_multi.cuh"
 #include "cuda_kernels_planes.cuh"
+#include "cuda_kernels_callers.cuh"

@@ -13,6 +13,8 @@ using pint::cuda::layout_desc;
 
 using binary_launch_t = cudaError_t (*)(const void* a, const void* b, void* out, size_t n, cudaStream_t, const launch_geom&);
 using pair_launch_t = cudaError_t (*)(const void* a, const void* b, void* out0, void* out1, size_t n, cudaStream_t, const launch_geom&);
+using scalar_launch_t = cudaError_t (*)(const void* a, uint64_t scalar, void* out, size_t n, cudaStream_t, const launch_geom&);
+using pairs_launch_t = cudaError_t (*)(const void* pairs, void* out, size_t n, cudaStream_t, const launch_geom&);
 using unpack_launch_t = cudaError_t (*)(const void* packed, const plane_ptrs&, size_t n, cudaStream_t, const launch_geom&);
 using repack_launch_t = cudaError_t (*)(const plane_ptrs&, void* packed, size_t n, cudaStream_t, const launch_geom&);
 
@@ -21,6 +23,8 @@ struct layout_kernels {
     binary_launch_t binary[pint::cuda::OP_NUM_BINARY];
     binary_launch_t fused[pint::cuda::OP_NUM_BINARY];
     pair_launch_t pair[pint::cuda::kernels::kNumOpPairs];  // one-pass kernels for kOpPairs
+    scalar_launch_t scalar[2][pint::cuda::OP_NUM_BINARY];  // [scalar_first][op]: OP(a[i], k) / OP(k, a[i])
+    pairs_launch_t pairs[pint::cuda::OP_NUM_BINARY];       // interleaved operands -> results
     unpack_launch_t unpack[2][2];  // [is_signed][plane_bytes == 8]
     repack_launch_t repack[2];     // [plane_bytes == 8]
 };

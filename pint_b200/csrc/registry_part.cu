@@ -32,6 +32,27 @@ cudaError_t pair_entry(const void* a, const void* b, void* out0, void* out1, siz
     return launch_binary_pair<typename SL::integer, kOpPairs[Pair][0], kOpPairs[Pair][1]>(a, b, out0, out1, n, static_masks<SL>{}, s, g);
 }
 
+// The functor of the extra caller shapes: at 2W bytes per element the ALU side weighs 1.5 x as much,
+// so 64-bit layouts with several distinct widths take the per-field functor (C4: 7.0 against 6.6
+// TB/s as a binary op), everything else the SWAR one.
+template <class SL, int Op>
+using caller_fn = typename std::conditional<sizeof(typename static_masks<SL>::word) == 8 && swar_fn<Op, static_masks<SL>>::heavy,
+                                            fused_fn<Op, static_fields<SL>>, swar_fn<Op, static_masks<SL>>>::type;
+
+template <class SL, int Op, bool First>
+cudaError_t scalar_entry(const void* a, uint64_t scalar, void* out, size_t n, cudaStream_t s, const launch_geom& g)
+{
+    using E = typename SL::integer;
+    const scalar_fn<caller_fn<SL, Op>, First> fn{caller_fn<SL, Op>{}, replicate_scalar<E>(scalar)};
+    return launch_map1<E>(a, out, n, fn, s, g);
+}
+
+template <class SL, int Op>
+cudaError_t pairs_entry(const void* pairs, void* out, size_t n, cudaStream_t s, const launch_geom& g)
+{
+    return launch_pairs_map<typename SL::integer>(pairs, out, n, caller_fn<SL, Op>{}, s, g);
+}
+
 template <class SL, int... Pairs>
 void add_pairs(layout_kernels& k, std::integer_sequence<int, Pairs...>)
 {
@@ -58,6 +79,9 @@ layout_kernels make_kernels(std::integer_sequence<int, Ops...>)
     ((k.binary[Ops] = &binary_entry<SL, Ops>), ...);
     ((k.fused[Ops] = &fused_entry<SL, Ops>), ...);
     add_pairs<SL>(k, std::make_integer_sequence<int, kNumOpPairs>());
+    ((k.scalar[0][Ops] = &scalar_entry<SL, Ops, false>), ...);
+    ((k.scalar[1][Ops] = &scalar_entry<SL, Ops, true>), ...);
+    ((k.pairs[Ops] = &pairs_entry<SL, Ops>), ...);
     k.unpack[0][0] = &unpack_entry<SL, false, 4>;
     k.unpack[0][1] = &unpack_entry<SL, false, 8>;
     k.unpack[1][0] = &unpack_entry<SL, true, 4>;

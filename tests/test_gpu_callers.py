@@ -16,7 +16,7 @@ from gpu_util import to_dev, to_np  # noqa: E402
 
 DT = {1: np.uint8, 2: np.uint16, 4: np.uint32, 8: np.uint64}
 SPOT = [(4, (8, 8, 8, 8)), (2, (5, 6, 5)), (8, (3, 7, 11, 13, 17, 13)), (1, (2, 3, 3)), (4, (7, 9, 3)), (8, (64,)),
-        (2, (1, 1, 1, 1, 1)), (4, (1, 2, 3, 4, 5, 6, 11))]
+        (2, (1, 1, 1, 1, 1)), (4, (1, 2, 3, 4, 5, 6, 11)), (8, (16, 16, 16, 16)), (8, (8, 8, 8, 8, 8, 8, 8, 8))]
 
 
 @pytest.fixture(scope="module")
@@ -27,11 +27,21 @@ def P():
     return pint_b200, ops
 
 
+@pytest.fixture(params=["static_or_generic", "force_generic"])
+def mode(request, P):
+    """Registered layouts run functors with compiled-in masks; force_generic sends them through the
+    run-time-mask kernels every other layout uses."""
+    _, ops = P
+    ops.set_option("force_generic", 1 if request.param == "force_generic" else 0)
+    yield request.param
+    ops.set_option("force_generic", 0)
+
+
 def interleave(a, b):
     return np.stack([a, b], axis=1).reshape(-1)
 
 
-def test_golden_binary_pairs(P, refvec):
+def test_golden_binary_pairs(P, refvec, mode):
     """13 ops x 33 layouts on interleaved operands == the unmodified reference header's results."""
     pint_b200, ops = P
     for key, eb, bits in refvec.layouts():
@@ -42,7 +52,7 @@ def test_golden_binary_pairs(P, refvec):
                                           err_msg=f"pairs {L} {op}")
 
 
-def test_golden_binary_scalar(P, refvec, oracle, ref):
+def test_golden_binary_scalar(P, refvec, oracle, ref, mode):
     """OP(a[i], k) and OP(k, a[i]) for k taken from the reference vectors (structured edge values
     and random words, unused high bits set), 13 ops x 33 layouts."""
     pint_b200, ops = P
@@ -65,7 +75,7 @@ def test_golden_binary_scalar(P, refvec, oracle, ref):
 
 
 @pytest.mark.parametrize("eb,bits", SPOT)
-def test_pairs_large_and_alignments(P, oracle, eb, bits):
+def test_pairs_large_and_alignments(P, oracle, eb, bits, mode):
     """Whole tiles, partial tile, vector body with scalar head and tail, and operand addresses that
     force the element-granular kernel (pairs not reaching a 32-byte boundary where out reaches 16)."""
     pint_b200, ops = P
@@ -87,7 +97,7 @@ def test_pairs_large_and_alignments(P, oracle, eb, bits):
 
 
 @pytest.mark.parametrize("eb,bits", SPOT)
-def test_scalar_large_alignments_in_place(P, oracle, eb, bits):
+def test_scalar_large_alignments_in_place(P, oracle, eb, bits, mode):
     pint_b200, ops = P
     L = pint_b200.Layout(eb, *bits)
     n = (1 << 18) + 4 * 1024 + 5

@@ -144,10 +144,8 @@ def main():
             best, med = timed(lambda i: ops.binary_pairs(op, L3, x3, out=o3[: 1 << 28]))
             report("binary_pairs (interleaved operands -> results)", 1 << 28, 24, best, med, op=op, layout=repr(L3))
         del x3, o3
-        # directional ceilings of this box, for reading the write-heavy rows (unpack: 75 % writes):
-        # write-only (the generator kernel and cudaMemset), read-only (checksum), copy
-        best, med = timed(lambda i: ops.fill_splitmix(x, 5))
-        report("ceiling: write-only (fill_splitmix kernel)", n, 4, best, med)
+        # directional figures of this box, for reading the write-heavy rows (unpack: 75 % writes):
+        # write-only (cudaMemset: constant data, so an upper bound only), read-only (checksum), copy
         best, med = timed(lambda i: x.zero_())
         report("ceiling: write-only (cudaMemsetAsync via torch zero_)", n, 4, best, med)
         best, med = timed(lambda i: ops.checksum(x))
