@@ -159,3 +159,32 @@ def test_callers_error_codes(P):
     bad.bits[0], bad.bits[1] = 9, 8
     assert lib.pint_cuda_binary_pairs(0, C.byref(bad), p, p + 64, 16, None) == -5
     assert lib.pint_cuda_binary_scalar(0, C.byref(bad), p, 0, 0, p, 16, None) == -5
+
+
+def test_callers_in_cuda_graph(P, oracle):
+    """Both entry points are plain asynchronous launches on the caller's stream: capturable, replayable."""
+    pint_b200, ops = P
+    eb, bits = 2, (5, 6, 5)
+    L = pint_b200.Layout(eb, *bits)
+    n = (1 << 16) + 11
+    a_h, b_h = oracle.fill(eb, n, 41), oracle.fill(eb, n, 42)
+    pairs = to_dev(interleave(a_h, b_h))
+    t1 = torch.empty(n, dtype=pairs.dtype, device="cuda")
+    out = torch.empty_like(t1)
+    k = 0x1234
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(s):
+        ops.binary_pairs("add_wrap", L, pairs, out=t1)  # warm-up outside capture
+        torch.cuda.synchronize()
+        with torch.cuda.graph(g, stream=s):
+            ops.binary_pairs("add_signed_saturate", L, pairs, out=t1)
+            ops.binary_scalar("sub_unsigned_saturate", L, t1, k, out=out)
+    want = oracle.binary("sub_unsigned_saturate", eb, bits, oracle.binary("add_signed_saturate", eb, bits, a_h, b_h),
+                         np.full_like(a_h, k))
+    for _ in range(3):
+        out.zero_()
+        g.replay()
+        torch.cuda.synchronize()
+        np.testing.assert_array_equal(to_np(out), want)

@@ -43,6 +43,15 @@ def test_no_writes_outside_outputs(eb, bits):
                 ops.fused_unpack_arith_repack(op, L, a, b, out=out)
             ops.shift_left(L, a, 1, out=out)
             ops.slice(L, 0, 1, a, out=out)
+            # the extra caller shapes: constant operand (either side), interleaved operands
+            pairs = torch.empty(2 * n + 16, dtype=udt, device="cuda")[2 * off_elems:2 * off_elems + 2 * n]
+            ops.fill_splitmix(pairs, 4)
+            for force in (0, 1):
+                ops.set_option("force_generic", force)
+                ops.binary_scalar("add_signed_saturate", L, a, 0x5A, out=out)
+                ops.binary_scalar("sub_wrap", L, a, 0x33, out=out, scalar_first=True)
+                ops.binary_pairs("add_unsigned_saturate", L, pairs, out=out)
+            ops.set_option("force_generic", 0)
             ops.fill_splitmix(out, 9)
             pb = 8 if max(bits) > 32 else 4
             pg = [Guarded(n * pb, (off_elems % 2) * pb) for _ in bits]
