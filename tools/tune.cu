@@ -191,6 +191,67 @@ __global__ void compare(const uint4* x, const uint4* y, size_t nvec, unsigned lo
     }
 }
 
+// ---- mode 10: L2 prefetch-size / eviction hints on the 256-bit loads and stores of the op-pair kernel ----
+template <int H>
+__device__ __forceinline__ vec32 ld32_hint(const vec32* p)
+{
+    vec32 r;
+#define PINT_LD32(QUAL)                                                                                       \
+    asm volatile("ld.global" QUAL ".v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"                                  \
+                 : "=r"(r.lo.x), "=r"(r.lo.y), "=r"(r.lo.z), "=r"(r.lo.w), "=r"(r.hi.x), "=r"(r.hi.y), "=r"(r.hi.z), "=r"(r.hi.w) \
+                 : "l"(p))
+    if constexpr (H == 0) PINT_LD32(".cs");
+    else if constexpr (H == 1) PINT_LD32(".cs.L2::256B");
+    else if constexpr (H == 2) PINT_LD32(".L1::no_allocate.L2::evict_first.L2::256B");
+    else if constexpr (H == 3) PINT_LD32(".nc.L1::no_allocate.L2::256B");
+    else if constexpr (H == 4) PINT_LD32(".cs.L2::128B");
+    else PINT_LD32("");
+#undef PINT_LD32
+    return r;
+}
+
+template <int H>
+__device__ __forceinline__ void st32_hint(vec32* p, const vec32& v)
+{
+#define PINT_ST32(QUAL)                                                                                       \
+    asm volatile("st.global" QUAL ".v8.u32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"                                  \
+                 :: "l"(p), "r"(v.lo.x), "r"(v.lo.y), "r"(v.lo.z), "r"(v.lo.w), "r"(v.hi.x), "r"(v.hi.y), "r"(v.hi.z), "r"(v.hi.w) \
+                 : "memory")
+    if constexpr (H == 0) PINT_ST32(".cs");
+    else if constexpr (H == 1) PINT_ST32(".L1::no_allocate.L2::evict_first");
+    else if constexpr (H == 2) PINT_ST32(".wt");
+    else PINT_ST32("");
+#undef PINT_ST32
+}
+
+template <class Fn, int LH, int SH>
+__global__ void __launch_bounds__(256)
+pair256_hint_kernel(const vec32* a, const vec32* b, vec32* o0, vec32* o1, size_t nvec, const __grid_constant__ Fn fn)
+{
+    using W = typename Fn::word;
+    const size_t i = size_t(blockIdx.x) * 256 + threadIdx.x;
+    if (i >= nvec) return;
+    const vec32 x = ld32_hint<LH>(a + i), y = ld32_hint<LH>(b + i);
+    vec32 r0, r1;
+    auto f0 = [&](W p, W q) { return fn.first(p, q); };
+    auto f1 = [&](W p, W q) { return fn.second(p, q); };
+    r0.lo = map_words2<W>(x.lo, y.lo, f0); r0.hi = map_words2<W>(x.hi, y.hi, f0);
+    r1.lo = map_words2<W>(x.lo, y.lo, f1); r1.hi = map_words2<W>(x.hi, y.hi, f1);
+    st32_hint<SH>(o0 + i, r0);
+    st32_hint<SH>(o1 + i, r1);
+}
+
+template <class Fn, int LH, int SH>
+static void run_hint(const void* a, const void* b, void* o0, void* o1, size_t nvec16)
+{
+    const size_t nvec = nvec16 / 2;
+    char name[128];
+    std::snprintf(name, sizeof name, "usat+ssat rgba8 pair 256-bit, load hint %d, store hint %d", LH, SH);
+    time_it(name, double(nvec) * 128, [&] {
+        pair256_hint_kernel<Fn, LH, SH><<<unsigned((nvec + 255) / 256), 256>>>((const vec32*)a, (const vec32*)b, (vec32*)o0, (vec32*)o1, nvec, Fn{});
+    });
+}
+
 int main(int argc, char** argv)
 {
     const int log2n = argc > 1 ? std::atoi(argv[1]) : 30;
@@ -217,6 +278,24 @@ int main(int argc, char** argv)
     using FnIF = fused_fn<OP_ADD_SIGNED_SATURATE, static_fields<IRR>>;
     using FnX = swar_fn<OP_XOR, static_masks<RGBA>>;
 
+    if (argc > 3 && std::atoi(argv[3]) == 10) {
+        using Pu = pair_fn<OP_ADD_UNSIGNED_SATURATE, OP_ADD_SIGNED_SATURATE, static_masks<RGBA>>;
+        for (int rep = 0; rep < 3; ++rep) {
+            run256<Pu, 1, 256, true>("usat+ssat rgba8 pair (library kernel)", a, b, out, out2, nvec);
+            run_hint<Pu, 0, 0>(a, b, out, out2, nvec);
+            run_hint<Pu, 1, 0>(a, b, out, out2, nvec);
+            run_hint<Pu, 2, 0>(a, b, out, out2, nvec);
+            run_hint<Pu, 3, 0>(a, b, out, out2, nvec);
+            run_hint<Pu, 4, 0>(a, b, out, out2, nvec);
+            run_hint<Pu, 5, 0>(a, b, out, out2, nvec);
+            run_hint<Pu, 0, 1>(a, b, out, out2, nvec);
+            run_hint<Pu, 0, 2>(a, b, out, out2, nvec);
+            run_hint<Pu, 0, 3>(a, b, out, out2, nvec);
+            run_hint<Pu, 1, 1>(a, b, out, out2, nvec);
+        }
+        std::printf("done\n");
+        return 0;
+    }
     if (argc > 3 && std::atoi(argv[3]) == 9) {
         using Pu = pair_fn<OP_ADD_UNSIGNED_SATURATE, OP_ADD_SIGNED_SATURATE, static_masks<RGBA>>;
         for (int rep = 0; rep < 2; ++rep) {
