@@ -208,6 +208,16 @@ inline void binary_pairs(pint_op op, const std::pair<Integer, Integer>* pairs, p
     check(pint_cuda_binary_pairs(op, &l, pairs, out, n, stream), "pint::cuda::binary_pairs");
 }
 
+// packed_int::operator== over arrays (pint.hpp:778-779): equal_out[i] = (a[i] == b[i]) as bytes and / or
+// the number of unequal elements in *not_equal_count (device uint64_t); either may be null.
+template <class Integer, size_t Bits0, size_t... Bits>
+inline void equal(const packed_int<Integer, Bits0, Bits...>* a, const packed_int<Integer, Bits0, Bits...>* b, size_t n,
+                  uint8_t* equal_out, uint64_t* not_equal_count, stream_t stream = nullptr)
+{
+    const pint_layout l = detail::layout_of<Integer, Bits0, Bits...>::get();
+    check(pint_cuda_equal(&l, a, b, n, equal_out, not_equal_count, stream), "pint::cuda::equal");
+}
+
 // Any of the above, computed as unpack -> per-field arithmetic -> repack in one kernel.
 template <class Integer, size_t Bits0, size_t... Bits>
 inline void fused_unpack_arith_repack(pint_op op, const packed_int<Integer, Bits0, Bits...>* a,

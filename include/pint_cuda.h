@@ -203,6 +203,14 @@ int pint_cuda_pairs_reduce(int op, const pint_layout* layout, const void* pairs,
 int pint_cuda_binary_pairs(int op, const pint_layout* layout, const void* pairs, void* out, size_t n,
                            pint_stream_t stream);
 
+/* ---- packed_int::operator== / operator!= (pint.hpp:778-779) over arrays ---- */
+/* equal_out[i] = (a[i] == b[i]) ? 1 : 0 (device bytes; may be NULL) and *not_equal_count_dev
+ * (device uint64_t; may be NULL) = number of i with a[i] != b[i]; at least one of the two.  The
+ * whole Integer is compared, unused high bits included, as the reference does.
+ * 2 * sizeof(Integer) (+ 1) bytes per element. */
+int pint_cuda_equal(const pint_layout* layout, const void* a, const void* b, size_t n, uint8_t* equal_out,
+                    uint64_t* not_equal_count_dev, pint_stream_t stream);
+
 /* ---- one operand the same for every element (2 * sizeof(Integer) bytes per element) ---- */
 /* out[i] = OP(a[i], packed_int(scalar)), or OP(packed_int(scalar), a[i]) when scalar_first != 0
  * (the order matters for the sub_* ops and for the unused high bits of min / max, which come from

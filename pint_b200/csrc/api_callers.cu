@@ -50,6 +50,82 @@ cudaError_t pairs_map_ops(int op, const layout_desc& d, const void* pairs, void*
     return rc;
 }
 
+// packed_int::operator== / operator!= (pint.hpp:778-779) over arrays: the whole Integer is compared,
+// unused high bits included.  equal[i] = (a[i] == b[i]) as one byte per element (optional) and the
+// number of unequal elements (optional; integer atomics: exact and order-independent).
+// One 16-byte vector of each operand per step, U steps in flight; a thread writes its PER flag bytes
+// with one store, so a warp's flags are contiguous.
+template <class Elem, bool Flags, bool Count>
+__global__ void __launch_bounds__(256)
+equal_kernel(const Elem* a, const Elem* b, size_t n, uint8_t* equal, unsigned long long* not_equal, bool vec_ok)
+{
+    constexpr int PER = 16 / sizeof(Elem), U = 4;
+    using flags_t = typename std::conditional<PER == 16, uint4, typename std::conditional<PER == 8, uint2,
+                    typename std::conditional<PER == 4, uint32_t, uint16_t>::type>::type>::type;
+    unsigned long long bad = 0;
+    const size_t nvec = vec_ok ? n / PER : 0;
+    const uint4* va = reinterpret_cast<const uint4*>(a);
+    const uint4* vb = reinterpret_cast<const uint4*>(b);
+    auto one = [&](size_t v, const uint4& x, const uint4& y) {
+        union { uint4 q; Elem e[PER]; } ux, uy;
+        union { flags_t f; uint8_t c[PER]; } uf;
+        ux.q = x; uy.q = y;
+#pragma unroll
+        for (int j = 0; j < PER; ++j) {
+            const bool eq = ux.e[j] == uy.e[j];
+            uf.c[j] = eq ? 1 : 0;
+            if (Count) bad += eq ? 0 : 1;
+        }
+        if (Flags) reinterpret_cast<flags_t*>(equal)[v] = uf.f;
+    };
+    const size_t tile = size_t(U) * blockDim.x, nfull = nvec / tile;
+    for (size_t t = blockIdx.x; t < nfull; t += gridDim.x) {
+        uint4 x[U], y[U];
+        const size_t base = t * tile + threadIdx.x;
+#pragma unroll
+        for (int k = 0; k < U; ++k) x[k] = ld16<CACHE_STREAMING>(va + base + size_t(k) * blockDim.x);
+#pragma unroll
+        for (int k = 0; k < U; ++k) y[k] = ld16<CACHE_STREAMING>(vb + base + size_t(k) * blockDim.x);
+#pragma unroll
+        for (int k = 0; k < U; ++k) one(base + size_t(k) * blockDim.x, x[k], y[k]);
+    }
+    for (size_t v = nfull * tile + size_t(blockIdx.x) * blockDim.x + threadIdx.x; v < nvec; v += size_t(gridDim.x) * blockDim.x)
+        one(v, ld16<CACHE_STREAMING>(va + v), ld16<CACHE_STREAMING>(vb + v));
+    for (size_t i = nvec * PER + size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) {
+        const bool eq = a[i] == b[i];
+        if (Flags) equal[i] = eq ? 1 : 0;
+        if (Count) bad += eq ? 0 : 1;
+    }
+    if (Count) {
+        __shared__ unsigned long long part[8];
+        for (int o = 16; o; o >>= 1) bad += __shfl_down_sync(0xffffffffu, bad, o);
+        if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = bad;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            for (int w = 1; w < int(blockDim.x >> 5); ++w) bad += part[w];
+            if (bad) atomicAdd(not_equal, bad);
+        }
+    }
+}
+
+template <class Elem>
+cudaError_t equal_launch(const void* a, const void* b, size_t n, uint8_t* equal, uint64_t* count, cudaStream_t s, launch_geom g)
+{
+    constexpr size_t per = 16 / sizeof(Elem);
+    // vectors need a and b 16-byte aligned and the flag bytes aligned to their per-vector store
+    const bool vec_ok = (((uintptr_t)a | (uintptr_t)b) & 15u) == 0 && (!equal || ((uintptr_t)equal % per) == 0);
+    if (count) g.ctas_per_sm = 8;  // one atomic per CTA at the end: persistent grid
+    const unsigned grid = grid_for((n / per + 1023) / 1024 + 1, g);
+    const Elem* ea = static_cast<const Elem*>(a);
+    const Elem* eb = static_cast<const Elem*>(b);
+    unsigned long long* c = reinterpret_cast<unsigned long long*>(count);
+    if (equal && count) equal_kernel<Elem, true, true><<<grid, 256, 0, s>>>(ea, eb, n, equal, c, vec_ok);
+    else if (equal) equal_kernel<Elem, true, false><<<grid, 256, 0, s>>>(ea, eb, n, equal, c, vec_ok);
+    else equal_kernel<Elem, false, true><<<grid, 256, 0, s>>>(ea, eb, n, equal, c, vec_ok);
+    count_launch(g);
+    return cudaGetLastError();
+}
+
 }  // namespace
 }  // namespace pint_cuda_impl
 
@@ -106,6 +182,31 @@ int pint_cuda_binary_pairs(int op, const pint_layout* layout, const void* pairs,
     case 2: return (int)pairs_map_ops<uint16_t>(op, d, pairs, out, n, s, g, ops);
     case 4: return (int)pairs_map_ops<uint32_t>(op, d, pairs, out, n, s, g, ops);
     default: return (int)pairs_map_ops<uint64_t>(op, d, pairs, out, n, s, g, ops);
+    }
+}
+
+int pint_cuda_equal(const pint_layout* layout, const void* a, const void* b, size_t n, uint8_t* equal_out,
+                    uint64_t* not_equal_count_dev, pint_stream_t stream)
+{
+    layout_desc d;
+    if (int rc = check_layout(layout, &d)) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (not_equal_count_dev)
+        if (cudaError_t e = cudaMemsetAsync(not_equal_count_dev, 0, sizeof(uint64_t), s)) return (int)e;
+    if (n == 0) return PINT_OK;  // (an empty flag array may well be a null pointer)
+    if (!equal_out && !not_equal_count_dev) return PINT_E_NULL;
+    if (!a || !b) return PINT_E_NULL;
+    if (((uintptr_t)a | (uintptr_t)b) % d.elem_bytes) return PINT_E_ARG;
+    if (equal_out) {
+        const uintptr_t o = (uintptr_t)equal_out, bytes = n * d.elem_bytes;
+        if ((o < (uintptr_t)a + bytes && (uintptr_t)a < o + n) || (o < (uintptr_t)b + bytes && (uintptr_t)b < o + n)) return PINT_E_ALIAS;
+    }
+    const launch_geom g = geom();
+    switch (d.elem_bytes) {
+    case 1: return (int)equal_launch<uint8_t>(a, b, n, equal_out, not_equal_count_dev, s, g);
+    case 2: return (int)equal_launch<uint16_t>(a, b, n, equal_out, not_equal_count_dev, s, g);
+    case 4: return (int)equal_launch<uint32_t>(a, b, n, equal_out, not_equal_count_dev, s, g);
+    default: return (int)equal_launch<uint64_t>(a, b, n, equal_out, not_equal_count_dev, s, g);
     }
 }
 

@@ -228,6 +228,22 @@ def binary_scalar(op, layout, a, scalar, out=None, stream=None, scalar_first=Fal
     return out
 
 
+def equal(layout, a, b, flags=True, count=True, out=None, stream=None):
+    """packed_int::operator== over arrays: (flags, not_equal) with flags[i] = (a[i] == b[i]) as a uint8
+    tensor (None unless `flags`) and not_equal = number of differing elements (None unless `count`)."""
+    n = _check(layout, a, b)
+    f = None
+    if flags:
+        f = out if out is not None else torch.empty(n, dtype=torch.uint8, device=a.device)
+        if f.numel() != n or f.element_size() != 1 or not f.is_cuda or not f.is_contiguous():
+            raise ValueError("flags must be n contiguous bytes on the device")
+    c = torch.zeros(1, dtype=torch.int64, device=a.device) if count else None
+    with torch.cuda.device(a.device):
+        _lib.check(_lib.lib().pint_cuda_equal(layout.ref, a.data_ptr(), b.data_ptr(), n, f.data_ptr() if flags else None,
+                                              c.data_ptr() if count else None, _stream(stream)), "pint_cuda_equal")
+    return f, (int(c.item()) if count else None)
+
+
 def fill_splitmix(out, seed, start=0, stream=None):
     """out[i] = (Integer) splitmix64(seed + start + i): the synthetic input of SURVEY.md 8(d)."""
     if not out.is_cuda or not out.is_contiguous():

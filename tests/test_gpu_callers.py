@@ -188,3 +188,59 @@ def test_callers_in_cuda_graph(P, oracle):
         g.replay()
         torch.cuda.synchronize()
         np.testing.assert_array_equal(to_np(out), want)
+
+
+@pytest.mark.parametrize("eb", [1, 2, 4, 8])
+def test_equal_matches_operator_eq(P, oracle, eb):
+    """packed_int::operator== / != (pint.hpp:778-779) compare the whole Integer, unused high bits
+    included: flags and the not-equal count against numpy on arrays that differ in scattered places
+    (some only above sum(Bits)); vector and element-granular paths, flags / count / both."""
+    pint_b200, ops = P
+    bits = {1: (2, 3), 2: (5, 6, 4), 4: (8, 8, 8), 8: (3, 7, 11, 13, 17)}[eb]   # all leave unused high bits
+    L = pint_b200.Layout(eb, *bits)
+    rng = np.random.default_rng(eb)
+    for n in (0, 1, 5, 16, 17, 1023, 4096, (1 << 18) + 4 * 1024 + 3):
+        a_h = oracle.fill(eb, n + 24, 77)
+        b_h = a_h.copy()
+        if n:
+            idx = rng.choice(n + 24, size=max(1, (n + 24) // 7), replace=False)
+            b_h[idx] ^= (DT[eb](1) << DT[eb](8 * eb - 1 - (idx % 3)))   # top bits: outside every field
+            idx2 = rng.choice(n + 24, size=max(1, (n + 24) // 11), replace=False)
+            b_h[idx2] ^= DT[eb](1)
+        da, db = to_dev(a_h), to_dev(b_h)
+        for off in (0, 1, 16 // eb):
+            x_h, y_h = a_h[off:off + n], b_h[off:off + n]
+            want = (x_h == y_h).astype(np.uint8)
+            f, c = ops.equal(L, da[off:off + n], db[off:off + n])
+            np.testing.assert_array_equal(f.cpu().numpy(), want, err_msg=f"eb={eb} n={n} off={off}")
+            assert c == int((want == 0).sum())
+            f2, c2 = ops.equal(L, da[off:off + n], db[off:off + n], count=False)
+            assert c2 is None
+            np.testing.assert_array_equal(f2.cpu().numpy(), want)
+            f3, c3 = ops.equal(L, da[off:off + n], db[off:off + n], flags=False)
+            assert f3 is None and c3 == int((want == 0).sum())
+            # flags at an odd address: element-granular path
+            buf = torch.full((n + 5,), 7, dtype=torch.uint8, device="cuda")
+            ops.equal(L, da[off:off + n], db[off:off + n], out=buf[3:3 + n], count=False)
+            got = buf.cpu().numpy()
+            np.testing.assert_array_equal(got[3:3 + n], want)
+            assert (got[:3] == 7).all() and (got[3 + n:] == 7).all()
+        f, c = ops.equal(L, da[:n], da[:n])
+        assert c == 0 and bool((f == 1).all())
+
+
+def test_equal_error_codes(P):
+    pint_b200, ops = P
+    from pint_b200 import _lib
+    lib = _lib.lib()
+    L = pint_b200.Layout.make(5, 6, 5)
+    x = torch.zeros(64, dtype=torch.int16, device="cuda")
+    f = torch.zeros(64, dtype=torch.uint8, device="cuda")
+    c = torch.zeros(1, dtype=torch.int64, device="cuda")
+    p = x.data_ptr()
+    assert lib.pint_cuda_equal(L.ref, p, p, 16, None, None, None) == -1
+    assert lib.pint_cuda_equal(L.ref, None, p, 16, f.data_ptr(), None, None) == -1
+    assert lib.pint_cuda_equal(L.ref, p, p + 1, 16, f.data_ptr(), None, None) == -15
+    assert lib.pint_cuda_equal(L.ref, p, p, 16, p + 8, None, None) == -14
+    assert lib.pint_cuda_equal(L.ref, p, p, 0, None, c.data_ptr(), None) == 0
+    assert lib.pint_cuda_equal(L.ref, p, p, 16, f.data_ptr(), c.data_ptr(), None) == 0

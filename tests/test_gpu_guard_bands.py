@@ -52,6 +52,10 @@ def test_no_writes_outside_outputs(eb, bits):
                 ops.binary_scalar("sub_wrap", L, a, 0x33, out=out, scalar_first=True)
                 ops.binary_pairs("add_unsigned_saturate", L, pairs, out=out)
             ops.set_option("force_generic", 0)
+            fg = Guarded(n, off_elems)
+            ops.equal(L, a, b, out=fg.view(torch.uint8))
+            torch.cuda.synchronize()
+            assert fg.intact(), f"write outside the equality flags: {L} n={n} off={off_elems}"
             ops.fill_splitmix(out, 9)
             pb = 8 if max(bits) > 32 else 4
             pg = [Guarded(n * pb, (off_elems % 2) * pb) for _ in bits]

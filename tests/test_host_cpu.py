@@ -57,6 +57,7 @@ def test_callers_argument_checks_need_no_device():
     assert lib.pint_cuda_binary_pairs(0, L.ref, p, p + 16, 16, None) == -14
     assert lib.pint_cuda_binary_pairs(13, L.ref, p, p + 64, 16, None) == -10
     assert lib.pint_cuda_binary_pairs(0, L.ref, p, p + 64, 0, None) == 0
+    assert lib.pint_cuda_equal(L.ref, p, p, 16, None, None, None) == -1
 
 
 def test_layout_validation_matches_oracle(oracle):

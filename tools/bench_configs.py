@@ -135,6 +135,12 @@ def main():
         for op in ("add_unsigned_saturate", "add_signed_saturate", "sub_signed_saturate"):
             best, med = timed(lambda i: ops.binary_scalar(op, L, x, 0x10203040, out=out))
             report("binary_scalar (one operand constant)", n, 8, best, med, op=op, layout=repr(L))
+        best, med = timed(lambda i: ops.equal(L, x, out, flags=False))
+        report("equal: count of a[i] != b[i] (operator==, read-only, includes the count read-back)", n, 8, best, med, layout=repr(L))
+        flags = torch.empty(n, dtype=torch.uint8, device="cuda")
+        best, med = timed(lambda i: ops.equal(L, x, out, out=flags, count=False))
+        report("equal: one flag byte per element", n, 9, best, med, layout=repr(L))
+        del flags
         L3 = pint_b200.Layout(8, 3, 7, 11, 13, 17, 13)
         x3 = alloc(L3, 1 << 29, 31)
         o3 = torch.empty_like(x3)
