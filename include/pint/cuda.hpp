@@ -261,7 +261,7 @@ template <class Plane, class Integer, size_t Bits0, size_t... Bits>
 inline void unpack(const packed_int<Integer, Bits0, Bits...>* packed, Plane* const (&planes)[sizeof...(Bits) + 1],
                    size_t n, stream_t stream = nullptr)
 {
-    static_assert(std::is_integral<Plane>::value && (sizeof(Plane) == 4 || sizeof(Plane) == 8),
+    static_assert(std::is_integral<Plane>::value && (sizeof(Plane) == 1 || sizeof(Plane) == 2 || sizeof(Plane) == 4 || sizeof(Plane) == 8),
                   "planes are 32- or 64-bit integers");
     const pint_layout l = detail::layout_of<Integer, Bits0, Bits...>::get();
     void* p[sizeof...(Bits) + 1];
@@ -275,7 +275,7 @@ template <class Plane, class Integer, size_t Bits0, size_t... Bits>
 inline void repack(const Plane* const (&planes)[sizeof...(Bits) + 1], packed_int<Integer, Bits0, Bits...>* packed,
                    size_t n, stream_t stream = nullptr)
 {
-    static_assert(std::is_integral<Plane>::value && (sizeof(Plane) == 4 || sizeof(Plane) == 8),
+    static_assert(std::is_integral<Plane>::value && (sizeof(Plane) == 1 || sizeof(Plane) == 2 || sizeof(Plane) == 4 || sizeof(Plane) == 8),
                   "planes are 32- or 64-bit integers");
     const pint_layout l = detail::layout_of<Integer, Bits0, Bits...>::get();
     const void* p[sizeof...(Bits) + 1];

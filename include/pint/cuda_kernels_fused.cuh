@@ -160,9 +160,10 @@ cudaError_t launch_unpack(const void* packed, const plane_ptrs& planes, uint32_t
     if (n == 0) return cudaSuccess;
     const Elem* src = static_cast<const Elem*>(packed);
     constexpr size_t quad_align = sizeof(Elem) * 4 < 16 ? sizeof(Elem) * 4 : 16;
+    constexpr size_t plane_quad_align = PlaneBytes * 4 < 16 ? PlaneBytes * 4 : 16;  // one quad of a plane is one access
     bool ok = (reinterpret_cast<uintptr_t>(packed) % quad_align) == 0;
     for (uint32_t f = 0; f < nfields; ++f)
-        if (planes.p[f] && !aligned16(planes.p[f])) ok = false;
+        if (planes.p[f] && (reinterpret_cast<uintptr_t>(planes.p[f]) % plane_quad_align) != 0) ok = false;
     const size_t nquads = ok ? n / 4 : 0;
     if (nquads) {
         const unsigned grid = grid_for((nquads + 255) / 256, g);
@@ -185,9 +186,10 @@ cudaError_t launch_repack(const plane_ptrs& planes, uint32_t nfields, void* pack
     if (n == 0) return cudaSuccess;
     Elem* dst = static_cast<Elem*>(packed);
     constexpr size_t quad_align = sizeof(Elem) * 4 < 16 ? sizeof(Elem) * 4 : 16;
+    constexpr size_t plane_quad_align = PlaneBytes * 4 < 16 ? PlaneBytes * 4 : 16;  // one quad of a plane is one access
     bool ok = (reinterpret_cast<uintptr_t>(packed) % quad_align) == 0;
     for (uint32_t f = 0; f < nfields; ++f)
-        if (!aligned16(planes.p[f])) ok = false;
+        if ((reinterpret_cast<uintptr_t>(planes.p[f]) % plane_quad_align) != 0) ok = false;
     const size_t nquads = ok ? n / 4 : 0;
     if (nquads) {
         const unsigned grid = grid_for((nquads + 255) / 256, g);

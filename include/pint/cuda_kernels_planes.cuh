@@ -83,8 +83,8 @@ __device__ __forceinline__ typename std::make_signed<Word>::type field_get_signe
 
 // ---------------------------------------------------------------------------
 // Four consecutive elements per thread ("quad"): plane accesses are 16-byte
-// vectors (int32 planes) or 2 x 16 bytes (int64 planes); a warp covers 512
-// contiguous bytes of every plane.
+// vectors (int32 planes), 2 x 16 bytes (int64 planes) or one 8- / 4-byte word
+// (int16 / int8 planes); a warp covers 128 ... 1024 contiguous bytes of every plane.
 
 template <class Elem, class Word>
 __device__ __forceinline__ void load_quad(const Elem* p, Word (&e)[4])
@@ -132,7 +132,14 @@ template <int PlaneBytes, int St = CACHE_STREAMING>
 __device__ __forceinline__ void store_plane_quad(void* plane, size_t q, const uint64_t (&v)[4])
 {
     constexpr int CACHE_ST = St;
-    if constexpr (PlaneBytes == 4) {
+    if constexpr (PlaneBytes == 1) {
+        // narrow planes (the plane type is the Integer itself for 8 / 16-bit packs): one 4- or 8-byte store
+        __stcs(reinterpret_cast<uint32_t*>(plane) + q, (uint32_t(v[0]) & 0xFFu) | ((uint32_t(v[1]) & 0xFFu) << 8) |
+                                                          ((uint32_t(v[2]) & 0xFFu) << 16) | (uint32_t(v[3]) << 24));
+    } else if constexpr (PlaneBytes == 2) {
+        __stcs(reinterpret_cast<uint2*>(plane) + q, make_uint2((uint32_t(v[0]) & 0xFFFFu) | (uint32_t(v[1]) << 16),
+                                                               (uint32_t(v[2]) & 0xFFFFu) | (uint32_t(v[3]) << 16)));
+    } else if constexpr (PlaneBytes == 4) {
         st16<CACHE_ST>(reinterpret_cast<uint4*>(plane) + q,
                               make_uint4(uint32_t(v[0]), uint32_t(v[1]), uint32_t(v[2]), uint32_t(v[3])));
     } else {
@@ -145,7 +152,15 @@ __device__ __forceinline__ void store_plane_quad(void* plane, size_t q, const ui
 template <int PlaneBytes>
 __device__ __forceinline__ void load_plane_quad(const void* plane, size_t q, uint64_t (&v)[4])
 {
-    if constexpr (PlaneBytes == 4) {
+    if constexpr (PlaneBytes == 1) {
+        const uint32_t x = __ldcs(reinterpret_cast<const uint32_t*>(plane) + q);
+        v[0] = uint64_t(int64_t(int8_t(x))); v[1] = uint64_t(int64_t(int8_t(x >> 8)));
+        v[2] = uint64_t(int64_t(int8_t(x >> 16))); v[3] = uint64_t(int64_t(int8_t(x >> 24)));
+    } else if constexpr (PlaneBytes == 2) {
+        const uint2 x = __ldcs(reinterpret_cast<const uint2*>(plane) + q);
+        v[0] = uint64_t(int64_t(int16_t(x.x))); v[1] = uint64_t(int64_t(int16_t(x.x >> 16)));
+        v[2] = uint64_t(int64_t(int16_t(x.y))); v[3] = uint64_t(int64_t(int16_t(x.y >> 16)));
+    } else if constexpr (PlaneBytes == 4) {
         const uint4 x = ld16<CACHE_STREAMING>(reinterpret_cast<const uint4*>(plane) + q);
         // int32 plane values are converted to the Integer as the field
         // constructor's value_type parameters are (pint.hpp:771-772): sign-extend
@@ -206,7 +221,9 @@ unpack_elem_kernel(const Elem* packed, const __grid_constant__ plane_ptrs planes
             void* dst = planes.p[f];
             if (!dst) return;
             const uint64_t v = Signed ? uint64_t(int64_t(field_get_signed<W>(e, off, w))) : uint64_t(field_get<W>(e, off, w));
-            if constexpr (PlaneBytes == 4) static_cast<uint32_t*>(dst)[i] = uint32_t(v);
+            if constexpr (PlaneBytes == 1) static_cast<uint8_t*>(dst)[i] = uint8_t(v);
+            else if constexpr (PlaneBytes == 2) static_cast<uint16_t*>(dst)[i] = uint16_t(v);
+            else if constexpr (PlaneBytes == 4) static_cast<uint32_t*>(dst)[i] = uint32_t(v);
             else static_cast<uint64_t*>(dst)[i] = v;
         });
     }
@@ -245,7 +262,9 @@ repack_elem_kernel(const __grid_constant__ plane_ptrs planes, Elem* packed, size
         W e = 0;
         fp.each_elem_field([&](uint32_t f, uint32_t off, uint32_t w) {
             uint64_t v;
-            if constexpr (PlaneBytes == 4) v = uint64_t(int64_t(static_cast<const int32_t*>(planes.p[f])[i]));
+            if constexpr (PlaneBytes == 1) v = uint64_t(int64_t(static_cast<const int8_t*>(planes.p[f])[i]));
+            else if constexpr (PlaneBytes == 2) v = uint64_t(int64_t(static_cast<const int16_t*>(planes.p[f])[i]));
+            else if constexpr (PlaneBytes == 4) v = uint64_t(int64_t(static_cast<const int32_t*>(planes.p[f])[i]));
             else v = static_cast<const uint64_t*>(planes.p[f])[i];
             e |= (W(v) << (WB - w)) >> (WB - w - off);
         });

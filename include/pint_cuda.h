@@ -139,13 +139,18 @@ int pint_cuda_slice(const pint_layout* layout, uint32_t start, uint32_t end, con
 /* ---- packed <-> planes ---- */
 /* planes[f][i] = get<f>(packed[i]) (pint.hpp:799-807) or get_signed<f>
  * (pint.hpp:809-822) when is_signed.  `planes` is a HOST array of nfields
- * DEVICE pointers; a null entry skips that field.  plane_bytes is 4
+ * DEVICE pointers; a null entry skips that field.  plane_bytes is 1, 2, 4
  * (int32_t/uint32_t planes) or 8; the value is narrowed or widened to the
- * plane type as a C cast would. */
+ * plane type as a C cast would -- with plane_bytes == sizeof(Integer) the planes
+ * have exactly the reference's return types (Integer / make_signed<Integer>),
+ * and e.g. RGB565 unpacks to three uint8_t channels at 2 + 3 bytes per element. */
 int pint_cuda_unpack(const pint_layout* layout, int is_signed, const void* packed, void* const* planes,
                      int plane_bytes, size_t n, pint_stream_t stream);
 /* packed[i] = packed_int(planes[0][i], planes[1][i], ...) -- the truncating
- * field constructor = make_truncate (pint.hpp:770-774, 592-601, 390-407). */
+ * field constructor = make_truncate (pint.hpp:770-774, 592-601, 390-407).
+ * Planes of 1, 2 or 4 bytes are read as signed integers and converted to the
+ * Integer (as the constructor's value_type parameters are), then truncated to
+ * the field; 8-byte planes are taken as they are. */
 int pint_cuda_repack(const pint_layout* layout, const void* const* planes, int plane_bytes, void* packed,
                      size_t n, pint_stream_t stream);
 

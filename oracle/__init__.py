@@ -187,10 +187,8 @@ class Oracle:
     def unpack(self, elem_bytes, bits, x, signed, plane_bytes=4, fields=None):
         l = clayout(elem_bytes, bits)
         x = np.ascontiguousarray(x, dtype=_DT[elem_bytes])
-        if signed:
-            pdt = np.int32 if plane_bytes == 4 else np.int64
-        else:
-            pdt = np.uint32 if plane_bytes == 4 else np.uint64
+        pdt = {(1, True): np.int8, (2, True): np.int16, (4, True): np.int32, (8, True): np.int64,
+               (1, False): np.uint8, (2, False): np.uint16, (4, False): np.uint32, (8, False): np.uint64}[(plane_bytes, bool(signed))]
         planes = [np.empty(x.size, dtype=pdt) if (fields is None or f in fields) else None
                   for f in range(len(bits))]
         rc = self.lib.pint_oracle_unpack(C.byref(l), int(signed), _ptr(x), _plane_ptrs(planes), plane_bytes, x.size)
@@ -200,7 +198,7 @@ class Oracle:
 
     def repack(self, elem_bytes, bits, planes, plane_bytes=4):
         l = clayout(elem_bytes, bits)
-        pdt = np.int32 if plane_bytes == 4 else np.uint64
+        pdt = {1: np.int8, 2: np.int16, 4: np.int32, 8: np.uint64}[plane_bytes]
         planes = [np.ascontiguousarray(p).view(pdt) for p in planes]
         out = np.empty(planes[0].size, dtype=_DT[elem_bytes])
         rc = self.lib.pint_oracle_repack(C.byref(l), _plane_ptrs(planes), plane_bytes, _ptr(out), out.size)

@@ -467,14 +467,18 @@ int pint_oracle_unpack(const pint_oracle_layout* l, int is_signed,
     pint_oracle_masks m;
     int rc = pint_oracle_make_masks(l, &m);
     if (rc) return rc;
-    if (plane_bytes != 4 && plane_bytes != 8) return -13;
+    if (plane_bytes != 1 && plane_bytes != 2 && plane_bytes != 4 && plane_bytes != 8) return -13;
     if (n && (!packed || !planes)) return -11;
     for (uint32_t f = 0; f < l->nfields; ++f) {
         if (!planes[f]) continue;
         for (size_t i = 0; i < n; ++i) {
             uint64_t v = load_elem(packed, l->elem_bytes, i);
             uint64_t x = is_signed ? (uint64_t)get_signed1(l, &m, f, v) : get1(l, &m, f, v);
-            if (plane_bytes == 4) ((uint32_t*)planes[f])[i] = (uint32_t)x;
+            /* narrowed or widened to the plane type as a C cast does (get returns Integer,
+             * get_signed make_signed<Integer>: pint.hpp:800, 810-811) */
+            if (plane_bytes == 1) ((uint8_t*)planes[f])[i] = (uint8_t)x;
+            else if (plane_bytes == 2) ((uint16_t*)planes[f])[i] = (uint16_t)x;
+            else if (plane_bytes == 4) ((uint32_t*)planes[f])[i] = (uint32_t)x;
             else ((uint64_t*)planes[f])[i] = x;
         }
     }
@@ -487,7 +491,7 @@ int pint_oracle_repack(const pint_oracle_layout* l, const void* const* planes,
     pint_oracle_masks m;
     int rc = pint_oracle_make_masks(l, &m);
     if (rc) return rc;
-    if (plane_bytes != 4 && plane_bytes != 8) return -13;
+    if (plane_bytes != 1 && plane_bytes != 2 && plane_bytes != 4 && plane_bytes != 8) return -13;
     if (n && (!packed || !planes)) return -11;
     for (uint32_t f = 0; f < l->nfields; ++f)
         if (!planes[f]) return -11;
@@ -496,7 +500,9 @@ int pint_oracle_repack(const pint_oracle_layout* l, const void* const* planes,
         for (uint32_t f = 0; f < l->nfields; ++f) {
             /* plane values are signed integers converted to Integer (the field
              * constructor's parameters are value_type, pint.hpp:771-772) */
-            vals[f] = plane_bytes == 4 ? (uint64_t)(int64_t)((const int32_t*)planes[f])[i]
+            vals[f] = plane_bytes == 1 ? (uint64_t)(int64_t)((const int8_t*)planes[f])[i]
+                    : plane_bytes == 2 ? (uint64_t)(int64_t)((const int16_t*)planes[f])[i]
+                    : plane_bytes == 4 ? (uint64_t)(int64_t)((const int32_t*)planes[f])[i]
                                        : ((const uint64_t*)planes[f])[i];
         }
         store_elem(packed, l->elem_bytes, i, pint_oracle_make_truncate1(l, &m, vals));

@@ -367,7 +367,7 @@ int pint_cuda_unpack(const pint_layout* layout, int is_signed, const void* packe
 {
     layout_desc d;
     if (int rc = check_layout(layout, &d)) return rc;
-    if (plane_bytes != 4 && plane_bytes != 8) return PINT_E_PLANE_BYTES;
+    if (plane_bytes != 1 && plane_bytes != 2 && plane_bytes != 4 && plane_bytes != 8) return PINT_E_PLANE_BYTES;
     if (n == 0) return PINT_OK;
     if (!packed || !planes) return PINT_E_NULL;
     if ((uintptr_t)packed % d.elem_bytes) return PINT_E_ARG;
@@ -378,7 +378,7 @@ int pint_cuda_unpack(const pint_layout* layout, int is_signed, const void* packe
     }
     const launch_geom g = geom();
     if (const layout_kernels* k = find_static(d))
-        return (int)k->unpack[is_signed ? 1 : 0][plane_bytes == 8](packed, pp, n, (cudaStream_t)stream, g);
+        return (int)k->unpack[is_signed ? 1 : 0][plane_index(plane_bytes)](packed, pp, n, (cudaStream_t)stream, g);
     return (int)generic_unpack(d, is_signed != 0, plane_bytes, packed, pp, n, (cudaStream_t)stream, g);
 }
 
@@ -387,7 +387,7 @@ int pint_cuda_repack(const pint_layout* layout, const void* const* planes, int p
 {
     layout_desc d;
     if (int rc = check_layout(layout, &d)) return rc;
-    if (plane_bytes != 4 && plane_bytes != 8) return PINT_E_PLANE_BYTES;
+    if (plane_bytes != 1 && plane_bytes != 2 && plane_bytes != 4 && plane_bytes != 8) return PINT_E_PLANE_BYTES;
     if (n == 0) return PINT_OK;
     if (!packed || !planes) return PINT_E_NULL;
     if ((uintptr_t)packed % d.elem_bytes) return PINT_E_ARG;
@@ -399,7 +399,7 @@ int pint_cuda_repack(const pint_layout* layout, const void* const* planes, int p
     }
     const launch_geom g = geom();
     if (const layout_kernels* k = find_static(d))
-        return (int)k->repack[plane_bytes == 8](pp, packed, n, (cudaStream_t)stream, g);
+        return (int)k->repack[plane_index(plane_bytes)](pp, packed, n, (cudaStream_t)stream, g);
     return (int)generic_repack(d, plane_bytes, pp, packed, n, (cudaStream_t)stream, g);
 }
 

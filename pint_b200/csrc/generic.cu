@@ -51,11 +51,21 @@ cudaError_t unpack_elem(const layout_desc& d, bool is_signed, int pb, const void
 {
     using W = word_of<Elem>;
     runtime_fields<W> fp{make_field_table<W>(d), make_word_masks<W>(d).A};
-    if (is_signed)
-        return pb == 4 ? launch_unpack<Elem, 4, true>(packed, planes, d.nfields, n, fp, s, g)
-                       : launch_unpack<Elem, 8, true>(packed, planes, d.nfields, n, fp, s, g);
-    return pb == 4 ? launch_unpack<Elem, 4, false>(packed, planes, d.nfields, n, fp, s, g)
-                   : launch_unpack<Elem, 8, false>(packed, planes, d.nfields, n, fp, s, g);
+    // the value of get / get_signed is narrowed or widened to the plane type as a C cast would
+    if (is_signed) {
+        switch (pb) {
+        case 1: return launch_unpack<Elem, 1, true>(packed, planes, d.nfields, n, fp, s, g);
+        case 2: return launch_unpack<Elem, 2, true>(packed, planes, d.nfields, n, fp, s, g);
+        case 4: return launch_unpack<Elem, 4, true>(packed, planes, d.nfields, n, fp, s, g);
+        default: return launch_unpack<Elem, 8, true>(packed, planes, d.nfields, n, fp, s, g);
+        }
+    }
+    switch (pb) {
+    case 1: return launch_unpack<Elem, 1, false>(packed, planes, d.nfields, n, fp, s, g);
+    case 2: return launch_unpack<Elem, 2, false>(packed, planes, d.nfields, n, fp, s, g);
+    case 4: return launch_unpack<Elem, 4, false>(packed, planes, d.nfields, n, fp, s, g);
+    default: return launch_unpack<Elem, 8, false>(packed, planes, d.nfields, n, fp, s, g);
+    }
 }
 
 template <class Elem>
@@ -64,8 +74,12 @@ cudaError_t repack_elem(const layout_desc& d, int pb, const plane_ptrs& planes, 
 {
     using W = word_of<Elem>;
     runtime_fields<W> fp{make_field_table<W>(d), make_word_masks<W>(d).A};
-    return pb == 4 ? launch_repack<Elem, 4>(planes, d.nfields, packed, n, fp, s, g)
-                   : launch_repack<Elem, 8>(planes, d.nfields, packed, n, fp, s, g);
+    switch (pb) {
+    case 1: return launch_repack<Elem, 1>(planes, d.nfields, packed, n, fp, s, g);
+    case 2: return launch_repack<Elem, 2>(planes, d.nfields, packed, n, fp, s, g);
+    case 4: return launch_repack<Elem, 4>(planes, d.nfields, packed, n, fp, s, g);
+    default: return launch_repack<Elem, 8>(planes, d.nfields, packed, n, fp, s, g);
+    }
 }
 
 }  // namespace

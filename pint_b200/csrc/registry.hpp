@@ -25,9 +25,11 @@ struct layout_kernels {
     pair_launch_t pair[pint::cuda::kernels::kNumOpPairs];  // one-pass kernels for kOpPairs
     scalar_launch_t scalar[2][pint::cuda::OP_NUM_BINARY];  // [scalar_first][op]: OP(a[i], k) / OP(k, a[i])
     pairs_launch_t pairs[pint::cuda::OP_NUM_BINARY];       // interleaved operands -> results
-    unpack_launch_t unpack[2][2];  // [is_signed][plane_bytes == 8]
-    repack_launch_t repack[2];     // [plane_bytes == 8]
+    unpack_launch_t unpack[2][4];  // [is_signed][log2(plane_bytes)]
+    repack_launch_t repack[4];     // [log2(plane_bytes)]
 };
+
+inline int plane_index(int plane_bytes) { return plane_bytes == 1 ? 0 : plane_bytes == 2 ? 1 : plane_bytes == 4 ? 2 : 3; }
 
 inline bool same_layout(const layout_desc& a, const layout_desc& b)
 {

@@ -82,12 +82,18 @@ layout_kernels make_kernels(std::integer_sequence<int, Ops...>)
     ((k.scalar[0][Ops] = &scalar_entry<SL, Ops, false>), ...);
     ((k.scalar[1][Ops] = &scalar_entry<SL, Ops, true>), ...);
     ((k.pairs[Ops] = &pairs_entry<SL, Ops>), ...);
-    k.unpack[0][0] = &unpack_entry<SL, false, 4>;
-    k.unpack[0][1] = &unpack_entry<SL, false, 8>;
-    k.unpack[1][0] = &unpack_entry<SL, true, 4>;
-    k.unpack[1][1] = &unpack_entry<SL, true, 8>;
-    k.repack[0] = &repack_entry<SL, 4>;
-    k.repack[1] = &repack_entry<SL, 8>;
+    k.unpack[0][0] = &unpack_entry<SL, false, 1>;
+    k.unpack[0][1] = &unpack_entry<SL, false, 2>;
+    k.unpack[0][2] = &unpack_entry<SL, false, 4>;
+    k.unpack[0][3] = &unpack_entry<SL, false, 8>;
+    k.unpack[1][0] = &unpack_entry<SL, true, 1>;
+    k.unpack[1][1] = &unpack_entry<SL, true, 2>;
+    k.unpack[1][2] = &unpack_entry<SL, true, 4>;
+    k.unpack[1][3] = &unpack_entry<SL, true, 8>;
+    k.repack[0] = &repack_entry<SL, 1>;
+    k.repack[1] = &repack_entry<SL, 2>;
+    k.repack[2] = &repack_entry<SL, 4>;
+    k.repack[3] = &repack_entry<SL, 8>;
     return k;
 }
 

@@ -27,7 +27,8 @@ OPS = [
 OP_CODE = {name: i for i, name in enumerate(OPS)}
 
 _UDT = {1: torch.uint8, 2: torch.uint16, 4: torch.uint32, 8: torch.uint64}
-_PLANE_DT = {(4, True): torch.int32, (4, False): torch.uint32, (8, True): torch.int64, (8, False): torch.uint64}
+_PLANE_DT = {(1, True): torch.int8, (1, False): torch.uint8, (2, True): torch.int16, (2, False): torch.uint16,
+             (4, True): torch.int32, (4, False): torch.uint32, (8, True): torch.int64, (8, False): torch.uint64}
 
 
 def dtype_of(layout):
@@ -147,8 +148,8 @@ def unpack(layout, packed, signed=False, plane_bytes=4, fields=None, out=None, s
 
     Returns a list with one tensor per field (None for fields not in `fields`)."""
     n = _check(layout, packed)
-    if plane_bytes not in (4, 8):
-        raise ValueError("plane_bytes must be 4 or 8")
+    if plane_bytes not in (1, 2, 4, 8):
+        raise ValueError("plane_bytes must be 1, 2, 4 or 8")
     pdt = _PLANE_DT[(plane_bytes, bool(signed))]
     if out is None:
         out = [torch.empty(n, dtype=pdt, device=packed.device) if (fields is None or f in fields) else None

@@ -1,0 +1,107 @@
+"""GPU parity for 1- and 2-byte planes in unpack / repack (plane_bytes == sizeof(Integer) gives the
+reference's own return types for 8 / 16-bit packs: get -> Integer, get_signed -> make_signed<Integer>,
+pint.hpp:800, 810-811).  Against the compiled reference's 8-byte plane vectors narrowed by a C cast,
+and against the oracle; bit-exact."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from gpu_util import to_dev, to_np  # noqa: E402
+
+NDT = {(1, 0): np.uint8, (1, 1): np.int8, (2, 0): np.uint16, (2, 1): np.int16}
+
+
+@pytest.fixture(scope="module")
+def P():
+    import pint_b200
+    from pint_b200 import ops
+    assert torch.cuda.is_available()
+    return pint_b200, ops
+
+
+@pytest.fixture(params=["static_or_generic", "force_generic"])
+def mode(request, P):
+    _, ops = P
+    ops.set_option("force_generic", 1 if request.param == "force_generic" else 0)
+    yield request.param
+    ops.set_option("force_generic", 0)
+
+
+def test_golden_narrow_unpack(P, refvec, oracle, mode):
+    pint_b200, ops = P
+    for key, eb, bits in refvec.layouts():
+        L = pint_b200.Layout(eb, *bits)
+        a_h = refvec[key + "_a"]
+        a = to_dev(a_h)
+        for signed in (0, 1):
+            for pb in (1, 2):
+                planes = ops.unpack(L, a, signed=bool(signed), plane_bytes=pb)
+                want_o = oracle.unpack(eb, bits, a_h, bool(signed), pb)
+                for f in range(len(bits)):
+                    wide = refvec[f"{key}_unpack{'S' if signed else 'U'}8_{f}"]
+                    want = wide.astype(NDT[(pb, signed)])           # the reference's value through a C cast
+                    got = to_np(planes[f], NDT[(pb, signed)])
+                    np.testing.assert_array_equal(got, want, err_msg=f"{L} f{f} s{signed} pb{pb} {mode}")
+                    np.testing.assert_array_equal(want_o[f], want)
+
+
+def test_narrow_repack_and_round_trip(P, refvec, oracle, mode):
+    pint_b200, ops = P
+    rng = np.random.default_rng(5)
+    for key, eb, bits in refvec.layouts():
+        L = pint_b200.Layout(eb, *bits)
+        a_h = refvec[key + "_a"]
+        n = a_h.size
+        A = L.masks()["A"]
+        for pb in (1, 2):
+            sdt = NDT[(pb, 1)]
+            planes_h = [rng.integers(np.iinfo(sdt).min, np.iinfo(sdt).max, n, dtype=sdt, endpoint=True) for _ in bits]
+            got = to_np(ops.repack(L, [to_dev(p.view(NDT[(pb, 0)])).view({1: torch.int8, 2: torch.int16}[pb]) for p in planes_h]))
+            np.testing.assert_array_equal(got, oracle.repack(eb, bits, planes_h, pb), err_msg=f"{L} pb{pb} {mode}")
+            if max(bits) <= 8 * pb:
+                back = to_np(ops.repack(L, ops.unpack(L, to_dev(a_h), signed=True, plane_bytes=pb)))
+                np.testing.assert_array_equal(back, a_h & np.array(A).astype(back.dtype))
+
+
+@pytest.mark.parametrize("eb,bits", [(2, (5, 6, 5)), (1, (2, 3, 3)), (4, (8, 8, 8, 8)), (8, (16, 16, 16, 16)), (4, (7, 9, 3))])
+def test_narrow_planes_large_and_misaligned(P, oracle, eb, bits):
+    """Whole quads plus a tail; planes and packed array at element offsets (element-granular kernels);
+    a skipped field; sentinel bands around the planes."""
+    pint_b200, ops = P
+    L = pint_b200.Layout(eb, *bits)
+    n = (1 << 18) + 7
+    x_h = oracle.fill(eb, n + 8, 99)
+    x = to_dev(x_h)
+    for pb in (1, 2):
+        tdt = {1: torch.int8, 2: torch.int16}[pb]
+        for x_off, p_off in ((0, 0), (1, 0), (0, 1), (4, 4 if pb == 2 else 8)):
+            want = oracle.unpack(eb, bits, x_h[x_off:x_off + n], True, pb, fields=[0, len(bits) - 1])
+            bufs = [torch.full((n + 32,), 0x5B, dtype=tdt, device="cuda") for _ in bits]
+            out = [b[p_off:p_off + n] if f in (0, len(bits) - 1) else None for f, b in enumerate(bufs)]
+            ops.unpack(L, x[x_off:x_off + n], signed=True, plane_bytes=pb, out=out)
+            for f in (0, len(bits) - 1):
+                got = bufs[f].cpu().numpy()
+                np.testing.assert_array_equal(got[p_off:p_off + n], want[f], err_msg=f"{L} pb{pb} f{f} off {x_off},{p_off}")
+                assert (got[:p_off] == 0x5B).all() and (got[p_off + n:] == 0x5B).all()
+            # repack from (mis)aligned narrow planes
+            full = oracle.unpack(eb, bits, x_h[x_off:x_off + n], True, pb)
+            src = [torch.empty(n + 32, dtype=tdt, device="cuda") for _ in bits]
+            for f in range(len(bits)):
+                src[f][p_off:p_off + n].copy_(torch.from_numpy(full[f].copy()))
+            got = to_np(ops.repack(L, [s_[p_off:p_off + n] for s_ in src]))
+            np.testing.assert_array_equal(got, oracle.repack(eb, bits, full, pb))
+
+
+def test_plane_bytes_error_code(P):
+    import ctypes as C
+    pint_b200, ops = P
+    from pint_b200 import _lib
+    lib = _lib.lib()
+    L = pint_b200.Layout.make(5, 6, 5)
+    x = torch.zeros(16, dtype=torch.int16, device="cuda")
+    planes = (C.c_void_p * 3)(x.data_ptr(), x.data_ptr(), x.data_ptr())
+    for pb in (0, 3, 5, 16):
+        assert lib.pint_cuda_unpack(L.ref, 0, x.data_ptr(), planes, pb, 4, None) == -13
+        assert lib.pint_cuda_repack(L.ref, planes, pb, x.data_ptr(), 4, None) == -13

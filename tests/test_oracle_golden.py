@@ -153,3 +153,18 @@ def test_reference_unit_tests_pass_here():
     out = subprocess.run([REF_TEST_BIN], capture_output=True, text=True, timeout=60)
     assert out.returncode == 0
     assert "ran 61 tests, 0 failures" in out.stdout
+
+
+def test_oracle_narrow_planes_are_the_reference_values_cast(oracle, refvec):
+    """1- and 2-byte planes: get / get_signed narrowed to the plane type as a C cast does."""
+    for key, eb, bits in refvec.layouts():
+        a = refvec[key + "_a"]
+        for signed in (0, 1):
+            for pb, dts in ((1, (np.uint8, np.int8)), (2, (np.uint16, np.int16))):
+                got = oracle.unpack(eb, bits, a, bool(signed), pb)
+                for f in range(len(bits)):
+                    wide = refvec[f"{key}_unpack{'S' if signed else 'U'}8_{f}"]
+                    np.testing.assert_array_equal(got[f], wide.astype(dts[signed]))
+                if max(bits) <= 8 * pb and signed:
+                    A = oracle.masks(eb, bits)[1].A
+                    np.testing.assert_array_equal(oracle.repack(eb, bits, got, pb), a & np.array(A).astype(a.dtype))
