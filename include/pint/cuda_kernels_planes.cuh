@@ -250,6 +250,155 @@ repack_quad_kernel(const __grid_constant__ plane_ptrs planes, Elem* packed, size
     }
 }
 
+// ---------------------------------------------------------------------------
+// Narrow planes (1 or 2 bytes per value): a quad would be a 4- or 8-byte plane access and 20-32 bytes
+// of work per thread (issue-bound: RGB565 -> three uint8 planes ran at 4.9 TB/s).  Here a thread takes
+// G = 16 / PlaneBytes consecutive elements, so every plane access is a 16-byte vector and the packed
+// side one or more 256-bit accesses (32 bytes per lane: whole sectors at any lane stride).
+template <class Elem, int G>
+struct group_words {
+    static constexpr int BYTES = G * int(sizeof(Elem));
+    static constexpr int NW = BYTES / 4;  // 32-bit words per group (>= 2)
+};
+
+template <class Elem, int G>
+__device__ __forceinline__ void load_group_words(const Elem* p, uint32_t (&w)[group_words<Elem, G>::NW])
+{
+    constexpr int BYTES = group_words<Elem, G>::BYTES;
+    if constexpr (BYTES >= 32) {
+#pragma unroll
+        for (int k = 0; k < BYTES / 32; ++k) {
+            const vec32 x = ld32(reinterpret_cast<const vec32*>(p) + k);
+            w[8 * k + 0] = x.lo.x; w[8 * k + 1] = x.lo.y; w[8 * k + 2] = x.lo.z; w[8 * k + 3] = x.lo.w;
+            w[8 * k + 4] = x.hi.x; w[8 * k + 5] = x.hi.y; w[8 * k + 6] = x.hi.z; w[8 * k + 7] = x.hi.w;
+        }
+    } else if constexpr (BYTES == 16) {
+        const uint4 x = ld16<CACHE_STREAMING>(reinterpret_cast<const uint4*>(p));
+        w[0] = x.x; w[1] = x.y; w[2] = x.z; w[3] = x.w;
+    } else {
+        const uint2 x = __ldcs(reinterpret_cast<const uint2*>(p));
+        w[0] = x.x; w[1] = x.y;
+    }
+}
+
+template <class Elem, int G>
+__device__ __forceinline__ void store_group_words(Elem* p, const uint32_t (&w)[group_words<Elem, G>::NW])
+{
+    constexpr int BYTES = group_words<Elem, G>::BYTES;
+    if constexpr (BYTES >= 32) {
+#pragma unroll
+        for (int k = 0; k < BYTES / 32; ++k) {
+            vec32 x;
+            x.lo = make_uint4(w[8 * k + 0], w[8 * k + 1], w[8 * k + 2], w[8 * k + 3]);
+            x.hi = make_uint4(w[8 * k + 4], w[8 * k + 5], w[8 * k + 6], w[8 * k + 7]);
+            st32(reinterpret_cast<vec32*>(p) + k, x);
+        }
+    } else if constexpr (BYTES == 16) {
+        st16<CACHE_STREAMING>(reinterpret_cast<uint4*>(p), make_uint4(w[0], w[1], w[2], w[3]));
+    } else {
+        __stcs(reinterpret_cast<uint2*>(p), make_uint2(w[0], w[1]));
+    }
+}
+
+// element j of a group held as 32-bit words, zero-extended to the processing Word
+template <class Elem, class Word, int NW>
+__device__ __forceinline__ Word group_elem(const uint32_t (&w)[NW], int j)
+{
+    if constexpr (sizeof(Elem) == 8) return Word((uint64_t(w[2 * j + 1]) << 32) | w[2 * j]);
+    else if constexpr (sizeof(Elem) == 4) return Word(w[j]);
+    else if constexpr (sizeof(Elem) == 2) return Word((w[j >> 1] >> (16 * (j & 1))) & 0xFFFFu);
+    else return Word((w[j >> 2] >> (8 * (j & 3))) & 0xFFu);
+}
+
+template <class Elem, int PlaneBytes, bool Signed, class FP>
+__global__ void __launch_bounds__(256)
+unpack_group_kernel(const Elem* packed, const __grid_constant__ plane_ptrs planes, size_t ngroups,
+                    const __grid_constant__ FP fp)
+{
+    using W = typename FP::word;
+    constexpr int G = 16 / PlaneBytes, NW = group_words<Elem, G>::NW;
+    for (size_t g = size_t(blockIdx.x) * blockDim.x + threadIdx.x; g < ngroups; g += size_t(gridDim.x) * blockDim.x) {
+        uint32_t w[NW];
+        load_group_words<Elem, G>(packed + size_t(G) * g, w);
+        fp.each_elem_field([&](uint32_t i, uint32_t off, uint32_t wd) {
+            void* dst = planes.p[i];
+            if (!dst) return;
+            uint32_t o[4] = {0, 0, 0, 0};
+#pragma unroll
+            for (int j = 0; j < G; ++j) {
+                const W e = group_elem<Elem, W, NW>(w, j);
+                const uint32_t v = Signed ? uint32_t(field_get_signed<W>(e, off, wd)) : uint32_t(field_get<W>(e, off, wd));
+                if constexpr (PlaneBytes == 1) o[j >> 2] |= (v & 0xFFu) << (8 * (j & 3));
+                else o[j >> 1] |= (v & 0xFFFFu) << (16 * (j & 1));
+            }
+            st16<CACHE_STREAMING>(reinterpret_cast<uint4*>(dst) + g, make_uint4(o[0], o[1], o[2], o[3]));
+        });
+    }
+}
+
+// int32 planes, eight consecutive elements per thread: every plane store is one 256-bit vector
+// (a warp writes 1 KB of each plane per instruction), the packed side 256-bit loads.
+template <class Elem, bool Signed, class FP>
+__global__ void __launch_bounds__(256)
+unpack_oct_kernel(const Elem* packed, const __grid_constant__ plane_ptrs planes, size_t nocts, const __grid_constant__ FP fp)
+{
+    using W = typename FP::word;
+    constexpr int G = 8, NW = group_words<Elem, G>::NW;
+    for (size_t g = size_t(blockIdx.x) * blockDim.x + threadIdx.x; g < nocts; g += size_t(gridDim.x) * blockDim.x) {
+        uint32_t w[NW];
+        load_group_words<Elem, G>(packed + size_t(G) * g, w);
+        fp.each_elem_field([&](uint32_t i, uint32_t off, uint32_t wd) {
+            void* dst = planes.p[i];
+            if (!dst) return;
+            uint32_t v[G];
+#pragma unroll
+            for (int j = 0; j < G; ++j) {
+                const W e = group_elem<Elem, W, NW>(w, j);
+                v[j] = Signed ? uint32_t(field_get_signed<W>(e, off, wd)) : uint32_t(field_get<W>(e, off, wd));
+            }
+            vec32 r;
+            r.lo = make_uint4(v[0], v[1], v[2], v[3]);
+            r.hi = make_uint4(v[4], v[5], v[6], v[7]);
+            st32(reinterpret_cast<vec32*>(dst) + g, r);
+        });
+    }
+}
+
+template <class Elem, int PlaneBytes, class FP>
+__global__ void __launch_bounds__(256)
+repack_group_kernel(const __grid_constant__ plane_ptrs planes, Elem* packed, size_t ngroups, const __grid_constant__ FP fp)
+{
+    using W = typename FP::word;
+    constexpr uint32_t WB = 8 * sizeof(W);
+    constexpr int G = 16 / PlaneBytes, NW = group_words<Elem, G>::NW;
+    for (size_t g = size_t(blockIdx.x) * blockDim.x + threadIdx.x; g < ngroups; g += size_t(gridDim.x) * blockDim.x) {
+        W e[G];
+#pragma unroll
+        for (int j = 0; j < G; ++j) e[j] = 0;
+        fp.each_elem_field([&](uint32_t i, uint32_t off, uint32_t wd) {
+            const uint4 x = ld16<CACHE_STREAMING>(reinterpret_cast<const uint4*>(planes.p[i]) + g);
+            const uint32_t o[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+            for (int j = 0; j < G; ++j) {
+                // plane values are signed integers converted to the Integer (pint.hpp:771-772), then truncated
+                const int32_t v = PlaneBytes == 1 ? int32_t(int8_t(o[j >> 2] >> (8 * (j & 3)))) : int32_t(int16_t(o[j >> 1] >> (16 * (j & 1))));
+                e[j] |= (W(int64_t(v)) << (WB - wd)) >> (WB - wd - off);
+            }
+        });
+        uint32_t w[NW];
+#pragma unroll
+        for (int k = 0; k < NW; ++k) w[k] = 0;
+#pragma unroll
+        for (int j = 0; j < G; ++j) {
+            if constexpr (sizeof(Elem) == 8) { w[2 * j] = uint32_t(e[j]); w[2 * j + 1] = uint32_t(uint64_t(e[j]) >> 32); }
+            else if constexpr (sizeof(Elem) == 4) w[j] = uint32_t(e[j]);
+            else if constexpr (sizeof(Elem) == 2) w[j >> 1] |= (uint32_t(e[j]) & 0xFFFFu) << (16 * (j & 1));
+            else w[j >> 2] |= (uint32_t(e[j]) & 0xFFu) << (8 * (j & 3));
+        }
+        store_group_words<Elem, G>(packed + size_t(G) * g, w);
+    }
+}
+
 template <class Elem, int PlaneBytes, class FP>
 __global__ void __launch_bounds__(256)
 repack_elem_kernel(const __grid_constant__ plane_ptrs planes, Elem* packed, size_t first, size_t n,

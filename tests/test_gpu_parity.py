@@ -326,6 +326,17 @@ def test_vector_width_option_same_results(P, oracle, vec256):
                     np.testing.assert_array_equal(to_np(ops.fused_unpack_arith_repack(op, L, a, b)), want)
                 np.testing.assert_array_equal(to_np(ops.shift_left(L, a, 1)), oracle.shift(1, eb, bits, 1, a_h))
                 np.testing.assert_array_equal(to_np(ops.slice(L, 1, len(bits), a)[0]), oracle.slice(eb, bits, 1, len(bits), a_h))
+                # int32 planes: eight elements per thread with 256-bit plane stores (vec256 >= 1, planes on
+                # 32-byte boundaries) or four with 16-byte stores (vec256 = 0, or planes only 16-byte aligned)
+                for signed in (False, True):
+                    want_planes = oracle.unpack(eb, bits, a_h, signed, 4)
+                    for p_off in (0, 4):
+                        bufs = [torch.zeros(n + 8, dtype=torch.int32 if signed else torch.uint32, device="cuda") for _ in bits]
+                        ops.unpack(L, a, signed=signed, out=[b_[p_off:p_off + n] for b_ in bufs])
+                        for f in range(len(bits)):
+                            np.testing.assert_array_equal(to_np(bufs[f][p_off:p_off + n], want_planes[f].dtype), want_planes[f],
+                                                          err_msg=f"unpack {L} f{f} off{off} p_off{p_off} vec256={vec256}")
+                            assert int(bufs[f][p_off + n:].view(torch.int32).abs().sum()) == 0
                 pair = ["add_unsigned_saturate", "add_signed_saturate"]
                 outs = [to_dev(np.zeros(n, dtype=a_h.dtype), off) for _ in pair]
                 ops.binary_multi(pair, L, a, b, outs=outs)

@@ -150,6 +150,20 @@ def main():
             best, med = timed(lambda i: ops.binary_pairs(op, L3, x3, out=o3[: 1 << 28]))
             report("binary_pairs (interleaved operands -> results)", 1 << 28, 24, best, med, op=op, layout=repr(L3))
         del x3, o3
+        # narrow planes: RGB565 <-> three uint8 channels (2 + 3 bytes per element instead of 2 + 12),
+        # RGBA8 <-> four uint8 channels (4 + 4 instead of 4 + 16)
+        for LL, nn in ((pint_b200.Layout(2, 5, 6, 5), 1 << 30), (L, 1 << 30)):
+            xx = alloc(LL, nn, 41)
+            for pb in (1, 4):
+                pl = [torch.empty(nn, dtype={1: torch.uint8, 4: torch.uint32}[pb], device="cuda") for _ in LL.bits]
+                best, med = timed(lambda i: ops.unpack(LL, xx, signed=False, plane_bytes=pb, out=pl))
+                report("unpack to %d-byte planes" % pb, nn, LL.elem_bytes + pb * LL.nfields, best, med, layout=repr(LL))
+                back = torch.empty_like(xx)
+                spl = [p.view({1: torch.int8, 4: torch.int32}[pb]) for p in pl]
+                best, med = timed(lambda i: ops.repack(LL, spl, out=back))
+                report("repack from %d-byte planes" % pb, nn, LL.elem_bytes + pb * LL.nfields, best, med, layout=repr(LL))
+                del pl, spl, back
+            del xx
         # directional figures of this box, for reading the write-heavy rows (unpack: 75 % writes):
         # write-only (cudaMemset: constant data, so an upper bound only), read-only (checksum), copy
         best, med = timed(lambda i: x.zero_())

@@ -10,7 +10,7 @@ tail -15 $out/${tag}_pytest_callers.log
 timeout 1500 python -m pytest tests -m gpu -x -q > $out/${tag}_pytest_gpu.log 2>&1; echo "pytest rc=$?" >> $out/${tag}_pytest_gpu.log
 tail -3 $out/${tag}_pytest_gpu.log
 timeout 600 python tools/bench_configs.py > $out/${tag}_configs.jsonl 2> $out/${tag}_configs.err; echo "configs rc=$?"
-grep -E "binary_pairs|binary_scalar|ceiling|equal" $out/${tag}_configs.jsonl | cut -c1-330
+grep -E "binary_pairs|binary_scalar|ceiling|equal|byte planes" $out/${tag}_configs.jsonl | cut -c1-330
 tail -3 $out/${tag}_configs.err
 PK="python tools/profile_callers.py 28"
 timeout 300 $PK > $out/${tag}_profile_callers.log 2>&1 && \
