@@ -188,7 +188,10 @@ cudaError_t launch_unpack(const void* packed, const plane_ptrs& planes, uint32_t
             if (planes.p[f] && (reinterpret_cast<uintptr_t>(planes.p[f]) & 31u)) ook = false;
         const size_t nocts = ook ? n / 8 : 0;
         if (nocts) {
-            unpack_oct_kernel<Elem, Signed, FP><<<grid_for((nocts + 255) / 256, g), 256, 0, stream>>>(src, planes, nocts, fp);
+            if (g.vec256 == 2)
+                unpack_oct_kernel<Elem, Signed, FP, 2><<<grid_for((nocts + 511) / 512, g), 256, 0, stream>>>(src, planes, nocts, fp);
+            else
+                unpack_oct_kernel<Elem, Signed, FP><<<grid_for((nocts + 255) / 256, g), 256, 0, stream>>>(src, planes, nocts, fp);
             count_launch(g);
             done = nocts * 8;
         }

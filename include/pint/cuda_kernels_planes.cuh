@@ -338,28 +338,38 @@ unpack_group_kernel(const Elem* packed, const __grid_constant__ plane_ptrs plane
 
 // int32 planes, eight consecutive elements per thread: every plane store is one 256-bit vector
 // (a warp writes 1 KB of each plane per instruction), the packed side 256-bit loads.
-template <class Elem, bool Signed, class FP>
+template <class Elem, bool Signed, class FP, int K = 1>
 __global__ void __launch_bounds__(256)
 unpack_oct_kernel(const Elem* packed, const __grid_constant__ plane_ptrs planes, size_t nocts, const __grid_constant__ FP fp)
 {
     using W = typename FP::word;
     constexpr int G = 8, NW = group_words<Elem, G>::NW;
-    for (size_t g = size_t(blockIdx.x) * blockDim.x + threadIdx.x; g < nocts; g += size_t(gridDim.x) * blockDim.x) {
-        uint32_t w[NW];
-        load_group_words<Elem, G>(packed + size_t(G) * g, w);
+    // K octs per thread, a block apart (every access of a warp stays contiguous), all loads first
+    for (size_t t = blockIdx.x; t * (size_t(K) * blockDim.x) < nocts; t += gridDim.x) {
+        uint32_t w[K][NW];
+        size_t g[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            g[k] = (t * K + k) * blockDim.x + threadIdx.x;
+            if (g[k] < nocts) load_group_words<Elem, G>(packed + size_t(G) * g[k], w[k]);
+        }
         fp.each_elem_field([&](uint32_t i, uint32_t off, uint32_t wd) {
             void* dst = planes.p[i];
             if (!dst) return;
-            uint32_t v[G];
 #pragma unroll
-            for (int j = 0; j < G; ++j) {
-                const W e = group_elem<Elem, W, NW>(w, j);
-                v[j] = Signed ? uint32_t(field_get_signed<W>(e, off, wd)) : uint32_t(field_get<W>(e, off, wd));
+            for (int k = 0; k < K; ++k) {
+                if (g[k] >= nocts) continue;
+                uint32_t v[G];
+#pragma unroll
+                for (int j = 0; j < G; ++j) {
+                    const W e = group_elem<Elem, W, NW>(w[k], j);
+                    v[j] = Signed ? uint32_t(field_get_signed<W>(e, off, wd)) : uint32_t(field_get<W>(e, off, wd));
+                }
+                vec32 r;
+                r.lo = make_uint4(v[0], v[1], v[2], v[3]);
+                r.hi = make_uint4(v[4], v[5], v[6], v[7]);
+                st32(reinterpret_cast<vec32*>(dst) + g[k], r);
             }
-            vec32 r;
-            r.lo = make_uint4(v[0], v[1], v[2], v[3]);
-            r.hi = make_uint4(v[4], v[5], v[6], v[7]);
-            st32(reinterpret_cast<vec32*>(dst) + g, r);
         });
     }
 }

@@ -39,7 +39,7 @@ for eb, bits, log2 in ((8, (3, 7, 11, 13, 17, 13), 28), (4, (8, 8, 8, 8), 29), (
     planes = [torch.empty(n, dtype=torch.int32, device="cuda") for _ in bits]
     ref = None
     for rep in range(2):
-        for v in (0, 1):
+        for v in (0, 1, 2):
             ops.set_option("vec256", v)
             ms = timed(lambda: ops.unpack(L, x, signed=True, out=planes))
             cs = [ops.checksum(p) for p in planes]
