@@ -262,7 +262,7 @@ inline void unpack(const packed_int<Integer, Bits0, Bits...>* packed, Plane* con
                    size_t n, stream_t stream = nullptr)
 {
     static_assert(std::is_integral<Plane>::value && (sizeof(Plane) == 1 || sizeof(Plane) == 2 || sizeof(Plane) == 4 || sizeof(Plane) == 8),
-                  "planes are 32- or 64-bit integers");
+                  "planes are 8-, 16-, 32- or 64-bit integers");
     const pint_layout l = detail::layout_of<Integer, Bits0, Bits...>::get();
     void* p[sizeof...(Bits) + 1];
     for (size_t i = 0; i < sizeof...(Bits) + 1; ++i) p[i] = planes[i];
@@ -276,7 +276,7 @@ inline void repack(const Plane* const (&planes)[sizeof...(Bits) + 1], packed_int
                    size_t n, stream_t stream = nullptr)
 {
     static_assert(std::is_integral<Plane>::value && (sizeof(Plane) == 1 || sizeof(Plane) == 2 || sizeof(Plane) == 4 || sizeof(Plane) == 8),
-                  "planes are 32- or 64-bit integers");
+                  "planes are 8-, 16-, 32- or 64-bit integers");
     const pint_layout l = detail::layout_of<Integer, Bits0, Bits...>::get();
     const void* p[sizeof...(Bits) + 1];
     for (size_t i = 0; i < sizeof...(Bits) + 1; ++i) p[i] = planes[i];
@@ -385,8 +385,8 @@ template <class P, class Plane>
 inline void to_planes(const stream_byte* dense_in, Plane* const (&planes)[layout_from<P>::nfields], size_t n,
                       stream_t stream = nullptr)
 {
-    static_assert(std::is_integral<Plane>::value && (sizeof(Plane) == 4 || sizeof(Plane) == 8),
-                  "planes are 32- or 64-bit integers");
+    static_assert(std::is_integral<Plane>::value && (sizeof(Plane) == 1 || sizeof(Plane) == 2 || sizeof(Plane) == 4 || sizeof(Plane) == 8),
+                  "planes are 8-, 16-, 32- or 64-bit integers");
     const pint_layout l = layout_from<P>::get();
     void* p[layout_from<P>::nfields];
     for (size_t i = 0; i < layout_from<P>::nfields; ++i) p[i] = planes[i];
@@ -398,8 +398,8 @@ template <class P, class Plane>
 inline void from_planes(const Plane* const (&planes)[layout_from<P>::nfields], stream_byte* dense_out, size_t n,
                         stream_t stream = nullptr)
 {
-    static_assert(std::is_integral<Plane>::value && (sizeof(Plane) == 4 || sizeof(Plane) == 8),
-                  "planes are 32- or 64-bit integers");
+    static_assert(std::is_integral<Plane>::value && (sizeof(Plane) == 1 || sizeof(Plane) == 2 || sizeof(Plane) == 4 || sizeof(Plane) == 8),
+                  "planes are 8-, 16-, 32- or 64-bit integers");
     const pint_layout l = layout_from<P>::get();
     const void* p[layout_from<P>::nfields];
     for (size_t i = 0; i < layout_from<P>::nfields; ++i) p[i] = planes[i];

@@ -101,7 +101,8 @@ __global__ void dense_extract_kernel(const uint4* dense, Elem* padded, size_t n,
         if constexpr (Side == SIDE_PADDED) {
             padded[first + e] = Elem(x);
         } else {
-            using PT = typename std::conditional<PlaneBytes == 8, uint64_t, uint32_t>::type;
+            using PT = typename std::conditional<PlaneBytes == 8, uint64_t, typename std::conditional<PlaneBytes == 4, uint32_t,
+                       typename std::conditional<PlaneBytes == 2, uint16_t, uint8_t>::type>::type>::type;
             for (uint32_t i = 0; i < f.t.nfields; ++i) {
                 PT* plane = static_cast<PT*>(f.planes.p[i]);
                 if (plane) plane[first + e] = PT(field(x, i));
@@ -126,7 +127,8 @@ __global__ void dense_insert_kernel(const Elem* padded, uint4* dense, size_t n, 
                                     const __grid_constant__ dense_fields f)
 {
     constexpr uint32_t WB = 8 * sizeof(W);
-    using ST = typename std::conditional<PlaneBytes == 8, int64_t, int32_t>::type;
+    using ST = typename std::conditional<PlaneBytes == 8, int64_t, typename std::conditional<PlaneBytes == 4, int32_t,
+               typename std::conditional<PlaneBytes == 2, int16_t, int8_t>::type>::type>::type;
     // what is staged per element: the padded element, or the element assembled from its planes
     using Staged = typename std::conditional<Side == SIDE_PADDED, Elem, W>::type;
     extern __shared__ __align__(128) unsigned char dense_smem[];

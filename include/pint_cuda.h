@@ -75,7 +75,7 @@ enum pint_error {
     PINT_E_TOO_WIDE = -5,      /* sum(Bits) > 8 * sizeof(Integer) (pint.hpp:763-764) */
     PINT_E_OP = -10,           /* unknown operation code */
     PINT_E_INDEX = -12,        /* field index / slice bounds (pint.hpp:748, 802, 813) */
-    PINT_E_PLANE_BYTES = -13,  /* plane element size is not 4 or 8 */
+    PINT_E_PLANE_BYTES = -13,  /* plane element size is not 1, 2, 4 or 8 */
     PINT_E_ALIAS = -14,        /* partially overlapping in/out */
     PINT_E_ARG = -15           /* other invalid argument */
 };
@@ -181,7 +181,8 @@ int pint_cuda_dense_shift(int left, const pint_layout* layout, uint64_t amount, 
 int pint_cuda_dense_pack(const pint_layout* layout, const void* padded, void* dense, size_t n, pint_stream_t stream);
 int pint_cuda_dense_unpack(const pint_layout* layout, const void* dense, void* padded, size_t n, pint_stream_t stream);
 /* get / get_signed (pint.hpp:799-822) of every field straight from a dense stream, and the
- * truncating field constructor (pint.hpp:770-774) straight into one; planes as in pint_cuda_unpack. */
+ * truncating field constructor (pint.hpp:770-774) straight into one; planes as in pint_cuda_unpack
+ * (1, 2, 4 or 8 bytes: dense RGB24 <-> three uint8_t planes is interleaved <-> planar RGB). */
 int pint_cuda_dense_to_planes(const pint_layout* layout, int is_signed, const void* dense, void* const* planes,
                               int plane_bytes, size_t n, pint_stream_t stream);
 int pint_cuda_dense_from_planes(const pint_layout* layout, const void* const* planes, int plane_bytes, void* dense,

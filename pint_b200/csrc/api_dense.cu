@@ -158,14 +158,28 @@ cudaError_t planes_launch(bool to_dense, bool is_signed, int pb, const void* den
 {
     const launch_geom g = geom();
     void* dn = const_cast<void*>(dense);
-    if (to_dense)
-        return pb == 4 ? dense::launch_dense_insert<W, W, dense::SIDE_PLANES, 4>(nullptr, dn, n, S, f, s, g)
-                       : dense::launch_dense_insert<W, W, dense::SIDE_PLANES, 8>(nullptr, dn, n, S, f, s, g);
-    if (is_signed)
-        return pb == 4 ? dense::launch_dense_extract<W, W, dense::SIDE_PLANES, 4, true>(dense, nullptr, n, S, f, s, g)
-                       : dense::launch_dense_extract<W, W, dense::SIDE_PLANES, 8, true>(dense, nullptr, n, S, f, s, g);
-    return pb == 4 ? dense::launch_dense_extract<W, W, dense::SIDE_PLANES, 4, false>(dense, nullptr, n, S, f, s, g)
-                   : dense::launch_dense_extract<W, W, dense::SIDE_PLANES, 8, false>(dense, nullptr, n, S, f, s, g);
+    if (to_dense) {
+        switch (pb) {
+        case 1: return dense::launch_dense_insert<W, W, dense::SIDE_PLANES, 1>(nullptr, dn, n, S, f, s, g);
+        case 2: return dense::launch_dense_insert<W, W, dense::SIDE_PLANES, 2>(nullptr, dn, n, S, f, s, g);
+        case 4: return dense::launch_dense_insert<W, W, dense::SIDE_PLANES, 4>(nullptr, dn, n, S, f, s, g);
+        default: return dense::launch_dense_insert<W, W, dense::SIDE_PLANES, 8>(nullptr, dn, n, S, f, s, g);
+        }
+    }
+    if (is_signed) {
+        switch (pb) {
+        case 1: return dense::launch_dense_extract<W, W, dense::SIDE_PLANES, 1, true>(dense, nullptr, n, S, f, s, g);
+        case 2: return dense::launch_dense_extract<W, W, dense::SIDE_PLANES, 2, true>(dense, nullptr, n, S, f, s, g);
+        case 4: return dense::launch_dense_extract<W, W, dense::SIDE_PLANES, 4, true>(dense, nullptr, n, S, f, s, g);
+        default: return dense::launch_dense_extract<W, W, dense::SIDE_PLANES, 8, true>(dense, nullptr, n, S, f, s, g);
+        }
+    }
+    switch (pb) {
+    case 1: return dense::launch_dense_extract<W, W, dense::SIDE_PLANES, 1, false>(dense, nullptr, n, S, f, s, g);
+    case 2: return dense::launch_dense_extract<W, W, dense::SIDE_PLANES, 2, false>(dense, nullptr, n, S, f, s, g);
+    case 4: return dense::launch_dense_extract<W, W, dense::SIDE_PLANES, 4, false>(dense, nullptr, n, S, f, s, g);
+    default: return dense::launch_dense_extract<W, W, dense::SIDE_PLANES, 8, false>(dense, nullptr, n, S, f, s, g);
+    }
 }
 
 int planes_impl(bool to_dense, const pint_layout* layout, int is_signed, const void* dense, const void* const* planes,
@@ -173,7 +187,7 @@ int planes_impl(bool to_dense, const pint_layout* layout, int is_signed, const v
 {
     layout_desc d;
     if (int rc = check_layout(layout, &d)) return rc;
-    if (plane_bytes != 4 && plane_bytes != 8) return PINT_E_PLANE_BYTES;
+    if (plane_bytes != 1 && plane_bytes != 2 && plane_bytes != 4 && plane_bytes != 8) return PINT_E_PLANE_BYTES;
     if (n == 0) return PINT_OK;
     if (!dense || !planes) return PINT_E_NULL;
     if ((uintptr_t)dense % 16) return PINT_E_ARG;
@@ -184,7 +198,7 @@ int planes_impl(bool to_dense, const pint_layout* layout, int is_signed, const v
         f.planes.p[i] = const_cast<void*>(planes[i]);
     }
     const uint32_t S = total_bits(d);
-    if (to_dense) {
+    if (to_dense && plane_bytes >= 4) {  // (the compiled-in-S insert kernels take 4- and 8-byte planes)
         size_t done = 0;
         if (cudaError_t rc = insert_fixed(S, 0, plane_bytes, nullptr, const_cast<void*>(dense), n, f, s, &done)) return (int)rc;
         if (done == n) return PINT_OK;

@@ -105,3 +105,39 @@ def test_plane_bytes_error_code(P):
     for pb in (0, 3, 5, 16):
         assert lib.pint_cuda_unpack(L.ref, 0, x.data_ptr(), planes, pb, 4, None) == -13
         assert lib.pint_cuda_repack(L.ref, planes, pb, x.data_ptr(), 4, None) == -13
+
+
+@pytest.mark.parametrize("eb,bits", [(4, (8, 8, 8)), (4, (7, 9, 3)), (2, (4, 4, 4)), (8, (12, 12, 12)), (8, (16, 16, 16)),
+                                     (1, (2, 3, 2)), (8, (21, 21, 21))])
+def test_dense_narrow_planes(P, oracle, eb, bits):
+    """Dense streams <-> 1- and 2-byte planes (dense RGB24 <-> three uint8 channels is interleaved <->
+    planar RGB at 3 + 3 bytes per pixel): to_planes against get / get_signed of the elements narrowed by
+    a C cast, from_planes against pack(field constructor); aligned planes (quads) and planes at an
+    element offset (element-granular), whole tiles plus a remainder."""
+    pint_b200, ops = P
+    from pint_b200 import dense
+    L = pint_b200.Layout(eb, *bits)
+    rng = np.random.default_rng(17)
+    for n in (1, 127, 4097, (1 << 17) + 77):
+        x_h = oracle.fill(eb, n, 55)
+        d = torch.from_numpy(oracle.dense_pack(eb, bits, x_h).copy()).cuda()
+        for pb in (1, 2):
+            tdt = {(1, 0): torch.uint8, (1, 1): torch.int8, (2, 0): torch.uint16, (2, 1): torch.int16}
+            for signed in (0, 1):
+                want = oracle.unpack(eb, bits, x_h, bool(signed), pb)
+                for p_off in (0, 1):
+                    bufs = [torch.zeros(n + 16, dtype=tdt[(pb, signed)], device="cuda") for _ in bits]
+                    dense.to_planes(L, d, n, signed=bool(signed), plane_bytes=pb, out=[b[p_off:p_off + n] for b in bufs])
+                    for f in range(len(bits)):
+                        got = to_np(bufs[f], NDT[(pb, signed)])
+                        np.testing.assert_array_equal(got[p_off:p_off + n], want[f], err_msg=f"{L} n={n} pb={pb} s={signed} f={f} off={p_off}")
+                        assert not got[:p_off].any() and not got[p_off + n:].any()
+            sdt = NDT[(pb, 1)]
+            planes_h = [rng.integers(np.iinfo(sdt).min, np.iinfo(sdt).max, n, dtype=sdt, endpoint=True) for _ in bits]
+            want_d = oracle.dense_pack(eb, bits, oracle.repack(eb, bits, planes_h, pb))
+            for p_off in (0, 1):
+                src = [torch.zeros(n + 16, dtype=tdt[(pb, 1)], device="cuda") for _ in bits]
+                for f in range(len(bits)):
+                    src[f][p_off:p_off + n].copy_(torch.from_numpy(planes_h[f].copy()))
+                got_d = dense.from_planes(L, [s_[p_off:p_off + n] for s_ in src])
+                np.testing.assert_array_equal(got_d.cpu().numpy(), want_d, err_msg=f"from_planes {L} n={n} pb={pb} off={p_off}")

@@ -164,6 +164,22 @@ def main():
                 report("repack from %d-byte planes" % pb, nn, LL.elem_bytes + pb * LL.nfields, best, med, layout=repr(LL))
                 del pl, spl, back
             del xx
+        # dense RGB24 <-> three uint8 channels (interleaved <-> planar RGB, 3 + 3 bytes per pixel) against int32 planes
+        from pint_b200 import dense
+        L24 = pint_b200.Layout(4, 8, 8, 8)
+        n24 = 1 << 29
+        d24 = dense.pack(L24, alloc(L24, n24, 51))
+        for pb in (1, 4):
+            pl = [torch.empty(n24, dtype={1: torch.uint8, 4: torch.uint32}[pb], device="cuda") for _ in L24.bits]
+            best, med = timed(lambda i: dense.to_planes(L24, d24, n24, signed=False, plane_bytes=pb, out=pl))
+            report("dense RGB24 -> %d-byte planes" % pb, n24, 3 + 3 * pb, best, med, layout=repr(L24))
+            spl = [p.view({1: torch.int8, 4: torch.int32}[pb]) for p in pl]
+            back = torch.empty_like(d24)
+            best, med = timed(lambda i: dense.from_planes(L24, spl, out=back))
+            report("dense RGB24 <- %d-byte planes" % pb, n24, 3 + 3 * pb, best, med, layout=repr(L24))
+            assert torch.equal(back, d24)
+            del pl, spl, back
+        del d24
         # directional figures of this box, for reading the write-heavy rows (unpack: 75 % writes):
         # write-only (cudaMemset: constant data, so an upper bound only), read-only (checksum), copy
         best, med = timed(lambda i: x.zero_())
