@@ -25,4 +25,8 @@ PK="python tools/profile_kernels.py 26"
 timeout 300 $PK > $out/${tag}_profile_kernels.log 2>&1 && \
 timeout 1200 ncu --set full --clock-control none --import-source on -k regex:dense_binary -c 14 -o $out/${tag}_ncu_full_dense $PK > $out/${tag}_ncu_full_dense.log 2>&1
 echo "ncu dense rc=$?"
+PC="python tools/profile_callers.py 28"
+timeout 300 $PC > $out/${tag}_profile_callers.log 2>&1 && \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:"map1_stream|pairs_map_kernel" -c 6 -o $out/${tag}_ncu_full_callers $PC > $out/${tag}_ncu_full_callers.log 2>&1
+echo "ncu callers rc=$?"
 ls -la $out | tail -24
