@@ -149,3 +149,26 @@ def test_options_roundtrip():
     assert pint_b200.Layout(4, 8, 8, 8, 8).is_specialized()
     with pytest.raises(_lib.PintCudaError):
         ops.set_option("no_such_option", 1)
+
+
+def test_bench_reference_arm_line():
+    """`bench.py --impl reference` needs no GPU: one JSON line with the contract's keys; under torchrun
+    (RANK != 0) it prints nothing and exits 0."""
+    import json
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "2", "--warmup", "1", "--cpu-log2", "18"]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=120, check=True).stdout
+    lines = [l for l in out.splitlines() if l.startswith("{")]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["metric"] == "packed elements/sec" and d["unit"] == "elements/s"
+    assert d["value"] > 0 and d["higher_is_better"] is True and d["steps"] == 2 and d["vs_baseline"] is None
+    assert d["cpu_baseline"]["kind"] in ("reference", "port") and d["cpu_baseline"]["cores"] >= 1
+    assert d["e2e"] == {"value": d["value"], "unit": "elements/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert "workload" in d["config"] and "model" not in d["config"]
+    env = dict(os.environ, RANK="1", LOCAL_RANK="1", WORLD_SIZE="2")
+    r = subprocess.run(cmd + ["--gpus", "2"], capture_output=True, text=True, timeout=120, env=env)
+    assert r.returncode == 0 and not r.stdout.strip()
