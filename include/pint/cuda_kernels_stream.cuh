@@ -374,6 +374,17 @@ struct launch_geom {
     int vec256 = 1;               // 32-byte vectors: 0 never, 1 where measured faster (light functors), 2 wherever aligned
 };
 
+// The ordered persistent kernels take a counter slot chosen on the host at launch time: a graph
+// capture would bake the slot in and concurrent replays would share it (tiles split between the
+// replays, output left unwritten).  While the stream is capturing the plain one-CTA-per-tile kernels
+// run instead.
+inline bool stream_is_capturing(cudaStream_t s)
+{
+    cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(s, &st) != cudaSuccess) { cudaGetLastError(); return true; }
+    return st != cudaStreamCaptureStatusNone;
+}
+
 inline tile_counter* next_tile_counter(const launch_geom& g)
 {
     const unsigned slot = __atomic_fetch_add(g.counter_cursor, 1u, __ATOMIC_RELAXED) % kTileCounterSlots;
@@ -456,7 +467,8 @@ cudaError_t launch_binary(const void* a, const void* b, void* out, size_t n, con
         constexpr size_t tile = size_t(Cfg::UNROLL) * Cfg::BLOCK;
         const size_t ntiles = (nvec + tile - 1) / tile;
         const size_t ordered_grid = size_t(g.num_sms) * size_t(g.ordered_ctas_per_sm > 0 ? g.ordered_ctas_per_sm : 0);
-        if (!Fn::heavy && g.counters && g.ctas_per_sm == 0 && ordered_grid && ntiles > 2 * ordered_grid) {
+        if (!Fn::heavy && g.counters && g.ctas_per_sm == 0 && ordered_grid && ntiles > 2 * ordered_grid &&
+            !stream_is_capturing(stream)) {
             binary_stream_ordered_kernel<Fn, Cfg><<<unsigned(ordered_grid), Cfg::BLOCK, 0, stream>>>(
                 reinterpret_cast<const uint4*>(ea + head), reinterpret_cast<const uint4*>(eb + head),
                 reinterpret_cast<uint4*>(eo + head), nvec, next_tile_counter(g), fn);
@@ -509,7 +521,7 @@ cudaError_t launch_unary(const void* in, void* out, size_t n, const unary_params
         constexpr size_t tile = size_t(Cfg::UNROLL) * Cfg::BLOCK;
         const size_t ntiles = (nvec + tile - 1) / tile;
         const size_t ordered_grid = size_t(g.num_sms) * size_t(g.ordered_ctas_per_sm > 0 ? g.ordered_ctas_per_sm : 0);
-        if (g.counters && g.ctas_per_sm == 0 && ordered_grid && ntiles > 2 * ordered_grid) {
+        if (g.counters && g.ctas_per_sm == 0 && ordered_grid && ntiles > 2 * ordered_grid && !stream_is_capturing(stream)) {
             unary_stream_ordered_kernel<Word, Cfg><<<unsigned(ordered_grid), Cfg::BLOCK, 0, stream>>>(
                 reinterpret_cast<const uint4*>(ei + head), reinterpret_cast<uint4*>(eo + head), nvec,
                 next_tile_counter(g), u);

@@ -90,7 +90,7 @@ unsigned long long pint_cuda_launch_count(void);
  * "ctas_per_sm" (0 = one CTA per tile, the default; k > 0 = persistent grid of SMs * k CTAs),
  * "ordered_ctas_per_sm" (k > 0: bandwidth-bound ops on large arrays run a persistent grid of
  * SMs * k CTAs that draw tiles in address order; default 0 = always one CTA per tile),
- * "host_chunk_bytes" / "host_slots" (staging ring of the host-buffer path),
+ * "host_chunk_bytes" (4 KiB .. 1 GiB) / "host_slots" (1 .. 8) (staging ring of the host-buffer path),
  * "dense_threads" / "dense_tile_bytes" (CTA size and per-operand tile of the dense bit-stream
  * kernels; 0 = chosen from the layout), "vec256" (32-byte global accesses in the stream kernels:
  * 0 never, 1 = default, where measured faster, 2 wherever the operands are 32-byte congruent), "dense_windows" (1 = layouts without compiled-in dense
@@ -258,9 +258,26 @@ int pint_cuda_sharded_repack(const pint_layout* layout, int ngpu, const int* dev
                              const void* const* planes, int plane_bytes, void* const* packed,
                              const size_t* counts, const pint_stream_t* streams);
 
+/* An array that lives on ONE device, handed to / collected from the shards of
+ * pint_cuda_plan_shards(n, elem_bytes, ngpu): one cudaMemcpyPeerAsync per shard (NVLink when peer
+ * access is enabled, see below), shard k on streams[k] (NULL = default streams).  Asynchronous.
+ * shards[k] is a buffer of count[k] elements on devices[k]; a shard on the array's own device is
+ * copied like the others (or pass the sub-range of the array itself as that shard: a copy onto
+ * itself is skipped by the driver). */
+int pint_cuda_scatter_shards(const void* src, int src_device, uint32_t elem_bytes, size_t n, int ngpu,
+                             const int* devices, void* const* shards, const pint_stream_t* streams);
+int pint_cuda_gather_shards(void* dst, int dst_device, uint32_t elem_bytes, size_t n, int ngpu,
+                            const int* devices, const void* const* shards, const pint_stream_t* streams);
+/* cudaDeviceEnablePeerAccess between every pair of `devices` that can reach each other (already
+ * enabled is not an error).  Once per process; without it peer copies are staged by the driver. */
+int pint_cuda_enable_peer_access(int ngpu, const int* devices);
+
 /* ---- host-buffer entry points (the end-to-end path) ---- */
 /* Pinned host memory for the calls below (cudaHostAlloc / cudaFreeHost). */
 int pint_cuda_host_alloc(void** ptr, size_t bytes);
+#define PINT_HOST_PORTABLE 1u        /* cudaHostAllocPortable */
+#define PINT_HOST_WRITE_COMBINED 2u  /* cudaHostAllocWriteCombined: inputs the CPU only writes */
+int pint_cuda_host_alloc_flags(void** ptr, size_t bytes, unsigned flags);
 int pint_cuda_host_free(void* ptr);
 /* out_host[i] = OP(a_host[i], b_host[i]) with HOST arrays: chunks are copied to
  * the current device, processed and copied back on a ring of streams so that
@@ -276,6 +293,18 @@ int pint_cuda_binary_host(int op, const pint_layout* layout, const void* a_host,
 #define PINT_MAX_HOST_OPS 4
 int pint_cuda_binary_multi_host(int nops, const int* ops, const pint_layout* layout, const void* a_host,
                                 const void* b_host, void* const* outs_host, size_t n);
+/* The same over `ngpu` devices of this process: the HOST arrays (the reference's workload is a host
+ * vector, tests/pint_bench.cpp:22,75) are split into the contiguous shards of pint_cuda_plan_shards,
+ * shard k streams through devices[k]'s own staging ring, all rings are fed from the calling thread.
+ * Every device's link and copy engines work at once; no collective, no peer traffic.  Synchronous.
+ * Calls on different devices (this one or the two above) from different threads do not serialise:
+ * the staging ring and its lock are per device. */
+int pint_cuda_sharded_binary_multi_host(int nops, const int* ops, const pint_layout* layout, int ngpu,
+                                        const int* devices, const void* a_host, const void* b_host,
+                                        void* const* outs_host, size_t n);
+/* Frees the staging rings of every device (slots * (2 + nops) * host_chunk_bytes of device memory
+ * each, allocated on the first host-buffer call and otherwise kept for the life of the process). */
+int pint_cuda_host_release(void);
 
 #ifdef __cplusplus
 }

@@ -102,6 +102,8 @@ class Oracle:
         L.pint_oracle_fill.argtypes = [C.c_void_p, C.c_uint32, C.c_size_t, C.c_uint64, C.c_uint64]
         L.pint_oracle_checksum.argtypes = [C.c_void_p, C.c_uint32, C.c_size_t, C.c_void_p, C.c_void_p]
         L.pint_oracle_pairs_reduce.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+        L.pint_oracle_stream_checksum.argtypes = [C.c_int, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_size_t,
+                                                  C.c_void_p, C.c_void_p]
         L.pint_oracle_dense_bytes.restype = C.c_size_t
         L.pint_oracle_dense_bytes.argtypes = [C.c_uint32, C.c_size_t]
         L.pint_oracle_dense_pack.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
@@ -217,6 +219,30 @@ class Oracle:
         self.lib.pint_oracle_checksum(_ptr(x), x.dtype.itemsize, x.size, C.byref(s), C.byref(r))
         return s.value, r.value
 
+    def stream_checksum(self, op, elem_bytes, bits, seed_a, seed_b, start, n, nthreads=1):
+        """(sum, xor) of OP(a[i], b[i]) for i in [start, start + n) over the splitmix inputs, without the arrays."""
+        l = clayout(elem_bytes, bits)
+        code = OP_CODE[op] if isinstance(op, str) else op
+
+        def part(lo, cnt):
+            s, r = C.c_uint64(), C.c_uint64()
+            rc = self.lib.pint_oracle_stream_checksum(code, C.byref(l), seed_a, seed_b, start + lo, cnt, C.byref(s), C.byref(r))
+            if rc:
+                raise ValueError(f"pint_oracle_stream_checksum rc={rc}")
+            return s.value, r.value
+
+        if nthreads <= 1 or n < (1 << 16):
+            return part(0, n)
+        from concurrent.futures import ThreadPoolExecutor  # ctypes releases the GIL during the call
+        step = (n + nthreads - 1) // nthreads
+        with ThreadPoolExecutor(nthreads) as ex:
+            parts = list(ex.map(lambda lo: part(lo, min(step, n - lo)), range(0, n, step)))
+        s = x = 0
+        for ps, px in parts:
+            s = (s + ps) & 0xFFFFFFFFFFFFFFFF
+            x ^= px
+        return s, x
+
     def pairs_reduce(self, op, elem_bytes, bits, pairs):
         l = clayout(elem_bytes, bits)
         pairs = np.ascontiguousarray(pairs, dtype=_DT[elem_bytes])
@@ -280,6 +306,7 @@ class Ref:
         L.pint_ref_binary.argtypes = [C.c_int, u32, u32, vp, vp, vp, vp, sz, C.c_int]
         L.pint_ref_pairs_reduce.argtypes = [C.c_int, u32, u32, vp, vp, sz, vp]
         L.pint_ref_shift.argtypes = [C.c_int, u32, u32, vp, C.c_uint64, vp, vp, sz, C.c_int]
+        L.pint_ref_stream_checksum.argtypes = [C.c_int, u32, u32, vp, C.c_uint64, C.c_uint64, C.c_uint64, sz, C.c_int, vp]
         L.pint_ref_unpack.argtypes = [u32, u32, vp, C.c_int, vp, vp, C.c_int, sz]
         L.pint_ref_repack.argtypes = [u32, u32, vp, vp, C.c_int, vp, sz]
         L.pint_ref_slice.argtypes = [u32, u32, vp, u32, u32, vp, vp, sz]
@@ -324,6 +351,15 @@ class Ref:
         if rc:
             raise KeyError(f"pint_ref_binary rc={rc} for {(elem_bytes, bits)}")
         return out
+
+    def stream_checksum(self, op, elem_bytes, bits, seed_a, seed_b, start, n, nthreads=1):
+        """(sum, xor) of pint::OP(P(a[i]), P(b[i])).value() for i in [start, start + n) over the splitmix inputs."""
+        out = (C.c_uint64 * 2)()
+        rc = self.lib.pint_ref_stream_checksum(OP_CODE[op] if isinstance(op, str) else op, elem_bytes, len(bits),
+                                               self._bits(bits), seed_a, seed_b, start, n, nthreads, out)
+        if rc:
+            raise KeyError(f"pint_ref_stream_checksum rc={rc} for {(elem_bytes, bits)}")
+        return out[0], out[1]
 
     def pairs_reduce(self, op, elem_bytes, bits, pairs):
         pairs = np.ascontiguousarray(pairs, dtype=_DT[elem_bytes])

@@ -528,6 +528,28 @@ int pint_oracle_fill(void* out, uint32_t elem_bytes, size_t n, uint64_t seed, ui
     return 0;
 }
 
+/* (sum, xor) of OP(a[i], b[i]) over i in [start, start + n) for the synthetic inputs
+ * a[i] = (Integer) splitmix64(seed_a + start + i), b likewise: whole-array parity without
+ * materialising the arrays (what pint_cuda_checksum gives for the device output range). */
+int pint_oracle_stream_checksum(int op, const pint_oracle_layout* l, uint64_t seed_a, uint64_t seed_b,
+                                uint64_t start, size_t n, uint64_t* sum, uint64_t* xr)
+{
+    pint_oracle_masks m;
+    int rc = pint_oracle_make_masks(l, &m);
+    if (rc) return rc;
+    if (op < 0 || op >= PINT_O_NUM_BINARY) return -10;
+    uint64_t s = 0, r = 0;
+    for (size_t i = 0; i < n; ++i) {
+        const uint64_t a = pint_oracle_splitmix64(seed_a + start + (uint64_t)i) & m.word;
+        const uint64_t b = pint_oracle_splitmix64(seed_b + start + (uint64_t)i) & m.word;
+        const uint64_t v = binary1(op, &m, a, b);
+        s += v; r ^= v;
+    }
+    if (sum) *sum = s;
+    if (xr) *xr = r;
+    return 0;
+}
+
 int pint_oracle_checksum(const void* x, uint32_t elem_bytes, size_t n, uint64_t* sum, uint64_t* xr)
 {
     if (elem_bytes != 1 && elem_bytes != 2 && elem_bytes != 4 && elem_bytes != 8) return -2;

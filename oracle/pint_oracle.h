@@ -121,6 +121,9 @@ int pint_oracle_fill(void* out, uint32_t elem_bytes, size_t n, uint64_t seed, ui
 /* Checksum of an element array: sum and xor of the elements (zero-extended to
  * 64 bit), the same pair libpint_cuda's pint_cuda_checksum produces. */
 int pint_oracle_checksum(const void* x, uint32_t elem_bytes, size_t n, uint64_t* sum, uint64_t* xr);
+/* (sum, xor) of OP(a[i], b[i]), i in [start, start + n), a / b the splitmix inputs above */
+int pint_oracle_stream_checksum(int op, const pint_oracle_layout* l, uint64_t seed_a, uint64_t seed_b,
+                                uint64_t start, size_t n, uint64_t* sum, uint64_t* xr);
 
 /* AoS pair reduction of tests/pint_bench.cpp:90-94: sum += op(P(first), P(second)).value()
  * over (first, second) pairs of Integer, accumulated in the Integer's width. */

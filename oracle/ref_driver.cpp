@@ -42,6 +42,15 @@ void parallel_for(size_t n, int nthreads, F f)
     for (auto& t : th) t.join();
 }
 
+// the synthetic-input generator of SURVEY.md 8(d) (same function as pint_oracle_splitmix64 and the device fill)
+inline uint64_t splitmix64(uint64_t x)
+{
+    x += 0x9E3779B97F4A7C15ULL;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBULL;
+    return x ^ (x >> 31);
+}
+
 template <int Op, class P>
 inline P apply(P a, P b)
 {
@@ -114,6 +123,52 @@ struct Entry<pint::packed_int<I, B...>> {
         int hit = 0;
         ((op == Ops ? (*sum = pairs_loop<Ops>(pairs, n), hit = 1) : 0), ...);
         return hit ? 0 : -10;
+    }
+
+    // Whole-array parity without the arrays: the reference op over the synthetic inputs
+    // a[i] = (I) splitmix64(seed_a + start + i), b likewise, reduced to (sum, xor) of the results
+    // zero-extended to 64 bits -- what pint_cuda_checksum yields for the GPU's output range
+    // [start, start + n).  Used by bench.py's parity flag and tests/test_gpu_fullsize.py.
+    template <int Op>
+    static void stream_checksum_loop(uint64_t seed_a, uint64_t seed_b, uint64_t start, size_t n, int nt, uint64_t* out2)
+    {
+        const int slots = nt > 1 ? nt : 1;
+        std::vector<uint64_t> part(2 * size_t(slots), 0);
+        const size_t chunk = (n + slots - 1) / slots;
+        auto body = [&](int t) {
+            const size_t lo = size_t(t) * chunk, hi = lo + chunk < n ? lo + chunk : n;
+            uint64_t s = 0, x = 0;
+            for (size_t i = lo; i < hi; ++i) {
+                const I a = (I)splitmix64(seed_a + start + i), b = (I)splitmix64(seed_b + start + i);
+                const uint64_t v = apply<Op>(P(a), P(b)).value();
+                s += v;
+                x ^= v;
+            }
+            part[2 * t] = s;
+            part[2 * t + 1] = x;
+        };
+        if (slots == 1) body(0);
+        else {
+            std::vector<std::thread> th;
+            for (int t = 0; t < slots; ++t) th.emplace_back(body, t);
+            for (auto& t : th) t.join();
+        }
+        out2[0] = out2[1] = 0;
+        for (int t = 0; t < slots; ++t) { out2[0] += part[2 * t]; out2[1] ^= part[2 * t + 1]; }
+    }
+
+    template <int... Ops>
+    static int stream_checksum_dispatch(int op, uint64_t sa, uint64_t sb, uint64_t start, size_t n, int nt, uint64_t* out2,
+                                        std::integer_sequence<int, Ops...>)
+    {
+        int hit = 0;
+        ((op == Ops ? (stream_checksum_loop<Ops>(sa, sb, start, n, nt, out2), hit = 1) : 0), ...);
+        return hit ? 0 : -10;
+    }
+
+    static int stream_checksum(int op, uint64_t sa, uint64_t sb, uint64_t start, size_t n, int nt, uint64_t* out2)
+    {
+        return stream_checksum_dispatch(op, sa, sb, start, n, nt, out2, std::make_integer_sequence<int, OP_NUM>());
     }
 
     static int pairs_reduce(int op, const void* pairs, size_t n, uint64_t* sum)
@@ -215,6 +270,7 @@ struct VTable {
     bool (*match)(uint32_t, uint32_t, const uint8_t*);
     int (*binary)(int, const void*, const void*, void*, size_t, int);
     int (*pairs_reduce)(int, const void*, size_t, uint64_t*);
+    int (*stream_checksum)(int, uint64_t, uint64_t, uint64_t, size_t, int, uint64_t*);
     int (*shift)(int, uint64_t, const void*, void*, size_t, int);
     int (*unpack)(int, const void*, void* const*, int, size_t);
     int (*repack)(const void* const*, int, void*, size_t);
@@ -228,7 +284,7 @@ template <class I, size_t... B>
 VTable make_vtable()
 {
     using E = Entry<pint::packed_int<I, B...>>;
-    VTable v{&E::match, &E::binary, &E::pairs_reduce, &E::shift, &E::unpack, &E::repack, &E::slice,
+    VTable v{&E::match, &E::binary, &E::pairs_reduce, &E::stream_checksum, &E::shift, &E::unpack, &E::repack, &E::slice,
              &E::constants, (uint32_t)sizeof(I), (uint32_t)sizeof...(B), {uint8_t(B)...}};
     return v;
 }
@@ -299,6 +355,14 @@ int pint_ref_pairs_reduce(int op, uint32_t eb, uint32_t nf, const uint8_t* bits,
 {
     const VTable* v = find(eb, nf, bits);
     return v ? v->pairs_reduce(op, pairs, n, sum) : -1;
+}
+
+// out2[0] = sum, out2[1] = xor over i in [start, start + n) of OP(a[i], b[i]) with the synthetic inputs
+int pint_ref_stream_checksum(int op, uint32_t eb, uint32_t nf, const uint8_t* bits, uint64_t seed_a, uint64_t seed_b,
+                             uint64_t start, size_t n, int nthreads, uint64_t* out2)
+{
+    const VTable* v = find(eb, nf, bits);
+    return v ? v->stream_checksum(op, seed_a, seed_b, start, n, nthreads, out2) : -1;
 }
 
 int pint_ref_shift(int left, uint32_t eb, uint32_t nf, const uint8_t* bits, uint64_t amount,

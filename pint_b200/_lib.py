@@ -82,7 +82,13 @@ def lib():
             "pint_cuda_sharded_repack": (i, [LP, i, C.POINTER(i), C.POINTER(vp), i, C.POINTER(vp), C.POINTER(sz),
                                             C.POINTER(vp)]),
             "pint_cuda_host_alloc": (i, [C.POINTER(vp), sz]),
+            "pint_cuda_host_alloc_flags": (i, [C.POINTER(vp), sz, C.c_uint]),
             "pint_cuda_host_free": (i, [vp]),
+            "pint_cuda_host_release": (i, []),
+            "pint_cuda_sharded_binary_multi_host": (i, [i, C.POINTER(i), LP, i, C.POINTER(i), vp, vp, C.POINTER(vp), sz]),
+            "pint_cuda_scatter_shards": (i, [vp, i, u32, sz, i, C.POINTER(i), C.POINTER(vp), C.POINTER(vp)]),
+            "pint_cuda_gather_shards": (i, [vp, i, u32, sz, i, C.POINTER(i), C.POINTER(vp), C.POINTER(vp)]),
+            "pint_cuda_enable_peer_access": (i, [i, C.POINTER(i)]),
             "pint_cuda_binary_host": (i, [i, LP, vp, vp, vp, sz]),
             "pint_cuda_binary_multi_host": (i, [i, C.POINTER(i), LP, vp, vp, C.POINTER(vp), sz]),
         }

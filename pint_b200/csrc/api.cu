@@ -232,7 +232,7 @@ int pint_cuda_set_option(const char* key, long value)
     if (!std::strcmp(key, "force_generic")) { opts().force_generic = value != 0; return PINT_OK; }
     if (!std::strcmp(key, "ctas_per_sm")) { if (value < 0 || value > 64) return PINT_E_ARG; opts().ctas_per_sm = value; return PINT_OK; }
     if (!std::strcmp(key, "ordered_ctas_per_sm")) { if (value < 0 || value > 32) return PINT_E_ARG; opts().ordered_ctas_per_sm = value; return PINT_OK; }
-    if (!std::strcmp(key, "host_chunk_bytes")) { if (value < 4096) return PINT_E_ARG; opts().host_chunk_bytes = value; return PINT_OK; }
+    if (!std::strcmp(key, "host_chunk_bytes")) { if (value < 4096 || value > (1L << 30)) return PINT_E_ARG; opts().host_chunk_bytes = value; return PINT_OK; }
     if (!std::strcmp(key, "host_slots")) { if (value < 1 || value > 8) return PINT_E_ARG; opts().host_slots = value; return PINT_OK; }
     if (!std::strcmp(key, "vec256")) { if (value < 0 || value > 2) return PINT_E_ARG; opts().vec256 = value; return PINT_OK; }
     if (!std::strcmp(key, "dense_windows")) { opts().dense_windows = value != 0; return PINT_OK; }

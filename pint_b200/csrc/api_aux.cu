@@ -34,20 +34,23 @@ __global__ void __launch_bounds__(256) fill_kernel(Elem* out, size_t n, uint64_t
         out[i] = Elem(splitmix64(base + i));
 }
 
+// One atomic per CTA into result[0] (sum) and, only when WithXor, into result[1] (xor): a sum-only
+// caller (pairs_reduce: ONE device uint64_t, pint_cuda.h) never touches result[1].
+template <bool WithXor>
 __device__ __forceinline__ void block_reduce_sum_xor(uint64_t s, uint64_t x, uint64_t* result)
 {
     __shared__ uint64_t ss[8], sx[8];
     for (int o = 16; o; o >>= 1) {
         s += __shfl_down_sync(0xffffffffu, s, o);
-        x ^= __shfl_down_sync(0xffffffffu, x, o);
+        if constexpr (WithXor) x ^= __shfl_down_sync(0xffffffffu, x, o);
     }
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (lane == 0) { ss[warp] = s; sx[warp] = x; }
+    if (lane == 0) { ss[warp] = s; if constexpr (WithXor) sx[warp] = x; }
     __syncthreads();
     if (threadIdx.x == 0) {
-        for (int w = 1; w < (int)(blockDim.x >> 5); ++w) { s += ss[w]; x ^= sx[w]; }
+        for (int w = 1; w < (int)(blockDim.x >> 5); ++w) { s += ss[w]; if constexpr (WithXor) x ^= sx[w]; }
         atomicAdd(reinterpret_cast<unsigned long long*>(result), (unsigned long long)s);
-        if (result + 1) atomicXor(reinterpret_cast<unsigned long long*>(result + 1), (unsigned long long)x);
+        if constexpr (WithXor) atomicXor(reinterpret_cast<unsigned long long*>(result + 1), (unsigned long long)x);
     }
 }
 
@@ -62,7 +65,7 @@ __global__ void __launch_bounds__(256) checksum_kernel(const Elem* x, size_t n, 
         s += v;
         r ^= v;
     }
-    block_reduce_sum_xor(s, r, result);
+    block_reduce_sum_xor<true>(s, r, result);
 }
 
 template <class Elem>
@@ -76,7 +79,7 @@ __global__ void __launch_bounds__(256) checksum_vec_kernel(const uint4* x, size_
 #pragma unroll
         for (int j = 0; j < PER; ++j) { s += u.e[j]; r ^= u.e[j]; }
     }
-    block_reduce_sum_xor(s, r, result);
+    block_reduce_sum_xor<true>(s, r, result);
 }
 
 // tests/pint_bench.cpp:90-94: sum += op(P(pair.first), P(pair.second)).value()
@@ -125,7 +128,7 @@ pairs_reduce_kernel(const Elem* pairs, size_t n, uint64_t* sum, const __grid_con
         add_vec(ld16<CACHE_STREAMING>(vec + v));
     for (size_t i = nvec * PER + size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x)
         s += Elem(apply_op<Op>(W(pairs[2 * i]), W(pairs[2 * i + 1]), p));
-    block_reduce_sum_xor(s, 0, sum);
+    block_reduce_sum_xor<false>(s, 0, sum);
 }
 
 template <class Elem, int... Ops>
@@ -305,25 +308,95 @@ int pint_cuda_sharded_repack(const pint_layout* layout, int ngpu, const int* dev
 
 int pint_cuda_host_alloc(void** ptr, size_t bytes)
 {
+    return pint_cuda_host_alloc_flags(ptr, bytes, 0);
+}
+
+int pint_cuda_host_alloc_flags(void** ptr, size_t bytes, unsigned flags)
+{
     if (!ptr) return PINT_E_NULL;
-    return (int)cudaHostAlloc(ptr, bytes ? bytes : 1, cudaHostAllocDefault);
+    if (flags & ~(unsigned)(PINT_HOST_PORTABLE | PINT_HOST_WRITE_COMBINED)) return PINT_E_ARG;
+    unsigned f = cudaHostAllocDefault;
+    if (flags & PINT_HOST_PORTABLE) f |= cudaHostAllocPortable;
+    if (flags & PINT_HOST_WRITE_COMBINED) f |= cudaHostAllocWriteCombined;
+    return (int)cudaHostAlloc(ptr, bytes ? bytes : 1, f);
 }
 
 int pint_cuda_host_free(void* ptr) { return ptr ? (int)cudaFreeHost(ptr) : PINT_OK; }
 
+int pint_cuda_enable_peer_access(int ngpu, const int* devices)
+{
+    if (ngpu < 1 || !devices) return PINT_E_ARG;
+    int prev = 0;
+    if (cudaError_t e = cudaGetDevice(&prev)) return (int)e;
+    int rc = PINT_OK;
+    for (int i = 0; i < ngpu && rc == PINT_OK; ++i) {
+        if (cudaError_t e = cudaSetDevice(devices[i])) { rc = (int)e; break; }
+        for (int j = 0; j < ngpu; ++j) {
+            if (devices[j] == devices[i]) continue;
+            int can = 0;
+            if (cudaError_t e = cudaDeviceCanAccessPeer(&can, devices[i], devices[j])) { rc = (int)e; break; }
+            if (!can) continue;  // copies between the two are staged by the driver instead
+            const cudaError_t e = cudaDeviceEnablePeerAccess(devices[j], 0);
+            if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+            else if (e != cudaSuccess) { rc = (int)e; break; }
+        }
+    }
+    cudaSetDevice(prev);
+    return rc;
+}
+
+// One cudaMemcpyPeerAsync per shard; `to_shards` selects the direction.
+static int move_shards(bool to_shards, void* whole, int whole_device, uint32_t elem_bytes, size_t n, int ngpu,
+                       const int* devices, void* const* shards, const pint_stream_t* streams)
+{
+    if (ngpu < 1 || ngpu > 64 || !devices || !shards) return PINT_E_ARG;
+    size_t begin[64], count[64];
+    if (int rc = pint_cuda_plan_shards(n, elem_bytes, ngpu, begin, count)) return rc;
+    if (n == 0) return PINT_OK;
+    if (!whole) return PINT_E_NULL;
+    for (int k = 0; k < ngpu; ++k) {
+        if (!count[k]) continue;
+        if (!shards[k]) return PINT_E_NULL;
+        char* w = static_cast<char*>(whole) + begin[k] * elem_bytes;
+        const size_t bytes = count[k] * elem_bytes;
+        cudaStream_t s = streams ? (cudaStream_t)streams[k] : nullptr;
+        const cudaError_t e = to_shards ? cudaMemcpyPeerAsync(shards[k], devices[k], w, whole_device, bytes, s)
+                                        : cudaMemcpyPeerAsync(w, whole_device, shards[k], devices[k], bytes, s);
+        if (e != cudaSuccess) return (int)e;
+    }
+    return PINT_OK;
+}
+
+int pint_cuda_scatter_shards(const void* src, int src_device, uint32_t elem_bytes, size_t n, int ngpu, const int* devices,
+                             void* const* shards, const pint_stream_t* streams)
+{
+    return move_shards(true, const_cast<void*>(src), src_device, elem_bytes, n, ngpu, devices, shards, streams);
+}
+
+int pint_cuda_gather_shards(void* dst, int dst_device, uint32_t elem_bytes, size_t n, int ngpu, const int* devices,
+                            const void* const* shards, const pint_stream_t* streams)
+{
+    return move_shards(false, dst, dst_device, elem_bytes, n, ngpu, devices, const_cast<void* const*>(shards), streams);
+}
+
 }  // extern "C"
 
 // ---------------------------------------------------------------------------
-// Host-buffer path: a ring of `host_slots` slots, each with its own stream and
-// device staging for one chunk of a, b and out.  On a slot's stream the order is
-// H2D(a), H2D(b), kernel, D2H(out); different slots overlap, so both copy
-// engines and the SMs are busy at once.  Staging is allocated on first use per
-// device and kept (the device entry points above never allocate).  Several ops on
-// the same inputs share one upload (pint_cuda_binary_multi_host).
+// Host-buffer path: per device a ring of `host_slots` slots, each with its own stream and
+// device staging for one chunk of a, b and every output.  On a slot's stream the order is
+// H2D(a), H2D(b), kernel, D2H(out...); different slots overlap, so both copy engines and the
+// SMs are busy at once.  Staging is allocated on first use per device and kept until
+// pint_cuda_host_release (the device entry points above never allocate).  Several ops on the
+// same inputs share one upload.  Each device's ring has its own lock: calls on different
+// devices from different threads run concurrently; the sharded form drives all rings from
+// the calling thread (every call it makes is asynchronous) and locks them in device order.
 namespace pint_cuda_impl {
 namespace {
 
+constexpr int kMaxDevices = 64;
+
 struct host_ring {
+    std::mutex mutex;
     int device = -1;
     size_t chunk_bytes = 0;
     int slots = 0;
@@ -331,24 +404,21 @@ struct host_ring {
     void* buf[8][2 + PINT_MAX_HOST_OPS] = {};  // a, b, one output per op
 };
 
-std::mutex g_ring_mutex;
-host_ring g_rings[64];
+host_ring g_rings[kMaxDevices];
 
+// caller holds r.mutex and has r.device current
 void ring_release(host_ring& r)
 {
     for (int i = 0; i < r.slots; ++i) {
-        for (int j = 0; j < 2 + PINT_MAX_HOST_OPS; ++j) if (r.buf[i][j]) cudaFree(r.buf[i][j]);
-        if (r.stream[i]) cudaStreamDestroy(r.stream[i]);
+        for (int j = 0; j < 2 + PINT_MAX_HOST_OPS; ++j) if (r.buf[i][j]) { cudaFree(r.buf[i][j]); r.buf[i][j] = nullptr; }
+        if (r.stream[i]) { cudaStreamDestroy(r.stream[i]); r.stream[i] = nullptr; }
     }
-    r = host_ring{};
+    r.device = -1; r.chunk_bytes = 0; r.slots = 0;
 }
 
-cudaError_t ring_get(host_ring** out, int nops)
+// caller holds r.mutex and has `dev` current
+cudaError_t ring_prepare(host_ring& r, int dev, int nops)
 {
-    int dev = 0;
-    if (cudaError_t e = cudaGetDevice(&dev)) return e;
-    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
-    host_ring& r = g_rings[dev];
     const size_t want = (size_t)opts().host_chunk_bytes / 16 * 16;
     const int slots = (int)opts().host_slots;
     if (r.device != dev || r.chunk_bytes != want || r.slots != slots) {
@@ -361,8 +431,65 @@ cudaError_t ring_get(host_ring** out, int nops)
         for (int j = 0; j < 2 + nops; ++j)
             if (!r.buf[i][j])
                 if (cudaError_t e = cudaMalloc(&r.buf[i][j], want)) return e;
-    *out = &r;
     return cudaSuccess;
+}
+
+// One shard's pipeline: issue() queues the next chunk on the next slot (asynchronous).
+struct host_job {
+    host_ring* ring = nullptr;
+    int device = 0;
+    const char* a = nullptr;
+    const char* b = nullptr;
+    char* outs[PINT_MAX_HOST_OPS] = {};
+    size_t n = 0, done = 0;
+    int it = 0;
+
+    bool finished() const { return done >= n; }
+
+    // caller has `device` current
+    int issue(int nops, const int* ops, const pint_layout* layout, uint32_t elem_bytes)
+    {
+        host_ring& r = *ring;
+        const int slot = it++ % r.slots;
+        cudaStream_t s = r.stream[slot];
+        const size_t chunk_elems = r.chunk_bytes / elem_bytes;
+        const size_t cnt = n - done < chunk_elems ? n - done : chunk_elems;
+        const size_t bytes = cnt * elem_bytes, off = done * elem_bytes;
+        // stream order makes the slot's previous D2H copies finish before its buffers are overwritten
+        if (cudaError_t e = cudaMemcpyAsync(r.buf[slot][0], a + off, bytes, cudaMemcpyHostToDevice, s)) return (int)e;
+        if (cudaError_t e = cudaMemcpyAsync(r.buf[slot][1], b + off, bytes, cudaMemcpyHostToDevice, s)) return (int)e;
+        void* douts[PINT_MAX_HOST_OPS];
+        for (int j = 0; j < nops; ++j) douts[j] = r.buf[slot][2 + j];
+        if (int rc = binary_multi_impl(nops, ops, layout, r.buf[slot][0], r.buf[slot][1], douts, cnt, s)) return rc;  // one pass for all ops
+        for (int j = 0; j < nops; ++j)
+            if (cudaError_t e = cudaMemcpyAsync(outs[j] + off, r.buf[slot][2 + j], bytes, cudaMemcpyDeviceToHost, s)) return (int)e;
+        done += cnt;
+        return PINT_OK;
+    }
+
+    int drain()
+    {
+        int rc = PINT_OK;
+        for (int i = 0; i < ring->slots; ++i) {
+            const cudaError_t e = cudaStreamSynchronize(ring->stream[i]);
+            if (e != cudaSuccess && rc == PINT_OK) rc = (int)e;
+        }
+        return rc;
+    }
+};
+
+int check_host_args(int nops, const int* ops, const pint_layout* layout, layout_desc* d, const void* a_host,
+                    const void* b_host, void* const* outs_host, size_t n)
+{
+    if (int rc = check_layout(layout, d)) return rc;
+    if (nops < 1 || nops > PINT_MAX_HOST_OPS || !ops || !outs_host) return PINT_E_ARG;
+    for (int j = 0; j < nops; ++j)
+        if (ops[j] < 0 || ops[j] >= PINT_NUM_BINARY_OPS) return PINT_E_OP;
+    if (n == 0) return PINT_OK;
+    if (!a_host || !b_host) return PINT_E_NULL;
+    for (int j = 0; j < nops; ++j)
+        if (!outs_host[j]) return PINT_E_NULL;
+    return PINT_OK;
 }
 
 }  // namespace
@@ -372,44 +499,21 @@ extern "C" int pint_cuda_binary_multi_host(int nops, const int* ops, const pint_
                                            const void* b_host, void* const* outs_host, size_t n)
 {
     layout_desc d;
-    if (int rc = check_layout(layout, &d)) return rc;
-    if (nops < 1 || nops > PINT_MAX_HOST_OPS || !ops || !outs_host) return PINT_E_ARG;
-    for (int j = 0; j < nops; ++j)
-        if (ops[j] < 0 || ops[j] >= PINT_NUM_BINARY_OPS) return PINT_E_OP;
+    if (int rc = check_host_args(nops, ops, layout, &d, a_host, b_host, outs_host, n)) return rc;
     if (n == 0) return PINT_OK;
-    if (!a_host || !b_host) return PINT_E_NULL;
-    for (int j = 0; j < nops; ++j)
-        if (!outs_host[j]) return PINT_E_NULL;
-    std::lock_guard<std::mutex> lock(g_ring_mutex);
-    host_ring* r = nullptr;
-    if (cudaError_t e = ring_get(&r, nops)) return (int)e;
-    const size_t chunk_elems = r->chunk_bytes / d.elem_bytes;
-    const char* pa = (const char*)a_host;
-    const char* pb = (const char*)b_host;
+    int dev = 0;
+    if (cudaError_t e = cudaGetDevice(&dev)) return (int)e;
+    if (dev < 0 || dev >= kMaxDevices) return (int)cudaErrorInvalidDevice;
+    host_ring& r = g_rings[dev];
+    std::lock_guard<std::mutex> lock(r.mutex);
+    if (cudaError_t e = ring_prepare(r, dev, nops)) return (int)e;
+    host_job job;
+    job.ring = &r; job.device = dev; job.a = (const char*)a_host; job.b = (const char*)b_host; job.n = n;
+    for (int j = 0; j < nops; ++j) job.outs[j] = (char*)outs_host[j];
     int rc = PINT_OK;
-    size_t done = 0;
-    for (int it = 0; done < n && rc == PINT_OK; ++it) {
-        const int slot = it % r->slots;
-        cudaStream_t s = r->stream[slot];
-        const size_t cnt = n - done < chunk_elems ? n - done : chunk_elems;
-        const size_t bytes = cnt * d.elem_bytes, off = done * d.elem_bytes;
-        // stream order makes the slot's previous D2H copies finish before its buffers are overwritten
-        if (cudaError_t e = cudaMemcpyAsync(r->buf[slot][0], pa + off, bytes, cudaMemcpyHostToDevice, s)) { rc = (int)e; break; }
-        if (cudaError_t e = cudaMemcpyAsync(r->buf[slot][1], pb + off, bytes, cudaMemcpyHostToDevice, s)) { rc = (int)e; break; }
-        {
-            void* douts[PINT_MAX_HOST_OPS];
-            for (int j = 0; j < nops; ++j) douts[j] = r->buf[slot][2 + j];
-            rc = binary_multi_impl(nops, ops, layout, r->buf[slot][0], r->buf[slot][1], douts, cnt, s);  // one pass for all ops
-        }
-        for (int j = 0; j < nops && rc == PINT_OK; ++j)
-            if (cudaError_t e = cudaMemcpyAsync((char*)outs_host[j] + off, r->buf[slot][2 + j], bytes, cudaMemcpyDeviceToHost, s)) rc = (int)e;
-        done += cnt;
-    }
-    for (int i = 0; i < r->slots; ++i) {
-        const cudaError_t e = cudaStreamSynchronize(r->stream[i]);
-        if (e != cudaSuccess && rc == PINT_OK) rc = (int)e;
-    }
-    return rc;
+    while (!job.finished() && rc == PINT_OK) rc = job.issue(nops, ops, layout, d.elem_bytes);
+    const int rc2 = job.drain();
+    return rc != PINT_OK ? rc : rc2;
 }
 
 extern "C" int pint_cuda_binary_host(int op, const pint_layout* layout, const void* a_host, const void* b_host,
@@ -417,4 +521,79 @@ extern "C" int pint_cuda_binary_host(int op, const pint_layout* layout, const vo
 {
     void* outs[1] = {out_host};
     return pint_cuda_binary_multi_host(1, &op, layout, a_host, b_host, outs, n);
+}
+
+// The partitioner for HOST arrays (north_star (4); the reference's only array workload is a host
+// vector, tests/pint_bench.cpp:22,75): [0, n) is split by pint_cuda_plan_shards, shard k goes through
+// devices[k]'s ring, and the chunks of all shards are queued round-robin from this thread -- every
+// link and copy engine of the node works at once.  No collective, no peer traffic.
+extern "C" int pint_cuda_sharded_binary_multi_host(int nops, const int* ops, const pint_layout* layout, int ngpu,
+                                                   const int* devices, const void* a_host, const void* b_host,
+                                                   void* const* outs_host, size_t n)
+{
+    layout_desc d;
+    if (int rc = check_host_args(nops, ops, layout, &d, a_host, b_host, outs_host, n)) return rc;
+    if (ngpu < 1 || ngpu > kMaxDevices || !devices) return PINT_E_ARG;
+    for (int k = 0; k < ngpu; ++k) {
+        if (devices[k] < 0 || devices[k] >= kMaxDevices) return (int)cudaErrorInvalidDevice;
+        for (int i = 0; i < k; ++i)
+            if (devices[i] == devices[k]) return PINT_E_ARG;  // one ring per device: a device may own one shard
+    }
+    if (n == 0) return PINT_OK;
+    size_t begin[kMaxDevices], count[kMaxDevices];
+    if (int rc = pint_cuda_plan_shards(n, d.elem_bytes, ngpu, begin, count)) return rc;
+    int prev = 0;
+    if (cudaError_t e = cudaGetDevice(&prev)) return (int)e;
+    // lock the rings in ascending device order (two sharded calls with overlapping device sets cannot deadlock)
+    int order[kMaxDevices];
+    for (int k = 0; k < ngpu; ++k) order[k] = k;
+    for (int i = 1; i < ngpu; ++i)
+        for (int j = i; j > 0 && devices[order[j]] < devices[order[j - 1]]; --j) { const int t = order[j]; order[j] = order[j - 1]; order[j - 1] = t; }
+    for (int i = 0; i < ngpu; ++i) g_rings[devices[order[i]]].mutex.lock();
+    host_job jobs[kMaxDevices];
+    int rc = PINT_OK;
+    for (int k = 0; k < ngpu && rc == PINT_OK; ++k) {
+        host_ring& r = g_rings[devices[k]];
+        if (cudaError_t e = cudaSetDevice(devices[k])) { rc = (int)e; break; }
+        if (cudaError_t e = ring_prepare(r, devices[k], nops)) { rc = (int)e; break; }
+        host_job& j = jobs[k];
+        j.ring = &r; j.device = devices[k]; j.n = count[k];
+        j.a = (const char*)a_host + begin[k] * d.elem_bytes;
+        j.b = (const char*)b_host + begin[k] * d.elem_bytes;
+        for (int o = 0; o < nops; ++o) j.outs[o] = (char*)outs_host[o] + begin[k] * d.elem_bytes;
+    }
+    for (bool any = true; any && rc == PINT_OK;) {
+        any = false;
+        for (int k = 0; k < ngpu && rc == PINT_OK; ++k) {
+            if (jobs[k].finished()) continue;
+            any = true;
+            if (cudaError_t e = cudaSetDevice(devices[k])) { rc = (int)e; break; }
+            rc = jobs[k].issue(nops, ops, layout, d.elem_bytes);
+        }
+    }
+    for (int k = 0; k < ngpu; ++k) {
+        if (!jobs[k].ring) continue;
+        cudaSetDevice(devices[k]);
+        const int rc2 = jobs[k].drain();
+        if (rc == PINT_OK) rc = rc2;
+    }
+    for (int i = ngpu - 1; i >= 0; --i) g_rings[devices[order[i]]].mutex.unlock();
+    cudaSetDevice(prev);
+    return rc;
+}
+
+extern "C" int pint_cuda_host_release(void)
+{
+    int prev = 0, ndev = 0;
+    if (cudaError_t e = cudaGetDevice(&prev)) return (int)e;
+    if (cudaError_t e = cudaGetDeviceCount(&ndev)) return (int)e;
+    for (int dev = 0; dev < ndev && dev < kMaxDevices; ++dev) {
+        host_ring& r = g_rings[dev];
+        std::lock_guard<std::mutex> lock(r.mutex);
+        if (r.device < 0) continue;
+        cudaSetDevice(dev);
+        ring_release(r);
+    }
+    cudaSetDevice(prev);
+    return PINT_OK;
 }

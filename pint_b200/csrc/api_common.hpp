@@ -9,16 +9,24 @@
 
 namespace pint_cuda_impl {
 
+// process-wide option: relaxed atomic reads and writes (pint_cuda_set_option may race with launches)
+struct option_value {
+    long v;
+    constexpr option_value(long x = 0) : v(x) {}
+    operator long() const { return __atomic_load_n(&v, __ATOMIC_RELAXED); }
+    option_value& operator=(long x) { __atomic_store_n(&v, x, __ATOMIC_RELAXED); return *this; }
+};
+
 struct options {
-    long force_generic = 0;
-    long ctas_per_sm = 0;  // 0 = one CTA per tile (fastest, see launch_geom)
-    long host_chunk_bytes = 32L << 20;  // per operand per pipeline slot
-    long host_slots = 3;
-    long vec256 = 1;            // 32-byte vector kernels: 0 never, 1 auto (light functors), 2 wherever aligned
-    long dense_windows = 0;     // 1 = run-time dense layouts always use the element-by-element window kernels (testing)
-    long dense_threads = 0;     // dense bit-stream kernels: threads per CTA (0 = from the chunk size)
-    long dense_tile_bytes = 0;  // ... and tile bytes per operand (0 = 16 KB target)
-    long ordered_ctas_per_sm = 0;  // ordered persistent grid for bandwidth-bound functors; 0 = off (default, see cuda_kernels_stream.cuh)
+    option_value force_generic = 0;
+    option_value ctas_per_sm = 0;  // 0 = one CTA per tile (fastest, see launch_geom)
+    option_value host_chunk_bytes = 32L << 20;  // per operand per pipeline slot
+    option_value host_slots = 3;
+    option_value vec256 = 1;            // 32-byte vector kernels: 0 never, 1 auto (light functors), 2 wherever aligned
+    option_value dense_windows = 0;     // 1 = run-time dense layouts always use the element-by-element window kernels (testing)
+    option_value dense_threads = 0;     // dense bit-stream kernels: threads per CTA (0 = from the chunk size)
+    option_value dense_tile_bytes = 0;  // ... and tile bytes per operand (0 = 16 KB target)
+    option_value ordered_ctas_per_sm = 0;  // ordered persistent grid for bandwidth-bound functors; 0 = off (default, see cuda_kernels_stream.cuh)
 };
 options& opts();
 

@@ -118,3 +118,60 @@ def sharded_dense_binary(op, layout, a_shards, b_shards, out_shards, counts, str
                                                          _stream_array(a_shards, streams)),
                "pint_cuda_sharded_dense_binary")
     return out_shards
+
+
+# ---- arrays that start on the host or on one device ----
+
+def sharded_binary_multi_host(op_list, layout, devices, a, b, outs):
+    """outs[j][i] = op_list[j](a[i], b[i]) for HOST arrays (numpy or CPU tensors, ideally pinned) over
+    `devices` of this process: pint_cuda_sharded_binary_multi_host splits [0, n) into contiguous shards,
+    one per device, and streams every shard through its device's own staging ring.  Synchronous."""
+    def ptr_n(x):
+        if isinstance(x, torch.Tensor):
+            if x.is_cuda:
+                raise TypeError("host arrays required")
+            return x.data_ptr(), x.numel(), x.element_size()
+        return x.ctypes.data, x.size, x.itemsize
+    (pa, n, es), (pb_, nb, _) = ptr_n(a), ptr_n(b)
+    if n != nb or es != layout.elem_bytes or len(outs) != len(op_list):
+        raise ValueError("host arrays must match the layout and each other")
+    codes = (C.c_int * len(op_list))(*[OP_CODE[o] if isinstance(o, str) else int(o) for o in op_list])
+    po = (C.c_void_p * len(outs))()
+    for j, o in enumerate(outs):
+        pj, nj, _ = ptr_n(o)
+        if nj != n:
+            raise ValueError("output size mismatch")
+        po[j] = pj
+    devs = (C.c_int * len(devices))(*devices)
+    _lib.check(_lib.lib().pint_cuda_sharded_binary_multi_host(len(op_list), codes, layout.ref, len(devices), devs,
+                                                              pa, pb_, po, n), "pint_cuda_sharded_binary_multi_host")
+    return outs
+
+
+def enable_peer_access(devices):
+    devs = (C.c_int * len(devices))(*devices)
+    _lib.check(_lib.lib().pint_cuda_enable_peer_access(len(devices), devs), "pint_cuda_enable_peer_access")
+
+
+def _move(fn_name, whole, shards, streams):
+    k = len(shards)
+    devs = (C.c_int * k)(*[t.device.index for t in shards])
+    ps = (C.c_void_p * k)(*[t.data_ptr() for t in shards])
+    f = getattr(_lib.lib(), fn_name)
+    _lib.check(f(whole.data_ptr(), whole.device.index, whole.element_size(), whole.numel(), k, devs, ps,
+                 _stream_array(shards, streams)), fn_name)
+
+
+def scatter_shards(src, devices, streams=None):
+    """An array resident on ONE device -> the shards of plan_shards on `devices` (one peer copy per
+    shard, asynchronous on each destination's current stream).  Returns the shard tensors."""
+    plan = plan_shards(src.numel(), src.element_size(), len(devices))
+    shards = [torch.empty(cnt, dtype=src.dtype, device=torch.device("cuda", d)) for (_, cnt), d in zip(plan, devices)]
+    _move("pint_cuda_scatter_shards", src, shards, streams)
+    return shards
+
+
+def gather_shards(shards, dst, streams=None):
+    """The inverse: shard tensors (one per device) -> the contiguous array `dst` on its device."""
+    _move("pint_cuda_gather_shards", dst, shards, streams)
+    return dst

@@ -163,3 +163,116 @@ def test_cpp_template_layer():
     out = subprocess.run([exe], capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stdout + out.stderr
     assert "0 failures" in out.stdout
+
+
+def test_sharded_host_arrays_all_devices(oracle):
+    """pint_cuda_sharded_binary_multi_host: HOST arrays split over every visible device, each shard
+    through its device's ring; ragged n, several layouts, small chunks (many slot reuses)."""
+    import pint_b200
+    from pint_b200 import ops, sharded
+    ndev = torch.cuda.device_count()
+    ops.set_option("host_chunk_bytes", 1 << 19)
+    try:
+        for eb, bits in [(4, (8, 8, 8, 8)), (8, (16, 16, 16, 16)), (2, (5, 6, 5)), (4, (7, 9, 3))]:
+            L = pint_b200.Layout(eb, *bits)
+            for devices in ([0], list(range(ndev)), list(range(ndev))[::-1]):
+                n = 5 * (1 << 19) // eb * len(devices) + 4321
+                a, b = oracle.fill(eb, n, 61), oracle.fill(eb, n, 62)
+                pair = ["add_unsigned_saturate", "add_signed_saturate"]
+                outs = [np.zeros_like(a), np.zeros_like(a)]
+                sharded.sharded_binary_multi_host(pair, L, devices, a, b, outs)
+                for op, o in zip(pair, outs):
+                    np.testing.assert_array_equal(o, oracle.binary(op, eb, bits, a, b))
+                one = [np.zeros_like(a)]
+                sharded.sharded_binary_multi_host(["sub_signed_saturate"], L, devices, a, b, one)
+                np.testing.assert_array_equal(one[0], oracle.binary("sub_signed_saturate", eb, bits, a, b))
+        # tiny and empty arrays: fewer elements than devices * 128 bytes
+        L = pint_b200.Layout(4, 8, 8, 8, 8)
+        for n in (0, 1, 31, 33):
+            a, b = oracle.fill(4, n, 1), oracle.fill(4, n, 2)
+            out = [np.zeros_like(a)]
+            sharded.sharded_binary_multi_host(["add_wrap"], L, list(range(ndev)), a, b, out)
+            np.testing.assert_array_equal(out[0], oracle.binary("add_wrap", 4, (8, 8, 8, 8), a, b))
+    finally:
+        ops.set_option("host_chunk_bytes", 32 << 20)
+
+
+def test_sharded_host_argument_errors():
+    import pint_b200
+    from pint_b200 import _lib
+    lib = _lib.lib()
+    L = pint_b200.Layout(4, 8, 8, 8, 8)
+    a = np.zeros(16, dtype=np.uint32)
+    outs = (C.c_void_p * 1)(a.ctypes.data)
+    codes = (C.c_int * 1)(0)
+    dup = (C.c_int * 2)(0, 0)
+    f = lib.pint_cuda_sharded_binary_multi_host
+    assert f(1, codes, L.ref, 2, dup, a.ctypes.data, a.ctypes.data, outs, 16) == -15      # a device twice
+    assert f(1, codes, L.ref, 0, dup, a.ctypes.data, a.ctypes.data, outs, 16) == -15
+    assert f(1, codes, L.ref, 1, dup, None, a.ctypes.data, outs, 16) == -1
+    bad = (C.c_int * 1)(99)
+    assert f(1, bad, L.ref, 1, dup, a.ctypes.data, a.ctypes.data, outs, 16) == -10
+
+
+def test_host_calls_on_two_threads_and_release(oracle):
+    """Per-device ring lock: two threads on the same device serialise but stay correct, threads on
+    different devices run concurrently; pint_cuda_host_release frees the rings and the next call
+    allocates them again."""
+    import threading
+    import pint_b200
+    from pint_b200 import _lib, ops
+    L = pint_b200.Layout(4, 8, 8, 8, 8)
+    ndev = torch.cuda.device_count()
+    n = (1 << 21) + 17
+    a, b = oracle.fill(4, n, 71), oracle.fill(4, n, 72)
+    want = oracle.binary("add_signed_saturate", 4, (8, 8, 8, 8), a, b)
+    outs = [np.zeros_like(a) for _ in range(4)]
+    errs = []
+
+    def work(i):
+        try:
+            torch.cuda.set_device(i % ndev)
+            for _ in range(3):
+                ops.binary_host("add_signed_saturate", L, a, b, outs[i])
+        except Exception as e:  # noqa: BLE001
+            errs.append(e)
+    th = [threading.Thread(target=work, args=(i,)) for i in range(4)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert not errs, errs
+    for o in outs:
+        np.testing.assert_array_equal(o, want)
+    free0 = torch.cuda.mem_get_info(0)[0]
+    assert _lib.lib().pint_cuda_host_release() == 0
+    assert torch.cuda.mem_get_info(0)[0] > free0, "release must return the staging memory"
+    out = np.zeros_like(a)
+    ops.binary_host("add_signed_saturate", L, a, b, out)
+    np.testing.assert_array_equal(out, want)
+
+
+def test_scatter_compute_gather_from_one_device(oracle):
+    """An array resident on device 0 -> shards on all devices (one peer copy each) -> op per shard ->
+    gathered back onto device 0; equals the op run on the whole array."""
+    import pint_b200
+    from pint_b200 import ops, sharded
+    L = pint_b200.Layout(8, 3, 7, 11, 13, 17, 13)
+    bits = (3, 7, 11, 13, 17, 13)
+    ndev = torch.cuda.device_count()
+    devices = list(range(ndev)) if ndev > 1 else [0, 0, 0]
+    sharded.enable_peer_access(list(range(ndev)))
+    n = (1 << 20) + 777
+    a_h, b_h = oracle.fill(8, n, 81), oracle.fill(8, n, 82)
+    a, b = to_dev(a_h), to_dev(b_h)
+    torch.cuda.synchronize()
+    a_s, b_s = sharded.scatter_shards(a, devices), sharded.scatter_shards(b, devices)
+    for d in range(ndev):
+        torch.cuda.synchronize(d)
+    o_s = [torch.empty_like(t) for t in a_s]
+    sharded.sharded_binary("add_signed_saturate", L, a_s, b_s, o_s, fused=True)
+    for d in range(ndev):
+        torch.cuda.synchronize(d)
+    out = torch.zeros_like(a)
+    sharded.gather_shards(o_s, out)
+    for d in range(ndev):
+        torch.cuda.synchronize(d)
+    np.testing.assert_array_equal(to_np(out), oracle.binary("add_signed_saturate", 8, bits, a_h, b_h))
