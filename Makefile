@@ -38,11 +38,15 @@ oracle:
 	$(MAKE) -C oracle liboracle.so
 	@if [ -f /root/reference/include/pint/pint.hpp ]; then $(MAKE) -C oracle ref; fi
 
-tools: build/tune build/cpp_api_test
+tools: build/tune build/cpp_api_test build/e2e_ceiling
 
 build/tune: tools/tune.cu $(HDRS)
 	@mkdir -p build
 	$(NVCC) $(NVFLAGS) -o $@ tools/tune.cu
+
+build/e2e_ceiling: tools/e2e_ceiling.cu include/pint_cuda.h $(LIB)
+	@mkdir -p build
+	$(NVCC) -std=c++17 -O2 $(ARCH) -Iinclude -o $@ tools/e2e_ceiling.cu -Lpint_b200/lib -lpint_cuda -Xlinker -rpath -Xlinker '$$ORIGIN/../pint_b200/lib'
 
 build/cpp_api_test: tests/cpp/cpp_api_test.cpp include/pint/cuda.hpp $(LIB)
 	@mkdir -p build

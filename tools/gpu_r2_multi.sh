@@ -1,0 +1,33 @@
+#!/bin/bash
+# N-GPU box: raw host<->device ceiling and the host-buffer entry points on 1..N devices, the one-process
+# partitioner, bench.py + reference arm under torchrun at the given Ns, the multi-device tests.
+# Usage: bash tools/gpu_r2_multi.sh <tag> "<N list for bench.py>" [ceiling_log2] [single_process_log2]
+tag=${1:-r11m}
+NS=${2:-2}
+CL=${3:-29}
+SL=${4:-30}
+out=gpurun_out
+mkdir -p $out
+nvidia-smi -L > $out/${tag}_gpus.txt 2>&1; nvidia-smi topo -m >> $out/${tag}_gpus.txt 2>&1; nproc >> $out/${tag}_gpus.txt; free -g >> $out/${tag}_gpus.txt
+timeout 900 build/e2e_ceiling $CL 3 > $out/${tag}_e2e_ceiling.jsonl 2> $out/${tag}_e2e_ceiling.err; echo "ceiling rc=$?"
+tail -4 $out/${tag}_e2e_ceiling.jsonl
+timeout 900 python tools/bench_single_process.py $SL > $out/${tag}_single_process.jsonl 2> $out/${tag}_single_process.err; echo "single-process rc=$?"
+grep -c parity_ok $out/${tag}_single_process.jsonl; grep -c '"parity_ok": true' $out/${tag}_single_process.jsonl
+timeout 600 python -m pytest tests -q -m gpu -k "sharded or multi_device or devices or scatter or threads" > $out/${tag}_pytest_multi.log 2>&1
+tail -3 $out/${tag}_pytest_multi.log
+for N in $NS; do
+  TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512"
+  timeout 600 $TR bench.py --impl reference --gpus $N --steps 5 --warmup 1 > $out/${tag}_bench_ref_n$N.json 2> $out/${tag}_bench_ref_n$N.err; echo "ref N=$N rc=$?"
+  timeout 900 $TR bench.py --gpus $N --steps 20 --warmup 3 > $out/${tag}_bench_n$N.json 2> $out/${tag}_bench_n$N.err; echo "bench N=$N rc=$?"
+  python - <<PY
+import json
+for f in ("$out/${tag}_bench_ref_n$N.json", "$out/${tag}_bench_n$N.json"):
+    for l in open(f):
+        if l.startswith("{"):
+            d = json.loads(l)
+            print(d.get("impl", "ours"), d["n_gpus"], round(d["value"] / 1e9, 1), "Gelem/s", d.get("roofline", {}).get("achieved"),
+                  "e2e", round(d["e2e"]["value"] / 1e9, 2), d["e2e"].get("roofline"), "parity_ok", d.get("parity_ok"), d.get("clocks"))
+            for c in d.get("configs", []):
+                print("   ", c.get("config"), c.get("op", ""), c.get("gbs_per_gpu"), c.get("frac_spec_8000"), c.get("parity_ok"))
+PY
+done
