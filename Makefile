@@ -10,13 +10,24 @@ OBJ := build/obj
 LIB := pint_b200/lib/libpint_cuda.so
 HDRS := $(wildcard include/pint/*.hpp include/pint/*.cuh include/*.h $(SRC)/*.hpp $(SRC)/*.def)
 PARTS := 0 1 2 3
-OBJS := $(OBJ)/api.o $(OBJ)/api_aux.o $(OBJ)/api_dense.o $(OBJ)/api_callers.o $(OBJ)/dense_static.o $(foreach p,0 1 2,$(OBJ)/dense_generic_mw$(p).o) $(foreach p,0 1 2 3,$(OBJ)/dense_fixed$(p).o) $(OBJ)/generic.o $(foreach p,$(PARTS),$(OBJ)/registry_part$(p).o)
+JIT_HDRS := include/pint/cuda_std.hpp include/pint/cuda_layout.hpp include/pint/cuda_kernels.cuh include/pint/cuda_kernels_stream.cuh \
+            include/pint/cuda_kernels_multi.cuh include/pint/cuda_kernels_planes.cuh include/pint/cuda_kernels_planes_bulk.cuh \
+            include/pint/cuda_kernels_bulk.cuh include/pint/cuda_kernels_fused.cuh include/pint/cuda_kernels_callers.cuh
+OBJS := $(OBJ)/api.o $(OBJ)/api_aux.o $(OBJ)/jit.o $(OBJ)/api_dense.o $(OBJ)/api_callers.o $(OBJ)/dense_static.o $(foreach p,0 1 2,$(OBJ)/dense_generic_mw$(p).o) $(foreach p,0 1 2 3,$(OBJ)/dense_fixed$(p).o) $(OBJ)/generic.o $(foreach p,$(PARTS),$(OBJ)/registry_part$(p).o)
 
 all: $(LIB)
 
 $(OBJ)/%.o: $(SRC)/%.cu $(HDRS)
 	@mkdir -p $(OBJ)
 	$(NVCC) $(NVFLAGS) -c $< -o $@
+
+# the kernel templates as text, for the run-time (NVRTC) specialisation in jit.cu
+build/gen/jit_headers.inc: $(JIT_HDRS) tools/embed_headers.py
+	python tools/embed_headers.py $@ $(JIT_HDRS)
+
+$(OBJ)/jit.o: $(SRC)/jit.cu build/gen/jit_headers.inc $(HDRS)
+	@mkdir -p $(OBJ)
+	$(NVCC) $(NVFLAGS) -Ibuild/gen -c $< -o $@
 
 $(OBJ)/registry_part%.o: $(SRC)/registry_part.cu $(HDRS)
 	@mkdir -p $(OBJ)

@@ -18,12 +18,14 @@
 // ("pint.hpp:N" below); the formulas are our own where a cheaper one computes
 // the identical function (each such place says why it is identical).
 #pragma once
+#ifndef PINT_CUDA_KERNELS_CUH_INCLUDED
+#define PINT_CUDA_KERNELS_CUH_INCLUDED
 
-#include <cstddef>
-#include <cstdint>
-#include <utility>
+#include "cuda_std.hpp"
 
+#if !defined(__CUDACC_RTC__)
 #include <cuda_runtime.h>
+#endif
 
 #include "cuda_layout.hpp"
 
@@ -279,3 +281,5 @@ __device__ __forceinline__ Word apply_unary(Word v, const unary_params<Word>& u)
 #include "cuda_kernels_multi.cuh"
 #include "cuda_kernels_planes.cuh"
 #include "cuda_kernels_callers.cuh"
+
+#endif  // PINT_CUDA_KERNELS_CUH_INCLUDED

@@ -10,6 +10,8 @@
 // variants the library launches is a measured decision (tools/tune.cu,
 // profiles/).
 #pragma once
+#ifndef PINT_CUDA_KERNELS_BULK_CUH_INCLUDED
+#define PINT_CUDA_KERNELS_BULK_CUH_INCLUDED
 
 #include "cuda_kernels.cuh"
 
@@ -141,3 +143,5 @@ binary_bulk_kernel(const uint4* a, const uint4* b, uint4* out, size_t ntiles, co
 }  // namespace kernels
 }  // namespace cuda
 }  // namespace pint
+
+#endif  // PINT_CUDA_KERNELS_BULK_CUH_INCLUDED

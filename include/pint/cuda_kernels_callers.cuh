@@ -7,6 +7,8 @@
 // Both wrap any binary functor of the stream kernels (swar_fn / fused_fn, compiled-in or run-time
 // masks).  Included by cuda_kernels.cuh.
 #pragma once
+#ifndef PINT_CUDA_KERNELS_CALLERS_CUH_INCLUDED
+#define PINT_CUDA_KERNELS_CALLERS_CUH_INCLUDED
 
 namespace pint {
 namespace cuda {
@@ -67,6 +69,7 @@ map1_elem_kernel(const Elem* in, Elem* out, size_t n, const __grid_constant__ Fn
         out[i] = Elem(fn(W(in[i])));
 }
 
+#if !defined(__CUDACC_RTC__)  // host-side launchers: not part of a run-time (NVRTC) specialisation
 // out[i] = fn(in[i]) for a one-operand functor (scalar_fn); `out` may be `in`.
 template <class Elem, class Fn>
 cudaError_t launch_map1(const void* in, void* out, size_t n, const Fn& fn, cudaStream_t s, const launch_geom& g)
@@ -98,6 +101,8 @@ cudaError_t launch_map1(const void* in, void* out, size_t n, const Fn& fn, cudaS
     elems(n - tail, tail);
     return cudaGetLastError();
 }
+
+#endif  // !__CUDACC_RTC__
 
 // ---------------------------------------------------------------------------
 // Interleaved operands.  A thread turns 32 bytes of pairs into 16 bytes of results; the operands
@@ -161,6 +166,7 @@ pairs_map_elem_kernel(const Elem* pairs, Elem* out, size_t n, const __grid_const
 }
 
 // out[i] = fn(pairs[2i], pairs[2i+1]) for a binary functor; `out` must not overlap `pairs`.
+#if !defined(__CUDACC_RTC__)  // host-side launchers: not part of a run-time (NVRTC) specialisation
 template <class Elem, class Fn>
 cudaError_t launch_pairs_map(const void* pairs, void* out, size_t n, const Fn& fn, cudaStream_t s, const launch_geom& g)
 {
@@ -194,6 +200,10 @@ cudaError_t launch_pairs_map(const void* pairs, void* out, size_t n, const Fn& f
     return cudaGetLastError();
 }
 
+#endif  // !__CUDACC_RTC__
+
 }  // namespace kernels
 }  // namespace cuda
 }  // namespace pint
+
+#endif  // PINT_CUDA_KERNELS_CALLERS_CUH_INCLUDED

@@ -1,6 +1,8 @@
 // pint/cuda_kernels_fused.cuh -- fused unpack -> arithmetic -> repack, and the
 // launchers of the per-field kernels.  Included by cuda_kernels_planes.cuh.
 #pragma once
+#ifndef PINT_CUDA_KERNELS_FUSED_CUH_INCLUDED
+#define PINT_CUDA_KERNELS_FUSED_CUH_INCLUDED
 
 namespace pint {
 namespace cuda {
@@ -153,6 +155,7 @@ struct fused_fn {
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
+#if !defined(__CUDACC_RTC__)  // host-side launchers: not part of a run-time (NVRTC) specialisation
 template <class Elem, int PlaneBytes, bool Signed, class FP>
 cudaError_t launch_unpack(const void* packed, const plane_ptrs& planes, uint32_t nfields, size_t n, const FP& fp,
                           cudaStream_t stream, const launch_geom& g)
@@ -180,6 +183,35 @@ cudaError_t launch_unpack(const void* packed, const plane_ptrs& planes, uint32_t
         }
     }
     if constexpr (PlaneBytes == 4) {
+        // plane tiles staged in shared memory and written by bulk (TMA) stores (cuda_kernels_planes_bulk.cuh):
+        // +0.8 ... +0.9 % over the oct kernel on the same box (C3 6760 -> 6825, 6670 -> 6725 GB/s,
+        // profiles/r12_ab_unpack_bulk.log, r12_tune_unpack_bulk.log; flat in tile and CTA size), the default
+        // up to 12 fields (at most 48 KB of staging per CTA); option "unpack_bulk" = 0 keeps the register kernels.
+        // Whole tiles only, the remainder goes on below.
+        if (g.unpack_bulk > 0 && nfields <= 12 && (reinterpret_cast<uintptr_t>(packed) & 31u) == 0) {
+            bool bok = true;
+            for (uint32_t f = 0; f < nfields; ++f)
+                if (planes.p[f] && !aligned16(planes.p[f])) bok = false;
+            const size_t tile = nfields <= 6 ? 2048 : 1024;
+            const size_t ntiles = bok ? n / tile : 0;
+            if (ntiles) {
+                const size_t smem = size_t(nfields) * tile * 4;
+                if (tile == 2048)
+                    unpack_bulk_kernel<Elem, Signed, FP, 2048, 256><<<grid_for(ntiles, g), 256, smem, stream>>>(src, planes, ntiles, nfields, fp);
+                else
+                    unpack_bulk_kernel<Elem, Signed, FP, 1024, 256><<<grid_for(ntiles, g), 256, smem, stream>>>(src, planes, ntiles, nfields, fp);
+                count_launch(g);
+                done = ntiles * tile;
+                if (done == n) return cudaGetLastError();
+                // the tail: the same launcher on the remaining elements (planes advanced)
+                plane_ptrs rest{};
+                for (uint32_t f = 0; f < nfields; ++f)
+                    rest.p[f] = planes.p[f] ? static_cast<char*>(planes.p[f]) + done * 4 : nullptr;
+                launch_geom g2 = g;
+                g2.unpack_bulk = 0;
+                return launch_unpack<Elem, PlaneBytes, Signed, FP>(src + done, rest, nfields, n - done, fp, stream, g2);
+            }
+        }
         // 256-bit plane stores, eight elements per thread: +0.4 ... +2.3 % over the quad kernel on the same
         // box (C3 6515 -> 6665 GB/s, profiles/r07d_ab_unpack_oct.log); option vec256 = 0 keeps the quads
         constexpr size_t obytes = 8 * sizeof(Elem) < 32 ? 8 * sizeof(Elem) : 32;
@@ -252,6 +284,10 @@ cudaError_t launch_repack(const plane_ptrs& planes, uint32_t nfields, void* pack
     return cudaGetLastError();
 }
 
+#endif  // !__CUDACC_RTC__
+
 }  // namespace kernels
 }  // namespace cuda
 }  // namespace pint
+
+#endif  // PINT_CUDA_KERNELS_FUSED_CUH_INCLUDED

@@ -13,6 +13,8 @@
 // pairs of kOpPairs below; pint_cuda_binary_multi decomposes any op list into
 // those pairs plus single-op passes.  Included by cuda_kernels.cuh.
 #pragma once
+#ifndef PINT_CUDA_KERNELS_MULTI_CUH_INCLUDED
+#define PINT_CUDA_KERNELS_MULTI_CUH_INCLUDED
 
 namespace pint {
 namespace cuda {
@@ -128,6 +130,7 @@ binary_pair_stream256_kernel(const vec32* a, const vec32* b, vec32* out0, vec32*
 // misalignments go through the single-op launcher (element-granular kernels that
 // the library instantiates anyway).  Outputs must not overlap the inputs or each
 // other (checked at the C ABI).
+#if !defined(__CUDACC_RTC__)  // host-side launchers: not part of a run-time (NVRTC) specialisation
 template <class Elem, int Op0, int Op1, class P, class Cfg = stream_cfg_for<pair_fn<Op0, Op1, P>>>
 cudaError_t launch_binary_pair(const void* a, const void* b, void* out0, void* out1, size_t n, const P& p,
                                cudaStream_t stream, const launch_geom& g)
@@ -175,6 +178,10 @@ cudaError_t launch_binary_pair(const void* a, const void* b, void* out0, void* o
     return cudaGetLastError();
 }
 
+#endif  // !__CUDACC_RTC__
+
 }  // namespace kernels
 }  // namespace cuda
 }  // namespace pint
+
+#endif  // PINT_CUDA_KERNELS_MULTI_CUH_INCLUDED

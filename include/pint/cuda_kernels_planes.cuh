@@ -5,6 +5,8 @@
 // Bytes per element (W = sizeof(Integer), F planes of P bytes):
 //   unpack  W + P*F      repack  P*F + W      fused  3W (planes stay in registers)
 #pragma once
+#ifndef PINT_CUDA_KERNELS_PLANES_CUH_INCLUDED
+#define PINT_CUDA_KERNELS_PLANES_CUH_INCLUDED
 
 namespace pint {
 namespace cuda {
@@ -435,4 +437,7 @@ repack_elem_kernel(const __grid_constant__ plane_ptrs planes, Elem* packed, size
 }  // namespace cuda
 }  // namespace pint
 
+#include "cuda_kernels_planes_bulk.cuh"
 #include "cuda_kernels_fused.cuh"
+
+#endif  // PINT_CUDA_KERNELS_PLANES_CUH_INCLUDED

@@ -2,6 +2,8 @@
 // (binary ops: 2 reads + 1 write = 3W bytes/element; unary ops: 2W).
 // Included by cuda_kernels.cuh.
 #pragma once
+#ifndef PINT_CUDA_KERNELS_STREAM_CUH_INCLUDED
+#define PINT_CUDA_KERNELS_STREAM_CUH_INCLUDED
 
 namespace pint {
 namespace cuda {
@@ -355,6 +357,7 @@ unary_elem_kernel(const Elem* in, Elem* out, size_t n, const __grid_constant__ u
         out[i] = Elem(apply_unary(Word(in[i]), u));
 }
 
+#if !defined(__CUDACC_RTC__)  // host-side launchers: not part of a run-time (NVRTC) specialisation
 // ---------------------------------------------------------------------------
 // Launch geometry.  ctas_per_sm == 0 (default): one CTA per tile, handed out in
 // address order by the hardware block scheduler -- measured 10-15 % faster on
@@ -372,6 +375,7 @@ struct launch_geom {
     unsigned* counter_cursor = nullptr;
     int ordered_ctas_per_sm = 0;  // 0 = off
     int vec256 = 1;               // 32-byte vectors: 0 never, 1 where measured faster (light functors), 2 wherever aligned
+    int unpack_bulk = 1;          // unpack to int32 planes through shared memory + bulk stores (cuda_kernels_planes_bulk.cuh)
 };
 
 // The ordered persistent kernels take a counter slot chosen on the host at launch time: a graph
@@ -535,6 +539,10 @@ cudaError_t launch_unary(const void* in, void* out, size_t n, const unary_params
     return cudaGetLastError();
 }
 
+#endif  // !__CUDACC_RTC__
+
 }  // namespace kernels
 }  // namespace cuda
 }  // namespace pint
+
+#endif  // PINT_CUDA_KERNELS_STREAM_CUH_INCLUDED

@@ -25,10 +25,10 @@
 //
 // Requires C++17.  Host and device.
 #pragma once
+#ifndef PINT_CUDA_LAYOUT_HPP_INCLUDED
+#define PINT_CUDA_LAYOUT_HPP_INCLUDED
 
-#include <cstddef>
-#include <cstdint>
-#include <type_traits>
+#include "cuda_std.hpp"
 
 #if defined(__CUDACC__)
 #define PINT_HD __host__ __device__
@@ -297,3 +297,5 @@ struct static_layout {
 
 }  // namespace cuda
 }  // namespace pint
+
+#endif  // PINT_CUDA_LAYOUT_HPP_INCLUDED

@@ -77,7 +77,8 @@ enum pint_error {
     PINT_E_INDEX = -12,        /* field index / slice bounds (pint.hpp:748, 802, 813) */
     PINT_E_PLANE_BYTES = -13,  /* plane element size is not 1, 2, 4 or 8 */
     PINT_E_ALIAS = -14,        /* partially overlapping in/out */
-    PINT_E_ARG = -15           /* other invalid argument */
+    PINT_E_ARG = -15,          /* other invalid argument */
+    PINT_E_JIT = -20           /* option "jit" = 2 and the layout could not be specialised (pint_cuda_jit_last_error) */
 };
 
 /* ---- library ---- */
@@ -105,8 +106,24 @@ uint32_t pint_cuda_storage_bytes(uint32_t total_bits);
 /* mask_hiorder / mask_loorder / all_ones<sum> / detect_saturation_mask_type
  * (pint.hpp:324-348, 443-456) of one element, as the mask generator computes them */
 int pint_cuda_layout_masks(const pint_layout* layout, uint64_t* H, uint64_t* L, uint64_t* A, uint32_t* sat_type);
-/* 1 if kernels with compiled-in mask constants exist for this layout, else 0 */
+/* 1 if kernels with compiled-in mask constants were built into the library for this layout, 2 if
+ * they have been specialised at run time on the current device (option "jit"), else 0 */
 int pint_cuda_layout_is_specialized(const pint_layout* layout);
+/* Run-time specialisation (option "jit", default 0 = off).  The reference gives EVERY layout its mask
+ * constants at compile time (pint.hpp:324-337, 443-456); the library has them built in for a handful
+ * (registry_layouts.def) and runs the others with masks in the constant bank.  With "jit" = 1 or 2 the
+ * first packed -> packed call on such a layout compiles the same kernel templates for
+ * static_layout<Integer, Bits...> with NVRTC (libnvrtc.so.12, loaded on demand; headers embedded in
+ * the library), caches the cubin on disk ($PINT_CUDA_JIT_CACHE, else ~/.cache/pint_cuda) and uses it
+ * from then on: the call that compiles blocks for about a second.  pint_cuda_jit_compile does that
+ * ahead of time for all op families of a layout on the current device, so that later calls never block.
+ * "jit" = 1: a layout that cannot be specialised keeps running the run-time-mask kernels (identical
+ * results); "jit" = 2: such a call returns PINT_E_JIT.  pint_cuda_jit_last_error: why (thread-local copy). */
+int pint_cuda_jit_compile(const pint_layout* layout);
+/* The same compilation for compute capability sm_major.sm_minor WITHOUT a device: fills the disk
+ * cache only (a build machine can warm it for the machines that run). */
+int pint_cuda_jit_prebuild(const pint_layout* layout, int sm_major, int sm_minor);
+const char* pint_cuda_jit_last_error(void);
 /* result layout of slice<start, end> (sliced_int, pint.hpp:746-754) */
 int pint_cuda_slice_layout(const pint_layout* layout, uint32_t start, uint32_t end, pint_layout* result);
 

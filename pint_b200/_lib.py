@@ -47,6 +47,9 @@ def lib():
             "pint_cuda_storage_bytes": (u32, [u32]),
             "pint_cuda_layout_masks": (i, [LP, C.POINTER(u64), C.POINTER(u64), C.POINTER(u64), C.POINTER(u32)]),
             "pint_cuda_layout_is_specialized": (i, [LP]),
+            "pint_cuda_jit_compile": (i, [LP]),
+            "pint_cuda_jit_prebuild": (i, [LP, i, i]),
+            "pint_cuda_jit_last_error": (C.c_char_p, []),
             "pint_cuda_slice_layout": (i, [LP, u32, u32, LP]),
             "pint_cuda_binary": (i, [i, LP, vp, vp, vp, sz, vp]),
             "pint_cuda_fused_unpack_arith_repack": (i, [i, LP, vp, vp, vp, sz, vp]),

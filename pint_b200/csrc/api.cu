@@ -66,6 +66,7 @@ launch_geom geom()
     g.launch_counter = &g_launches;
     g.ordered_ctas_per_sm = (int)opts().ordered_ctas_per_sm;
     g.vec256 = (int)opts().vec256;
+    g.unpack_bulk = (int)opts().unpack_bulk;
     if (g.ordered_ctas_per_sm > 0) {
         g.counters = current_counters();
         g.counter_cursor = &g_counter_cursor;
@@ -109,6 +110,12 @@ int binary_impl(int op, bool fused, const pint_layout* layout, const void* a, co
     const launch_geom g = geom();
     if (const layout_kernels* k = find_static(d))
         return (int)(fused ? k->fused[op] : k->binary[op])(a, b, out, n, s, g);
+    if (const long jit = opts().jit) {
+        bool handled = false;
+        const int rc = jit_binary(op, fused, layout, d, a, b, out, n, s, g, &handled);
+        if (handled || (rc == PINT_E_JIT && jit >= 2)) return rc;
+        if (rc != PINT_OK && rc != PINT_E_JIT) return rc;
+    }
     return (int)generic_binary(op, fused, d, a, b, out, n, s, g);
 }
 
@@ -148,19 +155,28 @@ int binary_multi_impl(int nops, const int* ops, const pint_layout* layout, const
     for (int j = 0; j < nops; ++j) {
         if (done[j]) continue;
         done[j] = true;
-        int rc = -1;
-        for (int i = j + 1; i < nops && rc < 0; ++i) {
+        int rc = PINT_OK;
+        bool paired = false;
+        for (int i = j + 1; i < nops && !paired; ++i) {
             bool swapped = false;
             const int pi = done[i] ? -1 : pint::cuda::kernels::find_op_pair(m.op[j], m.op[i], &swapped);
             if (pi < 0) continue;
             done[i] = true;
+            paired = true;
             void* o0 = swapped ? m.out[i] : m.out[j];
             void* o1 = swapped ? m.out[j] : m.out[i];
-            rc = k ? (int)k->pair[pi](a, b, o0, o1, n, s, g) : (int)generic_binary_pair(pi, d, a, b, o0, o1, n, s, g);
+            if (k) {
+                rc = (int)k->pair[pi](a, b, o0, o1, n, s, g);
+            } else {
+                bool handled = false;
+                const long jit = opts().jit;
+                rc = jit ? jit_binary_pair(pi, d, a, b, o0, o1, n, s, g, &handled) : PINT_OK;
+                if (!handled && !(rc == PINT_E_JIT && jit >= 2) && (rc == PINT_OK || rc == PINT_E_JIT))
+                    rc = (int)generic_binary_pair(pi, d, a, b, o0, o1, n, s, g);
+            }
         }
-        if (rc < 0)
-            rc = k ? (int)k->binary[m.op[j]](a, b, m.out[j], n, s, g)
-                   : (int)generic_binary(m.op[j], false, d, a, b, m.out[j], n, s, g);
+        if (!paired)
+            rc = k ? (int)k->binary[m.op[j]](a, b, m.out[j], n, s, g) : binary_impl(m.op[j], false, layout, a, b, m.out[j], n, s);
         if (rc) return rc;
     }
     return PINT_OK;
@@ -220,6 +236,7 @@ const char* pint_cuda_error_string(int rc)
     case PINT_E_PLANE_BYTES: return "plane_bytes must be 4 or 8";
     case PINT_E_ALIAS: return "partially overlapping input and output";
     case PINT_E_ARG: return "invalid argument";
+    case PINT_E_JIT: return "layout could not be specialised at run time (pint_cuda_jit_last_error)";
     default: return rc > 0 ? cudaGetErrorString((cudaError_t)rc) : "unknown error";
     }
 }
@@ -236,6 +253,8 @@ int pint_cuda_set_option(const char* key, long value)
     if (!std::strcmp(key, "host_slots")) { if (value < 1 || value > 8) return PINT_E_ARG; opts().host_slots = value; return PINT_OK; }
     if (!std::strcmp(key, "vec256")) { if (value < 0 || value > 2) return PINT_E_ARG; opts().vec256 = value; return PINT_OK; }
     if (!std::strcmp(key, "dense_windows")) { opts().dense_windows = value != 0; return PINT_OK; }
+    if (!std::strcmp(key, "jit")) { if (value < 0 || value > 2) return PINT_E_ARG; opts().jit = value; return PINT_OK; }
+    if (!std::strcmp(key, "unpack_bulk")) { if (value < 0 || value > 1) return PINT_E_ARG; opts().unpack_bulk = value; return PINT_OK; }
     if (!std::strcmp(key, "dense_threads")) { if (value < 0 || value > 1024 || value % 32) return PINT_E_ARG; opts().dense_threads = value; return PINT_OK; }
     if (!std::strcmp(key, "dense_tile_bytes")) { if (value < 0 || value > 100 * 1024) return PINT_E_ARG; opts().dense_tile_bytes = value; return PINT_OK; }
     return PINT_E_ARG;
@@ -251,6 +270,8 @@ long pint_cuda_get_option(const char* key)
     if (!std::strcmp(key, "host_slots")) return opts().host_slots;
     if (!std::strcmp(key, "vec256")) return opts().vec256;
     if (!std::strcmp(key, "dense_windows")) return opts().dense_windows;
+    if (!std::strcmp(key, "unpack_bulk")) return opts().unpack_bulk;
+    if (!std::strcmp(key, "jit")) return opts().jit;
     if (!std::strcmp(key, "dense_threads")) return opts().dense_threads;
     if (!std::strcmp(key, "dense_tile_bytes")) return opts().dense_tile_bytes;
     return -1;
@@ -283,7 +304,8 @@ int pint_cuda_layout_is_specialized(const pint_layout* layout)
 {
     layout_desc d;
     if (int rc = check_layout(layout, &d)) return rc;
-    return find_static(d) ? 1 : 0;
+    if (find_static(d)) return 1;
+    return jit_is_loaded(d) ? 2 : 0;
 }
 
 int pint_cuda_slice_layout(const pint_layout* layout, uint32_t start, uint32_t end, pint_layout* result)

@@ -3,6 +3,7 @@
 
 #include <cstdint>
 #include <cstring>
+#include <string>
 
 #include "pint_cuda.h"
 #include "registry.hpp"
@@ -26,6 +27,8 @@ struct options {
     option_value dense_windows = 0;     // 1 = run-time dense layouts always use the element-by-element window kernels (testing)
     option_value dense_threads = 0;     // dense bit-stream kernels: threads per CTA (0 = from the chunk size)
     option_value dense_tile_bytes = 0;  // ... and tile bytes per operand (0 = 16 KB target)
+    option_value unpack_bulk = 1;   // unpack to int32 planes: 1 = plane tiles staged in shared memory, bulk (TMA) stores; 0 = register kernels
+    option_value jit = 0;           // 0 off; 1 = specialise unregistered layouts with NVRTC, fall back on failure; 2 = fail instead
     option_value ordered_ctas_per_sm = 0;  // ordered persistent grid for bandwidth-bound functors; 0 = off (default, see cuda_kernels_stream.cuh)
 };
 options& opts();
@@ -40,5 +43,16 @@ int binary_multi_impl(int nops, const int* ops, const pint_layout* layout, const
                       void* const* outs, size_t n, cudaStream_t s);
 int binary_impl(int op, bool fused, const pint_layout* layout, const void* a, const void* b, void* out, size_t n,
                 cudaStream_t s);
+
+
+// jit.cu: the kernel templates specialised at run time for a layout without pre-built constants.
+// *handled = false means the call was not (or could not be) served and nothing was launched.
+int jit_binary(int op, bool fused, const pint_layout* layout, const layout_desc& d, const void* a, const void* b, void* out,
+               size_t n, cudaStream_t s, const launch_geom& g, bool* handled);
+int jit_binary_pair(int pair, const layout_desc& d, const void* a, const void* b, void* out0, void* out1, size_t n,
+                    cudaStream_t s, const launch_geom& g, bool* handled);
+int jit_compile_all(const layout_desc& d);
+int jit_prebuild(const layout_desc& d, int major, int minor);
+bool jit_is_loaded(const layout_desc& d);
 
 }  // namespace pint_cuda_impl

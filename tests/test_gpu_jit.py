@@ -1,0 +1,97 @@
+"""GPU: run-time specialisation (option "jit"): layouts without pre-built constants get the SAME kernel
+templates compiled for static_layout<Integer, Bits...> by NVRTC and must give the reference's results --
+compiled reference vectors where oracle/_ref has the layout, the oracle everywhere."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from gpu_util import to_dev, to_np  # noqa: E402
+
+LAYOUTS = [(4, (7, 9, 3)), (4, (5, 6, 5, 3)), (8, (10, 10, 10, 10))]
+
+
+@pytest.fixture
+def jit_strict(tmp_path, monkeypatch):
+    from pint_b200 import ops
+    monkeypatch.setenv("PINT_CUDA_JIT_CACHE", str(tmp_path / "jit"))
+    ops.set_option("jit", 2)
+    yield ops
+    ops.set_option("jit", 0)
+
+
+@pytest.mark.parametrize("eb,bits", LAYOUTS)
+def test_jit_specialised_layouts_match_reference(jit_strict, oracle, eb, bits):
+    import pint_b200
+    from pint_b200 import _lib
+    ops = jit_strict
+    L = pint_b200.Layout(eb, *bits)
+    assert not L.is_specialized(), "pick layouts that are NOT in registry_layouts.def"
+    from oracle import Ref
+    ref = Ref() if Ref.available() else None
+    for n, off in ((1 << 18, 0), ((1 << 17) + 4099, 0), (100003, 3), (5, 0)):
+        a_h, b_h = oracle.fill(eb, n, 0x717 + n), oracle.fill(eb, n, 0x718 + n)
+        a, b = to_dev(a_h, off), to_dev(b_h, off)
+        for op in ops.OPS:
+            want = oracle.binary(op, eb, bits, a_h, b_h)
+            if ref is not None and ref.has(eb, bits):
+                np.testing.assert_array_equal(ref.binary(op, eb, bits, a_h, b_h), want)
+            np.testing.assert_array_equal(to_np(ops.binary(op, L, a, b)), want, err_msg=f"jit swar {L} {op} n={n}")
+            np.testing.assert_array_equal(to_np(ops.binary(op, L, a, b, fused=True)), want, err_msg=f"jit fused {L} {op} n={n}")
+        for pair in (("add_unsigned_saturate", "add_signed_saturate"), ("sub_signed_saturate", "add_signed_saturate"),
+                     ("min_unsigned", "max_unsigned"), ("sub_wrap", "add_wrap")):
+            o0, o1 = ops.binary_multi(list(pair), L, a, b)
+            np.testing.assert_array_equal(to_np(o0), oracle.binary(pair[0], eb, bits, a_h, b_h))
+            np.testing.assert_array_equal(to_np(o1), oracle.binary(pair[1], eb, bits, a_h, b_h))
+    assert _lib.lib().pint_cuda_layout_is_specialized(L.ref) == 2, "the calls above must have gone through the specialised module"
+    # in place, and the same results with the option off (run-time masks)
+    a_h, b_h = oracle.fill(eb, 1 << 16, 1), oracle.fill(eb, 1 << 16, 2)
+    a, b = to_dev(a_h), to_dev(b_h)
+    ops.binary("sub_unsigned_saturate", L, a, b, out=a)
+    np.testing.assert_array_equal(to_np(a), oracle.binary("sub_unsigned_saturate", eb, bits, a_h, b_h))
+    ops.set_option("jit", 0)
+    np.testing.assert_array_equal(to_np(ops.binary("sub_unsigned_saturate", L, to_dev(a_h), b)), to_np(a))
+
+
+def test_jit_compile_ahead_and_disk_cache(jit_strict, oracle, tmp_path):
+    """pint_cuda_jit_compile builds every family up front; a second process-level lookup of the same
+    layout is served from the disk cache (files present); launches are counted like any other."""
+    import os
+    import pint_b200
+    from pint_b200 import _lib
+    ops = jit_strict
+    L = pint_b200.Layout(2, 4, 4, 4)
+    lib = _lib.lib()
+    assert lib.pint_cuda_jit_compile(L.ref) == 0, lib.pint_cuda_jit_last_error()
+    files = os.listdir(tmp_path / "jit")
+    assert len([f for f in files if f.endswith(".cubin")]) == 3 and len([f for f in files if f.endswith(".names")]) == 3
+    n = (1 << 18) + 11
+    a_h, b_h = oracle.fill(2, n, 5), oracle.fill(2, n, 6)
+    before = ops.launch_count()
+    got = to_np(ops.binary("add_signed_saturate", L, to_dev(a_h), to_dev(b_h)))
+    assert ops.launch_count() > before
+    np.testing.assert_array_equal(got, oracle.binary("add_signed_saturate", 2, (4, 4, 4), a_h, b_h))
+
+
+def test_jit_in_graph_capture_after_warm_up(jit_strict, oracle):
+    """Once compiled, a specialised kernel is an ordinary launch: capturable in a CUDA graph."""
+    import pint_b200
+    ops = jit_strict
+    L = pint_b200.Layout(4, 7, 9, 3)
+    n = 1 << 18
+    a_h, b_h = oracle.fill(4, n, 9), oracle.fill(4, n, 10)
+    a, b = to_dev(a_h), to_dev(b_h)
+    out = torch.zeros_like(a)
+    ops.binary("add_signed_saturate", L, a, b, out=out)   # compiles
+    out.zero_()
+    g = torch.cuda.CUDAGraph()
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        with torch.cuda.graph(g, stream=s):
+            ops.binary("add_signed_saturate", L, a, b, out=out)
+    torch.cuda.current_stream().wait_stream(s)
+    g.replay()
+    torch.cuda.synchronize()
+    np.testing.assert_array_equal(to_np(out), oracle.binary("add_signed_saturate", 4, (7, 9, 3), a_h, b_h))

@@ -141,3 +141,43 @@ def test_dense_narrow_planes(P, oracle, eb, bits):
                     src[f][p_off:p_off + n].copy_(torch.from_numpy(planes_h[f].copy()))
                 got_d = dense.from_planes(L, [s_[p_off:p_off + n] for s_ in src])
                 np.testing.assert_array_equal(got_d.cpu().numpy(), want_d, err_msg=f"from_planes {L} n={n} pb={pb} off={p_off}")
+
+
+def test_unpack_bulk_store_kernel_matches(oracle):
+    """Option "unpack_bulk" (the default): int32 planes assembled in shared memory and written by bulk (TMA) stores
+    (unpack_bulk_kernel), whole 2048-element tiles + remainder through the register kernels.  Every
+    layout class (compiled-in / run-time fields, 1 ... 12 fields, all Integer sizes), signed and
+    unsigned, skipped planes, ragged sizes, against the oracle and against the default kernels."""
+    import pint_b200
+    from pint_b200 import ops
+    cases = [(8, (3, 7, 11, 13, 17, 13)), (4, (8, 8, 8, 8)), (2, (5, 6, 5)), (1, (2, 3, 3)), (4, (7, 9, 3)),
+             (8, (16, 16, 16, 16)), (8, (1, 63)), (4, (1, 2, 3, 4, 5, 6, 11)), (8, (5,) * 12), (8, (4,) * 13), (8, (33, 31))]
+    try:
+        for eb, bits in cases:
+            L = pint_b200.Layout(eb, *bits)
+            for n in (2048, 2048 * 5 + 1, 2048 * 37 + 1029, 100000):
+                x_h = oracle.fill(eb, n, 0xB01C + n)
+                x = to_dev(x_h)
+                for signed in (True, False):
+                    want = oracle.unpack(eb, bits, x_h, signed, 4)
+                    ops.set_option("unpack_bulk", 0)
+                    base = ops.unpack(L, x, signed=signed, plane_bytes=4)
+                    ops.set_option("unpack_bulk", 1)
+                    before = ops.launch_count()
+                    got = ops.unpack(L, x, signed=signed, plane_bytes=4)
+                    assert ops.launch_count() - before >= 1
+                    for f in range(len(bits)):
+                        np.testing.assert_array_equal(to_np(got[f], want[f].dtype), want[f], err_msg=f"{L} n={n} f={f} signed={signed}")
+                        assert torch.equal(got[f], base[f])
+                # only some planes wanted: the others are never touched
+                fields = [0, len(bits) - 1]
+                sent = [torch.full((n,), 0x5A5A5A5A, dtype=torch.int32, device="cuda") for _ in bits]
+                ops.unpack(L, x, signed=True, plane_bytes=4, fields=fields, out=[sent[f] if f in fields else None for f in range(len(bits))])
+                want = oracle.unpack(eb, bits, x_h, True, 4)
+                for f in range(len(bits)):
+                    if f in fields:
+                        np.testing.assert_array_equal(to_np(sent[f], np.int32), want[f])
+                    else:
+                        assert bool((sent[f] == 0x5A5A5A5A).all())
+    finally:
+        ops.set_option("unpack_bulk", 1)

@@ -172,3 +172,25 @@ def test_bench_reference_arm_line():
     env = dict(os.environ, RANK="1", LOCAL_RANK="1", WORLD_SIZE="2")
     r = subprocess.run(cmd + ["--gpus", "2"], capture_output=True, text=True, timeout=120, env=env)
     assert r.returncode == 0 and not r.stdout.strip()
+
+
+def test_jit_prebuild_without_a_device(tmp_path, monkeypatch):
+    """pint_cuda_jit_prebuild: the NVRTC specialisation of the embedded kernel templates for an
+    unregistered layout compiles for sm_100a on a machine with no GPU and fills the disk cache."""
+    import ctypes.util
+    import pint_b200
+    from pint_b200 import _lib
+    if not (os.path.exists("/usr/local/cuda/lib64/libnvrtc.so.12") or ctypes.util.find_library("nvrtc")):
+        pytest.skip("libnvrtc not installed")
+    monkeypatch.setenv("PINT_CUDA_JIT_CACHE", str(tmp_path / "jit"))
+    lib = _lib.lib()
+    L = pint_b200.Layout(4, 7, 9, 3)
+    rc = lib.pint_cuda_jit_prebuild(L.ref, 10, 0)
+    assert rc == 0, lib.pint_cuda_jit_last_error().decode()[:2000]
+    files = sorted(os.listdir(tmp_path / "jit"))
+    assert sorted(f.split("_")[1] for f in files) == ["binary.cubin", "binary.names", "fused.cubin", "fused.names", "pair.cubin", "pair.names"]
+    names = open(tmp_path / "jit" / [f for f in files if f.endswith("binary.names")][0]).read().split()
+    assert len(names) == 26 and all("binary_stream" in x and "static_layout" in x for x in names)
+    assert lib.pint_cuda_jit_prebuild(L.ref, 7, 0) == -15                      # not a target this library has
+    bad = pint_b200._lib.PintLayout(4, 2, (pint_b200._lib.C.c_uint8 * 64)(20, 20))
+    assert lib.pint_cuda_jit_prebuild(bad, 10, 0) == -5                        # the reference's static_assert (pint.hpp:763)

@@ -423,6 +423,44 @@ int main(int argc, char** argv)
         std::printf("done\n");
         return 0;
     }
+    if (argc > 3 && std::atoi(argv[3]) == 11) {
+        // unpack (C3) through shared memory + bulk (TMA) stores against the register-to-global kernels:
+        // tile size, CTA size, one tile per CTA or a persistent grid
+        const size_t n = size_t(1) << 28;
+        plane_ptrs pp{};
+        for (int f = 0; f < 6; ++f) pp.p[f] = (char*)(f < 3 ? b : out) + size_t(f % 3) * (n * 4);
+        time_it("unpack_oct_kernel K1 (library default)", double(n) * 32, [&] {
+            unpack_oct_kernel<uint64_t, true, static_fields<IRR>><<<unsigned((n / 8 + 255) / 256), 256>>>((const uint64_t*)a, pp, n / 8, static_fields<IRR>{});
+        });
+        time_it("unpack_oct_kernel K2", double(n) * 32, [&] {
+            unpack_oct_kernel<uint64_t, true, static_fields<IRR>, 2><<<unsigned((n / 8 + 511) / 512), 256>>>((const uint64_t*)a, pp, n / 8, static_fields<IRR>{});
+        });
+        auto bulk_run = [&](auto tile_tag, auto block_tag, int ctas_per_sm) {
+            constexpr int TILE = decltype(tile_tag)::value, BLOCK = decltype(block_tag)::value;
+            auto kern = unpack_bulk_kernel<uint64_t, true, static_fields<IRR>, TILE, BLOCK>;
+            const int smem = 6 * TILE * 4;
+            CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            const size_t ntiles = n / TILE;
+            const size_t grid = ctas_per_sm > 0 ? std::min(ntiles, size_t(g_sms) * ctas_per_sm) : ntiles;
+            char name[160];
+            std::snprintf(name, sizeof name, "unpack_bulk_kernel TILE %d B%d smem %d KB ctas/sm %d", TILE, BLOCK, smem / 1024, ctas_per_sm);
+            time_it(name, double(n) * 32, [&] { kern<<<unsigned(grid), BLOCK, smem>>>((const uint64_t*)a, pp, ntiles, 6, static_fields<IRR>{}); });
+        };
+        using T512 = std::integral_constant<int, 512>; using T1K = std::integral_constant<int, 1024>; using T2K = std::integral_constant<int, 2048>;
+        using T4K = std::integral_constant<int, 4096>; using T8K = std::integral_constant<int, 8192>;
+        using B128 = std::integral_constant<int, 128>; using B256 = std::integral_constant<int, 256>; using B512 = std::integral_constant<int, 512>;
+        for (int cps : {0, 2, 4, 8}) {
+            bulk_run(T512{}, B128{}, cps);
+            bulk_run(T1K{}, B128{}, cps); bulk_run(T1K{}, B256{}, cps);
+            bulk_run(T2K{}, B128{}, cps); bulk_run(T2K{}, B256{}, cps); bulk_run(T2K{}, B512{}, cps);
+            bulk_run(T4K{}, B256{}, cps); bulk_run(T4K{}, B512{}, cps);
+            bulk_run(T8K{}, B512{}, cps);
+        }
+        // directional ceilings of this box on the same buffers
+        time_it("cudaMemsetAsync 6 GiB (write-only, constant data)", double(n) * 24, [&] { CK(cudaMemsetAsync(b, 1, n * 12)); CK(cudaMemsetAsync(out, 1, n * 12)); });
+        std::printf("done\n");
+        return 0;
+    }
     if (argc > 3 && std::atoi(argv[3]) == 4) {
         // one CTA per tile, residency capped by an unused dynamic shared-memory request
         // (227 KB per SM / request = CTAs per SM): is full occupancy the best occupancy?
