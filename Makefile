@@ -49,7 +49,7 @@ oracle:
 	$(MAKE) -C oracle liboracle.so
 	@if [ -f /root/reference/include/pint/pint.hpp ]; then $(MAKE) -C oracle ref; fi
 
-tools: build/tune build/cpp_api_test build/e2e_ceiling
+tools: build/tune build/cpp_api_test build/e2e_ceiling build/cuda_api_nvcc_test build/r1_regress/libpint_cuda_r1.so static_masks_check
 
 build/tune: tools/tune.cu $(HDRS)
 	@mkdir -p build
@@ -59,6 +59,26 @@ build/e2e_ceiling: tools/e2e_ceiling.cu include/pint_cuda.h $(LIB)
 	@mkdir -p build
 	$(NVCC) -std=c++17 -O2 $(ARCH) -Iinclude -o $@ tools/e2e_ceiling.cu -Lpint_b200/lib -lpint_cuda -Xlinker -rpath -Xlinker '$$ORIGIN/../pint_b200/lib'
 
+# include/pint/cuda.hpp compiled by nvcc: kernels with compiled-in constants for ANY layout, in the user's TU
+build/cuda_api_nvcc_test: tests/cpp/cuda_api_nvcc_test.cu $(HDRS) $(LIB)
+	@mkdir -p build
+	$(NVCC) -std=c++17 -O3 $(ARCH) -lineinfo -Iinclude -o $@ tests/cpp/cuda_api_nvcc_test.cu -Lpint_b200/lib -lpint_cuda -Xlinker -rpath -Xlinker '$$ORIGIN/../pint_b200/lib'
+
+# today's library with round 1's pairs_reduce reduction put back (atomicXor 8 bytes past the caller's buffer):
+# tests/test_gpu_mapping_edge.py proves that the mapping-edge probe faults on it
+build/r1_regress/libpint_cuda_r1.so: $(LIB) $(SRC)/api_aux.cu
+	@mkdir -p build/r1_regress
+	sed 's/block_reduce_sum_xor<false>(s, 0, sum);/block_reduce_sum_xor<true>(s, 0, sum);/' $(SRC)/api_aux.cu > build/r1_regress/api_aux_r1.cu
+	grep -q 'block_reduce_sum_xor<true>(s, 0, sum)' build/r1_regress/api_aux_r1.cu
+	$(NVCC) $(NVFLAGS) -c build/r1_regress/api_aux_r1.cu -o build/r1_regress/api_aux_r1.o
+	$(NVCC) $(ARCH) -shared -cudart static -o $@ $(filter-out $(OBJ)/api_aux.o,$(OBJS)) build/r1_regress/api_aux_r1.o
+
+# compile-time equality of the mask generator with the reference's metafunctions (39 layouts); compiling IS the test
+static_masks_check:
+	@if [ -f /root/reference/include/pint/pint.hpp ]; then \
+	  g++ -std=c++17 -fsyntax-only -Iinclude -I/root/reference/include -Ioracle tests/cpp/static_masks_check.cpp && echo "static_masks_check: ok"; \
+	else echo "static_masks_check: skipped (/root/reference absent)"; fi
+
 build/cpp_api_test: tests/cpp/cpp_api_test.cpp include/pint/cuda.hpp $(LIB)
 	@mkdir -p build
 	g++ -std=c++11 -O2 -Iinclude -I/usr/local/cuda/include -o $@ tests/cpp/cpp_api_test.cpp -Lpint_b200/lib -lpint_cuda -L/usr/local/cuda/lib64 -lcudart -Wl,-rpath,'$$ORIGIN/../pint_b200/lib'
@@ -66,4 +86,4 @@ build/cpp_api_test: tests/cpp/cpp_api_test.cpp include/pint/cuda.hpp $(LIB)
 clean:
 	rm -rf build pint_b200/lib
 
-.PHONY: all oracle tools clean
+.PHONY: all oracle tools clean static_masks_check

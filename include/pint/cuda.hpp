@@ -36,6 +36,19 @@
 
 #include "../pint_cuda.h"
 
+// Compiled by nvcc (C++17): the packed -> packed operations, unpack and repack instantiate the kernel
+// templates for static_layout<Integer, Bits...> in the CALLER's translation unit, so that EVERY
+// layout gets its mask constants at compile time exactly as in the reference (pint.hpp:324-337,
+// 443-456), not only the ones built into libpint_cuda.so.  Same kernels, same results; heads,
+// tails and misaligned operands are handled by the same launchers the library uses.  Define
+// PINT_CUDA_NO_INLINE_KERNELS to keep nvcc translation units on the C ABI like any other compiler.
+#if defined(__CUDACC__) && !defined(PINT_CUDA_NO_INLINE_KERNELS) && __cplusplus >= 201703L
+#define PINT_CUDA_INLINE_KERNELS 1
+#include "cuda_kernels.cuh"
+#else
+#define PINT_CUDA_INLINE_KERNELS 0
+#endif
+
 namespace pint {
 
 using std::size_t;
@@ -126,7 +139,50 @@ struct sliced_int {
     typedef typename detail::slice_next<Start, End - Start, Integer, detail::bits_pack<>, Bits0, Bits...>::type type;
 };
 
+#if PINT_CUDA_INLINE_KERNELS
+namespace detail {
+
+// the argument checks of the C ABI (pint_b200/csrc/api.cu binary_impl), for launches made from this header
+inline int check_binary_arrays(const void* a, const void* b, const void* out, size_t n, size_t elem_bytes)
+{
+    if (n == 0) return PINT_OK;
+    if (!a || !b || !out) return PINT_E_NULL;
+    const uintptr_t o = (uintptr_t)out, bytes = n * elem_bytes;
+    const uintptr_t in[2] = {(uintptr_t)a, (uintptr_t)b};
+    for (int i = 0; i < 2; ++i)
+        if (in[i] != o && in[i] < o + bytes && o < in[i] + bytes) return PINT_E_ALIAS;
+    if (((uintptr_t)a | (uintptr_t)b | o) % elem_bytes) return PINT_E_ARG;
+    return PINT_OK;
+}
+
+template <int Op, bool Fused, class Integer, size_t... Bits>
+inline int inline_binary(const void* a, const void* b, void* out, size_t n, stream_t stream)
+{
+    layout_of<Integer, Bits...>::get();  // the reference's static_asserts
+    if (int rc = check_binary_arrays(a, b, out, n, sizeof(Integer))) return rc;
+    using SL = static_layout<Integer, Bits...>;
+    const kernels::launch_geom g;  // one CTA per tile
+    if (Fused) {
+        using Fn = kernels::fused_fn<Op, kernels::static_fields<SL>>;
+        return (int)kernels::launch_binary<Integer, Fn>(a, b, out, n, Fn{}, (cudaStream_t)stream, g);
+    }
+    using Fn = kernels::swar_fn<Op, kernels::static_masks<SL>>;
+    return (int)kernels::launch_binary<Integer, Fn>(a, b, out, n, Fn{}, (cudaStream_t)stream, g);
+}
+
+}  // namespace detail
+#endif
+
 // ---- the 13 binary operations: out[i] = OP(a[i], b[i]); out may be a or b ----
+#if PINT_CUDA_INLINE_KERNELS
+#define PINT_CUDA_BINARY(NAME, CODE)                                                                    \
+    template <class Integer, size_t Bits0, size_t... Bits>                                              \
+    inline void NAME(const packed_int<Integer, Bits0, Bits...>* a, const packed_int<Integer, Bits0, Bits...>* b, \
+                     packed_int<Integer, Bits0, Bits...>* out, size_t n, stream_t stream = nullptr)     \
+    {                                                                                                   \
+        check(detail::inline_binary<CODE, false, Integer, Bits0, Bits...>(a, b, out, n, stream), "pint::cuda::" #NAME); \
+    }
+#else
 #define PINT_CUDA_BINARY(NAME, CODE)                                                                    \
     template <class Integer, size_t Bits0, size_t... Bits>                                              \
     inline void NAME(const packed_int<Integer, Bits0, Bits...>* a, const packed_int<Integer, Bits0, Bits...>* b, \
@@ -135,6 +191,7 @@ struct sliced_int {
         const pint_layout l = detail::layout_of<Integer, Bits0, Bits...>::get();                        \
         check(pint_cuda_binary(CODE, &l, a, b, out, n, stream), "pint::cuda::" #NAME);                  \
     }
+#endif
 
 PINT_CUDA_BINARY(add_wrap, PINT_ADD_WRAP)                            // pint.hpp:826-838
 PINT_CUDA_BINARY(add_unsigned_saturate, PINT_ADD_UNSIGNED_SATURATE)  // pint.hpp:840-855
@@ -218,6 +275,17 @@ inline void equal(const packed_int<Integer, Bits0, Bits...>* a, const packed_int
     check(pint_cuda_equal(&l, a, b, n, equal_out, not_equal_count, stream), "pint::cuda::equal");
 }
 
+#if PINT_CUDA_INLINE_KERNELS
+// The fused pipeline with the operation as a template argument, instantiated for this layout in the
+// caller's translation unit (nvcc only; the run-time `op` form below goes through the library).
+template <pint_op Op, class Integer, size_t Bits0, size_t... Bits>
+inline void fused_unpack_arith_repack(const packed_int<Integer, Bits0, Bits...>* a, const packed_int<Integer, Bits0, Bits...>* b,
+                                      packed_int<Integer, Bits0, Bits...>* out, size_t n, stream_t stream = nullptr)
+{
+    check(detail::inline_binary<(int)Op, true, Integer, Bits0, Bits...>(a, b, out, n, stream), "pint::cuda::fused_unpack_arith_repack");
+}
+#endif
+
 // Any of the above, computed as unpack -> per-field arithmetic -> repack in one kernel.
 template <class Integer, size_t Bits0, size_t... Bits>
 inline void fused_unpack_arith_repack(pint_op op, const packed_int<Integer, Bits0, Bits...>* a,
@@ -264,10 +332,25 @@ inline void unpack(const packed_int<Integer, Bits0, Bits...>* packed, Plane* con
     static_assert(std::is_integral<Plane>::value && (sizeof(Plane) == 1 || sizeof(Plane) == 2 || sizeof(Plane) == 4 || sizeof(Plane) == 8),
                   "planes are 8-, 16-, 32- or 64-bit integers");
     const pint_layout l = detail::layout_of<Integer, Bits0, Bits...>::get();
+#if PINT_CUDA_INLINE_KERNELS
+    if (n == 0) return;
+    kernels::plane_ptrs pp{};
+    for (size_t i = 0; i < sizeof...(Bits) + 1; ++i) {
+        pp.p[i] = planes[i];
+        if ((uintptr_t)planes[i] % sizeof(Plane)) check(PINT_E_ARG, "pint::cuda::unpack");
+    }
+    if (!packed) check(PINT_E_NULL, "pint::cuda::unpack");
+    if ((uintptr_t)packed % sizeof(Integer)) check(PINT_E_ARG, "pint::cuda::unpack");
+    using SL = static_layout<Integer, Bits0, Bits...>;
+    check((int)kernels::launch_unpack<Integer, (int)sizeof(Plane), std::is_signed<Plane>::value>(
+              packed, pp, l.nfields, n, kernels::static_fields<SL>{}, (cudaStream_t)stream, kernels::launch_geom{}),
+          "pint::cuda::unpack");
+#else
     void* p[sizeof...(Bits) + 1];
     for (size_t i = 0; i < sizeof...(Bits) + 1; ++i) p[i] = planes[i];
     check(pint_cuda_unpack(&l, std::is_signed<Plane>::value ? 1 : 0, packed, p, (int)sizeof(Plane), n, stream),
           "pint::cuda::unpack");
+#endif
 }
 
 // the truncating field constructor over arrays (pint.hpp:770-774)
@@ -278,9 +361,25 @@ inline void repack(const Plane* const (&planes)[sizeof...(Bits) + 1], packed_int
     static_assert(std::is_integral<Plane>::value && (sizeof(Plane) == 1 || sizeof(Plane) == 2 || sizeof(Plane) == 4 || sizeof(Plane) == 8),
                   "planes are 8-, 16-, 32- or 64-bit integers");
     const pint_layout l = detail::layout_of<Integer, Bits0, Bits...>::get();
+#if PINT_CUDA_INLINE_KERNELS
+    if (n == 0) return;
+    kernels::plane_ptrs pp{};
+    for (size_t i = 0; i < sizeof...(Bits) + 1; ++i) {
+        if (!planes[i]) check(PINT_E_NULL, "pint::cuda::repack");
+        if ((uintptr_t)planes[i] % sizeof(Plane)) check(PINT_E_ARG, "pint::cuda::repack");
+        pp.p[i] = const_cast<Plane*>(planes[i]);
+    }
+    if (!packed) check(PINT_E_NULL, "pint::cuda::repack");
+    if ((uintptr_t)packed % sizeof(Integer)) check(PINT_E_ARG, "pint::cuda::repack");
+    using SL = static_layout<Integer, Bits0, Bits...>;
+    check((int)kernels::launch_repack<Integer, (int)sizeof(Plane)>(pp, l.nfields, packed, n, kernels::static_fields<SL>{},
+                                                                   (cudaStream_t)stream, kernels::launch_geom{}),
+          "pint::cuda::repack");
+#else
     const void* p[sizeof...(Bits) + 1];
     for (size_t i = 0; i < sizeof...(Bits) + 1; ++i) p[i] = planes[i];
     check(pint_cuda_repack(&l, p, (int)sizeof(Plane), packed, n, stream), "pint::cuda::repack");
+#endif
 }
 
 // Dense bit-stream storage (include/pint_cuda.h, "dense" section): element i of

@@ -123,11 +123,16 @@ struct static_masks {
 // at a fixed offset of the kernel parameter (constant bank operands cost
 // nothing; a loop over a table with a dynamic index does -- measured 2x slower).
 // Single-width layouts move the flag with one shift; all others smear.
-template <class Word>
+// Steps: how many smear steps the fill runs.  The default (all of them: 5 for 32-bit Words, 6 for
+// 64-bit ones) serves any layout; the run-time-mask launcher picks a 2- or 4-step instantiation
+// when the widest field is at most 4 / 16 bits (generic.cu), so that narrow-field layouts do not
+// pay for steps whose keep mask is zero.
+template <class Word, int Steps = (sizeof(Word) == 8 ? 6 : 5)>
 struct runtime_masks {
     using word = Word;
     static constexpr bool heavy_fill = true;
     static constexpr bool compiled_in = false;
+    static constexpr int steps = Steps;
     Word mH, mL, mA, mM1, mHL, mLM1;
     Word keep[6];
     uint32_t shift0;   // w - 1 when all fields have the same width
@@ -147,16 +152,16 @@ struct runtime_masks {
     __device__ __forceinline__ word fill(word c) const
     {
         if (nsmear == 0) return c | (c - (c >> shift0));
-        // all steps, unconditionally: keep[k] is 0 for the steps a layout does not need.  Skipping
+        // all Steps steps, unconditionally: keep[k] is 0 for the steps a layout does not need.  Skipping
         // them with warp-uniform branches on nsmear was measured and is slower where it matters
         // (padded <7,9,3> add_signed_saturate 6226 -> 5181 GB/s, profiles/r01q_extra.jsonl).
         word x = c;
-        x |= (x >> 1) & keep[0];
-        x |= (x >> 2) & keep[1];
-        x |= (x >> 4) & keep[2];
-        x |= (x >> 8) & keep[3];
-        x |= (x >> 16) & keep[4];
-        if constexpr (sizeof(Word) == 8) x |= (x >> 32) & keep[5];
+        if constexpr (Steps >= 1) x |= (x >> 1) & keep[0];
+        if constexpr (Steps >= 2) x |= (x >> 2) & keep[1];
+        if constexpr (Steps >= 3) x |= (x >> 4) & keep[2];
+        if constexpr (Steps >= 4) x |= (x >> 8) & keep[3];
+        if constexpr (Steps >= 5) x |= (x >> 16) & keep[4];
+        if constexpr (Steps >= 6 && sizeof(Word) == 8) x |= (x >> 32) & keep[5];
         return x;
     }
     __device__ __forceinline__ word below(word c) const

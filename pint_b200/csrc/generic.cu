@@ -20,8 +20,22 @@ cudaError_t binary_one(bool fused, const layout_desc& d, const void* a, const vo
         Fn fn{{make_field_table<W>(d), make_word_masks<W>(d).A}};
         return launch_binary<Elem, Fn>(a, b, out, n, fn, s, g);
     }
+    const auto m = make_word_masks<W>(d);
+    // ops that build a field-wide mask run only as many smear steps as the widest field needs
+    // (2 steps: fields up to 4 bits, 4 steps: up to 16 bits; profiles/: <7,9,3> add_signed_saturate)
+    constexpr bool fills = !(Op == OP_ADD_WRAP || Op == OP_SUB_WRAP || Op == OP_OR || Op == OP_AND || Op == OP_XOR);
+    if constexpr (fills) {
+        if (m.nsh > 1 && m.nsmear <= 2) {
+            using Fn = swar_fn<Op, runtime_masks<W, 2>>;
+            return launch_binary<Elem, Fn>(a, b, out, n, Fn{runtime_masks<W, 2>(m)}, s, g);
+        }
+        if (m.nsh > 1 && m.nsmear <= 4) {
+            using Fn = swar_fn<Op, runtime_masks<W, 4>>;
+            return launch_binary<Elem, Fn>(a, b, out, n, Fn{runtime_masks<W, 4>(m)}, s, g);
+        }
+    }
     using Fn = swar_fn<Op, runtime_masks<W>>;
-    Fn fn{runtime_masks<W>(make_word_masks<W>(d))};
+    Fn fn{runtime_masks<W>(m)};
     return launch_binary<Elem, Fn>(a, b, out, n, fn, s, g);
 }
 

@@ -165,6 +165,18 @@ def test_cpp_template_layer():
     assert "0 failures" in out.stdout
 
 
+def test_cpp_template_layer_compiled_by_nvcc():
+    """include/pint/cuda.hpp under nvcc instantiates the kernels for static_layout<Integer, Bits...> in the
+    user's translation unit (compiled-in constants for ANY layout): every op on four unregistered layouts
+    equals the library's parity-tested run-time-mask path bit for bit (tests/cpp/cuda_api_nvcc_test.cu)."""
+    exe = os.path.join(ROOT, "build", "cuda_api_nvcc_test")
+    if not os.path.exists(exe):
+        pytest.skip("build/cuda_api_nvcc_test not built (make tools)")
+    out = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert "total: 0 failures" in out.stdout
+
+
 def test_sharded_host_arrays_all_devices(oracle):
     """pint_cuda_sharded_binary_multi_host: HOST arrays split over every visible device, each shard
     through its device's ring; ragged n, several layouts, small chunks (many slot reuses)."""

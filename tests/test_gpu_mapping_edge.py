@@ -30,11 +30,10 @@ def test_probe_traps_a_stray_access():
 
 def test_round1_library_is_caught():
     """build/r1_regress/libpint_cuda_r1.so = this tree with round 1's pairs_reduce
-    (atomicXor(sum_dev + 1, 0)), built by tools/build_r1_regress.sh where git
-    history is available: the probe must fail on it."""
+    (atomicXor(sum_dev + 1, 0), VERDICT r1 weak #1), built by `make tools`: the probe must fail on it."""
     old = os.path.join(ROOT, "build", "r1_regress", "libpint_cuda_r1.so")
     if not os.path.exists(old):
-        pytest.skip("regression library not built (tools/build_r1_regress.sh)")
+        pytest.skip("regression library not built (make tools)")
     r = run_probe("--lib", old)
     assert r.returncode != 0, "round 1's out-of-bounds atomic went unnoticed:\n" + r.stdout[-2000:]
     assert "pairs_reduce" in r.stdout + r.stderr

@@ -194,3 +194,18 @@ def test_jit_prebuild_without_a_device(tmp_path, monkeypatch):
     assert lib.pint_cuda_jit_prebuild(L.ref, 7, 0) == -15                      # not a target this library has
     bad = pint_b200._lib.PintLayout(4, 2, (pint_b200._lib.C.c_uint8 * 64)(20, 20))
     assert lib.pint_cuda_jit_prebuild(bad, 10, 0) == -5                        # the reference's static_assert (pint.hpp:763)
+
+
+def test_mask_generator_equals_reference_metafunctions_at_compile_time():
+    """tests/cpp/static_masks_check.cpp static_asserts H / L / A / saturation-mask type of
+    static_layout<Integer, Bits...> against the reference's metafunctions (pint.hpp:324-348, 443-456)
+    for every layout of oracle/ref_layouts.def: compiling it IS the test."""
+    import shutil
+    import subprocess
+    ref = "/root/reference/include/pint/pint.hpp"
+    if not os.path.exists(ref) or not shutil.which("g++"):
+        pytest.skip("needs /root/reference and g++ (build container only)")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run(["g++", "-std=c++17", "-fsyntax-only", "-Iinclude", "-I/root/reference/include", "-Ioracle",
+                        "tests/cpp/static_masks_check.cpp"], cwd=root, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-3000:]

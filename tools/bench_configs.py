@@ -115,6 +115,30 @@ def main():
         L = pint_b200.Layout(8, 3, 7, 11, 13, 17, 13)
         binary_case("C4 (per-GPU share: 8 GiB/array)", L, 1 << 30, ["add_signed_saturate", "add_unsigned_saturate"], fused=True)
         binary_case("C4-swar (same op, SWAR kernel)", L, 1 << 30, ["add_signed_saturate", "add_unsigned_saturate"])
+    if "jit" in which:
+        # layouts without pre-built constants: run-time masks (smear steps bucketed by the widest field) against
+        # the same kernel templates specialised at run time by NVRTC (option "jit"); first call compiles
+        for LL in (pint_b200.Layout(4, 7, 9, 3), pint_b200.Layout(4, 5, 6, 5, 3), pint_b200.Layout(8, 10, 10, 10, 10), pint_b200.Layout(2, 4, 4, 4)):
+            for jit in (0, 2):
+                ops.set_option("jit", jit)
+                n = 1 << 30 if LL.elem_bytes <= 4 else 1 << 29
+                a, b = alloc(LL, n, 1), alloc(LL, n, 2)
+                o = torch.empty_like(a)
+                for op in ("add_unsigned_saturate", "add_signed_saturate", "min_signed", "add_wrap"):
+                    best, med = timed(lambda i: ops.binary(op, LL, a, b, out=o))
+                    report("unregistered layout", n, 3 * LL.elem_bytes, best, med, op=op, layout=repr(LL),
+                           kernel="NVRTC-specialised (compiled-in masks)" if jit else "run-time masks")
+                if jit:
+                    o2 = torch.empty_like(a)
+                    pair = ["add_unsigned_saturate", "add_signed_saturate"]
+                    best, med = timed(lambda i: ops.binary_multi(pair, LL, a, b, outs=[o, o2]))
+                    report("unregistered layout, two ops one pass", n, 4 * LL.elem_bytes, best, med, op="+".join(pair), layout=repr(LL), kernel="NVRTC-specialised pair")
+                    best, med = timed(lambda i: ops.binary("add_signed_saturate", LL, a, b, out=o, fused=True))
+                    report("unregistered layout, fused", n, 3 * LL.elem_bytes, best, med, op="add_signed_saturate", layout=repr(LL), kernel="NVRTC-specialised fused")
+                    del o2
+                del a, b, o
+                torch.cuda.empty_cache()
+        ops.set_option("jit", 0)
     if "extra" in which:
         binary_case("bench-layout type2", pint_b200.Layout(4, 1, 2, 3, 4, 5, 6, 11), 1 << 30, ["add_wrap", "add_unsigned_saturate", "add_signed_saturate"])
         binary_case("u8 <1,1,1>", pint_b200.Layout(1, 1, 1, 1), 1 << 30, ["add_signed_saturate", "sub_wrap"])
