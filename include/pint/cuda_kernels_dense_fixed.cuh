@@ -81,6 +81,28 @@ __device__ __forceinline__ void load_plane_quads(const void* plane, size_t q0, u
             v[q + 1][0] = uint64_t(int64_t(int32_t(x.hi.x))); v[q + 1][1] = uint64_t(int64_t(int32_t(x.hi.y)));
             v[q + 1][2] = uint64_t(int64_t(int32_t(x.hi.z))); v[q + 1][3] = uint64_t(int64_t(int32_t(x.hi.w)));
         }
+    } else if constexpr (PlaneBytes == 1 && NQ % 4 == 0) {
+        // narrow planes: 16 consecutive int8 values per 16-byte load (the caller's units start on 16-byte
+        // boundaries of every plane: unit_in_bytes is a multiple of 16)
+#pragma unroll
+        for (uint32_t q = 0; q < NQ; q += 4) {
+            const uint4 x = ld16<CACHE_STREAMING>(reinterpret_cast<const uint4*>(static_cast<const uint32_t*>(plane) + q0 + q));
+            const uint32_t w[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+            for (uint32_t k = 0; k < 4; ++k)
+#pragma unroll
+                for (uint32_t i = 0; i < 4; ++i) v[q + k][i] = uint64_t(int64_t(int8_t(w[k] >> (8 * i))));
+        }
+    } else if constexpr (PlaneBytes == 2 && NQ % 2 == 0) {
+#pragma unroll
+        for (uint32_t q = 0; q < NQ; q += 2) {
+            const uint4 x = ld16<CACHE_STREAMING>(reinterpret_cast<const uint4*>(static_cast<const uint2*>(plane) + q0 + q));
+            const uint32_t w[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+            for (uint32_t k = 0; k < 2; ++k)
+#pragma unroll
+                for (uint32_t i = 0; i < 4; ++i) v[q + k][i] = uint64_t(int64_t(int16_t(w[2 * k + (i >> 1)] >> (16 * (i & 1)))));
+        }
     } else {
 #pragma unroll
         for (uint32_t q = 0; q < NQ; ++q) load_plane_quad<PlaneBytes>(plane, q0 + q, v[q]);
@@ -336,6 +358,9 @@ cudaError_t launch_dense_insert_fixed(const void* other, void* dense, size_t n, 
     // to bring the output tile to ~16 KB
     unsigned T = 256;
     while (T > 32 && T * Geo::unit_out_bytes > 16384) T >>= 1;
+    // a thread takes at least UB units per round (narrow planes: up to 64 elements in flight): keep that tile
+    // within the 48 KB a kernel gets without opting in
+    while (T > 32 && T * Geo::UB * Geo::unit_out_bytes > 32768) T >>= 1;
     uint32_t upt = 16384 / (T * Geo::unit_out_bytes) / Geo::UB * Geo::UB;
     if (upt < Geo::UB) upt = Geo::UB;
     const size_t smem = size_t(T) * upt * Geo::unit_out_bytes;
@@ -380,20 +405,24 @@ cudaError_t launch_dense_insert_fixed(const void* other, void* dense, size_t n, 
 // uint16_t / uint64_t elements, where it wins on the same box (profiles/r03m_ab_dense_convert.log:
 // 7-bit 3662 -> 5454, 12-bit 5669 -> 6035, 63-bit 5277 -> 6785 GB/s; 32-byte stores for uint64_t);
 // for uint32_t elements and for planes the run-time-geometry kernel stays 0-2 % ahead and is kept.
-template <class Elem, uint32_t S, int Side>
+template <class Elem, uint32_t S, int Side, int PlaneBytes = 4>
 struct group_geom {
     using W = typename std::conditional<(S <= 32), uint32_t, uint64_t>::type;
     static constexpr uint32_t WB = 8 * sizeof(W);
-    static constexpr uint32_t GP = Side == SIDE_PADDED ? (sizeof(Elem) >= 4 ? 4u : 16u / uint32_t(sizeof(Elem))) : 4u;
+    // planes of 1 or 2 bytes: 16 / PlaneBytes elements per thread, so that every plane store is one 16-byte vector
+    // (dense RGB24 -> three uint8 planes ran at 4.6 TB/s with quads: 4-byte stores, issue-bound)
+    static constexpr uint32_t GP = Side == SIDE_PADDED ? (sizeof(Elem) >= 4 ? 4u : 16u / uint32_t(sizeof(Elem)))
+                                                       : (PlaneBytes <= 2 ? 16u / uint32_t(PlaneBytes) : 4u);
     static constexpr uint32_t NA = (GP * S + WB - 1) / WB;  // aligned words that hold the group
     static constexpr uint32_t NW = NA + 1;                  // words loaded: the group may start anywhere in the first
 };
 
 template <class Elem, uint32_t S, int Side, int PlaneBytes, bool Signed>
 __global__ void __launch_bounds__(256)
-dense_extract_fixed_kernel(const uint4* dense, Elem* padded, uint32_t tile_elems, const __grid_constant__ dense_fields f)
+dense_extract_fixed_kernel(const uint4* dense, Elem* padded, uint32_t tile_elems, const __grid_constant__ dense_fields f,
+                           uint32_t narrow_signed = 0)
 {
-    using Geo = group_geom<Elem, S, Side>;
+    using Geo = group_geom<Elem, S, Side, PlaneBytes>;
     using W = typename Geo::W;
     constexpr uint32_t GP = Geo::GP, NA = Geo::NA, NW = Geo::NW, WB = Geo::WB;
     extern __shared__ __align__(128) unsigned char dense_smem[];
@@ -449,6 +478,26 @@ dense_extract_fixed_kernel(const uint4* dense, Elem* padded, uint32_t tile_elems
                 for (uint32_t i = 0; i < PV; ++i) v.x[i] = Elem(x[i]);
                 st16<CACHE_STREAMING>(reinterpret_cast<uint4*>(padded + e0), v.q);
             }
+        } else if constexpr (PlaneBytes <= 2) {
+            // GP values per plane as ONE 16-byte store; get / get_signed (pint.hpp:799-822) narrowed to the plane
+            // type as a C cast does.  The sign is a run-time (uniform) flag here: (v ^ m) - m with m = the field's
+            // sign bit extends, m = 0 leaves the unsigned value.
+            for (uint32_t fi = 0; fi < f.t.nfields; ++fi) {
+                void* plane = f.planes.p[fi];
+                if (!plane) continue;
+                const uint32_t foff = f.t.off[fi], wdt = f.t.bits[fi];
+                const W fm = ones_w<W>(wdt);
+                const W sm = narrow_signed ? W(W(1) << (wdt - 1)) : W(0);
+                uint32_t o[4] = {0, 0, 0, 0};
+#pragma unroll
+                for (uint32_t i = 0; i < GP; ++i) {
+                    const W u = W(x[i] >> foff) & fm;
+                    const uint32_t v = uint32_t(W(u ^ sm) - sm);
+                    if constexpr (PlaneBytes == 1) o[i >> 2] |= (v & 0xFFu) << (8 * (i & 3));
+                    else o[i >> 1] |= (v & 0xFFFFu) << (16 * (i & 1));
+                }
+                st16<CACHE_STREAMING>(reinterpret_cast<uint4*>(static_cast<unsigned char*>(plane) + e0 * PlaneBytes), make_uint4(o[0], o[1], o[2], o[3]));
+            }
         } else {
             for (uint32_t fi = 0; fi < f.t.nfields; ++fi) {
                 void* plane = f.planes.p[fi];
@@ -468,9 +517,9 @@ dense_extract_fixed_kernel(const uint4* dense, Elem* padded, uint32_t tile_elems
 // uint64_t padded array, which is stored with 32-byte vectors).
 template <class Elem, uint32_t S, int Side, int PlaneBytes, bool Signed>
 cudaError_t launch_dense_extract_fixed(const void* dense, void* other, size_t n, const dense_fields& f, cudaStream_t stream,
-                                       const launch_geom& g, size_t* done)
+                                       const launch_geom& g, size_t* done, uint32_t narrow_signed = 0)
 {
-    using W = typename group_geom<Elem, S, Side>::W;
+    using W = typename group_geom<Elem, S, Side, PlaneBytes>::W;
     const uint32_t tile_elems = convert_tile_elems(S);  // ~16 KB of stream, a multiple of 128 elements
     const size_t smem = size_t(tile_elems) / 8 * S + 16;
     const size_t ntiles = n / tile_elems;
@@ -479,7 +528,7 @@ cudaError_t launch_dense_extract_fixed(const void* dense, void* other, size_t n,
     if (ntiles > 0x7FFFFFFFull) return cudaErrorInvalidValue;
     (void)sizeof(W);
     dense_extract_fixed_kernel<Elem, S, Side, PlaneBytes, Signed><<<unsigned(ntiles), 256, smem, stream>>>(
-        static_cast<const uint4*>(dense), static_cast<Elem*>(other), tile_elems, f);
+        static_cast<const uint4*>(dense), static_cast<Elem*>(other), tile_elems, f, narrow_signed);
     count_launch(g);
     return cudaGetLastError();
 }

@@ -197,7 +197,9 @@ static_assert(chunk_layout<12>::kN == 3 && chunk_layout<12>::masks.H.w[0] == 0x0
 // 32-bit word of stream this costs what the padded run-time kernels cost per word, and moves the
 // same 12 bytes per word -- so any layout with N <= kMaxMwWords runs at the padded kernels' speed
 // without being compiled in (the element-by-element windows were ALU-bound at 2.8-4.8 TB/s).
-template <int N>
+// Steps: smear steps the fill runs (6 = any layout; the launcher picks 2 / 4 when the widest field has at
+// most 4 / 16 bits -- a step on mw<N> is N funnel shifts and 2 N logic ops, so skipped steps count here).
+template <int N, int Steps = 6>
 struct runtime_chunk_masks {
     using word = mw<N>;
     static constexpr bool heavy_fill = true;
@@ -222,12 +224,13 @@ struct runtime_chunk_masks {
     {
         if (nsmear == 0) return c | (c - (c >> shift0));
         word x = c;
-        x |= (x >> 1) & keep[0];
-        x |= (x >> 2) & keep[1];
-        x |= (x >> 4) & keep[2];
-        x |= (x >> 8) & keep[3];
-        x |= (x >> 16) & keep[4];
-        if (nsmear > 5) x |= (x >> 32) & keep[5];  // fields wider than 32 bits only
+        if constexpr (Steps >= 1) x |= (x >> 1) & keep[0];
+        if constexpr (Steps >= 2) x |= (x >> 2) & keep[1];
+        if constexpr (Steps >= 3) x |= (x >> 4) & keep[2];
+        if constexpr (Steps >= 4) x |= (x >> 8) & keep[3];
+        if constexpr (Steps >= 5) x |= (x >> 16) & keep[4];
+        if constexpr (Steps >= 6)
+            if (nsmear > 5) x |= (x >> 32) & keep[5];  // fields wider than 32 bits only
         return x;
     }
     __device__ __forceinline__ word below(const word& c) const

@@ -3,6 +3,7 @@
 #include "api_common.hpp"
 #include "dense_registry.hpp"
 #include "pint/cuda_kernels_dense_convert.cuh"
+#include "pint/cuda_kernels_dense_bytes.cuh"
 
 namespace pint_cuda_impl {
 namespace {
@@ -88,17 +89,23 @@ cudaError_t insert_fixed(uint32_t S, uint32_t elem_bytes, int plane_bytes, const
 }
 
 // dense -> padded with S compiled in: uint8_t / uint16_t / uint64_t elements (dense_fixed.cu says why)
-cudaError_t extract_fixed(uint32_t S, uint32_t elem_bytes, const void* dn, void* other, size_t n, cudaStream_t s, size_t* done)
+cudaError_t extract_fixed(uint32_t S, uint32_t elem_bytes, const void* dn, void* other, size_t n, cudaStream_t s, size_t* done,
+                          int plane_bytes = 0, bool is_signed = false, const dense::dense_fields* planes = nullptr)
 {
     *done = 0;
-    if (opts().dense_windows || reinterpret_cast<uintptr_t>(other) % 16) return cudaSuccess;
+    if (opts().dense_windows) return cudaSuccess;
+    uintptr_t align = reinterpret_cast<uintptr_t>(other);
+    const dense::dense_fields none{};
+    const dense::dense_fields& f = planes ? *planes : none;
+    if (planes)
+        for (uint32_t i = 0; i < f.t.nfields; ++i) align |= reinterpret_cast<uintptr_t>(f.planes.p[i]);
+    if (align % 16) return cudaSuccess;
     const launch_geom g = geom();
-    const dense::dense_fields f{};
     cudaError_t rc = cudaSuccess;
-    if (dense_extract_fixed_part0(S, elem_bytes, dn, other, n, f, s, g, done, &rc) ||
-        dense_extract_fixed_part1(S, elem_bytes, dn, other, n, f, s, g, done, &rc) ||
-        dense_extract_fixed_part2(S, elem_bytes, dn, other, n, f, s, g, done, &rc) ||
-        dense_extract_fixed_part3(S, elem_bytes, dn, other, n, f, s, g, done, &rc))
+    if (dense_extract_fixed_part0(S, elem_bytes, plane_bytes, is_signed, dn, other, n, f, s, g, done, &rc) ||
+        dense_extract_fixed_part1(S, elem_bytes, plane_bytes, is_signed, dn, other, n, f, s, g, done, &rc) ||
+        dense_extract_fixed_part2(S, elem_bytes, plane_bytes, is_signed, dn, other, n, f, s, g, done, &rc) ||
+        dense_extract_fixed_part3(S, elem_bytes, plane_bytes, is_signed, dn, other, n, f, s, g, done, &rc))
         return rc;
     return cudaSuccess;
 }
@@ -198,11 +205,54 @@ int planes_impl(bool to_dense, const pint_layout* layout, int is_signed, const v
         f.planes.p[i] = const_cast<void*>(planes[i]);
     }
     const uint32_t S = total_bits(d);
-    if (to_dense && plane_bytes >= 4) {  // (the compiled-in-S insert kernels take 4- and 8-byte planes)
+    if (S == 8 || S == 16 || S == 32 || S == 64) {
+        // no padding to remove: the stream IS the padded array of make_packed_int's Integer, and the padded
+        // unpack / repack kernels (group form for narrow planes) serve it; the stream's tail past n stays zero
+        pint_layout p = *layout;
+        p.elem_bytes = S / 8;
+        if (!to_dense) return pint_cuda_unpack(&p, is_signed, dense, const_cast<void* const*>(planes), plane_bytes, n, (pint_stream_t)s);
+        if (int rc = pint_cuda_repack(&p, planes, plane_bytes, const_cast<void*>(dense), n, (pint_stream_t)s)) return rc;
+        const size_t used = n * p.elem_bytes, total = dense_bytes(S, n);
+        if (total > used) return (int)cudaMemsetAsync(static_cast<char*>(const_cast<void*>(dense)) + used, 0, total - used, s);
+        return PINT_OK;
+    }
+    // every field exactly one plane value wide (RGB24 <-> three uint8_t planes, RGB48 <-> three uint16_t
+    // planes ...): interleaved <-> planar is a byte permutation (cuda_kernels_dense_bytes.cuh)
+    {
+        bool bytes_only = plane_bytes <= 2 && !opts().dense_windows;
+        uintptr_t align = 0;
+        for (uint32_t i = 0; i < d.nfields; ++i) {
+            bytes_only = bytes_only && d.bits[i] == 8 * plane_bytes;
+            align |= reinterpret_cast<uintptr_t>(planes[i]);
+        }
+        if (bytes_only && align % 16 == 0) {
+            size_t done = 0;
+            cudaError_t rc = cudaSuccess;
+            if (dense::dense_bytes_dispatch(d.nfields, plane_bytes, to_dense, f.planes, const_cast<void*>(dense), n, s, geom(), &done, &rc)) {
+                if (rc != cudaSuccess) return (int)rc;
+                if (done == n) return PINT_OK;
+                for (uint32_t i = 0; i < d.nfields; ++i)
+                    if (f.planes.p[i]) f.planes.p[i] = static_cast<char*>(f.planes.p[i]) + done * plane_bytes;
+                dense = static_cast<const char*>(dense) + done / 8 * S;
+                n -= done;
+                planes = nullptr;  // (f.planes carries the advanced pointers from here on)
+            }
+        }
+    }
+    // kernels with S compiled in take the whole tiles: every plane width into a stream, 1- and 2-byte planes
+    // out of one (for 4- and 8-byte planes the run-time-geometry kernel is as fast, profiles/r03m_ab_dense_convert.log)
+    if (to_dense || plane_bytes <= 2) {
         size_t done = 0;
-        if (cudaError_t rc = insert_fixed(S, 0, plane_bytes, nullptr, const_cast<void*>(dense), n, f, s, &done)) return (int)rc;
+        bool all = true;
+        for (uint32_t i = 0; i < d.nfields; ++i) all = all && f.planes.p[i];
+        if (to_dense) {
+            if (cudaError_t rc = insert_fixed(S, 0, plane_bytes, nullptr, const_cast<void*>(dense), n, f, s, &done)) return (int)rc;
+        } else if (all) {
+            if (cudaError_t rc = extract_fixed(S, 0, dense, nullptr, n, s, &done, plane_bytes, is_signed != 0, &f)) return (int)rc;
+        }
         if (done == n) return PINT_OK;
-        for (uint32_t i = 0; i < d.nfields; ++i) f.planes.p[i] = static_cast<char*>(f.planes.p[i]) + done * plane_bytes;
+        for (uint32_t i = 0; i < d.nfields; ++i)
+            if (f.planes.p[i]) f.planes.p[i] = static_cast<char*>(f.planes.p[i]) + done * plane_bytes;
         dense = static_cast<const char*>(dense) + done / 8 * S;
         n -= done;
     }

@@ -29,6 +29,10 @@ bool insert_s(uint32_t elem_bytes, int plane_bytes, const void* other, void* dn,
     if (elem_bytes) {
         if (elem_bytes != sizeof(E)) return false;
         *rc = dense::launch_dense_insert_fixed<E, S, dense::SIDE_PADDED, 4>(other, dn, n, f, s, g, done);
+    } else if (plane_bytes == 1) {
+        *rc = dense::launch_dense_insert_fixed<W, S, dense::SIDE_PLANES, 1>(nullptr, dn, n, f, s, g, done);
+    } else if (plane_bytes == 2) {
+        *rc = dense::launch_dense_insert_fixed<W, S, dense::SIDE_PLANES, 2>(nullptr, dn, n, f, s, g, done);
     } else if (plane_bytes == 4) {
         *rc = dense::launch_dense_insert_fixed<W, S, dense::SIDE_PLANES, 4>(nullptr, dn, n, f, s, g, done);
     } else {
@@ -37,14 +41,22 @@ bool insert_s(uint32_t elem_bytes, int plane_bytes, const void* other, void* dn,
     return true;
 }
 
-// dense -> padded only, and not for uint32_t: same-box A/B (profiles/r03m_ab_dense_convert.log) has the
+// dense -> padded (not for uint32_t) and dense -> planes of 1 or 2 bytes: same-box A/B (profiles/r03m_ab_dense_convert.log) has the
 // group-owner kernel ahead for uint8_t / uint16_t / uint64_t elements (5454 vs 3662, 6035 vs 5669,
 // 6785 vs 5277 GB/s) and 2 % behind the run-time-geometry kernel for uint32_t and for planes.
 template <uint32_t S>
-bool extract_s(uint32_t elem_bytes, const void* dn, void* other, size_t n, const dense::dense_fields& f, cudaStream_t s,
-               const launch_geom& g, size_t* done, cudaError_t* rc)
+bool extract_s(uint32_t elem_bytes, int plane_bytes, bool is_signed, const void* dn, void* other, size_t n,
+               const dense::dense_fields& f, cudaStream_t s, const launch_geom& g, size_t* done, cudaError_t* rc)
 {
     using E = natural_int<S>;
+    if (!elem_bytes) {
+        // dense -> planes of 1 or 2 bytes: 16 / plane_bytes elements per thread, one 16-byte store per plane
+        using W = typename dense::fixed_geom<S, 4>::W;
+        if (plane_bytes == 1) *rc = dense::launch_dense_extract_fixed<W, S, dense::SIDE_PLANES, 1, false>(dn, nullptr, n, f, s, g, done, is_signed ? 1u : 0u);
+        else if (plane_bytes == 2) *rc = dense::launch_dense_extract_fixed<W, S, dense::SIDE_PLANES, 2, false>(dn, nullptr, n, f, s, g, done, is_signed ? 1u : 0u);
+        else return false;
+        return true;
+    }
     if constexpr (sizeof(E) == 4) {
         return false;
     } else {
@@ -56,15 +68,15 @@ bool extract_s(uint32_t elem_bytes, const void* dn, void* other, size_t n, const
 }
 
 template <uint32_t Lo, uint32_t Hi>
-bool extract_range(uint32_t S, uint32_t elem_bytes, const void* dn, void* other, size_t n, const dense::dense_fields& f,
-                   cudaStream_t s, const launch_geom& g, size_t* done, cudaError_t* rc)
+bool extract_range(uint32_t S, uint32_t elem_bytes, int plane_bytes, bool is_signed, const void* dn, void* other, size_t n,
+                   const dense::dense_fields& f, cudaStream_t s, const launch_geom& g, size_t* done, cudaError_t* rc)
 {
     if constexpr (Lo >= Hi) {
         return false;
     } else {
         if constexpr (Lo != 0 && Lo != 8 && Lo != 16 && Lo != 32)
-            if (S == Lo) return extract_s<Lo>(elem_bytes, dn, other, n, f, s, g, done, rc);
-        return extract_range<Lo + 1, Hi>(S, elem_bytes, dn, other, n, f, s, g, done, rc);
+            if (S == Lo) return extract_s<Lo>(elem_bytes, plane_bytes, is_signed, dn, other, n, f, s, g, done, rc);
+        return extract_range<Lo + 1, Hi>(S, elem_bytes, plane_bytes, is_signed, dn, other, n, f, s, g, done, rc);
     }
 }
 
@@ -95,11 +107,12 @@ bool PINT_CAT(dense_insert_fixed_part, PINT_FIXED_PART)(uint32_t S, uint32_t ele
                                                                           done, rc);
 }
 
-bool PINT_CAT(dense_extract_fixed_part, PINT_FIXED_PART)(uint32_t S, uint32_t elem_bytes, const void* dn, void* other, size_t n,
-                                                         const dense::dense_fields& f, cudaStream_t s, const launch_geom& g,
-                                                         size_t* done, cudaError_t* rc)
+bool PINT_CAT(dense_extract_fixed_part, PINT_FIXED_PART)(uint32_t S, uint32_t elem_bytes, int plane_bytes, bool is_signed,
+                                                         const void* dn, void* other, size_t n, const dense::dense_fields& f,
+                                                         cudaStream_t s, const launch_geom& g, size_t* done, cudaError_t* rc)
 {
-    return extract_range<16 * PINT_FIXED_PART, 16 * PINT_FIXED_PART + 16>(S, elem_bytes, dn, other, n, f, s, g, done, rc);
+    return extract_range<16 * PINT_FIXED_PART, 16 * PINT_FIXED_PART + 16>(S, elem_bytes, plane_bytes, is_signed, dn, other, n, f, s,
+                                                                           g, done, rc);
 }
 
 }  // namespace pint_cuda_impl

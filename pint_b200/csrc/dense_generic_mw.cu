@@ -17,10 +17,25 @@ template <int N, int... Ops>
 cudaError_t binary_n(int op, const layout_desc& d, uint32_t S, const void* a, const void* b, void* out, size_t n,
                      cudaStream_t s, const launch_geom& g, const dense_tuning& tune, std::integer_sequence<int, Ops...>)
 {
-    using P = dense::runtime_chunk_masks<N>;
-    const P p(dense::make_chunk_masks<N>(d));
+    const auto m = dense::make_chunk_masks<N>(d);
     cudaError_t rc = cudaErrorInvalidValue;
-    ((op == Ops ? (rc = dense::launch_dense_binary(a, b, out, n, swar_fn<Ops, P>{p}, dense::mw_geom<N>{S, 1}, s, g, tune), 0) : 0), ...);
+    auto run = [&](auto steps_tag, auto op_tag) {
+        constexpr int St = decltype(steps_tag)::value, Op = decltype(op_tag)::value;
+        using P = dense::runtime_chunk_masks<N, St>;
+        rc = dense::launch_dense_binary(a, b, out, n, swar_fn<Op, P>{P(m)}, dense::mw_geom<N>{S, 1}, s, g, tune);
+    };
+    // ops that build a field-wide mask run only as many smear steps as the widest field needs
+    const int steps = m.nsh > 1 && m.nsmear <= 2 ? 2 : (m.nsh > 1 && m.nsmear <= 4 ? 4 : 6);
+    auto pick = [&](auto op_tag) {
+        constexpr int Op = decltype(op_tag)::value;
+        constexpr bool fills = !(Op == OP_ADD_WRAP || Op == OP_SUB_WRAP || Op == OP_OR || Op == OP_AND || Op == OP_XOR);
+        if constexpr (fills) {
+            if (steps == 2) return run(std::integral_constant<int, 2>{}, op_tag);
+            if (steps == 4) return run(std::integral_constant<int, 4>{}, op_tag);
+        }
+        run(std::integral_constant<int, 6>{}, op_tag);
+    };
+    ((op == Ops ? (pick(std::integral_constant<int, Ops>{}), 0) : 0), ...);
     return rc;
 }
 
@@ -29,12 +44,25 @@ cudaError_t pair_n(int pair, const layout_desc& d, uint32_t S, const void* a, co
                    size_t n, cudaStream_t s, const launch_geom& g, const dense_tuning& tune,
                    std::integer_sequence<int, Pairs...>)
 {
-    using P = dense::runtime_chunk_masks<N>;
-    const P p(dense::make_chunk_masks<N>(d));
+    const auto m = dense::make_chunk_masks<N>(d);
     cudaError_t rc = cudaErrorInvalidValue;
-    ((pair == Pairs ? (rc = dense::launch_dense_binary<pair_fn<kOpPairs[Pairs][0], kOpPairs[Pairs][1], P>, dense::mw_geom<N>, true>(
-                                a, b, out0, n, pair_fn<kOpPairs[Pairs][0], kOpPairs[Pairs][1], P>{p}, dense::mw_geom<N>{S, 1}, s,
-                                g, tune, out1), 0) : 0), ...);
+    auto run = [&](auto steps_tag, auto pair_tag) {
+        constexpr int St = decltype(steps_tag)::value, Pi = decltype(pair_tag)::value;
+        using P = dense::runtime_chunk_masks<N, St>;
+        using Fn = pair_fn<kOpPairs[Pi][0], kOpPairs[Pi][1], P>;
+        rc = dense::launch_dense_binary<Fn, dense::mw_geom<N>, true>(a, b, out0, n, Fn{P(m)}, dense::mw_geom<N>{S, 1}, s, g, tune, out1);
+    };
+    const int steps = m.nsh > 1 && m.nsmear <= 2 ? 2 : (m.nsh > 1 && m.nsmear <= 4 ? 4 : 6);
+    auto pick = [&](auto pair_tag) {
+        constexpr int Pi = decltype(pair_tag)::value;
+        constexpr bool fills = !(kOpPairs[Pi][0] == OP_ADD_WRAP && kOpPairs[Pi][1] == OP_SUB_WRAP);
+        if constexpr (fills) {
+            if (steps == 2) return run(std::integral_constant<int, 2>{}, pair_tag);
+            if (steps == 4) return run(std::integral_constant<int, 4>{}, pair_tag);
+        }
+        run(std::integral_constant<int, 6>{}, pair_tag);
+    };
+    ((pair == Pairs ? (pick(std::integral_constant<int, Pairs>{}), 0) : 0), ...);
     return rc;
 }
 

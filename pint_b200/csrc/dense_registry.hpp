@@ -43,14 +43,15 @@ PINT_MW_PART_DECL(2)
 // conversions into a dense stream with S compiled in (dense_fixed.cu, part p covers S in [16 p, 16 p + 16));
 // elem_bytes != 0: padded elements of that Integer, else planes of plane_bytes each.  false: no kernel for
 // this (S, Integer).  Converts whole tiles only: *done elements, the caller finishes the rest.
-// dense_extract_fixed_part: dense -> padded for uint8_t / uint16_t / uint64_t elements.
+// dense_extract_fixed_part: dense -> padded for uint8_t / uint16_t / uint64_t elements (elem_bytes != 0), dense -> planes
+// of 1 or 2 bytes (elem_bytes == 0).
 #define PINT_FIXED_PART_DECL(P)                                                                                       \
     bool dense_insert_fixed_part##P(uint32_t S, uint32_t elem_bytes, int plane_bytes, const void* other, void* dn,    \
                                     size_t n, const pint::cuda::kernels::dense::dense_fields& f, cudaStream_t s,      \
                                     const launch_geom& g, size_t* done, cudaError_t* rc);                             \
-    bool dense_extract_fixed_part##P(uint32_t S, uint32_t elem_bytes, const void* dn, void* other, size_t n,          \
-                                     const pint::cuda::kernels::dense::dense_fields& f, cudaStream_t s,               \
-                                     const launch_geom& g, size_t* done, cudaError_t* rc);
+    bool dense_extract_fixed_part##P(uint32_t S, uint32_t elem_bytes, int plane_bytes, bool is_signed, const void* dn, \
+                                     void* other, size_t n, const pint::cuda::kernels::dense::dense_fields& f,        \
+                                     cudaStream_t s, const launch_geom& g, size_t* done, cudaError_t* rc);
 PINT_FIXED_PART_DECL(0)
 PINT_FIXED_PART_DECL(1)
 PINT_FIXED_PART_DECL(2)

@@ -108,12 +108,18 @@ def test_plane_bytes_error_code(P):
 
 
 @pytest.mark.parametrize("eb,bits", [(4, (8, 8, 8)), (4, (7, 9, 3)), (2, (4, 4, 4)), (8, (12, 12, 12)), (8, (16, 16, 16)),
-                                     (1, (2, 3, 2)), (8, (21, 21, 21))])
+                                     (1, (2, 3, 2)), (8, (21, 21, 21)), (8, (10, 10, 10, 10)), (4, (5, 5, 5)), (8, (11, 11, 11)),
+                                     # every field one plane value wide: the byte-permute kernels (interleaved <-> planar)
+                                     (8, (8, 8, 8, 8, 8)), (8, (8, 8, 8, 8, 8, 8)), (8, (8, 8, 8, 8, 8, 8, 8)),
+                                     # S = 8 / 16 / 32 / 64: the stream is the padded array of the natural Integer
+                                     (4, (8, 8, 8, 8)), (2, (5, 6, 5)), (8, (16, 16, 16, 16)), (1, (3, 5)), (8, (8, 8, 8, 8))])
 def test_dense_narrow_planes(P, oracle, eb, bits):
     """Dense streams <-> 1- and 2-byte planes (dense RGB24 <-> three uint8 channels is interleaved <->
     planar RGB at 3 + 3 bytes per pixel): to_planes against get / get_signed of the elements narrowed by
     a C cast, from_planes against pack(field constructor); aligned planes (quads) and planes at an
-    element offset (element-granular), whole tiles plus a remainder."""
+    element offset (element-granular), whole tiles plus a remainder.  Aligned planes with whole tiles run the
+    kernels with S compiled in (16 / plane_bytes elements per thread, one 16-byte access per plane), the
+    rest the run-time-geometry kernels; both must agree with the oracle."""
     pint_b200, ops = P
     from pint_b200 import dense
     L = pint_b200.Layout(eb, *bits)
