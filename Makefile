@@ -51,9 +51,9 @@ oracle:
 
 tools: build/tune build/cpp_api_test build/e2e_ceiling build/cuda_api_nvcc_test build/r1_regress/libpint_cuda_r1.so static_masks_check
 
-build/tune: tools/tune.cu $(HDRS)
+build/tune: tools/tune.cu tools/binary_bulk_variant.cuh $(HDRS)
 	@mkdir -p build
-	$(NVCC) $(NVFLAGS) -o $@ tools/tune.cu
+	$(NVCC) $(NVFLAGS) -Itools -o $@ tools/tune.cu
 
 build/e2e_ceiling: tools/e2e_ceiling.cu include/pint_cuda.h $(LIB)
 	@mkdir -p build

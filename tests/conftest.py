@@ -30,6 +30,13 @@ def ref():
 
 
 @pytest.fixture(scope="session")
+def readme_kats():
+    """The worked examples of the reference's README (lines 100-410) in the KAT format."""
+    with open(os.path.join(GOLDEN, "readme_examples.json")) as f:
+        return json.load(f)["examples"]
+
+
+@pytest.fixture(scope="session")
 def kats():
     with open(os.path.join(GOLDEN, "kat_pint_test.json")) as f:
         return json.load(f)["kats"]

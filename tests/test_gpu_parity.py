@@ -127,8 +127,7 @@ def test_pairs_reduce_large_and_alignments(P, oracle, eb, bits):
         ops.set_option("vec256", 1)
 
 
-def test_reference_kats_through_cuda(P, oracle, kats):
-    """The reference's own 61 unit tests (tests/pint_test.cpp), executed by the CUDA kernels."""
+def run_kats_through_cuda(P, kats):
     pint_b200, ops = P
     ran = 0
 
@@ -172,7 +171,17 @@ def test_reference_kats_through_cuda(P, oracle, kats):
             assert val(ops.binary(k["op"], L, a, b)) == val(want), k
             assert val(ops.fused_unpack_arith_repack(k["op"], L, a, b)) == val(want), k
         ran += 1
-    assert ran == 78
+    return ran
+
+
+def test_reference_kats_through_cuda(P, oracle, kats):
+    """The reference's own 61 unit tests (tests/pint_test.cpp), executed by the CUDA kernels."""
+    assert run_kats_through_cuda(P, kats) == 78
+
+
+def test_readme_examples_through_cuda(P, readme_kats):
+    """The worked examples of the reference's README (lines 100-410), executed by the CUDA kernels."""
+    assert run_kats_through_cuda(P, readme_kats) == 18
 
 
 LAYOUTS_BIG = [(2, (5, 6, 5)), (4, (8, 8, 8, 8)), (8, (16, 16, 16, 16)), (8, (3, 7, 11, 13, 17, 13)),

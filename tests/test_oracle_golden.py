@@ -24,7 +24,7 @@ def test_kat_count(kats):
     assert sum(k["kind"] == "storage" for k in kats) == 12
 
 
-def test_kats_against_oracle(oracle, kats):
+def check_kats_against_oracle(oracle, kats):
     checked = 0
     for k in kats:
         kind = k["kind"]
@@ -56,7 +56,27 @@ def test_kats_against_oracle(oracle, kats):
         else:
             raise AssertionError(kind)
         checked += 1
-    assert checked == len(kats) == 78
+    return checked
+
+
+def test_kats_against_oracle(oracle, kats):
+    assert check_kats_against_oracle(oracle, kats) == len(kats) == 78
+
+
+def test_readme_examples_against_oracle(oracle, readme_kats):
+    """Every worked example of /root/reference/README.md:100-410 (tests/golden/readme_examples.json;
+    tests/cpp/readme_examples_check.cpp static_asserts the same statements against the header)."""
+    assert check_kats_against_oracle(oracle, readme_kats) == len(readme_kats) == 18
+
+
+def test_readme_examples_hold_for_the_reference_header():
+    import shutil
+    if not os.path.exists("/root/reference/include/pint/pint.hpp") or not shutil.which("g++"):
+        pytest.skip("needs /root/reference and g++ (build container only)")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run(["g++", "-std=c++17", "-fsyntax-only", "-I/root/reference/include", "tests/cpp/readme_examples_check.cpp"],
+                       cwd=root, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-3000:]
 
 
 def test_readme_example(oracle):

@@ -11,6 +11,7 @@
 
 #include "pint/cuda_kernels.cuh"
 #include "pint/cuda_kernels_bulk.cuh"
+#include "binary_bulk_variant.cuh"
 
 using namespace pint::cuda;
 using namespace pint::cuda::kernels;
