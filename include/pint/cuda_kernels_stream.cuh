@@ -140,10 +140,20 @@ struct swar_fn {
 // Fn is the per-Word function object (swar_fn below, or fused_fn in
 // cuda_kernels_planes.cuh); it travels as a __grid_constant__ parameter, so a
 // static-mask Fn is empty and a runtime-mask Fn lives in the constant bank.
+// Programmatic dependent launch (option "pdl"): the next launch in the stream may bring its CTAs onto the
+// SMs while this grid drains (launch_dependents), and nothing is read or written before the grids this
+// one depends on have completed and flushed (wait).  Both are no-ops for an ordinary launch.
+__device__ __forceinline__ void pdl_prologue()
+{
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 template <class Fn, class Cfg>
 __global__ void __launch_bounds__(Cfg::BLOCK)
 binary_stream_kernel(const uint4* a, const uint4* b, uint4* out, size_t nvec, const __grid_constant__ Fn fn)
 {
+    pdl_prologue();
     using W = typename Fn::word;
     constexpr int U = Cfg::UNROLL, B = Cfg::BLOCK;
     constexpr size_t tile = size_t(U) * B;
@@ -173,6 +183,7 @@ template <class Fn, class Cfg>
 __global__ void __launch_bounds__(Cfg::BLOCK)
 binary_stream256_kernel(const vec32* a, const vec32* b, vec32* out, size_t nvec, const __grid_constant__ Fn fn)
 {
+    pdl_prologue();
     using W = typename Fn::word;
     constexpr int U = Cfg::UNROLL / 2 > 0 ? Cfg::UNROLL / 2 : 1, B = Cfg::BLOCK;
     constexpr size_t tile = size_t(U) * B;
@@ -375,6 +386,7 @@ struct launch_geom {
     unsigned* counter_cursor = nullptr;
     int ordered_ctas_per_sm = 0;  // 0 = off
     int vec256 = 1;               // 32-byte vectors: 0 never, 1 where measured faster (light functors), 2 wherever aligned
+    int pdl = 0;                  // 1 = the binary stream kernels are launched with programmatic stream serialization
     int unpack_bulk = 1;          // unpack to int32 planes through shared memory + bulk stores (cuda_kernels_planes_bulk.cuh)
 };
 
@@ -404,6 +416,29 @@ inline unsigned grid_for(size_t ntiles, const launch_geom& g)
     }
     if (n > 0x7FFFFFFFull) n = 0x7FFFFFFFull;  // gridDim.x limit; the kernels grid-stride beyond it
     return unsigned(n ? n : 1);
+}
+
+// kern<<<grid, block, 0, stream>>>(args...), or the same launch with programmatic stream serialization
+// allowed: the grid may start while the previous launch of the stream drains (the kernel's pdl_prologue
+// holds its work until that launch has completed)
+template <class... KArgs, class... Args>
+inline cudaError_t launch_stream_kernel(void (*kern)(KArgs...), unsigned grid, unsigned block, cudaStream_t stream, bool pdl, Args&&... args)
+{
+    if (!pdl) {
+        kern<<<grid, block, 0, stream>>>(KArgs(args)...);
+        return cudaSuccess;
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(block);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
 }
 
 inline void count_launch(const launch_geom& g)
@@ -454,9 +489,10 @@ cudaError_t launch_binary(const void* a, const void* b, void* out, size_t n, con
         elems(0, head);
         constexpr size_t tile = size_t(Cfg::UNROLL / 2 > 0 ? Cfg::UNROLL / 2 : 1) * Cfg::BLOCK;
         const size_t ntiles = (nvec + tile - 1) / tile;
-        binary_stream256_kernel<Fn, Cfg><<<grid_for(ntiles, g), Cfg::BLOCK, 0, stream>>>(
-            reinterpret_cast<const vec32*>(ea + head), reinterpret_cast<const vec32*>(eb + head),
-            reinterpret_cast<vec32*>(eo + head), nvec, fn);
+        if (cudaError_t e = launch_stream_kernel(binary_stream256_kernel<Fn, Cfg>, grid_for(ntiles, g), Cfg::BLOCK, stream, g.pdl != 0,
+                                                 reinterpret_cast<const vec32*>(ea + head), reinterpret_cast<const vec32*>(eb + head),
+                                                 reinterpret_cast<vec32*>(eo + head), nvec, fn))
+            return e;
         count_launch(g);
         elems(n - tail, tail);
         return cudaGetLastError();
@@ -477,9 +513,10 @@ cudaError_t launch_binary(const void* a, const void* b, void* out, size_t n, con
                 reinterpret_cast<const uint4*>(ea + head), reinterpret_cast<const uint4*>(eb + head),
                 reinterpret_cast<uint4*>(eo + head), nvec, next_tile_counter(g), fn);
         } else {
-            binary_stream_kernel<Fn, Cfg><<<grid_for(ntiles, g), Cfg::BLOCK, 0, stream>>>(
-                reinterpret_cast<const uint4*>(ea + head), reinterpret_cast<const uint4*>(eb + head),
-                reinterpret_cast<uint4*>(eo + head), nvec, fn);
+            if (cudaError_t e = launch_stream_kernel(binary_stream_kernel<Fn, Cfg>, grid_for(ntiles, g), Cfg::BLOCK, stream, g.pdl != 0,
+                                                     reinterpret_cast<const uint4*>(ea + head), reinterpret_cast<const uint4*>(eb + head),
+                                                     reinterpret_cast<uint4*>(eo + head), nvec, fn))
+                return e;
         }
         count_launch(g);
     }

@@ -95,7 +95,16 @@ unsigned long long pint_cuda_launch_count(void);
  * "dense_threads" / "dense_tile_bytes" (CTA size and per-operand tile of the dense bit-stream
  * kernels; 0 = chosen from the layout), "vec256" (32-byte global accesses in the stream kernels:
  * 0 never, 1 = default, where measured faster, 2 wherever the operands are 32-byte congruent), "dense_windows" (1 = layouts without compiled-in dense
- * kernels always use the element-by-element window kernels; testing).  Returns 0 or PINT_E_ARG. */
+ * kernels always use the element-by-element window kernels; testing), "unpack_bulk" (unpack to int32 planes:
+ * 1 = default, plane tiles staged in shared memory and written by bulk (TMA) stores; 0 = straight from
+ * registers), "jit" (0 = default, 1, 2: run-time specialisation of unregistered layouts, see
+ * pint_cuda_jit_compile), "pdl" (1 = the packed -> packed stream kernels are launched with programmatic
+ * stream serialization: back-to-back passes over SMALL arrays overlap one pass's tail with the next one's
+ * launch; results and ordering are unchanged, every kernel waits for the previous launch of its stream
+ * before touching memory; default 0).  Returns 0 or PINT_E_ARG.
+ * Options are process-wide; each one is read and written atomically, so setting one while other threads
+ * launch is safe (a launch sees the old or the new value, never a torn one), but a change is not
+ * synchronised with launches already being prepared on other threads. */
 int pint_cuda_set_option(const char* key, long value);
 long pint_cuda_get_option(const char* key);
 

@@ -67,6 +67,7 @@ launch_geom geom()
     g.ordered_ctas_per_sm = (int)opts().ordered_ctas_per_sm;
     g.vec256 = (int)opts().vec256;
     g.unpack_bulk = (int)opts().unpack_bulk;
+    g.pdl = (int)opts().pdl;
     if (g.ordered_ctas_per_sm > 0) {
         g.counters = current_counters();
         g.counter_cursor = &g_counter_cursor;
@@ -253,6 +254,7 @@ int pint_cuda_set_option(const char* key, long value)
     if (!std::strcmp(key, "host_slots")) { if (value < 1 || value > 8) return PINT_E_ARG; opts().host_slots = value; return PINT_OK; }
     if (!std::strcmp(key, "vec256")) { if (value < 0 || value > 2) return PINT_E_ARG; opts().vec256 = value; return PINT_OK; }
     if (!std::strcmp(key, "dense_windows")) { opts().dense_windows = value != 0; return PINT_OK; }
+    if (!std::strcmp(key, "pdl")) { opts().pdl = value != 0; return PINT_OK; }
     if (!std::strcmp(key, "jit")) { if (value < 0 || value > 2) return PINT_E_ARG; opts().jit = value; return PINT_OK; }
     if (!std::strcmp(key, "unpack_bulk")) { if (value < 0 || value > 1) return PINT_E_ARG; opts().unpack_bulk = value; return PINT_OK; }
     if (!std::strcmp(key, "dense_threads")) { if (value < 0 || value > 1024 || value % 32) return PINT_E_ARG; opts().dense_threads = value; return PINT_OK; }
@@ -272,6 +274,7 @@ long pint_cuda_get_option(const char* key)
     if (!std::strcmp(key, "dense_windows")) return opts().dense_windows;
     if (!std::strcmp(key, "unpack_bulk")) return opts().unpack_bulk;
     if (!std::strcmp(key, "jit")) return opts().jit;
+    if (!std::strcmp(key, "pdl")) return opts().pdl;
     if (!std::strcmp(key, "dense_threads")) return opts().dense_threads;
     if (!std::strcmp(key, "dense_tile_bytes")) return opts().dense_tile_bytes;
     return -1;
