@@ -78,7 +78,8 @@ enum pint_error {
     PINT_E_PLANE_BYTES = -13,  /* plane element size is not 1, 2, 4 or 8 */
     PINT_E_ALIAS = -14,        /* partially overlapping in/out */
     PINT_E_ARG = -15,          /* other invalid argument */
-    PINT_E_JIT = -20           /* option "jit" = 2 and the layout could not be specialised (pint_cuda_jit_last_error) */
+    PINT_E_JIT = -20,          /* option "jit" = 2 and the layout could not be specialised (pint_cuda_jit_last_error) */
+    PINT_E_TOO_LARGE = -21     /* more elements than a fixed-scratch entry point takes (PINT_STATIC_MAX_PAIRS) */
 };
 
 /* ---- library ---- */
@@ -229,6 +230,19 @@ int pint_cuda_sharded_dense_binary(int op, const pint_layout* layout, int ngpu, 
  * is the low 32 bits. */
 int pint_cuda_pairs_reduce(int op, const pint_layout* layout, const void* pairs, size_t n,
                            uint64_t* sum_dev, pint_stream_t stream);
+/* The same reduction for callers that may not allocate device memory (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Two passes -- one partial sum per CTA, then one CTA adds the partials into *sum_dev --
+ * with the partials in a file-scope static device array of the library (64 KiB, held by every GPU that loads the
+ * library until the process exits).  The call itself performs no cudaMalloc / cudaFree and calls no allocating
+ * routine; `pairs` and `sum_dev` are still the caller's.  n > PINT_STATIC_MAX_PAIRS returns PINT_E_TOO_LARGE
+ * (use pint_cuda_pairs_reduce).  Every call on a device shares the one scratch array, which keeps the previous
+ * call's contents (nothing in it needs to start at zero: each call writes the slots it reads): calls in one
+ * stream are ordered, calls that OVERLAP on the GPU (different streams or threads) race and must be serialised
+ * by the caller.  Result identical to pint_cuda_pairs_reduce (integer sum, order-independent). */
+#define PINT_STATIC_MAX_PAIRS (8192ull * 16384ull) /* 2^27 pairs: 8192 partial slots x 16384 pairs per CTA */
+int pint_cuda_pairs_reduce_static(int op, const pint_layout* layout, const void* pairs, size_t n,
+                                  uint64_t* sum_dev, pint_stream_t stream);
 /* out[i] = OP(pairs[2i], pairs[2i+1]): the same interleaved operands (std::pair<Integer, Integer>
  * array, tests/pint_bench.cpp:22), the results kept as a plain array instead of summed.
  * 3 * sizeof(Integer) bytes per element; `out` must not overlap `pairs`. */

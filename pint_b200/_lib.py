@@ -70,6 +70,7 @@ def lib():
             "pint_cuda_sharded_dense_binary": (i, [i, LP, i, C.POINTER(i), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp),
                                                   C.POINTER(sz), C.POINTER(vp)]),
             "pint_cuda_pairs_reduce": (i, [i, LP, vp, sz, vp, vp]),
+            "pint_cuda_pairs_reduce_static": (i, [i, LP, vp, sz, vp, vp]),
             "pint_cuda_equal": (i, [LP, vp, vp, sz, vp, vp, vp]),
             "pint_cuda_binary_pairs": (i, [i, LP, vp, vp, sz, vp]),
             "pint_cuda_binary_scalar": (i, [i, LP, vp, u64, i, vp, sz, vp]),

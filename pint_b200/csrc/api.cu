@@ -238,6 +238,7 @@ const char* pint_cuda_error_string(int rc)
     case PINT_E_ALIAS: return "partially overlapping input and output";
     case PINT_E_ARG: return "invalid argument";
     case PINT_E_JIT: return "layout could not be specialised at run time (pint_cuda_jit_last_error)";
+    case PINT_E_TOO_LARGE: return "more elements than this fixed-scratch entry point takes (PINT_STATIC_MAX_PAIRS): use the general entry point";
     default: return rc > 0 ? cudaGetErrorString((cudaError_t)rc) : "unknown error";
     }
 }
