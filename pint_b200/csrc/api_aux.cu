@@ -83,9 +83,11 @@ __global__ void __launch_bounds__(256) checksum_vec_kernel(const uint4* x, size_
 }
 
 // tests/pint_bench.cpp:90-94: sum += op(P(pair.first), P(pair.second)).value()
-template <class Elem, int Op, bool V32 = false>
+// P: the mask policy -- static_masks<SL> for the layouts of registry_layouts.def (constants folded into the code),
+// runtime_masks<W, Steps> otherwise (Steps smear steps: 2 / 4 for layouts whose widest field has at most 4 / 16 bits)
+template <class Elem, int Op, bool V32, class P>
 __global__ void __launch_bounds__(256)
-pairs_reduce_kernel(const Elem* pairs, size_t n, uint64_t* sum, const __grid_constant__ runtime_masks<word_of<Elem>> p)
+pairs_reduce_kernel(const Elem* pairs, size_t n, uint64_t* sum, const __grid_constant__ P p)
 {
     using W = word_of<Elem>;
     constexpr int PER = 8 / sizeof(Elem);  // pairs per 16-byte vector
@@ -131,21 +133,52 @@ pairs_reduce_kernel(const Elem* pairs, size_t n, uint64_t* sum, const __grid_con
     block_reduce_sum_xor<false>(s, 0, sum);
 }
 
-template <class Elem, int... Ops>
-cudaError_t pairs_ops(int op, const layout_desc& d, const void* pairs, size_t n, uint64_t* sum, cudaStream_t s,
+template <class Elem, class P, int... Ops>
+cudaError_t pairs_ops(int op, const P& p, const void* pairs, size_t n, uint64_t* sum, cudaStream_t s,
                       const launch_geom& g, std::integer_sequence<int, Ops...>)
 {
-    using W = word_of<Elem>;
-    runtime_masks<W> p(make_word_masks<W>(d));
     const unsigned grid = grid_for((n + 1023) / 1024, g);
     // 256-bit loads, 128 bytes in flight per thread: 6221 -> 6950 GB/s (profiles/r03s_ab_pairs_reduce.log)
     if (g.vec256 != 0 && (uintptr_t)pairs % 32 == 0)
-        ((op == Ops ? (pairs_reduce_kernel<Elem, Ops, true><<<grid, 256, 0, s>>>((const Elem*)pairs, n, sum, p), 0) : 0), ...);
+        ((op == Ops ? (pairs_reduce_kernel<Elem, Ops, true, P><<<grid, 256, 0, s>>>((const Elem*)pairs, n, sum, p), 0) : 0), ...);
     else
-        ((op == Ops ? (pairs_reduce_kernel<Elem, Ops><<<grid, 256, 0, s>>>((const Elem*)pairs, n, sum, p), 0) : 0), ...);
+        ((op == Ops ? (pairs_reduce_kernel<Elem, Ops, false, P><<<grid, 256, 0, s>>>((const Elem*)pairs, n, sum, p), 0) : 0), ...);
     count_launch(g);
     return cudaGetLastError();
 }
+
+// run-time masks: as many smear steps as the widest field needs (the benchmark's own type-2 layout
+// <1,2,3,4,5,6,11> with add_signed_saturate was ALU-bound at 3.3 TB/s with all five, profiles/r17_replay_pint_bench.jsonl)
+template <class Elem>
+cudaError_t pairs_runtime(int op, const layout_desc& d, const void* pairs, size_t n, uint64_t* sum, cudaStream_t s, const launch_geom& g)
+{
+    using W = word_of<Elem>;
+    const auto m = make_word_masks<W>(d);
+    auto ops = std::make_integer_sequence<int, pint::cuda::OP_NUM_BINARY>();
+    if (m.nsh > 1 && m.nsmear <= 2) return pairs_ops<Elem>(op, runtime_masks<W, 2>(m), pairs, n, sum, s, g, ops);
+    if (m.nsh > 1 && m.nsmear <= 4) return pairs_ops<Elem>(op, runtime_masks<W, 4>(m), pairs, n, sum, s, g, ops);
+    return pairs_ops<Elem>(op, runtime_masks<W>(m), pairs, n, sum, s, g, ops);
+}
+
+// compiled-in masks for the layouts of registry_layouts.def (which include the five layouts of the reference's
+// benchmark, tests/pint_bench.cpp:88,158,376,469,639)
+struct static_pairs_entry {
+    layout_desc desc;
+    cudaError_t (*run)(int op, const void* pairs, size_t n, uint64_t* sum, cudaStream_t s, const launch_geom& g);
+};
+
+template <class SL>
+cudaError_t pairs_static(int op, const void* pairs, size_t n, uint64_t* sum, cudaStream_t s, const launch_geom& g)
+{
+    return pairs_ops<typename SL::integer>(op, static_masks<SL>{}, pairs, n, sum, s, g,
+                                           std::make_integer_sequence<int, pint::cuda::OP_NUM_BINARY>());
+}
+
+const static_pairs_entry kStaticPairs[] = {
+#define X(part, I, ...) {static_layout<I, __VA_ARGS__>::desc, &pairs_static<static_layout<I, __VA_ARGS__>>},
+#include "registry_layouts.def"
+#undef X
+};
 
 }  // namespace
 }  // namespace pint_cuda_impl
@@ -218,12 +251,14 @@ int pint_cuda_pairs_reduce(int op, const pint_layout* layout, const void* pairs,
     if ((uintptr_t)pairs % d.elem_bytes) return PINT_E_ARG;
     launch_geom g = geom();
     g.ctas_per_sm = 8;  // one atomic per CTA at the end: persistent grid
-    auto ops = std::make_integer_sequence<int, pint::cuda::OP_NUM_BINARY>();
+    if (!opts().force_generic)
+        for (const static_pairs_entry& e : kStaticPairs)
+            if (same_layout(e.desc, d)) return (int)e.run(op, pairs, n, sum_dev, s, g);
     switch (d.elem_bytes) {
-    case 1: return (int)pairs_ops<uint8_t>(op, d, pairs, n, sum_dev, s, g, ops);
-    case 2: return (int)pairs_ops<uint16_t>(op, d, pairs, n, sum_dev, s, g, ops);
-    case 4: return (int)pairs_ops<uint32_t>(op, d, pairs, n, sum_dev, s, g, ops);
-    default: return (int)pairs_ops<uint64_t>(op, d, pairs, n, sum_dev, s, g, ops);
+    case 1: return (int)pairs_runtime<uint8_t>(op, d, pairs, n, sum_dev, s, g);
+    case 2: return (int)pairs_runtime<uint16_t>(op, d, pairs, n, sum_dev, s, g);
+    case 4: return (int)pairs_runtime<uint32_t>(op, d, pairs, n, sum_dev, s, g);
+    default: return (int)pairs_runtime<uint64_t>(op, d, pairs, n, sum_dev, s, g);
     }
 }
 

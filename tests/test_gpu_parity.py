@@ -102,8 +102,13 @@ def test_golden_pairs_reduce(P, refvec):
         L = pint_b200.Layout(eb, *bits)
         pairs = to_dev(np.stack([refvec[key + "_a"], refvec[key + "_b"]], axis=1).reshape(-1))
         want = refvec[f"{key}_pairsum"]
-        for i, op in enumerate(OPS):
-            assert ops.pairs_reduce(op, L, pairs) == int(want[i]), (L, op)
+        for generic in (0, 1):   # compiled-in masks where the layout is registered / run-time masks (bucketed smear steps)
+            ops.set_option("force_generic", generic)
+            try:
+                for i, op in enumerate(OPS):
+                    assert ops.pairs_reduce(op, L, pairs) == int(want[i]), (L, op, generic)
+            finally:
+                ops.set_option("force_generic", 0)
 
 
 @pytest.mark.parametrize("eb,bits", [(4, (8, 8, 8, 8)), (2, (5, 6, 5)), (8, (3, 7, 11, 13, 17, 13)), (1, (2, 3, 3))])
