@@ -413,17 +413,18 @@ def main():
             ops.fill_splitmix(y, 0xC0B + 2 * k, start=b0)
             bufs.append((x, y, torch.empty_like(x)))
         ms0 = timed_launches(lambda i: ops.binary("add_wrap", L0, *bufs[i % sets][:2], out=bufs[i % sets][2]), 5 * sets)
-        configs.append(config_line("C0", "add_wrap over 2^26 packed_int<uint16_t,5,6,5> per GPU, one launch per pass, "
+        configs.append(config_line("C0", "add_wrap over 2^26 packed_int<uint16_t,5,6,5> per GPU, one launch per pass (programmatic dependent launch, the default), "
                                    "8 rotating buffer sets (L2 cannot hold a pass)", "weak", c0, n0 * world, 6, ms0,
                                    kernel="binary_stream256_kernel<swar_fn<add_wrap, static <5,6,5>>>"))
-        # the same passes with programmatic dependent launch: the next pass's CTAs come onto the SMs while this one drains
+        # the same passes as plain launches (option pdl = 0): the default launches the stream kernels with programmatic
+        # stream serialization, so the next pass's CTAs come onto the SMs while this one drains
         try:
-            ops.set_option("pdl", 1)
+            ops.set_option("pdl", 0)
             msp = timed_launches(lambda i: ops.binary("add_wrap", L0, *bufs[i % sets][:2], out=bufs[i % sets][2]), 5 * sets)
-            configs.append(config_line("C0-pdl", "the same passes launched with programmatic stream serialization (option pdl)", "weak",
+            configs.append(config_line("C0-no-pdl", "the same passes as plain launches (option pdl = 0)", "weak",
                                        c0, n0 * world, 6, msp, kernel="binary_stream256_kernel<swar_fn<add_wrap, static <5,6,5>>>"))
         finally:
-            ops.set_option("pdl", 0)
+            ops.set_option("pdl", 1)
         # the same 40 passes as ONE CUDA graph launch (launch latency and the ramp between passes amortised)
         try:
             g = torch.cuda.CUDAGraph()

@@ -61,6 +61,7 @@ __global__ void __launch_bounds__(Cfg::BLOCK)
 binary_pair_stream_kernel(const uint4* a, const uint4* b, uint4* out0, uint4* out1, size_t nvec,
                           const __grid_constant__ Fn fn)
 {
+    pdl_prologue();
     using W = typename Fn::word;
     constexpr int U = Cfg::UNROLL, B = Cfg::BLOCK;
     constexpr size_t tile = size_t(U) * B;
@@ -96,6 +97,7 @@ __global__ void __launch_bounds__(Cfg::BLOCK)
 binary_pair_stream256_kernel(const vec32* a, const vec32* b, vec32* out0, vec32* out1, size_t nvec,
                              const __grid_constant__ Fn fn)
 {
+    pdl_prologue();
     using W = typename Fn::word;
     constexpr int U = Cfg::UNROLL / 2 > 0 ? Cfg::UNROLL / 2 : 1, B = Cfg::BLOCK;
     constexpr size_t tile = size_t(U) * B;
@@ -157,9 +159,10 @@ cudaError_t launch_binary_pair(const void* a, const void* b, void* out0, void* o
         if (cudaError_t rc = single(0, head)) return rc;
         constexpr size_t tile = size_t(Cfg::UNROLL / 2 > 0 ? Cfg::UNROLL / 2 : 1) * Cfg::BLOCK;
         const size_t ntiles = (nvec + tile - 1) / tile;
-        binary_pair_stream256_kernel<Fn, Cfg><<<grid_for(ntiles, g), Cfg::BLOCK, 0, stream>>>(
-            reinterpret_cast<const vec32*>(ea + head), reinterpret_cast<const vec32*>(eb + head),
-            reinterpret_cast<vec32*>(e0 + head), reinterpret_cast<vec32*>(e1 + head), nvec, Fn{p});
+        if (cudaError_t e = launch_stream_kernel(binary_pair_stream256_kernel<Fn, Cfg>, grid_for(ntiles, g), Cfg::BLOCK, stream, g.pdl != 0,
+                                                 reinterpret_cast<const vec32*>(ea + head), reinterpret_cast<const vec32*>(eb + head),
+                                                 reinterpret_cast<vec32*>(e0 + head), reinterpret_cast<vec32*>(e1 + head), nvec, Fn{p}))
+            return e;
         count_launch(g);
         if (cudaError_t rc = single(n - tail, tail)) return rc;
         return cudaGetLastError();
@@ -169,9 +172,10 @@ cudaError_t launch_binary_pair(const void* a, const void* b, void* out0, void* o
     if (nvec) {
         constexpr size_t tile = size_t(Cfg::UNROLL) * Cfg::BLOCK;
         const size_t ntiles = (nvec + tile - 1) / tile;
-        binary_pair_stream_kernel<Fn, Cfg><<<grid_for(ntiles, g), Cfg::BLOCK, 0, stream>>>(
-            reinterpret_cast<const uint4*>(ea + head), reinterpret_cast<const uint4*>(eb + head),
-            reinterpret_cast<uint4*>(e0 + head), reinterpret_cast<uint4*>(e1 + head), nvec, Fn{p});
+        if (cudaError_t e = launch_stream_kernel(binary_pair_stream_kernel<Fn, Cfg>, grid_for(ntiles, g), Cfg::BLOCK, stream, g.pdl != 0,
+                                                 reinterpret_cast<const uint4*>(ea + head), reinterpret_cast<const uint4*>(eb + head),
+                                                 reinterpret_cast<uint4*>(e0 + head), reinterpret_cast<uint4*>(e1 + head), nvec, Fn{p}))
+            return e;
         count_launch(g);
     }
     if (cudaError_t rc = single(n - tail, tail)) return rc;

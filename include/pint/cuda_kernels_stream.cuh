@@ -386,7 +386,7 @@ struct launch_geom {
     unsigned* counter_cursor = nullptr;
     int ordered_ctas_per_sm = 0;  // 0 = off
     int vec256 = 1;               // 32-byte vectors: 0 never, 1 where measured faster (light functors), 2 wherever aligned
-    int pdl = 0;                  // 1 = the binary stream kernels are launched with programmatic stream serialization
+    int pdl = 1;                  // the binary stream kernels are launched with programmatic stream serialization (0 = plain launches)
     int unpack_bulk = 1;          // unpack to int32 planes through shared memory + bulk stores (cuda_kernels_planes_bulk.cuh)
 };
 

@@ -28,7 +28,7 @@ struct options {
     option_value dense_threads = 0;     // dense bit-stream kernels: threads per CTA (0 = from the chunk size)
     option_value dense_tile_bytes = 0;  // ... and tile bytes per operand (0 = 16 KB target)
     option_value unpack_bulk = 1;   // unpack to int32 planes: 1 = plane tiles staged in shared memory, bulk (TMA) stores; 0 = register kernels
-    option_value pdl = 0;           // 1 = binary stream kernels launched with programmatic stream serialization (small arrays back to back)
+    option_value pdl = 1;           // packed -> packed stream kernels launched with programmatic stream serialization (default; +4...14 % on arrays up to 2^26 elements, profiles/r19_ab_pdl.log)
     option_value jit = 0;           // 0 off; 1 = specialise unregistered layouts with NVRTC, fall back on failure; 2 = fail instead
     option_value ordered_ctas_per_sm = 0;  // ordered persistent grid for bandwidth-bound functors; 0 = off (default, see cuda_kernels_stream.cuh)
 };

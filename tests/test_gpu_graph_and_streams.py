@@ -137,7 +137,7 @@ def test_dense_kernels_in_graph_and_host_threads(oracle):
 
 
 def test_programmatic_dependent_launch_keeps_stream_order(oracle):
-    """Option "pdl": the stream kernels are launched with programmatic stream serialization, so a pass may be
+    """Option "pdl" (default on): the stream kernels are launched with programmatic stream serialization, so a pass may be
     brought onto the SMs while the previous one drains.  A chain of DEPENDENT in-place passes (each reads what
     the one before wrote) and a write-after-read chain must give exactly what ordinary launches give, for
     sizes from one CTA to many waves, also when captured in a CUDA graph."""
@@ -160,7 +160,7 @@ def test_programmatic_dependent_launch_keeps_stream_order(oracle):
                     torch.cuda.synchronize()
                     results.append((to_np(x).copy(), to_np(y).copy(), to_np(b).copy()))
                 finally:
-                    ops.set_option("pdl", 0)
+                    ops.set_option("pdl", 1)
             for u, v in zip(results[0], results[1]):
                 np.testing.assert_array_equal(u, v, err_msg=f"{L} n={n}")
     # captured: 8 passes in one graph with the option on
@@ -184,5 +184,5 @@ def test_programmatic_dependent_launch_keeps_stream_order(oracle):
         g.replay()
         torch.cuda.synchronize()
     finally:
-        ops.set_option("pdl", 0)
+        ops.set_option("pdl", 1)
     np.testing.assert_array_equal(to_np(x), want)
