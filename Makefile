@@ -12,7 +12,8 @@ HDRS := $(wildcard include/pint/*.hpp include/pint/*.cuh include/*.h $(SRC)/*.hp
 PARTS := 0 1 2 3
 JIT_HDRS := include/pint/cuda_std.hpp include/pint/cuda_layout.hpp include/pint/cuda_kernels.cuh include/pint/cuda_kernels_stream.cuh \
             include/pint/cuda_kernels_multi.cuh include/pint/cuda_kernels_planes.cuh include/pint/cuda_kernels_planes_bulk.cuh \
-            include/pint/cuda_kernels_bulk.cuh include/pint/cuda_kernels_fused.cuh include/pint/cuda_kernels_callers.cuh
+            include/pint/cuda_kernels_bulk.cuh include/pint/cuda_kernels_fused.cuh include/pint/cuda_kernels_callers.cuh \
+            include/pint/cuda_kernels_dense.cuh include/pint/cuda_kernels_dense_mw.cuh
 OBJS := $(OBJ)/api.o $(OBJ)/api_aux.o $(OBJ)/api_static.o $(OBJ)/jit.o $(OBJ)/api_dense.o $(OBJ)/api_callers.o $(OBJ)/dense_static.o $(foreach p,0 1 2,$(OBJ)/dense_generic_mw$(p).o) $(foreach p,0 1 2 3,$(OBJ)/dense_fixed$(p).o) $(OBJ)/generic.o $(foreach p,$(PARTS),$(OBJ)/registry_part$(p).o)
 
 all: $(LIB)

@@ -35,6 +35,8 @@
 // shared memory and uses the chunk mapping again, so both sides stay coalesced and
 // nothing needs atomics.
 #pragma once
+#ifndef PINT_CUDA_KERNELS_DENSE_CUH_INCLUDED
+#define PINT_CUDA_KERNELS_DENSE_CUH_INCLUDED
 
 #include "cuda_kernels.cuh"
 #include "cuda_kernels_bulk.cuh"
@@ -462,6 +464,7 @@ inline void choose_tile(uint32_t cw, const dense_tuning& tune, uint32_t* threads
     *chunks_per_thread = R;
 }
 
+#if !defined(__CUDACC_RTC__)  // host-side launcher: not part of a run-time (NVRTC) specialisation
 // a, b, out: 16-byte aligned dense streams of n elements (ceil(n*S/128)*16 bytes each)
 template <class Fn, class Geo, int Mode = 0>
 cudaError_t launch_dense_binary(const void* a, const void* b, void* out, size_t n, const Fn& fn, Geo geo,
@@ -491,7 +494,11 @@ cudaError_t launch_dense_binary(const void* a, const void* b, void* out, size_t 
     return cudaGetLastError();
 }
 
+#endif  // !__CUDACC_RTC__
+
 }  // namespace dense
 }  // namespace kernels
 }  // namespace cuda
 }  // namespace pint
+
+#endif  // PINT_CUDA_KERNELS_DENSE_CUH_INCLUDED

@@ -16,6 +16,8 @@
 // masks (static_masks<chunk_layout<Bits...>>) or run-time masks (runtime_chunk_masks<N>).
 // Included by cuda_kernels_dense.cuh (after its helpers, before its kernels).
 #pragma once
+#ifndef PINT_CUDA_KERNELS_DENSE_MW_CUH_INCLUDED
+#define PINT_CUDA_KERNELS_DENSE_MW_CUH_INCLUDED
 
 namespace pint {
 namespace cuda {
@@ -319,3 +321,5 @@ __device__ __forceinline__ void process_chunk_mw_pair(uint32_t* A, uint32_t* B, 
 }  // namespace kernels
 }  // namespace cuda
 }  // namespace pint
+
+#endif  // PINT_CUDA_KERNELS_DENSE_MW_CUH_INCLUDED

@@ -8,6 +8,8 @@
 #include "pint_cuda.h"
 #include "registry.hpp"
 
+namespace pint { namespace cuda { namespace kernels { namespace dense { struct dense_tuning; } } } }
+
 namespace pint_cuda_impl {
 
 // process-wide option: relaxed atomic reads and writes (pint_cuda_set_option may race with launches)
@@ -52,6 +54,9 @@ int jit_binary(int op, bool fused, const pint_layout* layout, const layout_desc&
                size_t n, cudaStream_t s, const launch_geom& g, bool* handled);
 int jit_binary_pair(int pair, const layout_desc& d, const void* a, const void* b, void* out0, void* out1, size_t n,
                     cudaStream_t s, const launch_geom& g, bool* handled);
+// dense bit streams (whole-chunk layouts): op >= 0 one op, pair >= 0 one of kOpPairs with both results
+int jit_dense(int op, int pair, const layout_desc& d, const void* a, const void* b, void* out, void* out1, size_t n,
+              cudaStream_t s, const launch_geom& g, const pint::cuda::kernels::dense::dense_tuning& tune, bool* handled);
 int jit_compile_all(const layout_desc& d);
 int jit_prebuild(const layout_desc& d, int major, int minor);
 bool jit_is_loaded(const layout_desc& d);

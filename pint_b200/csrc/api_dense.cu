@@ -300,6 +300,17 @@ int pint_cuda_dense_binary_multi(int nops, const int* ops, const pint_layout* la
     }
     cudaStream_t s = (cudaStream_t)stream;
     const bool padded_format = S == 8 || S == 16 || S == 32 || S == 64;
+    if (padded_format) {
+        // no padding to remove: the streams ARE padded arrays of make_packed_int's Integer, and the padded multi-op
+        // entry (one-pass pair kernels) serves them; every output's tail past n stays zero
+        pint_layout p = *layout;
+        p.elem_bytes = S / 8;
+        if (int rc = binary_multi_impl(nops, ops, &p, a, b, outs, n, s)) return rc;
+        const size_t used = n * p.elem_bytes;
+        for (int j = 0; j < nops && bytes > used; ++j)
+            if (cudaError_t e = cudaMemsetAsync(static_cast<char*>(outs[j]) + used, 0, bytes - used, s)) return (int)e;
+        return PINT_OK;
+    }
     const launch_geom g = geom();
     const dense_layout_kernels* k = opts().force_generic ? nullptr : find_dense_static(d);
     bool done[PINT_MAX_MULTI_OPS] = {};
@@ -318,7 +329,16 @@ int pint_cuda_dense_binary_multi(int nops, const int* ops, const pint_layout* la
             cudaError_t mrc = cudaSuccess;
             // one pass for whole-chunk kernels only; window kernels (chunks above 19 words, or the
             // dense_windows option) run the two ops as two launches, which is faster there
-            if (k && k->pair[pi])
+            bool jit_done = false;
+            if (!k && opts().jit && !opts().dense_windows) {
+                const int jrc = jit_dense(-1, pi, d, a, b, o0, o1, n, s, g, tuning(), &jit_done);
+                if (jit_done) rc = jrc;
+                else if (jrc == PINT_E_JIT && opts().jit >= 2) return jrc;
+                else if (jrc != PINT_OK && jrc != PINT_E_JIT) return jrc;
+            }
+            if (jit_done)
+                ;
+            else if (k && k->pair[pi])
                 rc = (int)k->pair[pi](a, b, o0, o1, n, s, g, tuning());
             else if (!k && !opts().dense_windows &&
                      (dense_mw_pair_part0(N, pi, d, S, a, b, o0, o1, n, s, g, tuning(), &mrc) ||
@@ -366,8 +386,17 @@ int pint_cuda_dense_binary(int op, const pint_layout* layout, const void* a, con
     const launch_geom g = geom();
     if (!opts().force_generic)
         if (const dense_layout_kernels* k = find_dense_static(d)) return (int)k->binary[op](a, b, out, n, s, g, tuning());
-    // any layout whose chunk is short enough computes whole chunks with run-time masks ...
     const int N = int(S / dense::gcd_u32(S, 32));
+    // option "jit": the whole-chunk kernel with this layout's chunk masks compiled in, specialised at run time (jit.cu)
+    if (const long jit = opts().jit) {
+        if (!opts().dense_windows) {
+            bool handled = false;
+            const int rc = jit_dense(op, -1, d, a, b, out, nullptr, n, s, g, tuning(), &handled);
+            if (handled || (rc == PINT_E_JIT && jit >= 2)) return rc;
+            if (rc != PINT_OK && rc != PINT_E_JIT) return rc;
+        }
+    }
+    // any layout whose chunk is short enough computes whole chunks with run-time masks ...
     if (!opts().dense_windows) {
         cudaError_t rc = cudaSuccess;
         if (dense_mw_binary_part0(N, op, d, S, a, b, out, n, s, g, tuning(), &rc) ||

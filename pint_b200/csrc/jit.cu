@@ -31,6 +31,7 @@
 #include <cuda.h>
 
 #include "api_common.hpp"
+#include "pint/cuda_kernels_dense.cuh"  // choose_tile, dense_tuning, kMaxMwWords (host side of the dense launcher)
 
 namespace pint_cuda_impl {
 namespace {
@@ -70,6 +71,7 @@ struct driver_api {
     CUresult (*ModuleGetGlobal)(CUdeviceptr*, size_t*, CUmodule, const char*) = nullptr;
     CUresult (*MemcpyDtoH)(void*, CUdeviceptr, size_t) = nullptr;
     CUresult (*LaunchKernel)(CUfunction, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, CUstream, void**, void**) = nullptr;
+    CUresult (*FuncSetAttribute)(CUfunction, CUfunction_attribute, int) = nullptr;
 };
 
 std::mutex g_jit_mutex;
@@ -169,15 +171,44 @@ bool load_driver()
               get("cuModuleGetFunction", reinterpret_cast<void**>(&g_drv.ModuleGetFunction)) &&
               get("cuModuleGetGlobal", reinterpret_cast<void**>(&g_drv.ModuleGetGlobal)) &&
               get("cuMemcpyDtoH", reinterpret_cast<void**>(&g_drv.MemcpyDtoH)) &&
-              get("cuLaunchKernel", reinterpret_cast<void**>(&g_drv.LaunchKernel));
+              get("cuLaunchKernel", reinterpret_cast<void**>(&g_drv.LaunchKernel)) &&
+              get("cuFuncSetAttribute", reinterpret_cast<void**>(&g_drv.FuncSetAttribute));
     if (!ok) { cudaGetLastError(); g_last_error = "driver entry points unavailable"; }
     g_drv_ok = ok;
     return ok;
 }
 
 // ---- what gets compiled ----
-enum family : int { FAM_BINARY = 0, FAM_FUSED = 1, FAM_PAIR = 2, FAM_COUNT = 3 };
-const char* const kFamilyName[FAM_COUNT] = {"binary", "fused", "pair"};
+// FAM_DENSE / FAM_DENSE_PAIR: the whole-chunk kernels of the dense bit-stream format (cuda_kernels_dense_mw.cuh) with the
+// chunk masks of chunk_layout<Bits...> compiled in -- what dense_static.cu instantiates for the layouts of dense_layouts.def.
+// They exist for layouts whose chunk is at most kMaxMwWords words and whose sum(Bits) is not 8 / 16 / 32 / 64.
+enum family : int { FAM_BINARY = 0, FAM_FUSED = 1, FAM_PAIR = 2, FAM_DENSE = 3, FAM_DENSE_PAIR = 4, FAM_COUNT = 5 };
+const char* const kFamilyName[FAM_COUNT] = {"binary", "fused", "pair", "dense", "densepair"};
+
+uint32_t sum_bits(const layout_desc& d)
+{
+    uint32_t t = 0;
+    for (uint32_t i = 0; i < d.nfields; ++i) t += d.bits[i];
+    return t;
+}
+
+int dense_chunk_words(const layout_desc& d)
+{
+    const uint32_t S = sum_bits(d);
+    return int(S / pint::cuda::kernels::dense::gcd_u32(S, 32));
+}
+
+bool is_dense_family(int fam) { return fam == FAM_DENSE || fam == FAM_DENSE_PAIR; }
+
+bool family_applies(const layout_desc& d, int fam)
+{
+    if (!is_dense_family(fam)) return true;
+    const uint32_t S = sum_bits(d);
+    return S != 8 && S != 16 && S != 32 && S != 64 && dense_chunk_words(d) <= (int)pint::cuda::kernels::dense::kMaxMwWords;
+}
+
+// kernels per entry of a family: 16- and 32-byte vector forms for the padded families, one for the dense ones
+int family_variants(int fam) { return is_dense_family(fam) ? 1 : 2; }
 
 struct jit_kernel {
     CUfunction f128 = nullptr, f256 = nullptr;
@@ -203,13 +234,15 @@ const char* integer_name(uint32_t eb)
     return eb == 1 ? "uint8_t" : eb == 2 ? "uint16_t" : eb == 4 ? "uint32_t" : "uint64_t";
 }
 
-int family_count(int fam) { return fam == FAM_PAIR ? kNumOpPairs : (int)pint::cuda::OP_NUM_BINARY; }
+int family_count(int fam) { return (fam == FAM_PAIR || fam == FAM_DENSE_PAIR) ? kNumOpPairs : (int)pint::cuda::OP_NUM_BINARY; }
 
 std::string kernel_fn(int fam, int i)
 {
     char buf[96];
     if (fam == FAM_BINARY) std::snprintf(buf, sizeof buf, "pint_jit::BFn<%d>", i);
     else if (fam == FAM_FUSED) std::snprintf(buf, sizeof buf, "pint_jit::FFn<%d>", i);
+    else if (fam == FAM_DENSE) std::snprintf(buf, sizeof buf, "pint_jit::DFn<%d>", i);
+    else if (fam == FAM_DENSE_PAIR) std::snprintf(buf, sizeof buf, "pint_jit::DPFn<%d>", i);
     else std::snprintf(buf, sizeof buf, "pint_jit::PFn<%d>", i);
     return buf;
 }
@@ -217,13 +250,32 @@ std::string kernel_fn(int fam, int i)
 std::string kernel_expr(int fam, int i, bool wide)
 {
     const std::string fn = kernel_fn(fam, i);
+    if (is_dense_family(fam))  // Mode 0: one result; Mode 1: the second result of an op pair leaves over the b tile
+        return "pint::cuda::kernels::dense::dense_binary_kernel<" + fn + ", pint_jit::DGeo, " + (fam == FAM_DENSE_PAIR ? "1" : "0") + ">";
     const char* base = fam == FAM_PAIR ? (wide ? "binary_pair_stream256_kernel" : "binary_pair_stream_kernel")
                                        : (wide ? "binary_stream256_kernel" : "binary_stream_kernel");
     return std::string("pint::cuda::kernels::") + base + "<" + fn + ", pint_jit::Cfg<" + fn + ">>";
 }
 
+std::string make_dense_source(const layout_desc& d, int fam)
+{
+    std::string s = "#include \"pint/cuda_kernels_dense.cuh\"\nnamespace pint_jit {\nusing namespace pint::cuda;\nusing namespace pint::cuda::kernels;\n";
+    s += "using CL = dense::chunk_layout<";
+    for (uint32_t i = 0; i < d.nfields; ++i) s += (i ? ", " : "") + std::to_string((unsigned)d.bits[i]);
+    s += ">;\nusing M = static_masks<CL>;\nusing DGeo = dense::mw_geom<CL::kN>;\n"
+         "template <int Op> using DFn = swar_fn<Op, M>;\n"
+         "template <int P> using DPFn = pair_fn<kOpPairs[P][0], kOpPairs[P][1], M>;\n"
+         "}\n";
+    // sanity data for the host: chunk words, element bits (must equal what the host computes from the layout)
+    s += "extern \"C\" __device__ const int pint_jit_cfg[" + std::to_string(family_count(fam)) + "][4] = {\n";
+    for (int i = 0; i < family_count(fam); ++i) s += "  {pint_jit::CL::kN, int(pint_jit::CL::kS), int(sizeof(pint_jit::DGeo)), 0},\n";
+    s += "};\n";
+    return s;
+}
+
 std::string make_source(const layout_desc& d, int fam)
 {
+    if (is_dense_family(fam)) return make_dense_source(d, fam);
     std::string s = "#include \"pint/cuda_kernels.cuh\"\nnamespace pint_jit {\nusing namespace pint::cuda;\nusing namespace pint::cuda::kernels;\n";
     s += "using SL = static_layout<" + std::string(integer_name(d.elem_bytes));
     for (uint32_t i = 0; i < d.nfields; ++i) s += ", " + std::to_string((unsigned)d.bits[i]);
@@ -315,7 +367,7 @@ bool build_cubin(const layout_desc& d, int fam, int cc_major, int cc_minor, std:
                 if (c == '\n') { lowered->push_back(cur); cur.clear(); }
                 else cur.push_back(c);
             }
-            if ((int)lowered->size() == 2 * nk) return true;
+            if ((int)lowered->size() == family_variants(fam) * nk) return true;
         }
     }
     if (!load_nvrtc()) return false;
@@ -339,7 +391,7 @@ bool build_cubin(const layout_desc& d, int fam, int cc_major, int cc_minor, std:
     std::vector<std::string> exprs;
     for (int i = 0; i < nk; ++i) {
         exprs.push_back(kernel_expr(fam, i, false));
-        exprs.push_back(kernel_expr(fam, i, true));
+        if (family_variants(fam) == 2) exprs.push_back(kernel_expr(fam, i, true));
     }
     for (const auto& e : exprs) g_nvrtc.AddNameExpression(prog, e.c_str());
     const std::string inc = "-I" + g_nvrtc.include_dir;
@@ -422,9 +474,10 @@ jit_module* get_module(const layout_desc& d, int fam)
     }
     for (int i = 0; i < nk; ++i) {
         jit_kernel& k = m.k[i];
-        if (g_drv.ModuleGetFunction(&k.f128, m.mod, lowered[2 * i].c_str()) != CUDA_SUCCESS ||
-            g_drv.ModuleGetFunction(&k.f256, m.mod, lowered[2 * i + 1].c_str()) != CUDA_SUCCESS) {
-            g_last_error = "cuModuleGetFunction failed for " + lowered[2 * i];
+        const int nv = family_variants(fam);
+        if (g_drv.ModuleGetFunction(&k.f128, m.mod, lowered[nv * i].c_str()) != CUDA_SUCCESS ||
+            (nv == 2 && g_drv.ModuleGetFunction(&k.f256, m.mod, lowered[nv * i + 1].c_str()) != CUDA_SUCCESS)) {
+            g_last_error = "cuModuleGetFunction failed for " + lowered[nv * i];
             return nullptr;
         }
         k.unroll = cfg[4 * i]; k.block = cfg[4 * i + 1]; k.vec256 = cfg[4 * i + 2]; k.heavy = cfg[4 * i + 3];
@@ -507,10 +560,50 @@ int jit_binary_pair(int pair, const layout_desc& d, const void* a, const void* b
     return launch_body(m->k[pair], d.elem_bytes, ptrs, 4, n, s, g, rest, handled);
 }
 
+// Dense bit streams: op >= 0 runs one op (out1 unused), pair >= 0 one of kOpPairs with both results.  The launch
+// geometry is launch_dense_binary's (cuda_kernels_dense.cuh): same tile chooser, same shared-memory size, same
+// argument list -- only the functor carries compiled-in chunk masks instead of run-time ones.
+int jit_dense(int op, int pair, const layout_desc& d, const void* a, const void* b, void* out, void* out1, size_t n,
+              cudaStream_t s, const launch_geom& g, const pint::cuda::kernels::dense::dense_tuning& tune, bool* handled)
+{
+    namespace dn = pint::cuda::kernels::dense;
+    *handled = false;
+    const int fam = pair >= 0 ? FAM_DENSE_PAIR : FAM_DENSE;
+    if (!family_applies(d, fam)) return PINT_OK;  // not a whole-chunk layout: the caller's own kernels take it
+    jit_module* m = lookup(d, fam);
+    if (!m) return PINT_E_JIT;
+    if (n == 0) { *handled = true; return PINT_OK; }
+    const jit_kernel& k = m->k[pair >= 0 ? pair : op];
+    const uint32_t S = sum_bits(d), N = (uint32_t)dense_chunk_words(d);
+    if (k.unroll != (int)N || k.block != (int)S || k.vec256 != 8) {  // pint_jit_cfg: {CL::kN, CL::kS, sizeof(mw_geom)}
+        std::lock_guard<std::mutex> lock(g_jit_mutex);
+        g_last_error = "dense module does not match the layout's chunk geometry";
+        return PINT_E_JIT;
+    }
+    uint32_t T = 0, R = 0;
+    dn::choose_tile<uint32_t>(N, tune, &T, &R);
+    struct { uint32_t s, chunks_per_thread; } geo = {S, R};  // dense::mw_geom<N>
+    uint64_t valid_bits = uint64_t(n) * S;
+    size_t total_vec = size_t((valid_bits + 127) / 128);
+    const size_t tile_bytes = size_t(T) * R * N * sizeof(uint32_t);
+    const size_t ntiles = (total_vec * 16 + tile_bytes - 1) / tile_bytes;
+    const size_t smem = 2 * tile_bytes + 16;
+    if (ntiles > 0x7FFFFFFFull) return (int)cudaErrorInvalidValue;
+    if (smem > 48 * 1024 && g_drv.FuncSetAttribute(k.f128, CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES, (int)smem) != CUDA_SUCCESS)
+        return (int)cudaErrorInvalidValue;
+    char empty_fn = 0;
+    void* args[8] = {(void*)&a, (void*)&b, (void*)&out, (void*)&out1, &total_vec, &valid_bits, &empty_fn, &geo};
+    if (g_drv.LaunchKernel(k.f128, unsigned(ntiles), 1, 1, T, 1, 1, (unsigned)smem, (CUstream)s, args, nullptr) != CUDA_SUCCESS)
+        return (int)cudaErrorLaunchFailure;
+    count_launch(g);
+    *handled = true;
+    return PINT_OK;
+}
+
 int jit_compile_all(const layout_desc& d)
 {
     for (int fam = 0; fam < FAM_COUNT; ++fam)
-        if (!lookup(d, fam)) return PINT_E_JIT;
+        if (family_applies(d, fam) && !lookup(d, fam)) return PINT_E_JIT;
     return PINT_OK;
 }
 
@@ -519,6 +612,7 @@ int jit_prebuild(const layout_desc& d, int major, int minor)
 {
     std::lock_guard<std::mutex> lock(g_jit_mutex);
     for (int fam = 0; fam < FAM_COUNT; ++fam) {
+        if (!family_applies(d, fam)) continue;
         std::vector<char> cubin;
         std::vector<std::string> lowered;
         if (!build_cubin(d, fam, major, minor, &cubin, &lowered)) return PINT_E_JIT;

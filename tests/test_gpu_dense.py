@@ -249,7 +249,8 @@ def test_dense_conversions_misaligned_other_side(P, oracle, eb, bits, convert_mo
         np.testing.assert_array_equal(got.cpu().numpy(), want)
 
 
-@pytest.mark.parametrize("eb,bits", [(4, (8, 8, 8)), (2, (12,)), (4, (5, 6, 5, 3)), (8, (10, 10, 10, 10)), (4, (8, 8, 8, 8))])
+@pytest.mark.parametrize("eb,bits", [(4, (8, 8, 8)), (2, (12,)), (4, (5, 6, 5, 3)), (8, (10, 10, 10, 10)), (4, (8, 8, 8, 8)),
+                                     (8, (16, 16)), (2, (5, 6, 5)), (8, (4, 4)), (8, (16, 16, 16, 16))])  # S = 32 / 16 / 8 / 64: padded format
 def test_dense_binary_multi(P, oracle, eb, bits, mode):
     """Op pairs in one pass over dense streams == the ops run one by one; lists mixing pairs and singles."""
     pint_b200, ops, dense = P

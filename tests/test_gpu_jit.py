@@ -65,7 +65,8 @@ def test_jit_compile_ahead_and_disk_cache(jit_strict, oracle, tmp_path):
     lib = _lib.lib()
     assert lib.pint_cuda_jit_compile(L.ref) == 0, lib.pint_cuda_jit_last_error()
     files = os.listdir(tmp_path / "jit")
-    assert len([f for f in files if f.endswith(".cubin")]) == 3 and len([f for f in files if f.endswith(".names")]) == 3
+    # binary, fused, pair + (sum(Bits) = 12 is a whole-chunk dense layout) dense, densepair
+    assert len([f for f in files if f.endswith(".cubin")]) == 5 and len([f for f in files if f.endswith(".names")]) == 5
     n = (1 << 18) + 11
     a_h, b_h = oracle.fill(2, n, 5), oracle.fill(2, n, 6)
     before = ops.launch_count()
@@ -95,3 +96,35 @@ def test_jit_in_graph_capture_after_warm_up(jit_strict, oracle):
     g.replay()
     torch.cuda.synchronize()
     np.testing.assert_array_equal(to_np(out), oracle.binary("add_signed_saturate", 4, (7, 9, 3), a_h, b_h))
+
+
+@pytest.mark.parametrize("eb,bits", [(4, (5, 6, 5, 3)), (8, (10, 10, 10, 10)), (4, (7, 9, 3)), (2, (4, 4, 3))])
+def test_jit_dense_streams_match_oracle(jit_strict, oracle, eb, bits):
+    """Dense bit streams of layouts without compiled-in chunk masks: with option "jit" the whole-chunk kernel is
+    specialised for chunk_layout<Bits...> at run time.  Every op and every op pair against the oracle's dense
+    model (pack(op(unpack))), ragged sizes, in place, and equal to the run-time-mask kernels."""
+    import pint_b200
+    from pint_b200 import dense
+    ops = jit_strict
+    L = pint_b200.Layout(eb, *bits)
+    for n in (1, 127, 4097, (1 << 18) + 77):
+        a_h, b_h = oracle.fill(eb, n, 0xDE5E + n), oracle.fill(eb, n, 0xDE5F + n)
+        da_h, db_h = oracle.dense_pack(eb, bits, a_h), oracle.dense_pack(eb, bits, b_h)
+        da, db = torch.from_numpy(da_h.copy()).cuda(), torch.from_numpy(db_h.copy()).cuda()
+        for op in ops.OPS:
+            want = oracle.dense_binary(op, eb, bits, da_h, db_h, n)
+            before = ops.launch_count()
+            got = dense.binary(op, L, da, db, n)
+            assert ops.launch_count() == before + 1
+            np.testing.assert_array_equal(got.cpu().numpy(), want, err_msg=f"jit dense {L} {op} n={n}")
+        for pair in (("add_unsigned_saturate", "add_signed_saturate"), ("sub_signed_saturate", "add_signed_saturate"),
+                     ("min_signed", "max_signed"), ("sub_wrap", "add_wrap")):
+            o0, o1 = dense.binary_multi(list(pair), L, da, db, n)
+            np.testing.assert_array_equal(o0.cpu().numpy(), oracle.dense_binary(pair[0], eb, bits, da_h, db_h, n))
+            np.testing.assert_array_equal(o1.cpu().numpy(), oracle.dense_binary(pair[1], eb, bits, da_h, db_h, n))
+        # in place, and the same bytes with the option off
+        x = da.clone()
+        dense.binary("sub_unsigned_saturate", L, x, db, n, out=x)
+        ops.set_option("jit", 0)
+        np.testing.assert_array_equal(x.cpu().numpy(), dense.binary("sub_unsigned_saturate", L, da, db, n).cpu().numpy())
+        ops.set_option("jit", 2)
