@@ -123,8 +123,8 @@ int pint_cuda_layout_is_specialized(const pint_layout* layout);
 /* Run-time specialisation (option "jit", default 0 = off).  The reference gives EVERY layout its mask
  * constants at compile time (pint.hpp:324-337, 443-456); the library has them built in for a handful
  * (registry_layouts.def) and runs the others with masks in the constant bank.  With "jit" = 1 or 2 the
- * first packed -> packed call (or dense bit-stream binary / multi call, for layouts whose chunk is at most 19
- * words) on such a layout compiles the same kernel templates for
+ * first packed -> packed call (binary, multi, fused, binary_scalar, binary_pairs; or a dense bit-stream binary /
+ * multi call, for layouts whose chunk is at most 19 words) on such a layout compiles the same kernel templates for
  * static_layout<Integer, Bits...> with NVRTC (libnvrtc.so.12, loaded on demand; headers embedded in
  * the library), caches the cubin on disk ($PINT_CUDA_JIT_CACHE, else ~/.cache/pint_cuda) and uses it
  * from then on: the call that compiles blocks for about a second.  pint_cuda_jit_compile does that

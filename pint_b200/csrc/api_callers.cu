@@ -16,9 +16,21 @@ cudaError_t scalar_one(const layout_desc& d, const void* a, uint64_t scalar, voi
                        const launch_geom& g)
 {
     using W = word_of<Elem>;
-    using Bin = swar_fn<Op, runtime_masks<W>>;
-    const scalar_fn<Bin, ScalarFirst> fn{Bin{runtime_masks<W>(make_word_masks<W>(d))}, replicate_scalar<Elem>(scalar)};
-    return launch_map1<Elem>(a, out, n, fn, s, g);
+    const auto m = make_word_masks<W>(d);
+    auto run = [&](auto steps_tag) {
+        using RM = runtime_masks<W, decltype(steps_tag)::value>;
+        using Bin = swar_fn<Op, RM>;
+        const scalar_fn<Bin, ScalarFirst> fn{Bin{RM(m)}, replicate_scalar<Elem>(scalar)};
+        return launch_map1<Elem>(a, out, n, fn, s, g);
+    };
+    // ops that build a field-wide mask run only as many smear steps as the widest field needs (as generic.cu does):
+    // at 2W bytes per element the ALU side weighs 1.5 x what it does for the array-array op
+    constexpr bool fills = !(Op == OP_ADD_WRAP || Op == OP_SUB_WRAP || Op == OP_OR || Op == OP_AND || Op == OP_XOR);
+    if constexpr (fills) {
+        if (m.nsh > 1 && m.nsmear <= 2) return run(std::integral_constant<int, 2>{});
+        if (m.nsh > 1 && m.nsmear <= 4) return run(std::integral_constant<int, 4>{});
+    }
+    return run(std::integral_constant<int, (sizeof(W) == 8 ? 6 : 5)>{});
 }
 
 template <class Elem, int... Ops>
@@ -37,8 +49,17 @@ template <class Elem, int Op>
 cudaError_t pairs_one(const layout_desc& d, const void* pairs, void* out, size_t n, cudaStream_t s, const launch_geom& g)
 {
     using W = word_of<Elem>;
-    using Fn = swar_fn<Op, runtime_masks<W>>;
-    return launch_pairs_map<Elem>(pairs, out, n, Fn{runtime_masks<W>(make_word_masks<W>(d))}, s, g);
+    const auto m = make_word_masks<W>(d);
+    auto run = [&](auto steps_tag) {
+        using RM = runtime_masks<W, decltype(steps_tag)::value>;
+        return launch_pairs_map<Elem>(pairs, out, n, swar_fn<Op, RM>{RM(m)}, s, g);
+    };
+    constexpr bool fills = !(Op == OP_ADD_WRAP || Op == OP_SUB_WRAP || Op == OP_OR || Op == OP_AND || Op == OP_XOR);
+    if constexpr (fills) {
+        if (m.nsh > 1 && m.nsmear <= 2) return run(std::integral_constant<int, 2>{});
+        if (m.nsh > 1 && m.nsmear <= 4) return run(std::integral_constant<int, 4>{});
+    }
+    return run(std::integral_constant<int, (sizeof(W) == 8 ? 6 : 5)>{});
 }
 
 template <class Elem, int... Ops>
@@ -152,6 +173,29 @@ int pint_cuda_binary_scalar(int op, const pint_layout* layout, const void* a, ui
     const bool first = scalar_first != 0;
     if (const layout_kernels* k = find_static(d)) return (int)k->scalar[first][op](a, scalar, out, n, s, g);
     auto ops = std::make_integer_sequence<int, pint::cuda::OP_NUM_BINARY>();
+    auto runtime = [&](size_t start, size_t count) -> int {
+        if (!count) return PINT_OK;
+        const char* pa = static_cast<const char*>(a) + start * d.elem_bytes;
+        char* po = static_cast<char*>(out) + start * d.elem_bytes;
+        switch (d.elem_bytes) {
+        case 1: return (int)scalar_ops<uint8_t>(op, first, d, pa, scalar, po, count, s, g, ops);
+        case 2: return (int)scalar_ops<uint16_t>(op, first, d, pa, scalar, po, count, s, g, ops);
+        case 4: return (int)scalar_ops<uint32_t>(op, first, d, pa, scalar, po, count, s, g, ops);
+        default: return (int)scalar_ops<uint64_t>(op, first, d, pa, scalar, po, count, s, g, ops);
+        }
+    };
+    // option "jit": the vector body with this layout's constants compiled in at run time (jit.cu), the rest as before
+    if (const long jit = opts().jit) {
+        size_t head = 0, body = 0;
+        bool handled = false;
+        const int rc = jit_scalar_body(op, first, d, a, scalar, out, n, s, g, &head, &body, &handled);
+        if (handled) {
+            if (int r = runtime(0, head)) return r;
+            return runtime(head + body, n - head - body);
+        }
+        if (rc == PINT_E_JIT && jit >= 2) return rc;
+        if (rc != PINT_OK && rc != PINT_E_JIT) return rc;
+    }
     switch (d.elem_bytes) {
     case 1: return (int)scalar_ops<uint8_t>(op, first, d, a, scalar, out, n, s, g, ops);
     case 2: return (int)scalar_ops<uint16_t>(op, first, d, a, scalar, out, n, s, g, ops);
@@ -177,6 +221,28 @@ int pint_cuda_binary_pairs(int op, const pint_layout* layout, const void* pairs,
     cudaStream_t s = (cudaStream_t)stream;
     if (const layout_kernels* k = find_static(d)) return (int)k->pairs[op](pairs, out, n, s, g);
     auto ops = std::make_integer_sequence<int, pint::cuda::OP_NUM_BINARY>();
+    auto runtime = [&](size_t start, size_t count) -> int {
+        if (!count) return PINT_OK;
+        const char* pp = static_cast<const char*>(pairs) + 2 * start * d.elem_bytes;
+        char* po = static_cast<char*>(out) + start * d.elem_bytes;
+        switch (d.elem_bytes) {
+        case 1: return (int)pairs_map_ops<uint8_t>(op, d, pp, po, count, s, g, ops);
+        case 2: return (int)pairs_map_ops<uint16_t>(op, d, pp, po, count, s, g, ops);
+        case 4: return (int)pairs_map_ops<uint32_t>(op, d, pp, po, count, s, g, ops);
+        default: return (int)pairs_map_ops<uint64_t>(op, d, pp, po, count, s, g, ops);
+        }
+    };
+    if (const long jit = opts().jit) {
+        size_t head = 0, body = 0;
+        bool handled = false;
+        const int rc = jit_pairs_body(op, d, pairs, out, n, s, g, &head, &body, &handled);
+        if (handled) {
+            if (int r = runtime(0, head)) return r;
+            return runtime(head + body, n - head - body);
+        }
+        if (rc == PINT_E_JIT && jit >= 2) return rc;
+        if (rc != PINT_OK && rc != PINT_E_JIT) return rc;
+    }
     switch (d.elem_bytes) {
     case 1: return (int)pairs_map_ops<uint8_t>(op, d, pairs, out, n, s, g, ops);
     case 2: return (int)pairs_map_ops<uint16_t>(op, d, pairs, out, n, s, g, ops);

@@ -57,6 +57,11 @@ int jit_binary_pair(int pair, const layout_desc& d, const void* a, const void* b
 // dense bit streams (whole-chunk layouts): op >= 0 one op, pair >= 0 one of kOpPairs with both results
 int jit_dense(int op, int pair, const layout_desc& d, const void* a, const void* b, void* out, void* out1, size_t n,
               cudaStream_t s, const launch_geom& g, const pint::cuda::kernels::dense::dense_tuning& tune, bool* handled);
+// caller shapes: only the vector body is launched; *head elements before it and n - *head - *body after it are the caller's
+int jit_scalar_body(int op, bool first, const layout_desc& d, const void* a, uint64_t scalar, void* out, size_t n, cudaStream_t s,
+                    const launch_geom& g, size_t* head, size_t* body, bool* handled);
+int jit_pairs_body(int op, const layout_desc& d, const void* pairs, void* out, size_t n, cudaStream_t s, const launch_geom& g,
+                   size_t* head, size_t* body, bool* handled);
 int jit_compile_all(const layout_desc& d);
 int jit_prebuild(const layout_desc& d, int major, int minor);
 bool jit_is_loaded(const layout_desc& d);

@@ -182,8 +182,10 @@ bool load_driver()
 // FAM_DENSE / FAM_DENSE_PAIR: the whole-chunk kernels of the dense bit-stream format (cuda_kernels_dense_mw.cuh) with the
 // chunk masks of chunk_layout<Bits...> compiled in -- what dense_static.cu instantiates for the layouts of dense_layouts.def.
 // They exist for layouts whose chunk is at most kMaxMwWords words and whose sum(Bits) is not 8 / 16 / 32 / 64.
-enum family : int { FAM_BINARY = 0, FAM_FUSED = 1, FAM_PAIR = 2, FAM_DENSE = 3, FAM_DENSE_PAIR = 4, FAM_COUNT = 5 };
-const char* const kFamilyName[FAM_COUNT] = {"binary", "fused", "pair", "dense", "densepair"};
+// FAM_SCALAR / FAM_PAIRSMAP: the caller shapes of api_callers.cu -- one operand constant (26 kernels: op x operand side)
+// and interleaved std::pair operands (13) -- with the functor registry_part.cu picks for a registered layout (caller_fn).
+enum family : int { FAM_BINARY = 0, FAM_FUSED = 1, FAM_PAIR = 2, FAM_DENSE = 3, FAM_DENSE_PAIR = 4, FAM_SCALAR = 5, FAM_PAIRSMAP = 6, FAM_COUNT = 7 };
+const char* const kFamilyName[FAM_COUNT] = {"binary", "fused", "pair", "dense", "densepair", "scalar", "pairsmap"};
 
 uint32_t sum_bits(const layout_desc& d)
 {
@@ -208,7 +210,7 @@ bool family_applies(const layout_desc& d, int fam)
 }
 
 // kernels per entry of a family: 16- and 32-byte vector forms for the padded families, one for the dense ones
-int family_variants(int fam) { return is_dense_family(fam) ? 1 : 2; }
+int family_variants(int fam) { return fam <= FAM_PAIR ? 2 : 1; }
 
 struct jit_kernel {
     CUfunction f128 = nullptr, f256 = nullptr;
@@ -234,7 +236,12 @@ const char* integer_name(uint32_t eb)
     return eb == 1 ? "uint8_t" : eb == 2 ? "uint16_t" : eb == 4 ? "uint32_t" : "uint64_t";
 }
 
-int family_count(int fam) { return (fam == FAM_PAIR || fam == FAM_DENSE_PAIR) ? kNumOpPairs : (int)pint::cuda::OP_NUM_BINARY; }
+int family_count(int fam)
+{
+    if (fam == FAM_PAIR || fam == FAM_DENSE_PAIR) return kNumOpPairs;
+    if (fam == FAM_SCALAR) return 2 * (int)pint::cuda::OP_NUM_BINARY;  // index = scalar_first * 13 + op
+    return (int)pint::cuda::OP_NUM_BINARY;
+}
 
 std::string kernel_fn(int fam, int i)
 {
@@ -243,6 +250,8 @@ std::string kernel_fn(int fam, int i)
     else if (fam == FAM_FUSED) std::snprintf(buf, sizeof buf, "pint_jit::FFn<%d>", i);
     else if (fam == FAM_DENSE) std::snprintf(buf, sizeof buf, "pint_jit::DFn<%d>", i);
     else if (fam == FAM_DENSE_PAIR) std::snprintf(buf, sizeof buf, "pint_jit::DPFn<%d>", i);
+    else if (fam == FAM_SCALAR) std::snprintf(buf, sizeof buf, "pint_jit::SFn<%d, %s>", i % (int)pint::cuda::OP_NUM_BINARY, i >= (int)pint::cuda::OP_NUM_BINARY ? "true" : "false");
+    else if (fam == FAM_PAIRSMAP) std::snprintf(buf, sizeof buf, "pint_jit::CFn<%d>", i);
     else std::snprintf(buf, sizeof buf, "pint_jit::PFn<%d>", i);
     return buf;
 }
@@ -252,6 +261,8 @@ std::string kernel_expr(int fam, int i, bool wide)
     const std::string fn = kernel_fn(fam, i);
     if (is_dense_family(fam))  // Mode 0: one result; Mode 1: the second result of an op pair leaves over the b tile
         return "pint::cuda::kernels::dense::dense_binary_kernel<" + fn + ", pint_jit::DGeo, " + (fam == FAM_DENSE_PAIR ? "1" : "0") + ">";
+    if (fam == FAM_SCALAR) return "pint::cuda::kernels::map1_stream_kernel<" + fn + ", 4>";                              // launch_map1's U
+    if (fam == FAM_PAIRSMAP) return "pint::cuda::kernels::pairs_map_kernel<pint_jit::SL::integer, " + fn + ", 2>";   // launch_pairs_map's U
     const char* base = fam == FAM_PAIR ? (wide ? "binary_pair_stream256_kernel" : "binary_pair_stream_kernel")
                                        : (wide ? "binary_stream256_kernel" : "binary_stream_kernel");
     return std::string("pint::cuda::kernels::") + base + "<" + fn + ", pint_jit::Cfg<" + fn + ">>";
@@ -283,6 +294,8 @@ std::string make_source(const layout_desc& d, int fam)
          "template <int Op> using BFn = swar_fn<Op, M>;\n"
          "template <int Op> using FFn = fused_fn<Op, F>;\n"
          "template <int P> using PFn = pair_fn<kOpPairs[P][0], kOpPairs[P][1], M>;\n"
+         "template <int Op> using CFn = typename std::conditional<sizeof(typename M::word) == 8 && swar_fn<Op, M>::heavy, fused_fn<Op, F>, swar_fn<Op, M>>::type;\n"
+         "template <int Op, bool First> using SFn = scalar_fn<CFn<Op>, First>;\n"
          "template <class Fn> using Cfg = stream_cfg_for<Fn>;\n"
          "template <class Fn> struct wide { static constexpr int value = int(Fn::vec256); };\n"
          "template <int A, int B, class P> struct wide<pair_fn<A, B, P>> { static constexpr int value = (!pair_fn<A, B, P>::heavy && sizeof(typename P::word) == 4) ? 1 : 0; };\n"
@@ -291,7 +304,13 @@ std::string make_source(const layout_desc& d, int fam)
     s += "extern \"C\" __device__ const int pint_jit_cfg[" + std::to_string(family_count(fam)) + "][4] = {\n";
     for (int i = 0; i < family_count(fam); ++i) {
         const std::string fn = kernel_fn(fam, i);
-        s += "  {pint_jit::Cfg<" + fn + ">::UNROLL, pint_jit::Cfg<" + fn + ">::BLOCK, pint_jit::wide<" + fn + ">::value, int(" + fn + "::heavy)},\n";
+        if (fam == FAM_SCALAR)  // size of the functor parameter and where its scalar word sits: the host builds the same bytes
+            // k is scalar_fn's last member and as wide as the struct's alignment: it sits in the last sizeof(word) bytes
+            s += "  {int(sizeof(" + fn + ")), int(sizeof(" + fn + ") - sizeof(typename " + fn + "::word)), int(sizeof(typename " + fn + "::word)), 0},\n";
+        else if (fam == FAM_PAIRSMAP)
+            s += "  {int(sizeof(" + fn + ")), 0, 0, 0},\n";
+        else
+            s += "  {pint_jit::Cfg<" + fn + ">::UNROLL, pint_jit::Cfg<" + fn + ">::BLOCK, pint_jit::wide<" + fn + ">::value, int(" + fn + "::heavy)},\n";
     }
     s += "};\n";
     return s;
@@ -596,6 +615,78 @@ int jit_dense(int op, int pair, const layout_desc& d, const void* a, const void*
     if (g_drv.LaunchKernel(k.f128, unsigned(ntiles), 1, 1, T, 1, 1, (unsigned)smem, (CUstream)s, args, nullptr) != CUDA_SUCCESS)
         return (int)cudaErrorLaunchFailure;
     count_launch(g);
+    *handled = true;
+    return PINT_OK;
+}
+
+// One operand constant: launches the 16-byte-vector body of [0, n) with the specialised kernel and reports where it
+// starts and how many elements it covers; the caller runs its own kernels on what is left on either side.
+int jit_scalar_body(int op, bool first, const layout_desc& d, const void* a, uint64_t scalar, void* out, size_t n, cudaStream_t s,
+                    const launch_geom& g, size_t* head, size_t* body, bool* handled)
+{
+    *handled = false;
+    jit_module* m = lookup(d, FAM_SCALAR);
+    if (!m) return PINT_E_JIT;
+    const jit_kernel& k = m->k[(first ? (int)pint::cuda::OP_NUM_BINARY : 0) + op];
+    const int wbytes = d.elem_bytes == 8 ? 8 : 4;
+    if (k.vec256 != wbytes || k.unroll > 16 || k.block + wbytes > k.unroll) {  // {sizeof(Fn), offsetof(Fn, k), sizeof(word)}
+        std::lock_guard<std::mutex> lock(g_jit_mutex);
+        g_last_error = "scalar module: unexpected functor layout";
+        return PINT_E_JIT;
+    }
+    const void* ptrs[2] = {a, out};
+    size_t h = 0, nvec = 0, tail = 0;
+    if (!(split_aligned(d.elem_bytes, n, ptrs, 2, &h, &nvec, &tail, 16) && nvec)) return PINT_OK;
+    // the scalar replicated over the processing word, as replicate_scalar does
+    uint64_t kw = scalar;
+    if (d.elem_bytes == 2) kw = uint32_t(uint16_t(scalar)) * 0x00010001u;
+    if (d.elem_bytes == 1) kw = uint32_t(uint8_t(scalar)) * 0x01010101u;
+    if (d.elem_bytes == 4) kw = uint32_t(scalar);
+    alignas(8) unsigned char fn[16] = {};
+    std::memcpy(fn + k.block, &kw, (size_t)wbytes);  // little-endian: the low 4 bytes are the 32-bit word
+    const void* in_v = static_cast<const char*>(a) + h * d.elem_bytes;
+    void* out_v = static_cast<char*>(out) + h * d.elem_bytes;
+    const size_t ntiles = (nvec + 4 * 256 - 1) / (4 * 256);
+    void* args[4] = {(void*)&in_v, (void*)&out_v, &nvec, fn};
+    if (g_drv.LaunchKernel(k.f128, grid_for(ntiles, g), 1, 1, 256, 1, 1, 0, (CUstream)s, args, nullptr) != CUDA_SUCCESS)
+        return (int)cudaErrorLaunchFailure;
+    count_launch(g);
+    *head = h;
+    *body = nvec * (16 / d.elem_bytes);
+    *handled = true;
+    return PINT_OK;
+}
+
+// Interleaved operands: launch_pairs_map's geometry (results 16-byte aligned, pairs 32-byte aligned at the same element)
+int jit_pairs_body(int op, const layout_desc& d, const void* pairs, void* out, size_t n, cudaStream_t s, const launch_geom& g,
+                   size_t* head, size_t* body, bool* handled)
+{
+    *handled = false;
+    jit_module* m = lookup(d, FAM_PAIRSMAP);
+    if (!m) return PINT_E_JIT;
+    const jit_kernel& k = m->k[op];
+    if (k.unroll != 1) {  // sizeof(Fn): an empty functor
+        std::lock_guard<std::mutex> lock(g_jit_mutex);
+        g_last_error = "pairsmap module: unexpected functor layout";
+        return PINT_E_JIT;
+    }
+    const size_t eb = d.elem_bytes, per = 16 / eb;
+    const uintptr_t off = reinterpret_cast<uintptr_t>(out) & 15u;
+    size_t h = off ? (16 - off) / eb : 0;
+    if (h > n) h = n;
+    const char* pv = static_cast<const char*>(pairs) + 2 * h * eb;
+    if (reinterpret_cast<uintptr_t>(pv) & 31u) return PINT_OK;
+    size_t nvec = (n - h) / per;
+    if (!nvec) return PINT_OK;
+    void* ov = static_cast<char*>(out) + h * eb;
+    const size_t ntiles = (nvec + 2 * 256 - 1) / (2 * 256);
+    char empty_fn = 0;
+    void* args[4] = {(void*)&pv, (void*)&ov, &nvec, &empty_fn};
+    if (g_drv.LaunchKernel(k.f128, grid_for(ntiles, g), 1, 1, 256, 1, 1, 0, (CUstream)s, args, nullptr) != CUDA_SUCCESS)
+        return (int)cudaErrorLaunchFailure;
+    count_launch(g);
+    *head = h;
+    *body = nvec * per;
     *handled = true;
     return PINT_OK;
 }

@@ -65,8 +65,8 @@ def test_jit_compile_ahead_and_disk_cache(jit_strict, oracle, tmp_path):
     lib = _lib.lib()
     assert lib.pint_cuda_jit_compile(L.ref) == 0, lib.pint_cuda_jit_last_error()
     files = os.listdir(tmp_path / "jit")
-    # binary, fused, pair + (sum(Bits) = 12 is a whole-chunk dense layout) dense, densepair
-    assert len([f for f in files if f.endswith(".cubin")]) == 5 and len([f for f in files if f.endswith(".names")]) == 5
+    # binary, fused, pair, scalar, pairsmap + (sum(Bits) = 12 is a whole-chunk dense layout) dense, densepair
+    assert len([f for f in files if f.endswith(".cubin")]) == 7 and len([f for f in files if f.endswith(".names")]) == 7
     n = (1 << 18) + 11
     a_h, b_h = oracle.fill(2, n, 5), oracle.fill(2, n, 6)
     before = ops.launch_count()
@@ -128,3 +128,29 @@ def test_jit_dense_streams_match_oracle(jit_strict, oracle, eb, bits):
         ops.set_option("jit", 0)
         np.testing.assert_array_equal(x.cpu().numpy(), dense.binary("sub_unsigned_saturate", L, da, db, n).cpu().numpy())
         ops.set_option("jit", 2)
+
+
+@pytest.mark.parametrize("eb,bits", [(4, (7, 9, 3)), (8, (10, 10, 10, 10)), (2, (4, 4, 4)), (1, (3, 5)), (8, (3, 7, 11, 13, 17, 12))])
+def test_jit_caller_shapes_match_oracle(jit_strict, oracle, eb, bits):
+    """binary_scalar (either operand side) and binary_pairs on layouts without pre-built constants, specialised at
+    run time: every op against the oracle; arrays at a misaligned element offset (head / tail through the run-time-mask
+    kernels around the specialised body), sizes below one vector, in place for the scalar form."""
+    import pint_b200
+    ops = jit_strict
+    from pint_b200 import _lib
+    L = pint_b200.Layout(eb, *bits)
+    assert _lib.lib().pint_cuda_layout_is_specialized(L.ref) != 1, "pick layouts that are NOT built into the library"
+    for n, off in (((1 << 17) + 4099, 0), (70001, 3), (3, 0), (1 << 12, 1)):
+        a_h, b_h = oracle.fill(eb, n, 0xCA11 + n), oracle.fill(eb, n, 0xCA12 + n)
+        a = to_dev(a_h, off)
+        kval = int(b_h[n // 2])
+        kk = np.full_like(a_h, kval)
+        pairs = to_dev(np.stack([a_h, b_h], axis=1).reshape(-1), 2 * off)
+        for op in ops.OPS:
+            np.testing.assert_array_equal(to_np(ops.binary_scalar(op, L, a, kval)), oracle.binary(op, eb, bits, a_h, kk), err_msg=f"{L} {op} OP(a,k) n={n}")
+            np.testing.assert_array_equal(to_np(ops.binary_scalar(op, L, a, kval, scalar_first=True)), oracle.binary(op, eb, bits, kk, a_h),
+                                          err_msg=f"{L} {op} OP(k,a) n={n}")
+            np.testing.assert_array_equal(to_np(ops.binary_pairs(op, L, pairs)), oracle.binary(op, eb, bits, a_h, b_h), err_msg=f"{L} {op} pairs n={n}")
+        x = to_dev(a_h, off)
+        ops.binary_scalar("sub_signed_saturate", L, x, kval, out=x)
+        np.testing.assert_array_equal(to_np(x), oracle.binary("sub_signed_saturate", eb, bits, a_h, kk))

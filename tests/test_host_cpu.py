@@ -188,9 +188,12 @@ def test_jit_prebuild_without_a_device(tmp_path, monkeypatch):
     rc = lib.pint_cuda_jit_prebuild(L.ref, 10, 0)
     assert rc == 0, lib.pint_cuda_jit_last_error().decode()[:2000]
     files = sorted(os.listdir(tmp_path / "jit"))
-    # padded families (binary, fused, pair) and, since sum(Bits) = 19 is a whole-chunk dense layout, the dense ones
-    assert sorted(f.split("_")[1] for f in files) == ["binary.cubin", "binary.names", "dense.cubin", "dense.names", "densepair.cubin",
-                                                      "densepair.names", "fused.cubin", "fused.names", "pair.cubin", "pair.names"]
+    # padded families (binary, fused, pair), the caller shapes (scalar, pairsmap) and, since sum(Bits) = 19 is a
+    # whole-chunk dense layout, the dense ones
+    fams = ["binary", "dense", "densepair", "fused", "pair", "pairsmap", "scalar"]
+    assert sorted(f.split("_")[1] for f in files) == sorted(f"{x}.{e}" for x in fams for e in ("cubin", "names"))
+    sn = open(tmp_path / "jit" / [f for f in files if f.endswith("_scalar.names")][0]).read().split()
+    assert len(sn) == 26 and all("map1_stream_kernel" in x and "scalar_fn" in x for x in sn)
     dn = open(tmp_path / "jit" / [f for f in files if f.endswith("_dense.names")][0]).read().split()
     assert len(dn) == 13 and all("dense_binary_kernel" in x and "chunk_layout" in x for x in dn)
     names = open(tmp_path / "jit" / [f for f in files if f.endswith("binary.names")][0]).read().split()

@@ -253,6 +253,48 @@ static void run_hint(const void* a, const void* b, void* o0, void* o1, size_t nv
     });
 }
 
+// ---- read / write mix ceilings (mode 12): pure data movement with the stream counts of the library's kernels ----
+// NIN input streams are XOR-combined into NOUT identical output streams, 32-byte accesses, one CTA per tile,
+// U vectors per stream per thread: the same access pattern as the stream kernels, without their arithmetic.
+template <int NIN, int NOUT, int U>
+__global__ void __launch_bounds__(256) mix_kernel(const vec32* in, vec32* out, size_t nvec, size_t in_stride, size_t out_stride)
+{
+    constexpr int B = 256;
+    const size_t base = size_t(blockIdx.x) * (size_t(U) * B) + threadIdx.x;
+    vec32 v[NIN][U];
+#pragma unroll
+    for (int k = 0; k < NIN; ++k)
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (base + size_t(u) * B < nvec) v[k][u] = ld32(in + size_t(k) * in_stride + base + size_t(u) * B);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        if (base + size_t(u) * B >= nvec) continue;
+        vec32 r = v[0][u];
+#pragma unroll
+        for (int k = 1; k < NIN; ++k) {
+            r.lo.x ^= v[k][u].lo.x; r.lo.y ^= v[k][u].lo.y; r.lo.z ^= v[k][u].lo.z; r.lo.w ^= v[k][u].lo.w;
+            r.hi.x ^= v[k][u].hi.x; r.hi.y ^= v[k][u].hi.y; r.hi.z ^= v[k][u].hi.z; r.hi.w ^= v[k][u].hi.w;
+        }
+#pragma unroll
+        for (int k = 0; k < NOUT; ++k) {
+            r.lo.x += k;  // the outputs differ, so no store can be merged away
+            st32(out + size_t(k) * out_stride + base + size_t(u) * B, r);
+        }
+    }
+}
+
+template <int NIN, int NOUT, int U>
+static void run_mix(const void* in, void* out, size_t stream_bytes)
+{
+    const size_t nvec = stream_bytes / 32, tile = size_t(U) * 256;
+    char name[160];
+    std::snprintf(name, sizeof name, "mix %d read : %d write streams (%2.0f %% writes), U%d", NIN, NOUT, 100.0 * NOUT / (NIN + NOUT), U);
+    time_it(name, double(stream_bytes) * (NIN + NOUT), [&] {
+        mix_kernel<NIN, NOUT, U><<<unsigned((nvec + tile - 1) / tile), 256>>>((const vec32*)in, (vec32*)out, nvec, nvec, nvec);
+    });
+}
+
 int main(int argc, char** argv)
 {
     const int log2n = argc > 1 ? std::atoi(argv[1]) : 30;
@@ -421,6 +463,21 @@ int main(int argc, char** argv)
             unpack_run(I1{}, I0{}, block); unpack_run(I2{}, I0{}, block);
             unpack_run(I1{}, I1{}, block);
         }
+        std::printf("done\n");
+        return 0;
+    }
+    if (argc > 3 && std::atoi(argv[3]) == 12) {
+        // what the DRAM side delivers for each read / write mix, 1 GiB per stream: `a`+`b` hold up to 8 input streams,
+        // `out`+`out2` up to 8 output streams (the arrays are 4 GiB each at log2 = 30)
+        const size_t sb = size_t(1) << 30;
+        run_mix<1, 1, 2>(a, out, sb); run_mix<1, 1, 4>(a, out, sb);   // copy:        unary maps (slice, shift, binary_scalar)
+        run_mix<2, 1, 2>(a, out, sb); run_mix<2, 1, 4>(a, out, sb);   // 67 % reads:  binary ops
+        run_mix<2, 2, 1>(a, out, sb); run_mix<2, 2, 2>(a, out, sb);   // 50 / 50:     two ops per pass
+        run_mix<1, 3, 1>(a, out, sb); run_mix<1, 3, 2>(a, out, sb);   // 75 % writes: unpack u64 -> 6 int32 planes (8 B in, 24 B out)
+        run_mix<3, 1, 1>(a, out, sb); run_mix<3, 1, 2>(a, out, sb);   // 75 % reads:  repack
+        run_mix<1, 4, 1>(a, out, sb); run_mix<4, 1, 1>(a, out, sb);   // RGBA8 <-> four int32 planes (20 % / 80 %)
+        time_it("cudaMemsetAsync 4 GiB (write-only, constant data)", double(bytes), [&] { CK(cudaMemsetAsync(out, 1, bytes)); });
+        time_it("cudaMemcpyAsync D2D 4 GiB (50 / 50)", double(bytes) * 2, [&] { CK(cudaMemcpyAsync(out, a, bytes, cudaMemcpyDeviceToDevice)); });
         std::printf("done\n");
         return 0;
     }
