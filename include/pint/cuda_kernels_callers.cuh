@@ -41,6 +41,7 @@ template <class Fn, int U>
 __global__ void __launch_bounds__(256)
 map1_stream_kernel(const uint4* in, uint4* out, size_t nvec, const __grid_constant__ Fn fn)
 {
+    pdl_prologue();
     using W = typename Fn::word;
     constexpr int B = 256;
     constexpr size_t tile = size_t(U) * B;
@@ -94,8 +95,9 @@ cudaError_t launch_map1(const void* in, void* out, size_t n, const Fn& fn, cudaS
         // 6516-6896 GB/s on RGBA8 depending on the op's ALU weight, U = 4 6780-6800 for all of them)
         constexpr int U = 4;
         const size_t ntiles = (nvec + size_t(U) * 256 - 1) / (size_t(U) * 256);
-        map1_stream_kernel<Fn, U><<<grid_for(ntiles, g), 256, 0, s>>>(
-            reinterpret_cast<const uint4*>(ei + head), reinterpret_cast<uint4*>(eo + head), nvec, fn);
+        if (cudaError_t e = launch_stream_kernel(map1_stream_kernel<Fn, U>, grid_for(ntiles, g), 256, s, g.pdl != 0,
+                                                 reinterpret_cast<const uint4*>(ei + head), reinterpret_cast<uint4*>(eo + head), nvec, fn))
+            return e;
         count_launch(g);
     }
     elems(n - tail, tail);
@@ -136,6 +138,7 @@ template <class Elem, class Fn, int U>
 __global__ void __launch_bounds__(256)
 pairs_map_kernel(const vec32* pairs, uint4* out, size_t nvec, const __grid_constant__ Fn fn)
 {
+    pdl_prologue();
     constexpr int B = 256;
     constexpr size_t tile = size_t(U) * B;
     const size_t nfull = nvec / tile;
@@ -193,8 +196,9 @@ cudaError_t launch_pairs_map(const void* pairs, void* out, size_t n, const Fn& f
     elems(0, head);
     constexpr int U = 2;
     const size_t ntiles = (nvec + size_t(U) * 256 - 1) / (size_t(U) * 256);
-    pairs_map_kernel<Elem, Fn, U><<<grid_for(ntiles, g), 256, 0, s>>>(
-        reinterpret_cast<const vec32*>(ep + 2 * head), reinterpret_cast<uint4*>(eo + head), nvec, fn);
+    if (cudaError_t e = launch_stream_kernel(pairs_map_kernel<Elem, Fn, U>, grid_for(ntiles, g), 256, s, g.pdl != 0,
+                                             reinterpret_cast<const vec32*>(ep + 2 * head), reinterpret_cast<uint4*>(eo + head), nvec, fn))
+        return e;
     count_launch(g);
     elems(head + nvec * per, n - head - nvec * per);
     return cudaGetLastError();

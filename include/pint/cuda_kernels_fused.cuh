@@ -177,7 +177,7 @@ cudaError_t launch_unpack(const void* packed, const plane_ptrs& planes, uint32_t
             if (planes.p[f] && !aligned16(planes.p[f])) gok = false;
         const size_t ngroups = gok ? n / G : 0;
         if (ngroups) {
-            unpack_group_kernel<Elem, PlaneBytes, Signed, FP><<<grid_for((ngroups + 255) / 256, g), 256, 0, stream>>>(src, planes, ngroups, fp);
+            if (cudaError_t e = launch_stream_kernel(unpack_group_kernel<Elem, PlaneBytes, Signed, FP>, grid_for((ngroups + 255) / 256, g), 256, stream, g.pdl != 0, src, planes, ngroups, fp)) return e;
             count_launch(g);
             done = ngroups * G;
         }
@@ -197,9 +197,9 @@ cudaError_t launch_unpack(const void* packed, const plane_ptrs& planes, uint32_t
             if (ntiles) {
                 const size_t smem = size_t(nfields) * tile * 4;
                 if (tile == 2048)
-                    unpack_bulk_kernel<Elem, Signed, FP, 2048, 256><<<grid_for(ntiles, g), 256, smem, stream>>>(src, planes, ntiles, nfields, fp);
+                    { if (cudaError_t e = launch_stream_kernel_smem(unpack_bulk_kernel<Elem, Signed, FP, 2048, 256>, grid_for(ntiles, g), 256, smem, stream, g.pdl != 0, src, planes, ntiles, nfields, fp)) return e; }
                 else
-                    unpack_bulk_kernel<Elem, Signed, FP, 1024, 256><<<grid_for(ntiles, g), 256, smem, stream>>>(src, planes, ntiles, nfields, fp);
+                    { if (cudaError_t e = launch_stream_kernel_smem(unpack_bulk_kernel<Elem, Signed, FP, 1024, 256>, grid_for(ntiles, g), 256, smem, stream, g.pdl != 0, src, planes, ntiles, nfields, fp)) return e; }
                 count_launch(g);
                 done = ntiles * tile;
                 if (done == n) return cudaGetLastError();
@@ -221,9 +221,9 @@ cudaError_t launch_unpack(const void* packed, const plane_ptrs& planes, uint32_t
         const size_t nocts = ook ? n / 8 : 0;
         if (nocts) {
             if (g.vec256 == 2)
-                unpack_oct_kernel<Elem, Signed, FP, 2><<<grid_for((nocts + 511) / 512, g), 256, 0, stream>>>(src, planes, nocts, fp);
+                { if (cudaError_t e = launch_stream_kernel(unpack_oct_kernel<Elem, Signed, FP, 2>, grid_for((nocts + 511) / 512, g), 256, stream, g.pdl != 0, src, planes, nocts, fp)) return e; }
             else
-                unpack_oct_kernel<Elem, Signed, FP><<<grid_for((nocts + 255) / 256, g), 256, 0, stream>>>(src, planes, nocts, fp);
+                { if (cudaError_t e = launch_stream_kernel(unpack_oct_kernel<Elem, Signed, FP, 1>, grid_for((nocts + 255) / 256, g), 256, stream, g.pdl != 0, src, planes, nocts, fp)) return e; }
             count_launch(g);
             done = nocts * 8;
         }
@@ -231,7 +231,7 @@ cudaError_t launch_unpack(const void* packed, const plane_ptrs& planes, uint32_t
     const size_t nquads = (ok && !done) ? n / 4 : 0;
     if (nquads) {
         const unsigned grid = grid_for((nquads + 255) / 256, g);
-        unpack_quad_kernel<Elem, PlaneBytes, Signed, FP><<<grid, 256, 0, stream>>>(src, planes, nquads, fp);
+        if (cudaError_t e = launch_stream_kernel(unpack_quad_kernel<Elem, PlaneBytes, Signed, FP, 1, CACHE_STREAMING>, grid, 256, stream, g.pdl != 0, src, planes, nquads, fp)) return e;
         count_launch(g);
         done = 4 * nquads;
     }
@@ -263,7 +263,7 @@ cudaError_t launch_repack(const plane_ptrs& planes, uint32_t nfields, void* pack
             if (!aligned16(planes.p[f])) gok = false;
         const size_t ngroups = gok ? n / G : 0;
         if (ngroups) {
-            repack_group_kernel<Elem, PlaneBytes, FP><<<grid_for((ngroups + 255) / 256, g), 256, 0, stream>>>(planes, dst, ngroups, fp);
+            if (cudaError_t e = launch_stream_kernel(repack_group_kernel<Elem, PlaneBytes, FP>, grid_for((ngroups + 255) / 256, g), 256, stream, g.pdl != 0, planes, dst, ngroups, fp)) return e;
             count_launch(g);
             done = ngroups * G;
         }
@@ -271,7 +271,7 @@ cudaError_t launch_repack(const plane_ptrs& planes, uint32_t nfields, void* pack
     const size_t nquads = (ok && !done) ? n / 4 : 0;
     if (nquads) {
         const unsigned grid = grid_for((nquads + 255) / 256, g);
-        repack_quad_kernel<Elem, PlaneBytes, FP><<<grid, 256, 0, stream>>>(planes, dst, nquads, fp);
+        if (cudaError_t e = launch_stream_kernel(repack_quad_kernel<Elem, PlaneBytes, FP>, grid, 256, stream, g.pdl != 0, planes, dst, nquads, fp)) return e;
         count_launch(g);
         done = 4 * nquads;
     }

@@ -184,6 +184,7 @@ __global__ void __launch_bounds__(256)
 unpack_quad_kernel(const Elem* packed, const __grid_constant__ plane_ptrs planes, size_t nquads,
                    const __grid_constant__ FP fp)
 {
+    pdl_prologue();
     using W = typename FP::word;
     const size_t tile = size_t(Q) * blockDim.x;
     for (size_t t = blockIdx.x; t * tile < nquads; t += gridDim.x) {
@@ -238,6 +239,7 @@ __global__ void __launch_bounds__(256)
 repack_quad_kernel(const __grid_constant__ plane_ptrs planes, Elem* packed, size_t nquads,
                    const __grid_constant__ FP fp)
 {
+    pdl_prologue();
     using W = typename FP::word;
     constexpr uint32_t WB = 8 * sizeof(W);
     for (size_t q = size_t(blockIdx.x) * blockDim.x + threadIdx.x; q < nquads; q += size_t(gridDim.x) * blockDim.x) {
@@ -317,6 +319,7 @@ __global__ void __launch_bounds__(256)
 unpack_group_kernel(const Elem* packed, const __grid_constant__ plane_ptrs planes, size_t ngroups,
                     const __grid_constant__ FP fp)
 {
+    pdl_prologue();
     using W = typename FP::word;
     constexpr int G = 16 / PlaneBytes, NW = group_words<Elem, G>::NW;
     for (size_t g = size_t(blockIdx.x) * blockDim.x + threadIdx.x; g < ngroups; g += size_t(gridDim.x) * blockDim.x) {
@@ -344,6 +347,7 @@ template <class Elem, bool Signed, class FP, int K = 1>
 __global__ void __launch_bounds__(256)
 unpack_oct_kernel(const Elem* packed, const __grid_constant__ plane_ptrs planes, size_t nocts, const __grid_constant__ FP fp)
 {
+    pdl_prologue();
     using W = typename FP::word;
     constexpr int G = 8, NW = group_words<Elem, G>::NW;
     // K octs per thread, a block apart (every access of a warp stays contiguous), all loads first
@@ -380,6 +384,7 @@ template <class Elem, int PlaneBytes, class FP>
 __global__ void __launch_bounds__(256)
 repack_group_kernel(const __grid_constant__ plane_ptrs planes, Elem* packed, size_t ngroups, const __grid_constant__ FP fp)
 {
+    pdl_prologue();
     using W = typename FP::word;
     constexpr uint32_t WB = 8 * sizeof(W);
     constexpr int G = 16 / PlaneBytes, NW = group_words<Elem, G>::NW;

@@ -40,6 +40,7 @@ __global__ void __launch_bounds__(BLOCK)
 unpack_bulk_kernel(const Elem* packed, const __grid_constant__ plane_ptrs planes, size_t ntiles, uint32_t nfields,
                    const __grid_constant__ FP fp)
 {
+    pdl_prologue();
     using W = typename FP::word;
     static_assert(TILE % (4 * BLOCK) == 0, "a tile is a whole number of quads per thread");
     constexpr int QPT = TILE / 4 / BLOCK;

@@ -315,6 +315,7 @@ template <class Word, class Cfg>
 __global__ void __launch_bounds__(Cfg::BLOCK)
 unary_stream_kernel(const uint4* in, uint4* out, size_t nvec, const __grid_constant__ unary_params<Word> u)
 {
+    pdl_prologue();
     constexpr int U = Cfg::UNROLL, B = Cfg::BLOCK;
     constexpr size_t tile = size_t(U) * B;
     const size_t nfull = nvec / tile;
@@ -337,6 +338,7 @@ template <class Word, class Cfg>
 __global__ void __launch_bounds__(Cfg::BLOCK)
 unary_stream256_kernel(const vec32* in, vec32* out, size_t nvec, const __grid_constant__ unary_params<Word> u)
 {
+    pdl_prologue();
     constexpr int U = Cfg::UNROLL, B = Cfg::BLOCK;  // twice the bytes per thread of the 16-byte kernel: one stream only
     constexpr size_t tile = size_t(U) * B;
     const size_t nfull = nvec / tile;
@@ -422,16 +424,17 @@ inline unsigned grid_for(size_t ntiles, const launch_geom& g)
 // allowed: the grid may start while the previous launch of the stream drains (the kernel's pdl_prologue
 // holds its work until that launch has completed)
 template <class... KArgs, class... Args>
-inline cudaError_t launch_stream_kernel(void (*kern)(KArgs...), unsigned grid, unsigned block, cudaStream_t stream, bool pdl, Args&&... args)
+inline cudaError_t launch_stream_kernel_smem(void (*kern)(KArgs...), unsigned grid, unsigned block, size_t smem, cudaStream_t stream, bool pdl,
+                                            Args&&... args)
 {
     if (!pdl) {
-        kern<<<grid, block, 0, stream>>>(KArgs(args)...);
+        kern<<<grid, block, smem, stream>>>(KArgs(args)...);
         return cudaSuccess;
     }
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(grid);
     cfg.blockDim = dim3(block);
-    cfg.dynamicSmemBytes = 0;
+    cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
@@ -439,6 +442,12 @@ inline cudaError_t launch_stream_kernel(void (*kern)(KArgs...), unsigned grid, u
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
+template <class... KArgs, class... Args>
+inline cudaError_t launch_stream_kernel(void (*kern)(KArgs...), unsigned grid, unsigned block, cudaStream_t stream, bool pdl, Args&&... args)
+{
+    return launch_stream_kernel_smem(kern, grid, block, 0, stream, pdl, static_cast<Args&&>(args)...);
 }
 
 inline void count_launch(const launch_geom& g)
@@ -546,8 +555,9 @@ cudaError_t launch_unary(const void* in, void* out, size_t n, const unary_params
         elems(0, head);
         constexpr size_t tile = size_t(Cfg::UNROLL) * Cfg::BLOCK;
         const size_t ntiles = (nvec + tile - 1) / tile;
-        unary_stream256_kernel<Word, Cfg><<<grid_for(ntiles, g), Cfg::BLOCK, 0, stream>>>(
-            reinterpret_cast<const vec32*>(ei + head), reinterpret_cast<vec32*>(eo + head), nvec, u);
+        if (cudaError_t e = launch_stream_kernel(unary_stream256_kernel<Word, Cfg>, grid_for(ntiles, g), Cfg::BLOCK, stream, g.pdl != 0,
+                                                 reinterpret_cast<const vec32*>(ei + head), reinterpret_cast<vec32*>(eo + head), nvec, u))
+            return e;
         count_launch(g);
         elems(n - tail, tail);
         return cudaGetLastError();
@@ -567,8 +577,9 @@ cudaError_t launch_unary(const void* in, void* out, size_t n, const unary_params
                 reinterpret_cast<const uint4*>(ei + head), reinterpret_cast<uint4*>(eo + head), nvec,
                 next_tile_counter(g), u);
         } else {
-            unary_stream_kernel<Word, Cfg><<<grid_for(ntiles, g), Cfg::BLOCK, 0, stream>>>(
-                reinterpret_cast<const uint4*>(ei + head), reinterpret_cast<uint4*>(eo + head), nvec, u);
+            if (cudaError_t e = launch_stream_kernel(unary_stream_kernel<Word, Cfg>, grid_for(ntiles, g), Cfg::BLOCK, stream, g.pdl != 0,
+                                                     reinterpret_cast<const uint4*>(ei + head), reinterpret_cast<uint4*>(eo + head), nvec, u))
+                return e;
         }
         count_launch(g);
     }
