@@ -127,6 +127,13 @@ struct slice_step<2, 0, 0, Integer, bits_pack<T0, Taken...>, Rest...> {
 }  // namespace detail
 
 // packed_int<Integer, Bits...> as the ABI's descriptor
+namespace detail {
+// bytes of one array element: a packed_int is its Integer (pint.hpp:25; the class may be incomplete here)
+template <class T> struct elem_size { static const size_t value = sizeof(T); };
+template <class Integer, size_t Bits0, size_t... Bits>
+struct elem_size<packed_int<Integer, Bits0, Bits...> > { static const size_t value = sizeof(Integer); };
+}  // namespace detail
+
 template <class Integer, size_t Bits0, size_t... Bits>
 inline pint_layout layout(const packed_int<Integer, Bits0, Bits...>* = nullptr)
 {
@@ -560,7 +567,119 @@ inline void dense_binary(pint_op op, int ngpu, const int* devices, const unsigne
           "pint::cuda::sharded::dense_binary");
 }
 
+// one array on src_device -> the shards of plan() on devices[] (peer copies, one stream each) and back:
+// the partitioner for an array that is already resident on ONE GPU
+template <class T>
+inline void scatter(const T* src, int src_device, size_t n, int ngpu, const int* devices, T* const* shards,
+                    const stream_t* streams = nullptr)
+{
+    check(pint_cuda_scatter_shards(src, src_device, (uint32_t)detail::elem_size<T>::value, n, ngpu, devices,
+                                   reinterpret_cast<void* const*>(shards), streams),
+          "pint::cuda::sharded::scatter");
+}
+
+template <class T>
+inline void gather(T* dst, int dst_device, size_t n, int ngpu, const int* devices, const T* const* shards,
+                   const stream_t* streams = nullptr)
+{
+    check(pint_cuda_gather_shards(dst, dst_device, (uint32_t)detail::elem_size<T>::value, n, ngpu, devices,
+                                  reinterpret_cast<const void* const*>(shards), streams),
+          "pint::cuda::sharded::gather");
+}
+
+inline void enable_peer_access(int ngpu, const int* devices)
+{
+    check(pint_cuda_enable_peer_access(ngpu, devices), "pint::cuda::sharded::enable_peer_access");
+}
+
 }  // namespace sharded
+
+// The reference benchmark's loop as one call (tests/pint_bench.cpp:90-94): *sum_dev (device) = sum over i of
+// OP(packed_int(pairs[i].first), packed_int(pairs[i].second)).value() mod 2^64; P names the layout:
+//     pint::cuda::pairs_reduce<rgba>(PINT_ADD_SIGNED_SATURATE, pairs, n, sum_dev, stream);
+template <class P>
+inline void pairs_reduce(pint_op op,
+                         const std::pair<typename dense::layout_from<P>::integer, typename dense::layout_from<P>::integer>* pairs,
+                         size_t n, uint64_t* sum_dev, stream_t stream = nullptr)
+{
+    const pint_layout l = dense::layout_from<P>::get();
+    check(pint_cuda_pairs_reduce(op, &l, pairs, n, sum_dev, stream), "pint::cuda::pairs_reduce");
+}
+
+// The same for callers that may not allocate (no counterpart in the reference; pint_cuda.h:
+// pint_cuda_pairs_reduce_static): n <= max_pairs_no_alloc, calls that overlap on one GPU must be serialised.
+static const unsigned long long max_pairs_no_alloc = PINT_STATIC_MAX_PAIRS;
+template <class P>
+inline void pairs_reduce_no_alloc(pint_op op,
+                                  const std::pair<typename dense::layout_from<P>::integer, typename dense::layout_from<P>::integer>* pairs,
+                                  size_t n, uint64_t* sum_dev, stream_t stream = nullptr)
+{
+    const pint_layout l = dense::layout_from<P>::get();
+    check(pint_cuda_pairs_reduce_static(op, &l, pairs, n, sum_dev, stream), "pint::cuda::pairs_reduce_no_alloc");
+}
+
+// Mask constants for ANY layout without nvcc in the caller's build: compiles the kernels for
+// static_layout<Integer, Bits...> with NVRTC on the current device ahead of time (about a second per family, cached
+// on disk) and switches the "jit" option on so later calls use them.  0 = run-time masks, 1 = registered at
+// build time, 2 = specialised at run time.
+template <class P>
+inline int specialization()
+{
+    const pint_layout l = dense::layout_from<P>::get();
+    return pint_cuda_layout_is_specialized(&l);
+}
+
+template <class P>
+inline void specialize()
+{
+    const pint_layout l = dense::layout_from<P>::get();
+    if (pint_cuda_get_option("jit") == 0) check(pint_cuda_set_option("jit", 1), "pint::cuda::specialize");
+    const int rc = pint_cuda_jit_compile(&l);
+    if (rc != PINT_OK) throw error(rc, (std::string("pint::cuda::specialize: ") + pint_cuda_jit_last_error()).c_str());
+}
+
+// HOST arrays (the reference's workload is a host vector, tests/pint_bench.cpp:22,75): copied through per-device
+// staging rings so that H2D, kernel and D2H overlap; synchronous.  Pinned buffers (host::alloc) run at the
+// link's rate, pageable ones at the driver's staging rate.
+namespace host {
+
+template <class T>
+inline T* alloc(size_t count, unsigned flags = 0)
+{
+    void* p = nullptr;
+    check(pint_cuda_host_alloc_flags(&p, count * detail::elem_size<T>::value, flags), "pint::cuda::host::alloc");
+    return static_cast<T*>(p);
+}
+
+inline void dealloc(void* p) { check(pint_cuda_host_free(p), "pint::cuda::host::dealloc"); }
+inline void release_staging() { check(pint_cuda_host_release(), "pint::cuda::host::release_staging"); }
+
+template <class Integer, size_t Bits0, size_t... Bits>
+inline void binary(pint_op op, const packed_int<Integer, Bits0, Bits...>* a, const packed_int<Integer, Bits0, Bits...>* b,
+                   packed_int<Integer, Bits0, Bits...>* out, size_t n)
+{
+    const pint_layout l = detail::layout_of<Integer, Bits0, Bits...>::get();
+    check(pint_cuda_binary_host(op, &l, a, b, out, n), "pint::cuda::host::binary");
+}
+
+// several ops over ONE upload of a and b; ngpu > 0 splits the arrays into plan()'s shards over devices[]
+template <size_t NOps, class Integer, size_t Bits0, size_t... Bits>
+inline void binary_multi(const pint_op (&ops)[NOps], const packed_int<Integer, Bits0, Bits...>* a,
+                         const packed_int<Integer, Bits0, Bits...>* b, packed_int<Integer, Bits0, Bits...>* const (&outs)[NOps],
+                         size_t n, int ngpu = 0, const int* devices = nullptr)
+{
+    static_assert(NOps >= 1 && NOps <= PINT_MAX_HOST_OPS, "1 .. PINT_MAX_HOST_OPS operations per pass");
+    const pint_layout l = detail::layout_of<Integer, Bits0, Bits...>::get();
+    int codes[NOps];
+    void* o[NOps];
+    for (size_t j = 0; j < NOps; ++j) { codes[j] = ops[j]; o[j] = outs[j]; }
+    if (ngpu > 0)
+        check(pint_cuda_sharded_binary_multi_host((int)NOps, codes, &l, ngpu, devices, a, b, o, n), "pint::cuda::host::binary_multi (sharded)");
+    else
+        check(pint_cuda_binary_multi_host((int)NOps, codes, &l, a, b, o, n), "pint::cuda::host::binary_multi");
+}
+
+}  // namespace host
 
 }  // namespace cuda
 }  // namespace pint

@@ -5,6 +5,7 @@
 // Built by `make tools` into build/cpp_api_test; run on a GPU by tests/test_gpu_cpp_api.py.
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <vector>
 
 #include <cuda_runtime.h>
@@ -154,7 +155,100 @@ int main()
             CK(cudaStreamSynchronize(s));
             CK(cudaMemcpy(ho.data(), out, n * 4, cudaMemcpyDeviceToHost));
             for (size_t i = 0; i < n; ++i) if (ho[i] != rgba_add_ssat(ha[i], hb[i])) { ++fails; if (fails < 5) std::printf("binary_pairs mismatch at %zu\n", i); }
+            // the benchmark's loop as one call, and its no-allocation twin: both equal the host sum
+            uint64_t want_sum = 0, got_sum[2] = {1, 2}, *dsum;
+            for (size_t i = 0; i < n; ++i) want_sum += rgba_add_ssat(ha[i], hb[i]);
+            CK(cudaMalloc((void**)&dsum, 16));
+            pint::cuda::pairs_reduce<rgba>(PINT_ADD_SIGNED_SATURATE, dpairs, n, dsum, s);
+            pint::cuda::pairs_reduce_no_alloc<rgba>(PINT_ADD_SIGNED_SATURATE, dpairs, n, dsum + 1, s);
+            CK(cudaStreamSynchronize(s));
+            CK(cudaMemcpy(got_sum, dsum, 16, cudaMemcpyDeviceToHost));
+            if (got_sum[0] != want_sum || got_sum[1] != want_sum) { ++fails; std::printf("pairs_reduce %llu / %llu, want %llu\n", (unsigned long long)got_sum[0], (unsigned long long)got_sum[1], (unsigned long long)want_sum); }
+            bool too_large = false;
+            try { pint::cuda::pairs_reduce_no_alloc<rgba>(PINT_ADD_WRAP, dpairs, (size_t)pint::cuda::max_pairs_no_alloc + 1, dsum, s); }
+            catch (const pint::cuda::error& e) { too_large = e.code == PINT_E_TOO_LARGE; }
+            if (!too_large) { ++fails; std::printf("pairs_reduce_no_alloc beyond its maximum did not throw PINT_E_TOO_LARGE\n"); }
+            CK(cudaFree(dsum));
             CK(cudaFree(dpairs));
+        }
+
+        // ---- host arrays: one device, then the same arrays split over every device of the box ----
+        {
+            namespace ph = pint::cuda::host;
+            rgba* pa = ph::alloc<rgba>(n, PINT_HOST_PORTABLE);
+            rgba* pb = ph::alloc<rgba>(n, PINT_HOST_PORTABLE);
+            rgba* po[2] = {ph::alloc<rgba>(n, PINT_HOST_PORTABLE), ph::alloc<rgba>(n, PINT_HOST_PORTABLE)};
+            std::memcpy(pa, ha.data(), n * 4);
+            std::memcpy(pb, hb.data(), n * 4);
+            const pint_op two[2] = {PINT_ADD_UNSIGNED_SATURATE, PINT_ADD_SIGNED_SATURATE};
+            std::vector<int> devs(ndev);
+            for (int d = 0; d < ndev; ++d) devs[d] = d;
+            for (int pass = 0; pass < 2; ++pass) {
+                std::memset(po[0], 0xEE, n * 4);
+                std::memset(po[1], 0xEE, n * 4);
+                if (pass == 0) ph::binary_multi(two, pa, pb, po, n);
+                else ph::binary_multi(two, pa, pb, po, n, ndev, devs.data());
+                const uint32_t *u = (const uint32_t*)po[0], *v = (const uint32_t*)po[1];
+                for (size_t i = 0; i < n; ++i)
+                    if (u[i] != rgba_add_usat(ha[i], hb[i]) || v[i] != rgba_add_ssat(ha[i], hb[i])) { ++fails; if (fails < 5) std::printf("host::binary_multi pass %d mismatch at %zu\n", pass, i); }
+            }
+            ph::binary(PINT_SUB_WRAP, pa, pb, po[0], n);
+            for (size_t i = 0; i < n; ++i) {
+                uint32_t want = 0;
+                for (int f = 0; f < 4; ++f) want |= (((ha[i] >> (8 * f)) - (hb[i] >> (8 * f))) & 255u) << (8 * f);
+                if (((const uint32_t*)po[0])[i] != want) { ++fails; if (fails < 5) std::printf("host::binary mismatch at %zu\n", i); }
+            }
+            ph::dealloc(pa); ph::dealloc(pb); ph::dealloc(po[0]); ph::dealloc(po[1]);
+            ph::release_staging();
+        }
+
+        // ---- an array resident on device 0 split over every device, processed there and collected again ----
+        {
+            namespace sh = pint::cuda::sharded;
+            std::vector<int> devs(ndev);
+            for (int d = 0; d < ndev; ++d) devs[d] = d;
+            sh::enable_peer_access(ndev, devs.data());
+            std::vector<size_t> begin(ndev), count(ndev);
+            sh::plan(n, 4, ndev, begin.data(), count.data());
+            std::vector<rgba*> sa(ndev), sb(ndev), so(ndev);
+            for (int d = 0; d < ndev; ++d) {
+                CK(cudaSetDevice(d));
+                CK(cudaMalloc((void**)&sa[d], count[d] * 4 + 4)); CK(cudaMalloc((void**)&sb[d], count[d] * 4 + 4)); CK(cudaMalloc((void**)&so[d], count[d] * 4 + 4));
+            }
+            CK(cudaSetDevice(0));
+            CK(cudaStreamSynchronize(s));
+            sh::scatter(a, 0, n, ndev, devs.data(), sa.data());
+            sh::scatter(b, 0, n, ndev, devs.data(), sb.data());
+            sh::binary(PINT_ADD_SIGNED_SATURATE, ndev, devs.data(), sa.data(), sb.data(), so.data(), count.data());
+            CK(cudaMemset(out, 0, n * 4));
+            CK(cudaDeviceSynchronize());
+            sh::gather(out, 0, n, ndev, devs.data(), so.data());
+            for (int d = 0; d < ndev; ++d) { CK(cudaSetDevice(d)); CK(cudaDeviceSynchronize()); }
+            CK(cudaSetDevice(0));
+            CK(cudaMemcpy(ho.data(), out, n * 4, cudaMemcpyDeviceToHost));
+            for (size_t i = 0; i < n; ++i) if (ho[i] != rgba_add_ssat(ha[i], hb[i])) { ++fails; if (fails < 5) std::printf("scatter / sharded / gather mismatch at %zu\n", i); }
+            for (int d = 0; d < ndev; ++d) { CK(cudaSetDevice(d)); CK(cudaFree(sa[d])); CK(cudaFree(sb[d])); CK(cudaFree(so[d])); }
+            CK(cudaSetDevice(0));
+        }
+
+        // ---- constants for an unregistered layout at run time (NVRTC), then the same call again ----
+        {
+            typedef pint::packed_int<uint32_t, 7, 9, 3> odd;
+            std::vector<uint32_t> h1(n);
+            pint::cuda::add_signed_saturate((const odd*)a, (const odd*)b, (odd*)out, n, s);
+            CK(cudaStreamSynchronize(s));
+            CK(cudaMemcpy(ho.data(), out, n * 4, cudaMemcpyDeviceToHost));
+            const int before = pint::cuda::specialization<odd>();
+            bool have_nvrtc = true;
+            try { pint::cuda::specialize<odd>(); } catch (const pint::cuda::error& e) { have_nvrtc = false; std::printf("specialize skipped: %s\n", e.what()); }
+            if (have_nvrtc) {
+                if (pint::cuda::specialization<odd>() != 2 && before != 1) { ++fails; std::printf("specialize<odd> did not load (%d)\n", pint::cuda::specialization<odd>()); }
+                pint::cuda::add_signed_saturate((const odd*)a, (const odd*)b, (odd*)out, n, s);
+                CK(cudaStreamSynchronize(s));
+                CK(cudaMemcpy(h1.data(), out, n * 4, cudaMemcpyDeviceToHost));
+                for (size_t i = 0; i < n; ++i) if (h1[i] != ho[i]) { ++fails; if (fails < 5) std::printf("specialised kernel differs at %zu\n", i); }
+            }
+            pint_cuda_set_option("jit", 0);
         }
 
         // ---- dense bit streams: RGB24 = packed_int<uint32_t,8,8,8> at 3 bytes per element ----

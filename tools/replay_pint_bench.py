@@ -62,6 +62,21 @@ def main():
         e1.record()
         e1.synchronize()
         gpu_ms = e0.elapsed_time(e1) / reps
+        # the kernel alone: the same passes back to back on the stream, no read-back between them (the array is
+        # 6x the L2, so every pass reads HBM)
+        import ctypes as C
+        from pint_b200 import _lib
+        res = torch.zeros(1, dtype=torch.int64, device="cuda")
+        call = lambda: _lib.check(_lib.lib().pint_cuda_pairs_reduce(ops.OP_CODE[op], L.ref, C.c_void_p(pairs.data_ptr()), npairs,
+                                                                     C.c_void_p(res.data_ptr()), None), "pairs_reduce")
+        call()
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(reps):
+            call()
+        e1.record()
+        e1.synchronize()
+        kernel_ms = e0.elapsed_time(e1) / reps
         t0 = time.perf_counter()
         if ref is not None and ref.has(eb, bits):
             cpu_sum, kind = ref.pairs_reduce(op, eb, bits, host), "reference (unmodified pint.hpp, 1 thread)"
@@ -75,6 +90,7 @@ def main():
             "benchmark": name, "pint_bench_cpp_line": line, "layout": repr(L), "op": op, "pairs": npairs,
             "label_sum_u32": int(gpu_sum) & 0xFFFFFFFF, "sum_u64_gpu": int(gpu_sum), "sum_u64_cpu": int(cpu_sum), "sums_equal": same,
             "gpu_ms": round(gpu_ms, 4), "gpu_gpairs_s": round(npairs / gpu_ms / 1e6, 2), "gpu_gbs": round(8 * npairs / gpu_ms / 1e6, 1),
+            "kernel_ms": round(kernel_ms, 4), "kernel_gbs": round(8 * npairs / kernel_ms / 1e6, 1),
             "cpu_s": round(cpu_s, 4), "cpu_gpairs_s": round(npairs / cpu_s / 1e9, 3), "cpu_kind": kind,
             "speedup": round(cpu_s * 1e3 / gpu_ms, 1)}), flush=True)
     print(json.dumps({"benchmark": "AddSatU0/Pint64", "pint_bench_cpp_line": 469,
