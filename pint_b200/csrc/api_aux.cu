@@ -85,17 +85,33 @@ __global__ void __launch_bounds__(256) checksum_vec_kernel(const uint4* x, size_
 // tests/pint_bench.cpp:90-94: sum += op(P(pair.first), P(pair.second)).value()
 // P: the mask policy -- static_masks<SL> for the layouts of registry_layouts.def (constants folded into the code),
 // runtime_masks<W, Steps> otherwise (Steps smear steps: 2 / 4 for layouts whose widest field has at most 4 / 16 bits)
+__global__ void zero_sum_kernel(uint64_t* sum)
+{
+    pint::cuda::kernels::pdl_prologue();
+    if (threadIdx.x == 0) *sum = 0;
+}
+
+// loads per thread and tile: 4 keeps the memory-bound ops at the read ceiling (7.2 TB/s at 10^8 pairs); the ops that are
+// bound by the integer pipe (saturate / min / max on layouts with three or more field widths, e.g. the benchmark's
+// <1,2,3,4,5,6,11>) gain from CTAs that live twice as long: 3.3-3.8 -> 5.1-5.2 TB/s at 2^29 pairs (profiles/r26_ab_reduce.jsonl)
+template <int Op, class P>
+__host__ __device__ constexpr int reduce_unroll()
+{
+    return (P::heavy_fill && !(Op == OP_ADD_WRAP || Op == OP_SUB_WRAP || Op == OP_OR || Op == OP_AND || Op == OP_XOR)) ? 8 : 4;
+}
+
 template <class Elem, int Op, bool V32, class P>
 __global__ void __launch_bounds__(256)
 pairs_reduce_kernel(const Elem* pairs, size_t n, uint64_t* sum, const __grid_constant__ P p)
 {
+    pint::cuda::kernels::pdl_prologue();
     using W = word_of<Elem>;
     constexpr int PER = 8 / sizeof(Elem);  // pairs per 16-byte vector
     uint64_t s = 0;
     const bool vec_ok = (reinterpret_cast<uintptr_t>(pairs) & 15u) == 0;
     const size_t nvec = vec_ok ? n / PER : 0;
     // tiles of U * blockDim vectors, U independent loads per thread issued before the first use
-    constexpr int U = 4;
+    constexpr int U = reduce_unroll<Op, P>();
     const uint4* vec = reinterpret_cast<const uint4*>(pairs);
     const size_t tile = size_t(U) * blockDim.x, nfull = nvec / tile;
     auto add_vec = [&](const uint4& q) {
@@ -137,14 +153,23 @@ template <class Elem, class P, int... Ops>
 cudaError_t pairs_ops(int op, const P& p, const void* pairs, size_t n, uint64_t* sum, cudaStream_t s,
                       const launch_geom& g, std::integer_sequence<int, Ops...>)
 {
-    const unsigned grid = grid_for((n + 1023) / 1024, g);
+    // one CTA per tile of the main loop (U loads of 16 or 32 bytes per thread): a grid sized in PAIRS / 1024 launched
+    // 2 ... 16 times more CTAs than tiles, and every empty one still paid its launch, reduction and atomic
+    // (10^8 uint32_t pairs, add_wrap: 5131 -> 7224 GB/s, profiles/r26_ab_reduce.jsonl)
     // 256-bit loads, 128 bytes in flight per thread: 6221 -> 6950 GB/s (profiles/r03s_ab_pairs_reduce.log)
-    if (g.vec256 != 0 && (uintptr_t)pairs % 32 == 0)
-        ((op == Ops ? (pairs_reduce_kernel<Elem, Ops, true, P><<<grid, 256, 0, s>>>((const Elem*)pairs, n, sum, p), 0) : 0), ...);
-    else
-        ((op == Ops ? (pairs_reduce_kernel<Elem, Ops, false, P><<<grid, 256, 0, s>>>((const Elem*)pairs, n, sum, p), 0) : 0), ...);
+    const bool v32 = g.vec256 != 0 && (uintptr_t)pairs % 32 == 0;
+    cudaError_t rc = cudaSuccess;
+    auto launch = [&](auto opc) {
+        constexpr int O = decltype(opc)::value;
+        const size_t tile_pairs = size_t(v32 ? 2 : 1) * reduce_unroll<O, P>() * 256 * (8 / sizeof(Elem));
+        const unsigned grid = grid_for((n + tile_pairs - 1) / tile_pairs, g);
+        if (v32) rc = launch_stream_kernel(pairs_reduce_kernel<Elem, O, true, P>, grid, 256, s, g.pdl != 0, (const Elem*)pairs, n, sum, p);
+        else rc = launch_stream_kernel(pairs_reduce_kernel<Elem, O, false, P>, grid, 256, s, g.pdl != 0, (const Elem*)pairs, n, sum, p);
+        return 0;
+    };
+    ((op == Ops ? launch(std::integral_constant<int, Ops>{}) : 0), ...);
     count_launch(g);
-    return cudaGetLastError();
+    return rc != cudaSuccess ? rc : cudaGetLastError();
 }
 
 // run-time masks: as many smear steps as the widest field needs (the benchmark's own type-2 layout
@@ -245,12 +270,19 @@ int pint_cuda_pairs_reduce(int op, const pint_layout* layout, const void* pairs,
     if (op < 0 || op >= PINT_NUM_BINARY_OPS) return PINT_E_OP;
     if (!sum_dev) return PINT_E_NULL;
     cudaStream_t s = (cudaStream_t)stream;
-    if (cudaError_t e = cudaMemsetAsync(sum_dev, 0, sizeof(uint64_t), s)) return (int)e;
-    if (n == 0) return PINT_OK;
+    if (n == 0) return (int)cudaMemsetAsync(sum_dev, 0, sizeof(uint64_t), s);
     if (!pairs) return PINT_E_NULL;
     if ((uintptr_t)pairs % d.elem_bytes) return PINT_E_ARG;
-    launch_geom g = geom();
-    g.ctas_per_sm = 8;  // one atomic per CTA at the end: persistent grid
+    // One CTA per tile and one atomic per CTA (24 414 atomics for the benchmark's 10^8 uint32_t pairs): measured
+    // faster than 8 persistent CTAs per SM, 7224 against 6943 GB/s (profiles/r26_ab_reduce.jsonl).
+    const launch_geom g = geom();
+    // *sum_dev = 0 by a one-thread kernel instead of cudaMemsetAsync, and both launches with programmatic stream
+    // serialization (option "pdl"): the reduction's CTAs are resident and waiting when the zeroing completes, and the
+    // zeroing itself is resident when the previous pass of the stream drains.  Back-to-back passes over 10^8 pairs,
+    // with the grid above: 132 -> 121 us (profiles/r25_ / r28_replay_pint_bench.jsonl; letting the reduction read before
+    // its wait changed nothing, r28b).  Order is unchanged: every kernel waits for the launch before it.
+    if (cudaError_t e = launch_stream_kernel(zero_sum_kernel, 1, 32, s, g.pdl != 0, sum_dev)) return (int)e;
+    count_launch(g);
     if (!opts().force_generic)
         for (const static_pairs_entry& e : kStaticPairs)
             if (same_layout(e.desc, d)) return (int)e.run(op, pairs, n, sum_dev, s, g);

@@ -32,7 +32,7 @@ echo "ncu pair rc=$?"
 python tools/ncu_summary.py $out/${tag}_ncu_full_pair.ncu-rep $out/${tag}_ncu_full_pair_summary.txt
 PK="python tools/profile_planes.py 27"
 timeout 300 $PK > $out/${tag}_profile_planes.log 2>&1 && \
-timeout 1500 ncu --set full --clock-control none --import-source on -k regex:"unpack_oct|unpack_bulk|repack_quad|unpack_group|binary_stream|fused" -c 6 -o $out/${tag}_ncu_full_planes $PK > $out/${tag}_ncu_full_planes.log 2>&1
+timeout 1500 ncu --set full --clock-control none --import-source on -k regex:"unpack_oct|unpack_bulk|repack_quad|unpack_group|binary_stream|fused|pairs_reduce" -c 8 -o $out/${tag}_ncu_full_planes $PK > $out/${tag}_ncu_full_planes.log 2>&1
 echo "ncu planes rc=$?"
 python tools/ncu_summary.py $out/${tag}_ncu_full_planes.ncu-rep $out/${tag}_ncu_full_planes_summary.txt
 rm -f $out/*.ncu-rep
