@@ -50,11 +50,20 @@ oracle:
 	$(MAKE) -C oracle liboracle.so
 	@if [ -f /root/reference/include/pint/pint.hpp ]; then $(MAKE) -C oracle ref; fi
 
-tools: build/tune build/cpp_api_test build/e2e_ceiling build/cuda_api_nvcc_test build/r1_regress/libpint_cuda_r1.so static_masks_check
+tools: build/tune build/cpp_api_test build/e2e_ceiling build/cuda_api_nvcc_test build/ab_reduce build/ubench_pipes build/r1_regress/libpint_cuda_r1.so static_masks_check
 
 build/tune: tools/tune.cu tools/binary_bulk_variant.cuh $(HDRS)
 	@mkdir -p build
 	$(NVCC) $(NVFLAGS) -Itools -o $@ tools/tune.cu
+
+# variants of the pair reduction next to each other (grid, loads in flight, TMA ring); pipe-rate microbenchmark
+build/ab_reduce: tools/ab_reduce.cu $(HDRS)
+	@mkdir -p build
+	$(NVCC) -std=c++17 -O3 $(ARCH) -lineinfo -Iinclude -o $@ tools/ab_reduce.cu
+
+build/ubench_pipes: tools/ubench_pipes.cu
+	@mkdir -p build
+	$(NVCC) -O3 $(ARCH) -o $@ tools/ubench_pipes.cu
 
 build/e2e_ceiling: tools/e2e_ceiling.cu include/pint_cuda.h $(LIB)
 	@mkdir -p build
