@@ -154,3 +154,48 @@ def test_jit_caller_shapes_match_oracle(jit_strict, oracle, eb, bits):
         x = to_dev(a_h, off)
         ops.binary_scalar("sub_signed_saturate", L, x, kval, out=x)
         np.testing.assert_array_equal(to_np(x), oracle.binary("sub_signed_saturate", eb, bits, a_h, kk))
+
+
+def test_jit_first_calls_from_several_threads(jit_strict, oracle):
+    """Four threads make their FIRST calls at once: two on the same unregistered layout (one compilation, both
+    served), two on layouts of their own, each on its own stream.  Every result equals the oracle; nothing
+    deadlocks or compiles into another thread's module."""
+    import threading
+    import pint_b200
+    from pint_b200 import _lib
+    ops = jit_strict
+    plan = [(4, (6, 7, 9)), (4, (6, 7, 9)), (2, (3, 9, 2)), (8, (9, 21, 13, 5))]
+    n = (1 << 17) + 77
+    errors, results = [], [None] * len(plan)
+    start = threading.Barrier(len(plan))
+
+    def work(k):
+        try:
+            eb, bits = plan[k]
+            L = pint_b200.Layout(eb, *bits)
+            a_h, b_h = oracle.fill(eb, n, 40 + k), oracle.fill(eb, n, 50 + k)
+            torch.cuda.set_device(0)
+            s = torch.cuda.Stream()
+            with torch.cuda.stream(s):
+                a, b = to_dev(a_h), to_dev(b_h)
+                s.synchronize()
+                start.wait(timeout=60)
+                outs = [ops.binary(op, L, a, b, stream=s) for op in ("add_signed_saturate", "sub_unsigned_saturate", "max_signed")]
+                o0, o1 = ops.binary_multi(["add_unsigned_saturate", "add_signed_saturate"], L, a, b, stream=s)
+                s.synchronize()
+            results[k] = ([to_np(o) for o in outs] + [to_np(o0), to_np(o1)], a_h, b_h)
+        except Exception as e:  # noqa: BLE001 - reported by the main thread
+            errors.append((k, repr(e)))
+
+    threads = [threading.Thread(target=work, args=(k,)) for k in range(len(plan))]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(timeout=300)
+    assert not any(t.is_alive() for t in threads), "a first call is stuck"
+    assert not errors, errors
+    for k, (eb, bits) in enumerate(plan):
+        got, a_h, b_h = results[k]
+        for g, op in zip(got, ("add_signed_saturate", "sub_unsigned_saturate", "max_signed", "add_unsigned_saturate", "add_signed_saturate")):
+            np.testing.assert_array_equal(g, oracle.binary(op, eb, bits, a_h, b_h), err_msg=f"thread {k} {bits} {op}")
+        assert _lib.lib().pint_cuda_layout_is_specialized(pint_b200.Layout(eb, *bits).ref) == 2
