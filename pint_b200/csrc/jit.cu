@@ -67,6 +67,7 @@ struct nvrtc_api {
 
 struct driver_api {
     CUresult (*ModuleLoadData)(CUmodule*, const void*) = nullptr;
+    CUresult (*ModuleUnload)(CUmodule) = nullptr;  // optional: only used to drop a module whose disk-cache entry was damaged
     CUresult (*ModuleGetFunction)(CUfunction*, CUmodule, const char*) = nullptr;
     CUresult (*ModuleGetGlobal)(CUdeviceptr*, size_t*, CUmodule, const char*) = nullptr;
     CUresult (*MemcpyDtoH)(void*, CUdeviceptr, size_t) = nullptr;
@@ -174,6 +175,7 @@ bool load_driver()
               get("cuLaunchKernel", reinterpret_cast<void**>(&g_drv.LaunchKernel)) &&
               get("cuFuncSetAttribute", reinterpret_cast<void**>(&g_drv.FuncSetAttribute));
     if (!ok) { cudaGetLastError(); g_last_error = "driver entry points unavailable"; }
+    if (ok && !get("cuModuleUnload", reinterpret_cast<void**>(&g_drv.ModuleUnload))) { cudaGetLastError(); g_drv.ModuleUnload = nullptr; }
     g_drv_ok = ok;
     return ok;
 }
@@ -363,8 +365,10 @@ void write_file_atomic(const std::string& path, const std::vector<char>& data)
 
 // Compiles (or fetches from the disk cache) one family for one layout.  Lowered kernel names are
 // stored beside the cubin so that a cache hit needs no NVRTC at all.
-bool build_cubin(const layout_desc& d, int fam, int cc_major, int cc_minor, std::vector<char>* cubin, std::vector<std::string>* lowered)
+bool build_cubin(const layout_desc& d, int fam, int cc_major, int cc_minor, std::vector<char>* cubin, std::vector<std::string>* lowered,
+                 bool ignore_cache = false, bool* from_cache = nullptr)
 {
+    if (from_cache) *from_cache = false;
     const std::string src = make_source(d, fam);
     char arch[48];
     std::snprintf(arch, sizeof arch, "-arch=sm_%d%d%s", cc_major, cc_minor, cc_major >= 9 ? "a" : "");
@@ -377,16 +381,27 @@ bool build_cubin(const layout_desc& d, int fam, int cc_major, int cc_minor, std:
     std::snprintf(key, sizeof key, "%016llx", (unsigned long long)h);
     const std::string base = dir.empty() ? std::string() : dir + "/" + key + "_" + kFamilyName[fam];
     const int nk = family_count(fam);
-    if (!base.empty()) {
+    if (!base.empty() && !ignore_cache) {
         std::vector<char> names;
         if (read_file(base + ".cubin", cubin) && read_file(base + ".names", &names)) {
+            // first line: "#cubin <bytes> <fnv1a of the image>", so that a truncated or foreign file never reaches the driver
             lowered->clear();
-            std::string cur;
+            std::string cur, head;
+            bool first = true;
             for (char c : names) {
-                if (c == '\n') { lowered->push_back(cur); cur.clear(); }
-                else cur.push_back(c);
+                if (c == '\n') {
+                    if (first) { head = cur; first = false; }
+                    else lowered->push_back(cur);
+                    cur.clear();
+                } else cur.push_back(c);
             }
-            if ((int)lowered->size() == family_variants(fam) * nk) return true;
+            char want[80];
+            std::snprintf(want, sizeof want, "#cubin %zu %016llx", cubin->size(),
+                          (unsigned long long)fnv1a(0xCBF29CE484222325ULL, cubin->data(), cubin->size()));
+            if (head == want && (int)lowered->size() == family_variants(fam) * nk) {
+                if (from_cache) *from_cache = true;
+                return true;
+            }
         }
     }
     if (!load_nvrtc()) return false;
@@ -448,6 +463,10 @@ bool build_cubin(const layout_desc& d, int fam, int cc_major, int cc_minor, std:
     g_nvrtc.DestroyProgram(&prog);
     if (!base.empty()) {
         std::vector<char> names;
+        char head[80];
+        const int hn = std::snprintf(head, sizeof head, "#cubin %zu %016llx\n", cubin->size(),
+                                     (unsigned long long)fnv1a(0xCBF29CE484222325ULL, cubin->data(), cubin->size()));
+        names.insert(names.end(), head, head + hn);
         for (const auto& l : *lowered) { names.insert(names.end(), l.begin(), l.end()); names.push_back('\n'); }
         write_file_atomic(base + ".names", names);
         write_file_atomic(base + ".cubin", *cubin);
@@ -479,27 +498,40 @@ jit_module* get_module(const layout_desc& d, int fam)
     cudaDeviceGetAttribute(&minor, cudaDevAttrComputeCapabilityMinor, dev);
     std::vector<char> cubin;
     std::vector<std::string> lowered;
-    if (!build_cubin(d, fam, major, minor, &cubin, &lowered)) return nullptr;
-    if (g_drv.ModuleLoadData(&m.mod, cubin.data()) != CUDA_SUCCESS) { g_last_error = "cuModuleLoadData failed"; return nullptr; }
     const int nk = family_count(fam);
-    m.k.resize(nk);
-    std::vector<int> cfg(size_t(nk) * 4);
-    CUdeviceptr p = 0;
-    size_t bytes = 0;
-    if (g_drv.ModuleGetGlobal(&p, &bytes, m.mod, "pint_jit_cfg") != CUDA_SUCCESS || bytes != cfg.size() * sizeof(int) ||
-        g_drv.MemcpyDtoH(cfg.data(), p, bytes) != CUDA_SUCCESS) {
-        g_last_error = "pint_jit_cfg missing from the module";
-        return nullptr;
-    }
-    for (int i = 0; i < nk; ++i) {
-        jit_kernel& k = m.k[i];
-        const int nv = family_variants(fam);
-        if (g_drv.ModuleGetFunction(&k.f128, m.mod, lowered[nv * i].c_str()) != CUDA_SUCCESS ||
-            (nv == 2 && g_drv.ModuleGetFunction(&k.f256, m.mod, lowered[nv * i + 1].c_str()) != CUDA_SUCCESS)) {
-            g_last_error = "cuModuleGetFunction failed for " + lowered[nv * i];
-            return nullptr;
+    auto load = [&]() -> bool {
+        // a file that is not a loadable image: the driver parses it, so refuse the obviously truncated ones first
+        if (cubin.size() < 64 || std::memcmp(cubin.data(), "\177ELF", 4) != 0) { g_last_error = "not a cubin"; return false; }
+        if (g_drv.ModuleLoadData(&m.mod, cubin.data()) != CUDA_SUCCESS) { g_last_error = "cuModuleLoadData failed"; m.mod = nullptr; return false; }
+        m.k.assign(nk, jit_kernel{});
+        std::vector<int> cfg(size_t(nk) * 4);
+        CUdeviceptr p = 0;
+        size_t bytes = 0;
+        if (g_drv.ModuleGetGlobal(&p, &bytes, m.mod, "pint_jit_cfg") != CUDA_SUCCESS || bytes != cfg.size() * sizeof(int) ||
+            g_drv.MemcpyDtoH(cfg.data(), p, bytes) != CUDA_SUCCESS) {
+            g_last_error = "pint_jit_cfg missing from the module";
+            return false;
         }
-        k.unroll = cfg[4 * i]; k.block = cfg[4 * i + 1]; k.vec256 = cfg[4 * i + 2]; k.heavy = cfg[4 * i + 3];
+        for (int i = 0; i < nk; ++i) {
+            jit_kernel& k = m.k[i];
+            const int nv = family_variants(fam);
+            if (g_drv.ModuleGetFunction(&k.f128, m.mod, lowered[nv * i].c_str()) != CUDA_SUCCESS ||
+                (nv == 2 && g_drv.ModuleGetFunction(&k.f256, m.mod, lowered[nv * i + 1].c_str()) != CUDA_SUCCESS)) {
+                g_last_error = "cuModuleGetFunction failed for " + lowered[nv * i];
+                return false;
+            }
+            k.unroll = cfg[4 * i]; k.block = cfg[4 * i + 1]; k.vec256 = cfg[4 * i + 2]; k.heavy = cfg[4 * i + 3];
+        }
+        return true;
+    };
+    bool from_cache = false;
+    if (!build_cubin(d, fam, major, minor, &cubin, &lowered, false, &from_cache)) return nullptr;
+    if (!load()) {
+        // a damaged disk-cache entry (truncated file, another toolkit's image): compile afresh once, which rewrites it
+        if (!from_cache) return nullptr;
+        if (m.mod && g_drv.ModuleUnload) g_drv.ModuleUnload(m.mod);
+        m.mod = nullptr;
+        if (!build_cubin(d, fam, major, minor, &cubin, &lowered, true) || !load()) return nullptr;
     }
     m.state = 1;
     return &m;

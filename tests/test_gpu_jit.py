@@ -199,3 +199,36 @@ def test_jit_first_calls_from_several_threads(jit_strict, oracle):
         for g, op in zip(got, ("add_signed_saturate", "sub_unsigned_saturate", "max_signed", "add_unsigned_saturate", "add_signed_saturate")):
             np.testing.assert_array_equal(g, oracle.binary(op, eb, bits, a_h, b_h), err_msg=f"thread {k} {bits} {op}")
         assert _lib.lib().pint_cuda_layout_is_specialized(pint_b200.Layout(eb, *bits).ref) == 2
+
+
+def test_jit_recovers_from_a_damaged_cache_entry(jit_strict, oracle, tmp_path):
+    """A truncated cubin and one that is not an ELF image at all in the disk cache (a full disk, another process killed
+    mid-write before the rename existed, a stray file): the first call compiles afresh, rewrites the entry and gives
+    the oracle's result."""
+    import os
+    import pint_b200
+    from pint_b200 import _lib
+    ops = jit_strict
+    lib = _lib.lib()
+    n = (1 << 16) + 5
+    for (eb, bits), damage in (((4, (11, 4, 9)), "truncate"), ((2, (6, 3, 5)), "garbage")):
+        L = pint_b200.Layout(eb, *bits)
+        assert lib.pint_cuda_jit_prebuild(L.ref, 10, 0) == 0, lib.pint_cuda_jit_last_error()   # disk cache only, nothing loaded
+        cache = tmp_path / "jit"
+        cubins = sorted(f for f in os.listdir(cache) if f.endswith("_binary.cubin"))
+        assert cubins, os.listdir(cache)
+        sizes = {}
+        for f in cubins:
+            path = cache / f
+            sizes[f] = path.stat().st_size
+            data = path.read_bytes()
+            path.write_bytes(data[:len(data) // 2] if damage == "truncate" else b"not a cubin" * 100)
+        a_h, b_h = oracle.fill(eb, n, 3), oracle.fill(eb, n, 4)
+        got = to_np(ops.binary("add_signed_saturate", L, to_dev(a_h), to_dev(b_h)))
+        np.testing.assert_array_equal(got, oracle.binary("add_signed_saturate", eb, bits, a_h, b_h))
+        assert lib.pint_cuda_layout_is_specialized(L.ref) == 2
+        for f in cubins:   # the entry of this layout was rewritten whole
+            if (cache / f).stat().st_size == sizes[f]:
+                break
+        else:
+            raise AssertionError("no damaged cache entry was rewritten")

@@ -192,11 +192,18 @@ def test_jit_prebuild_without_a_device(tmp_path, monkeypatch):
     # whole-chunk dense layout, the dense ones
     fams = ["binary", "dense", "densepair", "fused", "pair", "pairsmap", "scalar"]
     assert sorted(f.split("_")[1] for f in files) == sorted(f"{x}.{e}" for x in fams for e in ("cubin", "names"))
-    sn = open(tmp_path / "jit" / [f for f in files if f.endswith("_scalar.names")][0]).read().split()
+    def kernel_names(suffix):
+        """the lowered kernel names of a cache entry; its first line is "#cubin <bytes> <fnv1a>" (checked against the image on load)"""
+        path = tmp_path / "jit" / [f for f in files if f.endswith(suffix)][0]
+        lines = open(path).read().splitlines()
+        head = lines[0].split()
+        assert head[0] == "#cubin" and int(head[1]) == os.path.getsize(str(path)[:-len(".names")] + ".cubin"), head
+        return lines[1:]
+    sn = kernel_names("_scalar.names")
     assert len(sn) == 26 and all("map1_stream_kernel" in x and "scalar_fn" in x for x in sn)
-    dn = open(tmp_path / "jit" / [f for f in files if f.endswith("_dense.names")][0]).read().split()
+    dn = kernel_names("_dense.names")
     assert len(dn) == 13 and all("dense_binary_kernel" in x and "chunk_layout" in x for x in dn)
-    names = open(tmp_path / "jit" / [f for f in files if f.endswith("binary.names")][0]).read().split()
+    names = kernel_names("binary.names")
     assert len(names) == 26 and all("binary_stream" in x and "static_layout" in x for x in names)
     assert lib.pint_cuda_jit_prebuild(L.ref, 7, 0) == -15                      # not a target this library has
     bad = pint_b200._lib.PintLayout(4, 2, (pint_b200._lib.C.c_uint8 * 64)(20, 20))
