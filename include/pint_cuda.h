@@ -126,7 +126,8 @@ int pint_cuda_layout_is_specialized(const pint_layout* layout);
  * first packed -> packed call (binary, multi, fused, binary_scalar, binary_pairs; or a dense bit-stream binary /
  * multi call, for layouts whose chunk is at most 19 words) on such a layout compiles the same kernel templates for
  * static_layout<Integer, Bits...> with NVRTC (libnvrtc.so.12, loaded on demand; headers embedded in
- * the library), caches the cubin on disk ($PINT_CUDA_JIT_CACHE, else ~/.cache/pint_cuda) and uses it
+ * the library), caches the cubin on disk ($PINT_CUDA_JIT_CACHE, else ~/.cache/pint_cuda; written by rename, each entry with the size and
+ * hash of its image, so a damaged or foreign file is recompiled, never loaded) and uses it
  * from then on: the call that compiles blocks for about a second.  pint_cuda_jit_compile does that
  * ahead of time for all op families of a layout on the current device, so that later calls never block.
  * "jit" = 1: a layout that cannot be specialised keeps running the run-time-mask kernels (identical
