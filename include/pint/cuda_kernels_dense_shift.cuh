@@ -1,0 +1,166 @@
+// pint/cuda_kernels_dense_shift.cuh -- shift_left / shift_right_unsigned (pint.hpp:1006-1029) on a dense bit stream as a
+// plain word stream: out = shift(stream & KEEP), KEEP being the per-field keep mask of one element repeated every
+// sum(Bits) bits.  The bits KEEP clears are exactly the ones that would cross a field boundary, so after the mask the
+// whole stream can be shifted as one long integer: a funnel shift of neighbouring 32-bit words.  No chunks, no shared
+// memory staging: 16-byte vectors in and out, the neighbour word comes from the next (previous) lane and only
+// the last (first) lane of a warp loads one extra word.
+//
+// KEEP has a period of N = S / gcd(S, 32) words; the host builds one period plus nine words of overlap
+// (dense_shift_table) and every CTA copies it to shared memory.  The funnel shift of word t needs word t + 1 (right)
+// or t - 1 (left) of the MASKED stream.
+//
+// Not for in-place calls (a warp reads one word that another warp may have overwritten) and only for amounts below
+// 32: the caller (pint_cuda_dense_shift) keeps the whole-chunk kernels for those.
+#pragma once
+#ifndef PINT_CUDA_KERNELS_DENSE_SHIFT_CUH_INCLUDED
+#define PINT_CUDA_KERNELS_DENSE_SHIFT_CUH_INCLUDED
+
+#include "cuda_kernels.cuh"
+
+namespace pint {
+namespace cuda {
+namespace kernels {
+namespace dense {
+
+constexpr int kShiftTableWords = 64 + 9;  // N <= 63 (S <= 64), + the nine words one thread looks ahead
+
+struct dense_shift_table {
+    uint32_t keep[kShiftTableWords];  // keep[x] = KEEP bits [32 x, 32 x + 32) of the periodic pattern, x < N + 9
+    uint32_t nwords;                  // N: period of the pattern in words
+    uint32_t amount;                  // < 32
+    uint32_t left;                    // 1 = shift_left, 0 = shift_right_unsigned
+};
+
+// pre = keep mask of ONE element (bits above S are 0), S = sum(Bits)
+inline dense_shift_table make_dense_shift_table(uint64_t pre, uint32_t S, uint32_t amount, bool left)
+{
+    dense_shift_table t{};
+    uint32_t g = S, b = 32;
+    while (b) { const uint32_t r = g % b; g = b; b = r; }
+    t.nwords = S / g;
+    t.amount = amount;
+    t.left = left ? 1u : 0u;
+    for (uint32_t x = 0; x < t.nwords + 9; ++x) {
+        uint32_t w = 0;
+        for (uint32_t bit = 0; bit < 32; ++bit) {
+            const uint64_t pos = (uint64_t(x % t.nwords) * 32 + bit) % S;  // position inside the element
+            w |= uint32_t((pre >> pos) & 1u) << bit;
+        }
+        t.keep[x] = w;
+    }
+    return t;
+}
+
+// in / out: the stream as 16-byte vectors (nvec of them, 4 words each); valid_bits = n * S: everything above is written as 0
+template <int U>
+__global__ void __launch_bounds__(256)
+dense_shift_stream_kernel(const uint4* in, uint4* out, size_t nvec, unsigned long long valid_bits,
+                          const __grid_constant__ dense_shift_table tab)
+{
+    pdl_prologue();
+    __shared__ uint32_t keep[kShiftTableWords];
+    __shared__ uint32_t tile_phase;
+    const uint32_t N = tab.nwords, k = tab.amount;
+    const bool left = tab.left != 0;
+    const unsigned lane = threadIdx.x & 31u;
+    const uint32_t* words = reinterpret_cast<const uint32_t*>(in);
+    const size_t nwords_total = 4 * nvec;
+    const size_t tile = size_t(U) * 256;
+    // position of a word in the mask period WITHOUT a 64-bit modulo per vector (that alone made the kernel ALU-bound,
+    // 5.6 TB/s): (first word of the tile) mod N once per CTA and tile, (4 * thread) mod N once per thread, then adds
+    // with a conditional subtract
+    const uint32_t thread_phase = (4u * threadIdx.x) % N;
+    const uint32_t step_phase = 1024u % N;  // 256 threads x 4 words between a thread's consecutive vectors
+    auto wrap = [N](uint32_t x) { return x >= N ? x - N : x; };
+    bool first_tile = true;
+    for (size_t base = size_t(blockIdx.x) * tile; base < nvec; base += size_t(gridDim.x) * tile) {
+        // every load of the tile is in flight before anything waits: the vectors, and on the last (first) lane of each
+        // warp the one word beyond the warp's 512 bytes that the funnel shift pulls bits from
+        uint4 q[U];
+        uint32_t far_edge[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const size_t v = base + size_t(u) * 256 + threadIdx.x;
+            q[u] = v < nvec ? ld16<CACHE_STREAMING>(in + v) : make_uint4(0, 0, 0, 0);
+            far_edge[u] = 0;
+            if (!left) { if (lane == 31 && v < nvec && 4 * v + 4 < nwords_total) far_edge[u] = __ldg(words + 4 * v + 4); }
+            else       { if (lane == 0 && v < nvec && v > 0) far_edge[u] = __ldg(words + 4 * v - 1); }
+        }
+        __syncthreads();  // the previous tile's readers of tile_phase are done
+        if (first_tile)
+            for (int x = threadIdx.x; x < kShiftTableWords; x += 256) keep[x] = tab.keep[x];
+        if (threadIdx.x == 0) tile_phase = uint32_t((4 * base) % N);
+        first_tile = false;
+        __syncthreads();
+        uint32_t phase = wrap(tile_phase + thread_phase);  // (4 * v) mod N for u = 0
+        if (left) phase = wrap(phase + N - 1);             // left shifts look one word back
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const size_t v = base + size_t(u) * 256 + threadIdx.x;
+            const bool have = v < nvec;                    // whole warps run on so that the shuffles stay convergent
+            const size_t i0 = 4 * v;                       // first word of this thread's vector
+            const uint32_t w[4] = {q[u].x, q[u].y, q[u].z, q[u].w};
+            uint32_t edge = far_edge[u];
+            if (!left) {
+                const uint32_t nb = __shfl_down_sync(0xffffffffu, w[0], 1);
+                if (lane != 31) edge = nb;
+            } else {
+                const uint32_t nb = __shfl_up_sync(0xffffffffu, w[3], 1);
+                if (lane != 0) edge = nb;
+            }
+            // masks of words i0 .. i0 + 4 (right) or i0 - 1 .. i0 + 3 (left)
+            const uint32_t j0 = phase;
+            phase = wrap(phase + step_phase);
+            if (!have) continue;
+            uint32_t m[5];
+            if (!left) {
+#pragma unroll
+                for (int t = 0; t < 4; ++t) m[t] = w[t] & keep[j0 + t];
+                m[4] = edge & keep[j0 + 4];
+            } else {
+                m[0] = edge & keep[j0];
+#pragma unroll
+                for (int t = 0; t < 4; ++t) m[t + 1] = w[t] & keep[j0 + 1 + t];
+            }
+            uint32_t r[4];
+#pragma unroll
+            for (int t = 0; t < 4; ++t)
+                r[t] = left ? __funnelshift_l(m[t], m[t + 1], k) : __funnelshift_r(m[t], m[t + 1], k);
+            // padding above the last element stays 0 whatever the input holds there
+            if ((unsigned long long)(i0 + 4) * 32ull > valid_bits) {
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    const unsigned long long lo = (unsigned long long)(i0 + t) * 32ull;
+                    if (lo >= valid_bits) r[t] = 0;
+                    else if (valid_bits - lo < 32ull) r[t] &= (1u << unsigned(valid_bits - lo)) - 1u;
+                }
+            }
+            st16<CACHE_STREAMING>(out + v, make_uint4(r[0], r[1], r[2], r[3]));
+        }
+    }
+}
+
+#if !defined(__CUDACC_RTC__)
+// bytes: length of both streams (a multiple of 16); in and out 16-byte aligned, not overlapping; amount < 32
+inline cudaError_t launch_dense_shift_stream(const void* in, void* out, size_t bytes, unsigned long long valid_bits,
+                                             const dense_shift_table& tab, cudaStream_t s, const launch_geom& g)
+{
+    constexpr int U = 4;
+    const size_t nvec = bytes / 16;
+    if (nvec) {
+        const size_t ntiles = (nvec + size_t(U) * 256 - 1) / (size_t(U) * 256);
+        if (cudaError_t e = launch_stream_kernel(dense_shift_stream_kernel<U>, grid_for(ntiles, g), 256, s, g.pdl != 0,
+                                                 static_cast<const uint4*>(in), static_cast<uint4*>(out), nvec, valid_bits, tab))
+            return e;
+        count_launch(g);
+    }
+    return cudaGetLastError();
+}
+#endif
+
+}  // namespace dense
+}  // namespace kernels
+}  // namespace cuda
+}  // namespace pint
+
+#endif  // PINT_CUDA_KERNELS_DENSE_SHIFT_CUH_INCLUDED

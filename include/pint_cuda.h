@@ -96,7 +96,8 @@ unsigned long long pint_cuda_launch_count(void);
  * "dense_threads" / "dense_tile_bytes" (CTA size and per-operand tile of the dense bit-stream
  * kernels; 0 = chosen from the layout), "vec256" (32-byte global accesses in the stream kernels:
  * 0 never, 1 = default, where measured faster, 2 wherever the operands are 32-byte congruent), "dense_windows" (1 = layouts without compiled-in dense
- * kernels always use the element-by-element window kernels; testing), "unpack_bulk" (unpack to int32 planes:
+ * kernels always use the element-by-element window kernels; testing), "dense_shift_stream" (1 = default: dense shifts
+ * by less than 32 bits that are not in place run as a masked funnel shift over the word stream; 0 = the whole-chunk kernels), "unpack_bulk" (unpack to int32 planes:
  * 1 = default, plane tiles staged in shared memory and written by bulk (TMA) stores; 0 = straight from
  * registers), "jit" (0 = default, 1, 2: run-time specialisation of unregistered layouts, see
  * pint_cuda_jit_compile), "pdl" (1 = default: the streaming kernels (binary, multi, fused, shift, slice, scalar, pairs, unpack, repack) are launched with

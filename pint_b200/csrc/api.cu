@@ -255,6 +255,7 @@ int pint_cuda_set_option(const char* key, long value)
     if (!std::strcmp(key, "host_slots")) { if (value < 1 || value > 8) return PINT_E_ARG; opts().host_slots = value; return PINT_OK; }
     if (!std::strcmp(key, "vec256")) { if (value < 0 || value > 2) return PINT_E_ARG; opts().vec256 = value; return PINT_OK; }
     if (!std::strcmp(key, "dense_windows")) { opts().dense_windows = value != 0; return PINT_OK; }
+    if (!std::strcmp(key, "dense_shift_stream")) { opts().dense_shift_stream = value != 0; return PINT_OK; }
     if (!std::strcmp(key, "pdl")) { opts().pdl = value != 0; return PINT_OK; }
     if (!std::strcmp(key, "jit")) { if (value < 0 || value > 2) return PINT_E_ARG; opts().jit = value; return PINT_OK; }
     if (!std::strcmp(key, "unpack_bulk")) { if (value < 0 || value > 1) return PINT_E_ARG; opts().unpack_bulk = value; return PINT_OK; }
@@ -273,6 +274,7 @@ long pint_cuda_get_option(const char* key)
     if (!std::strcmp(key, "host_slots")) return opts().host_slots;
     if (!std::strcmp(key, "vec256")) return opts().vec256;
     if (!std::strcmp(key, "dense_windows")) return opts().dense_windows;
+    if (!std::strcmp(key, "dense_shift_stream")) return opts().dense_shift_stream;
     if (!std::strcmp(key, "unpack_bulk")) return opts().unpack_bulk;
     if (!std::strcmp(key, "jit")) return opts().jit;
     if (!std::strcmp(key, "pdl")) return opts().pdl;

@@ -4,6 +4,7 @@
 #include "dense_registry.hpp"
 #include "pint/cuda_kernels_dense_convert.cuh"
 #include "pint/cuda_kernels_dense_bytes.cuh"
+#include "pint/cuda_kernels_dense_shift.cuh"
 
 namespace pint_cuda_impl {
 namespace {
@@ -453,6 +454,11 @@ int pint_cuda_dense_shift(int left, const pint_layout* layout, uint64_t amount, 
         pre = (left ? mask : ~mask) & m.A;
     }
     const launch_geom g = geom();
+    // the stream as one long integer: mask, then funnel-shift neighbouring words (cuda_kernels_dense_shift.cuh).  Not in
+    // place (a warp reads one word of its neighbour's vector) and only below 32 bits; the chunk kernels keep the rest.
+    if (opts().dense_shift_stream && !opts().dense_windows && in != out && amt < 32)
+        return (int)dense::launch_dense_shift_stream(in, out, bytes, (unsigned long long)n * S,
+                                                     dense::make_dense_shift_table(pre, S, amt, left != 0), s, g);
     const int N = int(S / dense::gcd_u32(S, 32));
     if (!opts().dense_windows) {
         cudaError_t rc = cudaSuccess;

@@ -89,6 +89,31 @@ def test_dense_shift_vs_oracle(P, oracle, eb, bits, mode):
         np.testing.assert_array_equal(inplace.cpu().numpy(), oracle.dense_pack(eb, bits, oracle.shift(True, eb, bits, 1, x)))
 
 
+@pytest.mark.parametrize("eb,bits", LAYOUTS)
+def test_dense_shift_chunk_kernels_still_agree(P, oracle, eb, bits):
+    """Out-of-place shifts by less than 32 bits take the word-stream kernel by default (cuda_kernels_dense_shift.cuh);
+    the whole-chunk kernels they replaced still serve in-place and wide shifts, so they stay under test: option off,
+    same streams, same oracle."""
+    pint_b200, ops, dense = P
+    L = pint_b200.Layout(eb, *bits)
+    S = sum(bits)
+    try:
+        for n in (129, (1 << 17) + 77):
+            x = oracle.fill(eb, n, 0x5F + n)
+            x = x & np.array((1 << S) - 1, dtype=x.dtype)
+            dx_h = oracle.dense_pack(eb, bits, x)
+            dx = dev_bytes(dx_h)
+            for left in (True, False):
+                for amt in sorted({0, 1, min(bits), max(bits) - 1}):
+                    want = oracle.dense_pack(eb, bits, oracle.shift(left, eb, bits, amt, x))
+                    for opt in (0, 1):
+                        ops.set_option("dense_shift_stream", opt)
+                        got = dense.shift(left, L, dx, amt, n).cpu().numpy()
+                        np.testing.assert_array_equal(got, want, err_msg=f"{L} left={left} amount={amt} n={n} dense_shift_stream={opt}")
+    finally:
+        ops.set_option("dense_shift_stream", 1)
+
+
 @pytest.mark.parametrize("eb,bits", LAYOUTS[:12])
 def test_dense_in_place_and_tiles(P, oracle, eb, bits):
     """In place on either operand; every tile geometry option gives the same stream."""
