@@ -114,6 +114,31 @@ def test_dense_shift_chunk_kernels_still_agree(P, oracle, eb, bits):
         ops.set_option("dense_shift_stream", 1)
 
 
+def test_dense_shift_every_total_width(P, oracle):
+    """sum(Bits) = 1 ... 63 with a seeded random split into fields: every period of the keep mask (1 ... 63 words) and
+    every phase of a field against the 32-bit words the stream kernel shifts, out of place and in place."""
+    pint_b200, ops, dense = P
+    rng = np.random.default_rng(0x5417F7)
+    for S in range(1, 64):
+        cuts = sorted(set(rng.integers(1, S, size=int(rng.integers(0, 5))).tolist())) if S > 1 else []
+        bits = tuple(b - a for a, b in zip([0] + cuts, cuts + [S]))
+        eb = 1 if S <= 8 else 2 if S <= 16 else 4 if S <= 32 else 8
+        L = pint_b200.Layout(eb, *bits)
+        for n in (1, 77, 5000):
+            x = oracle.fill(eb, n, S * 131 + n)
+            x = x & np.array((1 << S) - 1, dtype=x.dtype)
+            dx_h = oracle.dense_pack(eb, bits, x)
+            dx = dev_bytes(dx_h)
+            for left in (True, False):
+                for amt in sorted({0, 1, min(bits), max(bits) - 1, min(max(bits), 31)}):
+                    want = oracle.dense_pack(eb, bits, oracle.shift(left, eb, bits, amt, x))
+                    got = dense.shift(left, L, dx, amt, n).cpu().numpy()
+                    np.testing.assert_array_equal(got, want, err_msg=f"{L} left={left} amount={amt} n={n}")
+            inplace = dev_bytes(dx_h)
+            dense.shift(False, L, inplace, 1, n, out=inplace)
+            np.testing.assert_array_equal(inplace.cpu().numpy(), oracle.dense_pack(eb, bits, oracle.shift(False, eb, bits, 1, x)))
+
+
 @pytest.mark.parametrize("eb,bits", LAYOUTS[:12])
 def test_dense_in_place_and_tiles(P, oracle, eb, bits):
     """In place on either operand; every tile geometry option gives the same stream."""
