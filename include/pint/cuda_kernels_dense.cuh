@@ -366,6 +366,7 @@ template <class Fn, class Geo, int Mode = 0>
 __global__ void dense_binary_kernel(const uint4* a, const uint4* b, uint4* out, uint4* out1, size_t total_vec,
                                     uint64_t valid_bits, const __grid_constant__ Fn fn, const __grid_constant__ Geo geo)
 {
+    pdl_prologue();
     using W = typename Geo::unit;
     extern __shared__ __align__(128) unsigned char dense_smem[];
     __shared__ __align__(8) uint64_t full;
@@ -487,9 +488,11 @@ cudaError_t launch_dense_binary(const void* a, const void* b, void* out, size_t 
         if (rc != cudaSuccess) return rc;
     }
     if (ntiles > 0x7FFFFFFFull) return cudaErrorInvalidValue;
-    kernel<<<unsigned(ntiles), T, smem, stream>>>(static_cast<const uint4*>(a), static_cast<const uint4*>(b),
-                                                  static_cast<uint4*>(out), static_cast<uint4*>(out1), total_vec,
-                                                  valid_bits, fn, geo);
+    // programmatic dependent launch like the padded stream kernels: frame-sized streams (RGB24 1080p is 6 MB) are launch-bound
+    if (cudaError_t e = launch_stream_kernel_smem(kernel, unsigned(ntiles), T, smem, stream, g.pdl != 0, static_cast<const uint4*>(a),
+                                                  static_cast<const uint4*>(b), static_cast<uint4*>(out), static_cast<uint4*>(out1),
+                                                  total_vec, valid_bits, fn, geo))
+        return e;
     count_launch(g);
     return cudaGetLastError();
 }

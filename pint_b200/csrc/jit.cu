@@ -73,6 +73,7 @@ struct driver_api {
     CUresult (*MemcpyDtoH)(void*, CUdeviceptr, size_t) = nullptr;
     CUresult (*LaunchKernel)(CUfunction, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, CUstream, void**, void**) = nullptr;
     CUresult (*FuncSetAttribute)(CUfunction, CUfunction_attribute, int) = nullptr;
+    CUresult (*LaunchKernelEx)(const CUlaunchConfig*, CUfunction, void**, void**) = nullptr;  // optional: launches with the PDL attribute
 };
 
 std::mutex g_jit_mutex;
@@ -176,8 +177,29 @@ bool load_driver()
               get("cuFuncSetAttribute", reinterpret_cast<void**>(&g_drv.FuncSetAttribute));
     if (!ok) { cudaGetLastError(); g_last_error = "driver entry points unavailable"; }
     if (ok && !get("cuModuleUnload", reinterpret_cast<void**>(&g_drv.ModuleUnload))) { cudaGetLastError(); g_drv.ModuleUnload = nullptr; }
+    if (ok && !get("cuLaunchKernelEx", reinterpret_cast<void**>(&g_drv.LaunchKernelEx))) { cudaGetLastError(); g_drv.LaunchKernelEx = nullptr; }
     g_drv_ok = ok;
     return ok;
+}
+
+// One launch of a specialised kernel.  With option "pdl" the launch carries the programmatic-stream-serialization
+// attribute, like launch_stream_kernel does for the pre-built kernels (every kernel template starts with pdl_prologue).
+CUresult drv_launch(CUfunction f, unsigned grid, unsigned block, unsigned smem, cudaStream_t s, void** args, bool pdl)
+{
+    if (pdl && g_drv.LaunchKernelEx) {
+        CUlaunchConfig cfg{};
+        cfg.gridDimX = grid; cfg.gridDimY = 1; cfg.gridDimZ = 1;
+        cfg.blockDimX = block; cfg.blockDimY = 1; cfg.blockDimZ = 1;
+        cfg.sharedMemBytes = smem;
+        cfg.hStream = (CUstream)s;
+        CUlaunchAttribute attr[1];
+        attr[0].id = CU_LAUNCH_ATTRIBUTE_PROGRAMMATIC_STREAM_SERIALIZATION;
+        attr[0].value.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        return g_drv.LaunchKernelEx(&cfg, f, args, nullptr);
+    }
+    return g_drv.LaunchKernel(f, grid, 1, 1, block, 1, 1, smem, (CUstream)s, args, nullptr);
 }
 
 // ---- what gets compiled ----
@@ -572,7 +594,7 @@ int launch_body(const jit_kernel& k, uint32_t elem_bytes, const void* const* ptr
     }
     args[nptrs] = &nvec;
     args[nptrs + 1] = &empty_fn;
-    const CUresult cr = g_drv.LaunchKernel(wide ? k.f256 : k.f128, grid_for(ntiles, g), 1, 1, (unsigned)k.block, 1, 1, 0, (CUstream)s, args, nullptr);
+    const CUresult cr = drv_launch(wide ? k.f256 : k.f128, grid_for(ntiles, g), (unsigned)k.block, 0, s, args, g.pdl != 0);
     if (cr != CUDA_SUCCESS) return (int)cudaErrorLaunchFailure;
     count_launch(g);
     return rest(n - tail, tail);
@@ -644,7 +666,7 @@ int jit_dense(int op, int pair, const layout_desc& d, const void* a, const void*
         return (int)cudaErrorInvalidValue;
     char empty_fn = 0;
     void* args[8] = {(void*)&a, (void*)&b, (void*)&out, (void*)&out1, &total_vec, &valid_bits, &empty_fn, &geo};
-    if (g_drv.LaunchKernel(k.f128, unsigned(ntiles), 1, 1, T, 1, 1, (unsigned)smem, (CUstream)s, args, nullptr) != CUDA_SUCCESS)
+    if (drv_launch(k.f128, unsigned(ntiles), T, (unsigned)smem, s, args, g.pdl != 0) != CUDA_SUCCESS)
         return (int)cudaErrorLaunchFailure;
     count_launch(g);
     *handled = true;
@@ -680,7 +702,7 @@ int jit_scalar_body(int op, bool first, const layout_desc& d, const void* a, uin
     void* out_v = static_cast<char*>(out) + h * d.elem_bytes;
     const size_t ntiles = (nvec + 4 * 256 - 1) / (4 * 256);
     void* args[4] = {(void*)&in_v, (void*)&out_v, &nvec, fn};
-    if (g_drv.LaunchKernel(k.f128, grid_for(ntiles, g), 1, 1, 256, 1, 1, 0, (CUstream)s, args, nullptr) != CUDA_SUCCESS)
+    if (drv_launch(k.f128, grid_for(ntiles, g), 256, 0, s, args, g.pdl != 0) != CUDA_SUCCESS)
         return (int)cudaErrorLaunchFailure;
     count_launch(g);
     *head = h;
@@ -714,7 +736,7 @@ int jit_pairs_body(int op, const layout_desc& d, const void* pairs, void* out, s
     const size_t ntiles = (nvec + 2 * 256 - 1) / (2 * 256);
     char empty_fn = 0;
     void* args[4] = {(void*)&pv, (void*)&ov, &nvec, &empty_fn};
-    if (g_drv.LaunchKernel(k.f128, grid_for(ntiles, g), 1, 1, 256, 1, 1, 0, (CUstream)s, args, nullptr) != CUDA_SUCCESS)
+    if (drv_launch(k.f128, grid_for(ntiles, g), 256, 0, s, args, g.pdl != 0) != CUDA_SUCCESS)
         return (int)cudaErrorLaunchFailure;
     count_launch(g);
     *head = h;
