@@ -93,6 +93,7 @@ template <int F, int P>
 __global__ void __launch_bounds__(kByteTileBlocks)
 dense_bytes_to_planes_kernel(const uint4* stream, const __grid_constant__ plane_ptrs planes, size_t ntiles)
 {
+    pdl_prologue();
     using BB = byte_block<F, P>;
     __shared__ __align__(16) uint4 tile[kByteTileBlocks * F];
     for (size_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
@@ -124,6 +125,7 @@ template <int F, int P>
 __global__ void __launch_bounds__(kByteTileBlocks)
 dense_bytes_from_planes_kernel(const __grid_constant__ plane_ptrs planes, uint4* stream, size_t ntiles)
 {
+    pdl_prologue();
     using BB = byte_block<F, P>;
     __shared__ __align__(16) uint4 tile[kByteTileBlocks * F];
     for (size_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
@@ -156,10 +158,11 @@ cudaError_t launch_dense_bytes(bool to_stream, const plane_ptrs& planes, void* s
     const size_t ntiles = n / tile_elems;
     *done = ntiles * tile_elems;
     if (!ntiles) return cudaSuccess;
-    if (to_stream)
-        dense_bytes_from_planes_kernel<F, P><<<grid_for(ntiles, g), kByteTileBlocks, 0, s>>>(planes, static_cast<uint4*>(stream), ntiles);
-    else
-        dense_bytes_to_planes_kernel<F, P><<<grid_for(ntiles, g), kByteTileBlocks, 0, s>>>(static_cast<const uint4*>(stream), planes, ntiles);
+    if (cudaError_t e = to_stream ? launch_stream_kernel(dense_bytes_from_planes_kernel<F, P>, grid_for(ntiles, g), kByteTileBlocks, s, g.pdl != 0, planes,
+                                                         static_cast<uint4*>(stream), ntiles)
+                                  : launch_stream_kernel(dense_bytes_to_planes_kernel<F, P>, grid_for(ntiles, g), kByteTileBlocks, s, g.pdl != 0,
+                                                         static_cast<const uint4*>(stream), planes, ntiles))
+        return e;
     count_launch(g);
     return cudaGetLastError();
 }

@@ -36,6 +36,7 @@ template <class W, class Elem, int Side, int PlaneBytes, bool Signed>
 __global__ void dense_extract_kernel(const uint4* dense, Elem* padded, size_t n, uint32_t S, uint32_t tile_elems,
                                      size_t total_vec, uint32_t quads, const __grid_constant__ dense_fields f)
 {
+    pdl_prologue();
     constexpr uint32_t WB = 8 * sizeof(W);
     extern __shared__ __align__(128) unsigned char dense_smem[];
     __shared__ __align__(8) uint64_t full;
@@ -126,6 +127,7 @@ __global__ void dense_insert_kernel(const Elem* padded, uint4* dense, size_t n, 
                                     uint32_t chunks_per_tile, size_t total_vec, uint32_t quads,
                                     const __grid_constant__ dense_fields f)
 {
+    pdl_prologue();
     constexpr uint32_t WB = 8 * sizeof(W);
     using ST = typename std::conditional<PlaneBytes == 8, int64_t, typename std::conditional<PlaneBytes == 4, int32_t,
                typename std::conditional<PlaneBytes == 2, int16_t, int8_t>::type>::type>::type;
@@ -254,8 +256,9 @@ cudaError_t launch_dense_extract(const void* dense, void* other, size_t n, uint3
         for (uint32_t i = 0; i < f.t.nfields; ++i) align |= reinterpret_cast<uintptr_t>(f.planes.p[i]);
     }
     const uint32_t quads = (align & 15u) == 0 ? 1u : 0u;
-    dense_extract_kernel<W, Elem, Side, PlaneBytes, Signed><<<unsigned(ntiles), 256, smem, stream>>>(
-        static_cast<const uint4*>(dense), static_cast<Elem*>(other), n, S, te, total_vec, quads, f);
+    if (cudaError_t e = launch_stream_kernel_smem(dense_extract_kernel<W, Elem, Side, PlaneBytes, Signed>, unsigned(ntiles), 256, smem, stream, g.pdl != 0,
+                                                  static_cast<const uint4*>(dense), static_cast<Elem*>(other), n, S, te, total_vec, quads, f))
+        return e;
     count_launch(g);
     return cudaGetLastError();
 }
@@ -292,8 +295,9 @@ cudaError_t launch_dense_insert(const void* other, void* dense, size_t n, uint32
     if (Side == SIDE_PLANES)
         for (uint32_t i = 0; i < f.t.nfields; ++i) align |= reinterpret_cast<uintptr_t>(f.planes.p[i]);
     const uint32_t quads = (align & 15u) == 0 ? 1u : 0u;
-    kernel<<<unsigned(ntiles), threads, smem, stream>>>(static_cast<const Elem*>(other), static_cast<uint4*>(dense), n, S,
-                                                        log2G, Cw, cpt, total_vec, quads, f);
+    if (cudaError_t e = launch_stream_kernel_smem(kernel, unsigned(ntiles), threads, smem, stream, g.pdl != 0, static_cast<const Elem*>(other),
+                                                  static_cast<uint4*>(dense), n, S, log2G, Cw, cpt, total_vec, quads, f))
+        return e;
     count_launch(g);
     return cudaGetLastError();
 }

@@ -113,6 +113,7 @@ template <class Elem, uint32_t S, int Side, int PlaneBytes, bool V32 = false>
 __global__ void __launch_bounds__(256)
 dense_insert_fixed_kernel(const Elem* padded, uint4* dense, uint32_t units_per_thread, const __grid_constant__ dense_fields f)
 {
+    pdl_prologue();
     using Geo = fixed_geom<S, (Side == SIDE_PADDED ? uint32_t(sizeof(Elem)) : uint32_t(PlaneBytes))>;
     using W = typename Geo::W;
     constexpr uint32_t GE = Geo::GE, CW = Geo::CW, UB = Geo::UB, BEL = Geo::BEL;
@@ -220,6 +221,7 @@ template <class Elem, uint32_t S, int Side, int PlaneBytes>
 __global__ void __launch_bounds__(256)
 dense_insert_fixed_staged_kernel(const Elem* padded, uint4* dense, uint32_t units_per_tile, const __grid_constant__ dense_fields f)
 {
+    pdl_prologue();
     using Geo = fixed_geom<S, (Side == SIDE_PADDED ? uint32_t(sizeof(Elem)) : uint32_t(PlaneBytes))>;
     using W = typename Geo::W;
     using Staged = typename std::conditional<Side == SIDE_PADDED, Elem, W>::type;
@@ -349,8 +351,9 @@ cudaError_t launch_dense_insert_fixed(const void* other, void* dense, size_t n, 
         *done = ntiles * tile_elems;
         if (ntiles == 0) return cudaSuccess;
         if (ntiles > 0x7FFFFFFFull) return cudaErrorInvalidValue;
-        dense_insert_fixed_staged_kernel<Elem, S, Side, PlaneBytes><<<unsigned(ntiles), word_owner ? 256 : 128, smem, stream>>>(
-            static_cast<const Elem*>(other), static_cast<uint4*>(dense), U, f);
+        if (cudaError_t e = launch_stream_kernel_smem(dense_insert_fixed_staged_kernel<Elem, S, Side, PlaneBytes>, unsigned(ntiles), word_owner ? 256u : 128u,
+                                                      smem, stream, g.pdl != 0, static_cast<const Elem*>(other), static_cast<uint4*>(dense), U, f))
+            return e;
         count_launch(g);
         return cudaGetLastError();
     } else {
@@ -380,13 +383,15 @@ cudaError_t launch_dense_insert_fixed(const void* other, void* dense, size_t n, 
     if constexpr (sizeof(typename Geo::W) == 8 && (Geo::BEL * src_bytes) % 32 == 0) {
         if (g.vec256 != 0 && align % 32 == 0) {
             wide = true;
-            dense_insert_fixed_kernel<Elem, S, Side, PlaneBytes, true><<<unsigned(ntiles), T, smem, stream>>>(
-                static_cast<const Elem*>(other), static_cast<uint4*>(dense), upt, f);
+            if (cudaError_t e = launch_stream_kernel_smem(dense_insert_fixed_kernel<Elem, S, Side, PlaneBytes, true>, unsigned(ntiles), T, smem, stream,
+                                                          g.pdl != 0, static_cast<const Elem*>(other), static_cast<uint4*>(dense), upt, f))
+                return e;
         }
     }
     if (!wide)
-        dense_insert_fixed_kernel<Elem, S, Side, PlaneBytes, false><<<unsigned(ntiles), T, smem, stream>>>(
-            static_cast<const Elem*>(other), static_cast<uint4*>(dense), upt, f);
+        if (cudaError_t e = launch_stream_kernel_smem(dense_insert_fixed_kernel<Elem, S, Side, PlaneBytes, false>, unsigned(ntiles), T, smem, stream,
+                                                      g.pdl != 0, static_cast<const Elem*>(other), static_cast<uint4*>(dense), upt, f))
+            return e;
     count_launch(g);
     return cudaGetLastError();
     }
@@ -422,6 +427,7 @@ __global__ void __launch_bounds__(256)
 dense_extract_fixed_kernel(const uint4* dense, Elem* padded, uint32_t tile_elems, const __grid_constant__ dense_fields f,
                            uint32_t narrow_signed = 0)
 {
+    pdl_prologue();
     using Geo = group_geom<Elem, S, Side, PlaneBytes>;
     using W = typename Geo::W;
     constexpr uint32_t GP = Geo::GP, NA = Geo::NA, NW = Geo::NW, WB = Geo::WB;
@@ -527,8 +533,9 @@ cudaError_t launch_dense_extract_fixed(const void* dense, void* other, size_t n,
     if (ntiles == 0) return cudaSuccess;
     if (ntiles > 0x7FFFFFFFull) return cudaErrorInvalidValue;
     (void)sizeof(W);
-    dense_extract_fixed_kernel<Elem, S, Side, PlaneBytes, Signed><<<unsigned(ntiles), 256, smem, stream>>>(
-        static_cast<const uint4*>(dense), static_cast<Elem*>(other), tile_elems, f, narrow_signed);
+    if (cudaError_t e = launch_stream_kernel_smem(dense_extract_fixed_kernel<Elem, S, Side, PlaneBytes, Signed>, unsigned(ntiles), 256, smem, stream,
+                                                  g.pdl != 0, static_cast<const uint4*>(dense), static_cast<Elem*>(other), tile_elems, f, narrow_signed))
+        return e;
     count_launch(g);
     return cudaGetLastError();
 }
