@@ -100,7 +100,7 @@ unsigned long long pint_cuda_launch_count(void);
  * by less than 32 bits that are not in place run as a masked funnel shift over the word stream; 0 = the whole-chunk kernels), "unpack_bulk" (unpack to int32 planes:
  * 1 = default, plane tiles staged in shared memory and written by bulk (TMA) stores; 0 = straight from
  * registers), "jit" (0 = default, 1, 2: run-time specialisation of unregistered layouts, see
- * pint_cuda_jit_compile), "pdl" (1 = default: the streaming kernels (binary, multi, fused, shift, slice, scalar, pairs, unpack, repack, the pair reduction, dense binary / pair / shift / conversions, and the run-time-specialised ones) are launched with
+ * pint_cuda_jit_compile), "pdl" (1 = default: the streaming kernels (binary, multi, fused, shift, slice, scalar, pairs, unpack, repack, the pair reduction, operator== over arrays, dense binary / pair / shift / conversions, and the run-time-specialised ones) are launched with
  * programmatic stream serialization, so back-to-back passes overlap one pass's tail with the next one's
  * launch: +4 ... 14 % on arrays up to 2^26 elements, neutral above; results and ordering are unchanged, every
  * kernel waits for the previous launch of its stream before touching memory; 0 = plain launches).

@@ -71,6 +71,12 @@ cudaError_t pairs_map_ops(int op, const layout_desc& d, const void* pairs, void*
     return rc;
 }
 
+__global__ void zero_count_kernel(uint64_t* count)
+{
+    pdl_prologue();
+    if (threadIdx.x == 0) *count = 0;
+}
+
 // packed_int::operator== / operator!= (pint.hpp:778-779) over arrays: the whole Integer is compared,
 // unused high bits included.  equal[i] = (a[i] == b[i]) as one byte per element (optional) and the
 // number of unequal elements (optional; integer atomics: exact and order-independent).
@@ -80,6 +86,7 @@ template <class Elem, bool Flags, bool Count>
 __global__ void __launch_bounds__(256)
 equal_kernel(const Elem* a, const Elem* b, size_t n, uint8_t* equal, unsigned long long* not_equal, bool vec_ok)
 {
+    pdl_prologue();
     constexpr int PER = 16 / sizeof(Elem), U = 4;
     using flags_t = typename std::conditional<PER == 16, uint4, typename std::conditional<PER == 8, uint2,
                     typename std::conditional<PER == 4, uint32_t, uint16_t>::type>::type>::type;
@@ -140,9 +147,12 @@ cudaError_t equal_launch(const void* a, const void* b, size_t n, uint8_t* equal,
     const Elem* ea = static_cast<const Elem*>(a);
     const Elem* eb = static_cast<const Elem*>(b);
     unsigned long long* c = reinterpret_cast<unsigned long long*>(count);
-    if (equal && count) equal_kernel<Elem, true, true><<<grid, 256, 0, s>>>(ea, eb, n, equal, c, vec_ok);
-    else if (equal) equal_kernel<Elem, true, false><<<grid, 256, 0, s>>>(ea, eb, n, equal, c, vec_ok);
-    else equal_kernel<Elem, false, true><<<grid, 256, 0, s>>>(ea, eb, n, equal, c, vec_ok);
+    const bool pdl = g.pdl != 0;
+    cudaError_t rc;
+    if (equal && count) rc = launch_stream_kernel(equal_kernel<Elem, true, true>, grid, 256, s, pdl, ea, eb, n, equal, c, vec_ok);
+    else if (equal) rc = launch_stream_kernel(equal_kernel<Elem, true, false>, grid, 256, s, pdl, ea, eb, n, equal, c, vec_ok);
+    else rc = launch_stream_kernel(equal_kernel<Elem, false, true>, grid, 256, s, pdl, ea, eb, n, equal, c, vec_ok);
+    if (rc != cudaSuccess) return rc;
     count_launch(g);
     return cudaGetLastError();
 }
@@ -257,9 +267,10 @@ int pint_cuda_equal(const pint_layout* layout, const void* a, const void* b, siz
     layout_desc d;
     if (int rc = check_layout(layout, &d)) return rc;
     cudaStream_t s = (cudaStream_t)stream;
-    if (not_equal_count_dev)
-        if (cudaError_t e = cudaMemsetAsync(not_equal_count_dev, 0, sizeof(uint64_t), s)) return (int)e;
-    if (n == 0) return PINT_OK;  // (an empty flag array may well be a null pointer)
+    if (n == 0) {  // (an empty flag array may well be a null pointer)
+        if (not_equal_count_dev) return (int)cudaMemsetAsync(not_equal_count_dev, 0, sizeof(uint64_t), s);
+        return PINT_OK;
+    }
     if (!equal_out && !not_equal_count_dev) return PINT_E_NULL;
     if (!a || !b) return PINT_E_NULL;
     if (((uintptr_t)a | (uintptr_t)b) % d.elem_bytes) return PINT_E_ARG;
@@ -268,6 +279,12 @@ int pint_cuda_equal(const pint_layout* layout, const void* a, const void* b, siz
         if ((o < (uintptr_t)a + bytes && (uintptr_t)a < o + n) || (o < (uintptr_t)b + bytes && (uintptr_t)b < o + n)) return PINT_E_ALIAS;
     }
     const launch_geom g = geom();
+    // the count starts at 0: a one-thread kernel chained to the comparison by programmatic dependent launch, like
+    // pint_cuda_pairs_reduce (a cudaMemsetAsync and its launch gap cost 10-20 us per pass on frame-sized arrays)
+    if (not_equal_count_dev) {
+        if (cudaError_t e = launch_stream_kernel(zero_count_kernel, 1, 32, s, g.pdl != 0, not_equal_count_dev)) return (int)e;
+        count_launch(g);
+    }
     switch (d.elem_bytes) {
     case 1: return (int)equal_launch<uint8_t>(a, b, n, equal_out, not_equal_count_dev, s, g);
     case 2: return (int)equal_launch<uint16_t>(a, b, n, equal_out, not_equal_count_dev, s, g);
