@@ -9,8 +9,9 @@
 // (dense_shift_table) and every CTA copies it to shared memory.  The funnel shift of word t needs word t + 1 (right)
 // or t - 1 (left) of the MASKED stream.
 //
-// Not for in-place calls (a warp reads one word that another warp may have overwritten) and only for amounts below
-// 32: the caller (pint_cuda_dense_shift) keeps the whole-chunk kernels for those.
+// Tiles are whole chunks (lcm(S, 128) bits), i.e. they start and end on element boundaries, where nothing crosses; a
+// CTA performs all loads of its tile before its first store, so the same kernel serves in-place calls.  Only amounts
+// below 32 are taken here: the caller (pint_cuda_dense_shift) keeps the whole-chunk kernels for wider shifts.
 #pragma once
 #ifndef PINT_CUDA_KERNELS_DENSE_SHIFT_CUH_INCLUDED
 #define PINT_CUDA_KERNELS_DENSE_SHIFT_CUH_INCLUDED
@@ -51,54 +52,60 @@ inline dense_shift_table make_dense_shift_table(uint64_t pre, uint32_t S, uint32
     return t;
 }
 
-// in / out: the stream as 16-byte vectors (nvec of them, 4 words each); valid_bits = n * S: everything above is written as 0
+// in / out: the stream as 16-byte vectors (nvec of them, 4 words each); valid_bits = n * S: everything above is written as 0.
+// A CTA's tile is tile_vecs vectors.  cross_tile = 1 (out of place): 1024-vector tiles, the edge word of a tile comes from
+// the neighbouring tile of `in`.  cross_tile = 0 (in place): a whole number of chunks (lcm(S, 128) bits), so tiles begin
+// and end on element boundaries where nothing crosses (the bits that would are masked) and start at phase 0 of the mask;
+// every load of a tile is performed before its first store (the barrier below), which makes the kernel safe in place.
 template <int U>
 __global__ void __launch_bounds__(256)
-dense_shift_stream_kernel(const uint4* in, uint4* out, size_t nvec, unsigned long long valid_bits,
-                          const __grid_constant__ dense_shift_table tab)
+dense_shift_stream_kernel(const uint4* in, uint4* out, size_t nvec, uint32_t tile_vecs, uint32_t cross_tile,
+                          unsigned long long valid_bits, const __grid_constant__ dense_shift_table tab)
 {
+    static_assert(U * 256 == 1024, "the phase of a cross_tile tile assumes 1024 vectors per tile");
     pdl_prologue();
     __shared__ uint32_t keep[kShiftTableWords];
-    __shared__ uint32_t tile_phase;
     const uint32_t N = tab.nwords, k = tab.amount;
     const bool left = tab.left != 0;
     const unsigned lane = threadIdx.x & 31u;
     const uint32_t* words = reinterpret_cast<const uint32_t*>(in);
-    const size_t nwords_total = 4 * nvec;
-    const size_t tile = size_t(U) * 256;
-    // position of a word in the mask period WITHOUT a 64-bit modulo per vector (that alone made the kernel ALU-bound,
-    // 5.6 TB/s): (first word of the tile) mod N once per CTA and tile, (4 * thread) mod N once per thread, then adds
-    // with a conditional subtract
-    const uint32_t thread_phase = (4u * threadIdx.x) % N;
+    // position of a word in the mask period without a modulo per vector (a 64-bit one made the first version ALU-bound,
+    // 5.6 TB/s): (4 * thread) mod N once per thread, then adds with a conditional subtract
     const uint32_t step_phase = 1024u % N;  // 256 threads x 4 words between a thread's consecutive vectors
     auto wrap = [N](uint32_t x) { return x >= N ? x - N : x; };
+    uint32_t phase0 = (4u * threadIdx.x) % N;
+    if (left) phase0 = wrap(phase0 + N - 1);  // left shifts look one word back
     bool first_tile = true;
-    for (size_t base = size_t(blockIdx.x) * tile; base < nvec; base += size_t(gridDim.x) * tile) {
+    for (size_t base = size_t(blockIdx.x) * tile_vecs; base < nvec; base += size_t(gridDim.x) * tile_vecs) {
         // every load of the tile is in flight before anything waits: the vectors, and on the last (first) lane of each
         // warp the one word beyond the warp's 512 bytes that the funnel shift pulls bits from
         uint4 q[U];
         uint32_t far_edge[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            const size_t v = base + size_t(u) * 256 + threadIdx.x;
-            q[u] = v < nvec ? ld16<CACHE_STREAMING>(in + v) : make_uint4(0, 0, 0, 0);
+            const uint32_t local = uint32_t(u) * 256u + threadIdx.x;
+            const size_t v = base + local;
+            const bool have = local < tile_vecs && v < nvec;
+            q[u] = have ? ld16<CACHE_STREAMING>(in + v) : make_uint4(0, 0, 0, 0);
             far_edge[u] = 0;
-            if (!left) { if (lane == 31 && v < nvec && 4 * v + 4 < nwords_total) far_edge[u] = __ldg(words + 4 * v + 4); }
-            else       { if (lane == 0 && v < nvec && v > 0) far_edge[u] = __ldg(words + 4 * v - 1); }
+            // (plain loads: in place the word is written later by this CTA)
+            if (!left) { if (lane == 31 && have && v + 1 < nvec && (cross_tile || local + 1 < tile_vecs)) far_edge[u] = words[4 * v + 4]; }
+            else       { if (lane == 0 && have && v > 0 && (cross_tile || local > 0)) far_edge[u] = words[4 * v - 1]; }
         }
-        __syncthreads();  // the previous tile's readers of tile_phase are done
         if (first_tile)
             for (int x = threadIdx.x; x < kShiftTableWords; x += 256) keep[x] = tab.keep[x];
-        if (threadIdx.x == 0) tile_phase = uint32_t((4 * base) % N);
         first_tile = false;
-        __syncthreads();
-        uint32_t phase = wrap(tile_phase + thread_phase);  // (4 * v) mod N for u = 0
-        if (left) phase = wrap(phase + N - 1);             // left shifts look one word back
+        __syncthreads();  // the mask table is there; and (in place) every load of the tile precedes its first store
+        // a chunk-aligned tile starts at phase 0; a 1024-vector tile t at (4096 t) mod N, in 32-bit arithmetic (a stream has
+        // fewer than 2^32 tiles)
+        uint32_t phase = phase0;
+        if (cross_tile) phase = wrap(phase + ((4096u % N) * (uint32_t(base >> 10) % N)) % N);  // cross_tile tiles are U * 256 = 1024 vectors
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            const size_t v = base + size_t(u) * 256 + threadIdx.x;
-            const bool have = v < nvec;                    // whole warps run on so that the shuffles stay convergent
-            const size_t i0 = 4 * v;                       // first word of this thread's vector
+            const uint32_t local = uint32_t(u) * 256u + threadIdx.x;
+            const size_t v = base + local;
+            const bool have = local < tile_vecs && v < nvec;  // whole warps run on so that the shuffles stay convergent
+            const size_t i0 = 4 * v;                            // first word of this thread's vector
             const uint32_t w[4] = {q[u].x, q[u].y, q[u].z, q[u].w};
             uint32_t edge = far_edge[u];
             if (!left) {
@@ -137,20 +144,35 @@ dense_shift_stream_kernel(const uint4* in, uint4* out, size_t nvec, unsigned lon
             }
             st16<CACHE_STREAMING>(out + v, make_uint4(r[0], r[1], r[2], r[3]));
         }
+        __syncthreads();  // (grid-stride only) the next tile's table reads and loads start after this tile is done
     }
 }
 
 #if !defined(__CUDACC_RTC__)
-// bytes: length of both streams (a multiple of 16); in and out 16-byte aligned, not overlapping; amount < 32
-inline cudaError_t launch_dense_shift_stream(const void* in, void* out, size_t bytes, unsigned long long valid_bits,
+// bytes: length of both streams (a multiple of 16); in and out 16-byte aligned, the same stream or disjoint; amount < 32
+inline cudaError_t launch_dense_shift_stream(const void* in, void* out, size_t bytes, unsigned long long valid_bits, uint32_t S,
                                              const dense_shift_table& tab, cudaStream_t s, const launch_geom& g)
 {
     constexpr int U = 4;
     const size_t nvec = bytes / 16;
     if (nvec) {
-        const size_t ntiles = (nvec + size_t(U) * 256 - 1) / (size_t(U) * 256);
+        // Out of place: tiles of 1024 vectors (16 KiB, every thread busy, 6.5-6.9 TB/s); the one word a tile needs from its
+        // neighbour is read from `in`, which nobody writes.  In place that word could already be overwritten, so tiles are
+        // whole chunks there -- lcm(S, 128) bits, nothing crosses their edges -- and whole 128-byte lines (tiles 16 bytes off
+        // a line cost 6 %); up to 11 % of the threads idle in the last row, 6.0-6.6 TB/s (profiles/r36b, r37).
+        uint32_t tile_vecs = uint32_t(U) * 256u, cross_tile = 1;
+        if (in == out) {
+            uint32_t a = S, b = 128;
+            while (b) { const uint32_t r = a % b; a = b; b = r; }
+            const uint32_t chunk_vecs = S / a;  // lcm(S, 128) bits in 16-byte vectors: at most 63
+            uint32_t unit = chunk_vecs;
+            while (unit % 8) unit += chunk_vecs;  // lcm(chunk_vecs, 8) <= 504
+            tile_vecs = uint32_t(U) * 256u / unit * unit;
+            cross_tile = 0;
+        }
+        const size_t ntiles = (nvec + tile_vecs - 1) / tile_vecs;
         if (cudaError_t e = launch_stream_kernel(dense_shift_stream_kernel<U>, grid_for(ntiles, g), 256, s, g.pdl != 0,
-                                                 static_cast<const uint4*>(in), static_cast<uint4*>(out), nvec, valid_bits, tab))
+                                                 static_cast<const uint4*>(in), static_cast<uint4*>(out), nvec, tile_vecs, cross_tile, valid_bits, tab))
             return e;
         count_launch(g);
     }

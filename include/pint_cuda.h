@@ -97,7 +97,7 @@ unsigned long long pint_cuda_launch_count(void);
  * kernels; 0 = chosen from the layout), "vec256" (32-byte global accesses in the stream kernels:
  * 0 never, 1 = default, where measured faster, 2 wherever the operands are 32-byte congruent), "dense_windows" (1 = layouts without compiled-in dense
  * kernels always use the element-by-element window kernels; testing), "dense_shift_stream" (1 = default: dense shifts
- * by less than 32 bits that are not in place run as a masked funnel shift over the word stream; 0 = the whole-chunk kernels), "unpack_bulk" (unpack to int32 planes:
+ * by less than 32 bits, in place or not, run as a masked funnel shift over the word stream; 0 = the whole-chunk kernels), "unpack_bulk" (unpack to int32 planes:
  * 1 = default, plane tiles staged in shared memory and written by bulk (TMA) stores; 0 = straight from
  * registers), "jit" (0 = default, 1, 2: run-time specialisation of unregistered layouts, see
  * pint_cuda_jit_compile), "pdl" (1 = default: the streaming kernels (binary, multi, fused, shift, slice, scalar, pairs, unpack, repack, the pair reduction, operator== over arrays, dense binary / pair / shift / conversions, and the run-time-specialised ones) are launched with

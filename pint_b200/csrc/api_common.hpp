@@ -29,7 +29,7 @@ struct options {
     option_value dense_windows = 0;     // 1 = run-time dense layouts always use the element-by-element window kernels (testing)
     option_value dense_threads = 0;     // dense bit-stream kernels: threads per CTA (0 = from the chunk size)
     option_value dense_tile_bytes = 0;  // ... and tile bytes per operand (0 = 16 KB target)
-    option_value dense_shift_stream = 1;  // dense shifts by less than 32 bits, not in place: the word-stream kernel (cuda_kernels_dense_shift.cuh); 0 = whole-chunk kernels
+    option_value dense_shift_stream = 1;  // dense shifts by less than 32 bits: the word-stream kernel (cuda_kernels_dense_shift.cuh); 0 = whole-chunk kernels
     option_value unpack_bulk = 1;   // unpack to int32 planes: 1 = plane tiles staged in shared memory, bulk (TMA) stores; 0 = register kernels
     option_value pdl = 1;           // packed -> packed stream kernels launched with programmatic stream serialization (default; +4...14 % on arrays up to 2^26 elements, profiles/r19_ab_pdl.log)
     option_value jit = 0;           // 0 off; 1 = specialise unregistered layouts with NVRTC, fall back on failure; 2 = fail instead

@@ -454,10 +454,10 @@ int pint_cuda_dense_shift(int left, const pint_layout* layout, uint64_t amount, 
         pre = (left ? mask : ~mask) & m.A;
     }
     const launch_geom g = geom();
-    // the stream as one long integer: mask, then funnel-shift neighbouring words (cuda_kernels_dense_shift.cuh).  Not in
-    // place (a warp reads one word of its neighbour's vector) and only below 32 bits; the chunk kernels keep the rest.
-    if (opts().dense_shift_stream && !opts().dense_windows && in != out && amt < 32)
-        return (int)dense::launch_dense_shift_stream(in, out, bytes, (unsigned long long)n * S,
+    // the stream as one long integer: mask, then funnel-shift neighbouring words (cuda_kernels_dense_shift.cuh), in place
+    // or not; only below 32 bits, the chunk kernels keep wider shifts
+    if (opts().dense_shift_stream && !opts().dense_windows && amt < 32)
+        return (int)dense::launch_dense_shift_stream(in, out, bytes, (unsigned long long)n * S, S,
                                                      dense::make_dense_shift_table(pre, S, amt, left != 0), s, g);
     const int N = int(S / dense::gcd_u32(S, 32));
     if (!opts().dense_windows) {

@@ -91,9 +91,9 @@ def test_dense_shift_vs_oracle(P, oracle, eb, bits, mode):
 
 @pytest.mark.parametrize("eb,bits", LAYOUTS)
 def test_dense_shift_chunk_kernels_still_agree(P, oracle, eb, bits):
-    """Out-of-place shifts by less than 32 bits take the word-stream kernel by default (cuda_kernels_dense_shift.cuh);
-    the whole-chunk kernels they replaced still serve in-place and wide shifts, so they stay under test: option off,
-    same streams, same oracle."""
+    """Shifts by less than 32 bits take the word-stream kernel by default (cuda_kernels_dense_shift.cuh), in place or
+    not; the whole-chunk kernels they replaced still serve wide shifts, so they stay under test: option off, same
+    streams, same oracle, out of place and in place."""
     pint_b200, ops, dense = P
     L = pint_b200.Layout(eb, *bits)
     S = sum(bits)
@@ -110,6 +110,9 @@ def test_dense_shift_chunk_kernels_still_agree(P, oracle, eb, bits):
                         ops.set_option("dense_shift_stream", opt)
                         got = dense.shift(left, L, dx, amt, n).cpu().numpy()
                         np.testing.assert_array_equal(got, want, err_msg=f"{L} left={left} amount={amt} n={n} dense_shift_stream={opt}")
+                        work = dev_bytes(dx_h)
+                        dense.shift(left, L, work, amt, n, out=work)
+                        np.testing.assert_array_equal(work.cpu().numpy(), want, err_msg=f"in place {L} left={left} amount={amt} n={n} dense_shift_stream={opt}")
     finally:
         ops.set_option("dense_shift_stream", 1)
 

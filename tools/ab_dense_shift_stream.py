@@ -47,6 +47,16 @@ for eb, bits in ((4, (8, 8, 8)), (4, (10, 10, 10)), (2, (12,)), (4, (7, 9, 3)), 
             row["stream_gbs" if mode else "chunk_gbs"] = round(2 * n * S / 8 / ms / 1e6)
             outs[mode] = do
         row["equal"] = bool(torch.equal(outs[0], outs[1]))
+        # in place (the stream kernel's tiles are whole chunks, so it serves this too)
+        for mode in (0, 1):
+            ops.set_option("dense_shift_stream", mode)
+            work = da.clone()
+            ms = timed(lambda: dense.shift(left, L, work, 0, n, out=work))   # amount 0: the stream stays the same pass after pass
+            row["stream_inplace_gbs" if mode else "chunk_inplace_gbs"] = round(2 * n * S / 8 / ms / 1e6)
+            one = da.clone()
+            dense.shift(left, L, one, amount, n, out=one)
+            row["inplace_equal_" + ("stream" if mode else "chunk")] = bool(torch.equal(one, outs[1]))
+            del work, one
         print(json.dumps(row), flush=True)
         outs.clear()
     ops.set_option("dense_shift_stream", 1)
