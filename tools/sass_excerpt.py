@@ -16,8 +16,10 @@ WANT = [
     ("C3 repack from int32 planes", r"repack_quad_kernelImLi4E.*static_layoutImJLm3ELm7ELm11ELm13ELm17ELm13E"),
     ("dense RGB24 add_signed_saturate (TMA-staged tiles)", r"dense_binary_kernel.*swar_fnILi2E.*Lm8ELm8ELm8E"),
     ("dense RGB24 -> three uint8 planes (byte permutes)", r"dense_bytes_to_planes_kernelILi3ELi1E"),
+    ("dense shift as a masked funnel shift over the word stream", r"dense_shift_stream_kernelILi4E"),
+    ("the reference benchmark's pair reduction, type-2 layout, add_signed_saturate", r"pairs_reduce_kernelIjLi2ELb1E.*static_layoutIjJLm1ELm2ELm3ELm4ELm5ELm6ELm11E"),
 ]
-MEM = re.compile(r"\b(LDG|STG|LDS|STS|UBLKCP|UTMA\w*|SYNCS|BAR|FENCE|ATOM|RED|LDC|LDGSTS|PRMT)\b")
+MEM = re.compile(r"\b(LDG|STG|LDS|STS|UBLKCP|UTMA\w*|SYNCS|BAR|FENCE|ATOM|RED|LDC|LDGSTS|PRMT|SHFL|ACQBULK|CCTL)\b")
 
 
 def main():
